@@ -1,0 +1,203 @@
+/*
+ * viba_b200.h — C ABI of the B200-native VIBA inner Levenberg–Marquardt iteration.
+ *
+ * This is the drop-in boundary.  Every entry point replaces a piece of the
+ * reference's lib/small_thing runtime or of BaSpaCho as consumed by it; the reference file:line
+ * each one replaces is cited beside it.  Plain C: pointers + sizes, no C++/torch types.
+ * All functions return 0 on success, a VB_ERR_* code otherwise; vb_last_error() gives the text.
+ * There is no CPU fallback: every compute entry point fails with VB_ERR_CUDA when no sm_100
+ * device is usable.
+ */
+#ifndef VIBA_B200_H_
+#define VIBA_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VB_OK 0
+#define VB_ERR_ARG 1
+#define VB_ERR_CUDA 2
+#define VB_ERR_NUMERIC 3  /* non-SPD pivot, RS time shift out of table range, ... */
+#define VB_ERR_STATE 4
+
+/* Variable kinds (reference lib/small_thing/Variable.h:25-221,
+ * interfaces/ark/camera_model/CameraModelParam.h:124-149, interfaces/ark/imu_model/ImuCalibParam.h:23) */
+enum {
+  VB_VAR_VEC3 = 0,     /* landmark / velocity / omega: 3 data, 3 tangent, += */
+  VB_VAR_SE3 = 1,      /* 7 data = quat(x,y,z,w) + t ; 6 tangent [trans, rot] ; exp(d)*T */
+  VB_VAR_S2 = 2,       /* 3 data (+radius in var_aux) ; 2 tangent */
+  VB_VAR_CAM = 3,      /* 17 data = 15 Fisheye624 params, readout s, time offset s ; tangent 15..17 */
+  VB_VAR_IMUCALIB = 4, /* 32 data ; tangent <= 23 */
+  VB_VAR_VEC2 = 5
+};
+
+/* var_flags bits */
+#define VB_CAM_EST_READOUT 1u
+#define VB_CAM_EST_TIMEOFFSET 2u
+#define VB_CAM_HAS_READOUT 4u
+
+/* Factor types (one per FactorStore instantiation reachable from ark_vi_ba) */
+enum {
+  VB_F_VISUAL = 1,           /* B1  viba/problem/VisualFactor.cpp:36-82      vars: X,T_bw,T_cb,cam */
+  VB_F_VISUAL_RS = 2,        /* B2  VisualFactor.cpp:122-214                 vars: + vel_world */
+  VB_F_INERTIAL = 4,         /* B4  InertialFactor.cpp:19-127                calib,Tp,vp,Tn,vn,g */
+  VB_F_INERTIAL_SEC = 5,     /* B5  InertialFactor.cpp:256-301 (common extrinsics) */
+  VB_F_INERTIAL_SEC_SPLIT = 6, /* B6 InertialFactor.cpp:190-254 */
+  VB_F_RW_IMUCALIB = 7,      /* B7  RandomWalkFactor.cpp:16-57 */
+  VB_F_RW_CAM = 8,           /* B8  RandomWalkFactor.cpp:59-100 */
+  VB_F_RW_SE3 = 9,           /* B9/B10 RandomWalkFactor.cpp:102-168 */
+  VB_F_PRIOR_IMUCALIB = 11,  /* B11 PriorFactor.cpp:82-109 */
+  VB_F_PRIOR_CAM = 12,       /* B12 PriorFactor.cpp:111-138 */
+  VB_F_PRIOR_SE3 = 13,       /* B13/B14 PriorFactor.cpp:140-176 */
+  VB_F_OMEGA_PRIOR = 15,     /* B15 OmegaPriorFactor.cpp:24-31 */
+  VB_F_OMEGA_PRIOR_SEC = 16  /* B16 OmegaPriorFactor.cpp:35-53 */
+};
+
+/* One factor store = one FactorStore<...> instantiation (lib/small_thing/Factor.h:96-141).
+ * Factors are given in insertion order; `vars` are ids into the variable pool in functor
+ * argument order; `consts` is the per-factor payload (layout per type in DESIGN.md §3). */
+typedef struct vb_factor_store {
+  int32_t type;              /* VB_F_* */
+  int32_t nvars;             /* variables per factor */
+  int64_t count;
+  const int32_t* vars;       /* [count * nvars] */
+  int32_t consts_per_factor; /* doubles */
+  const double* consts;      /* [count * consts_per_factor] */
+  double loss_a, loss_k;     /* HuberLossWithCutoff(a,k) (SoftLoss.h:115-163); a<=0 => trivial loss */
+  int64_t aux_len;           /* doubles of store-level aux data (preintegration / RS tables) */
+  const double* aux;
+} vb_factor_store;
+
+/* The whole graph.  Registration order (var_index), factor order and store order are explicit
+ * inputs because the reference derives them from libstdc++ unordered_map iteration
+ * (lib/small_thing/Optimizer.cpp:25-39, Factor.h:737-785). */
+typedef struct vb_graph_desc {
+  int64_t num_vars;
+  const int32_t* var_kind;   /* VB_VAR_* */
+  const int32_t* var_tdim;   /* tangent dim */
+  const uint32_t* var_flags;
+  const int64_t* var_index;  /* param-block (registration) index, or -2 for constant (Variable.h:224-250) */
+  const int64_t* var_off;    /* offset of the variable's data in var_data (doubles) */
+  const double* var_aux;     /* one double per variable (S2 radius), may be NULL */
+  int64_t var_data_len;
+  const double* var_data;
+  int64_t num_points;        /* elimRanges = [0, num_points) in registration-index space
+                                (interfaces/ark/main_AriaKit_ViBa.cpp:76-77) */
+  int32_t num_stores;
+  const vb_factor_store* stores;
+} vb_graph_desc;
+
+/* LM settings: lib/small_thing/Optimizer.h:40-78 with the ark_vi_ba overrides
+ * (viba/common/Settings.cpp:313-320).  vb_settings_default() fills the library defaults. */
+typedef struct vb_settings {
+  double damping, damping_adjust_on_fail, damping_adjust_on_good, damping_adjust_on_average;
+  double damping_min, damping_max;
+  double min_relative_cost_reduction, step_factor_decrease, min_step_factor_for_good;
+  double absolute_cost_tolerance, relative_cost_tolerance, variables_tolerance;
+  int32_t max_step_factor_attempts, try_sub_step;
+  int32_t stop_if_no_improvement_for, distance_from_troubled_iteration, max_num_iterations;
+  int32_t verbose;
+} vb_settings;
+
+typedef struct vb_summary {  /* Optimizer::Summary, Optimizer.h:93-99 */
+  double initial_cost, final_cost;
+  int32_t num_troubled_seqs, largest_troubled_seq, num_iterations;
+  int32_t stop_reason; /* 0 converged, 1 iteration limit, 2 damping out of range */
+} vb_summary;
+
+typedef struct vb_cost_stats { /* CostStats, Factor.h:25-31 */
+  int64_t num_total, num_invalid, num_prev_invalid;
+} vb_cost_stats;
+
+typedef struct vb_iter_times { /* ms, CUDA-event timed; the split the reference logs (Optimizer.cpp:1062-1067) */
+  double grad_hess, damping, factor_schur, factor_chol, solve, apply, cost, total;
+} vb_iter_times;
+
+typedef struct vb_ctx vb_ctx;
+typedef struct vb_problem vb_problem;
+
+int vb_version(void);
+const char* vb_last_error(void);
+void vb_settings_default(vb_settings* s);
+
+/* device context (one host thread drives one context; Optimizer is not thread-safe either) */
+int vb_ctx_create(int device, vb_ctx** out);
+int vb_ctx_destroy(vb_ctx* ctx);
+
+/* Optimizer::initSolver (Optimizer.cpp:166-207) + FactorStore::registerBlocks (Factor.h:761-785)
+ * + BaSpaCho::createSolver: uploads the graph as SoA tables and runs the symbolic phase
+ * (block structure, ordering, supernodes, scatter maps).  Host arrays in `g` may be freed after. */
+int vb_problem_create(vb_ctx* ctx, const vb_graph_desc* g, vb_problem** out);
+int vb_problem_destroy(vb_problem* p);
+
+/* Solver::order(), dataSize() (Optimizer.cpp:339-340,777,783-784) and symbolic-phase outputs */
+int64_t vb_order(const vb_problem* p);
+int64_t vb_data_size(const vb_problem* p);
+int64_t vb_num_blocks(const vb_problem* p);
+int64_t vb_num_lumps(const vb_problem* p);
+/* accessor().paramStart(i) for every registration index (Factor.h:612) */
+int vb_get_param_start(const vb_problem* p, int64_t* out, int64_t n);
+/* elimination position of every registration index (the permutation) */
+int vb_get_perm(const vb_problem* p, int64_t* out, int64_t n);
+/* lump (supernode) boundaries in elimination positions: out[num_lumps+1] */
+int vb_get_lump_start(const vb_problem* p, int64_t* out, int64_t n);
+/* accessor().block(data,i,j): offset + row stride of block (i,j) (registration indices, any order);
+ * *transposed = 1 when the stored block is (j,i).  offset < 0 if the block is not in the structure. */
+int vb_block_offset(const vb_problem* p, int64_t i, int64_t j, int64_t* offset, int64_t* stride, int32_t* transposed);
+/* flops / bytes of the numeric phases from the symbolic analysis */
+int vb_get_work(const vb_problem* p, double* schur_flops, double* chol_flops, double* visual_bytes);
+
+/* Optimizer::computeGradHess (Optimizer.cpp:57-71 -> Factor.h:704-734,543-661).
+ * Zeroes grad (and hess when with_hess) first, as Optimizer.cpp:807-808 does. */
+int vb_eval_grad_hess(vb_problem* p, int with_hess, int update_cache, int dont_retry_failed, double* cost);
+/* Optimizer::computeCost (Optimizer.cpp:88-97 -> Factor.h:664-701,390-417) */
+int vb_eval_cost(vb_problem* p, int comparable, double* cost, vb_cost_stats* stats);
+/* Optimizer::addDamping (Optimizer.cpp:136-146) */
+int vb_damp(vb_problem* p, double lambda);
+/* step = grad (Optimizer.cpp:828) */
+int vb_step_from_grad(vb_problem* p);
+/* Solver::factor(hess) (Optimizer.cpp:223): landmark Schur elimination + supernodal Cholesky */
+int vb_factor(vb_problem* p);
+/* Solver::solve(hess, vec, order, 1) on the step vector (Optimizer.cpp:228); which=0 step, 1 grad_new */
+int vb_solve(vb_problem* p, int which);
+/* step.dot(grad), |grad|, |step| (Optimizer.cpp:833,858-859) */
+int vb_step_stats(vb_problem* p, double* step_dot_grad, double* grad_norm, double* step_norm);
+/* vec *= s (Optimizer.cpp:857,925,971); which=0 step, 1 grad_new */
+int vb_scale_vec(vb_problem* p, int which, double s);
+/* -grad_new . step * 0.5 support (Optimizer.cpp:921) */
+int vb_dot(vb_problem* p, int a, int b, double* out);
+/* Optimizer::applyStep (Optimizer.cpp:121-134 -> Variable.h:352-370): ratios = {inf, rms, mean} */
+int vb_apply_step(vb_problem* p, int which, double ratios[3]);
+/* Optimizer::backupVariables / restoreVariables (Optimizer.cpp:107-119) */
+int vb_backup(vb_problem* p);
+int vb_restore(vb_problem* p);
+/* compute grad only into the secondary vector (Optimizer.cpp:912-919) */
+int vb_eval_grad_new(vb_problem* p, int dont_retry_failed);
+
+/* Optimizer::optimize (Optimizer.cpp:768-1106): the whole LM loop, host-controlled, device-resident */
+int vb_optimize(vb_problem* p, const vb_settings* s, vb_summary* out);
+/* one accepted-path LM iteration with per-phase CUDA-event timing (bench / profiling) */
+int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times* t, double* cost_before, double* cost_after);
+
+/* data movement */
+int vb_download_vars(vb_problem* p, double* var_data, int64_t n);       /* all variable data */
+int vb_upload_vars(vb_problem* p, const double* var_data, int64_t n);
+int vb_download_grad(vb_problem* p, double* out, int64_t n);             /* permuted order */
+int vb_download_step(vb_problem* p, double* out, int64_t n);
+int vb_download_hess(vb_problem* p, double* out, int64_t n);
+int vb_upload_hess(vb_problem* p, const double* in, int64_t n);
+int vb_upload_grad(vb_problem* p, const double* in, int64_t n);
+int vb_download_factor_cache(vb_problem* p, int32_t store, double* out, int64_t n); /* ResultCache, Factor.h:92-94 */
+int vb_upload_store_aux(vb_problem* p, int32_t store, const double* aux, int64_t n); /* refreshed preint / RS tables */
+int vb_upload_store_consts(vb_problem* p, int32_t store, const double* consts, int64_t n);
+
+/* FP64 DMMA peak probe (mma.sync m8n8k4 f64) used as the tensor roofline denominator */
+int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VIBA_B200_H_ */

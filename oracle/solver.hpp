@@ -1,0 +1,231 @@
+// ORACLE (test infrastructure, CPU only) — see vmath.hpp header note.
+//
+// Stand-in for BaSpaCho::Solver::factor + solve as consumed at lib/small_thing/Optimizer.cpp:223,228
+// (BaSpaCho facebookresearch/baspacho@bd833260 is NOT in /root/reference: SURVEY.md F1).  The
+// published algorithm is restated in its simplest exact form: eliminate the landmark range
+// [0,P) block by block (3x3 Cholesky, Schur complement onto the camera-side blocks), then a
+// direct Cholesky of the reduced camera system, here an envelope (skyline) Cholesky under a
+// reverse Cuthill-McKee block ordering.  Ordering / supernodes / data layout: PARITY UNPINNED
+// (no reference source or golden file fixes them); the solution vector is ordering independent
+// up to rounding, which is what tests compare (rel 1e-9).
+#pragma once
+#include <queue>
+#include <numeric>
+#include "engine.hpp"
+
+namespace orc {
+
+struct SchurSkylineSolver {
+  const Engine* E = nullptr;
+  int64_t nP = 0, nB = 0, nC = 0;  // landmark blocks, all blocks, camera-side blocks
+  int64_t nr = 0;                  // reduced scalar order
+  std::vector<std::vector<int64_t>> colBlocks; // per landmark: CSR entry ids k of blocks (j,p)
+  std::vector<int64_t> cpos, cstart;           // camera block (reg index - nP) -> position / scalar start in reduced order
+  std::vector<int64_t> first, rowStart;        // skyline per scalar row
+  std::vector<double> S, gr;                   // skyline data, reduced rhs
+  std::vector<double> HppInv;                  // 9 per landmark (inverse of damped H_pp)
+  double flopsSchur = 0, flopsChol = 0;
+
+  void analyze(const Engine& eng) {
+    E = &eng;
+    nP = eng.P.npoints; nB = eng.P.nblocks; nC = nB - nP;
+    colBlocks.assign(nP, {});
+    std::vector<std::vector<int64_t>> adj(nC);
+    for (int64_t i = nP; i < nB; i++)
+      for (int64_t k = eng.rowPtr[i]; k < eng.rowPtr[i + 1] - 1; k++) {
+        const int64_t j = eng.colInd[k];
+        if (j < nP) colBlocks[j].push_back(k);
+        else { adj[i - nP].push_back(j - nP); adj[j - nP].push_back(i - nP); }
+      }
+    for (int64_t p = 0; p < nP; p++)
+      if (eng.rowPtr[p + 1] - eng.rowPtr[p] != 1) throw std::runtime_error("oracle: landmark-landmark block");
+    // row of each CSR entry
+    std::vector<int64_t> rowOf(eng.colInd.size());
+    for (int64_t i = 0; i < nB; i++) for (int64_t k = eng.rowPtr[i]; k < eng.rowPtr[i + 1]; k++) rowOf[k] = i;
+    rowOfEntry = rowOf;
+    for (int64_t p = 0; p < nP; p++) {
+      const auto& cb = colBlocks[p];
+      for (size_t a = 0; a < cb.size(); a++)
+        for (size_t b = 0; b < a; b++) {
+          const int64_t ia = rowOf[cb[a]] - nP, ib = rowOf[cb[b]] - nP;
+          adj[ia].push_back(ib); adj[ib].push_back(ia);
+        }
+    }
+    for (auto& a : adj) { std::sort(a.begin(), a.end()); a.erase(std::unique(a.begin(), a.end()), a.end()); }
+    // reverse Cuthill-McKee over all components, seeds = min degree unvisited
+    std::vector<int64_t> orderC; orderC.reserve(nC);
+    std::vector<char> vis(nC, 0);
+    std::vector<int64_t> byDeg(nC);
+    std::iota(byDeg.begin(), byDeg.end(), 0);
+    std::stable_sort(byDeg.begin(), byDeg.end(), [&](int64_t a, int64_t b) { return adj[a].size() < adj[b].size(); });
+    for (int64_t seed : byDeg) {
+      if (vis[seed]) continue;
+      std::queue<int64_t> q; q.push(seed); vis[seed] = 1;
+      while (!q.empty()) {
+        const int64_t u = q.front(); q.pop(); orderC.push_back(u);
+        std::vector<int64_t> nb;
+        for (int64_t w : adj[u]) if (!vis[w]) { vis[w] = 1; nb.push_back(w); }
+        std::stable_sort(nb.begin(), nb.end(), [&](int64_t a, int64_t b) { return adj[a].size() < adj[b].size(); });
+        for (int64_t w : nb) q.push(w);
+      }
+    }
+    std::reverse(orderC.begin(), orderC.end());
+    cpos.assign(nC, 0); cstart.assign(nC, 0);
+    for (int64_t i = 0; i < nC; i++) cpos[orderC[i]] = i;
+    nr = 0;
+    for (int64_t i = 0; i < nC; i++) { cstart[orderC[i]] = nr; nr += eng.P.blockSize[nP + orderC[i]]; }
+    // envelope
+    first.assign(nr, 0);
+    for (int64_t c = 0; c < nC; c++) {
+      int64_t f = cstart[c];
+      for (int64_t w : adj[c]) f = std::min(f, cstart[w]);
+      for (int a = 0; a < eng.P.blockSize[nP + c]; a++) first[cstart[c] + a] = f;
+    }
+    rowStart.assign(nr + 1, 0);
+    for (int64_t i = 0; i < nr; i++) rowStart[i + 1] = rowStart[i] + (i - first[i] + 1);
+    S.assign(rowStart[nr], 0.0);
+    gr.assign(nr, 0.0);
+    HppInv.assign(9 * nP, 0.0);
+    flopsChol = 0;
+    for (int64_t i = 0; i < nr; i++) { const double w = double(i - first[i]); flopsChol += w * w; }
+  }
+  std::vector<int64_t> rowOfEntry;
+
+  inline double& at(int64_t i, int64_t j) { return S[rowStart[i] + (j - first[i])]; } // i >= j >= first[i]
+
+  // add block (reg indices bi >= bj, camera side) d_i x d_j row-major with sign
+  void addBlock(int64_t bi, int64_t bj, const double* B, double sign) {
+    const int di = E->P.blockSize[bi], dj = E->P.blockSize[bj];
+    const int64_t si = cstart[bi - nP], sj = cstart[bj - nP];
+    if (bi == bj) {
+      for (int a = 0; a < di; a++) for (int b = 0; b <= a; b++) at(si + a, sj + b) += sign * B[a * dj + b];
+    } else if (si > sj) {
+      for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) at(si + a, sj + b) += sign * B[a * dj + b];
+    } else {
+      for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) at(sj + b, si + a) += sign * B[a * dj + b];
+    }
+  }
+
+  static void inv3sym(const double* A, double* I) { // symmetric 3x3 (lower used), via Cholesky
+    const double l00 = std::sqrt(A[0]), l10 = A[3] / l00, l20 = A[6] / l00;
+    const double l11 = std::sqrt(A[4] - l10 * l10), l21 = (A[7] - l20 * l10) / l11;
+    const double l22 = std::sqrt(A[8] - l20 * l20 - l21 * l21);
+    // inverse of L
+    const double i00 = 1 / l00, i11 = 1 / l11, i22 = 1 / l22;
+    const double i10 = -l10 * i00 * i11;
+    const double i21 = -l21 * i11 * i22;
+    const double i20 = -(l20 * i00 + l21 * i10) * i22;
+    // A^-1 = L^-T L^-1
+    I[0] = i00 * i00 + i10 * i10 + i20 * i20; I[1] = i10 * i11 + i20 * i21; I[2] = i20 * i22;
+    I[3] = I[1]; I[4] = i11 * i11 + i21 * i21; I[5] = i21 * i22;
+    I[6] = I[2]; I[7] = I[5]; I[8] = i22 * i22;
+  }
+
+  // factor(hess) + solve(hess, g) : x = H^-1 g, all in registration order
+  void factorAndSolve(const double* H, const double* g, double* x) {
+    const Engine& e = *E;
+    std::fill(S.begin(), S.end(), 0.0);
+    const int64_t c0 = e.paramStart[nP];
+    // camera-side blocks
+    for (int64_t i = nP; i < nB; i++)
+      for (int64_t k = e.rowPtr[i]; k < e.rowPtr[i + 1]; k++) {
+        const int64_t j = e.colInd[k];
+        if (j >= nP) addBlock(i, j, H + e.blkOff[k], 1.0);
+      }
+    for (int64_t c = 0; c < nC; c++)
+      for (int a = 0; a < e.P.blockSize[nP + c]; a++) gr[cstart[c] + a] = g[e.paramStart[nP + c] + a];
+    // landmark elimination
+    flopsSchur = 0;
+    std::vector<double> Y;
+    for (int64_t p = 0; p < nP; p++) {
+      const double* Hpp = H + e.blkOff[e.rowPtr[p + 1] - 1];
+      double* Hi = &HppInv[9 * p];
+      inv3sym(Hpp, Hi);
+      const double* gp = g + e.paramStart[p];
+      double hg[3];
+      mat3vec(Hi, gp, hg);
+      const auto& cb = colBlocks[p];
+      int64_t m = 0;
+      for (int64_t k : cb) m += e.P.blockSize[rowOfEntry[k]];
+      flopsSchur += 3.0 * m * m + 9.0 * m + 9.0;
+      // Y_a = W_a Hpp^-1 (d_a x 3), W_a = block (a,p) (d_a x 3)
+      Y.assign(3 * m, 0.0);
+      int64_t o = 0;
+      for (int64_t k : cb) {
+        const int da = e.P.blockSize[rowOfEntry[k]];
+        matmul(H + e.blkOff[k], Hi, &Y[3 * o], da, 3, 3);
+        o += da;
+      }
+      int64_t oa = 0;
+      double blk[23 * 23];
+      for (size_t a = 0; a < cb.size(); a++) {
+        const int64_t ba = rowOfEntry[cb[a]];
+        const int da = e.P.blockSize[ba];
+        const double* Wa = H + e.blkOff[cb[a]];
+        for (int t = 0; t < da; t++) gr[cstart[ba - nP] + t] -= dot3(Wa + 3 * t, hg);
+        int64_t ob = 0;
+        for (size_t b = 0; b <= a; b++) {
+          const int64_t bb = rowOfEntry[cb[b]];
+          const int db = e.P.blockSize[bb];
+          const double* Wb = H + e.blkOff[cb[b]];
+          // Y_a W_b^T : da x db
+          for (int s = 0; s < da; s++) for (int t = 0; t < db; t++) blk[s * db + t] = dot3(&Y[3 * (oa + s)], Wb + 3 * t);
+          addBlock(ba, bb, blk, -1.0); // ba > bb since CSR rows ascend
+          ob += db;
+        }
+        oa += da;
+      }
+    }
+    // envelope Cholesky (row by row)
+    for (int64_t i = 0; i < nr; i++) {
+      double* Li = &S[rowStart[i]];
+      const int64_t fi = first[i];
+      for (int64_t j = fi; j < i; j++) {
+        const double* Lj = &S[rowStart[j]];
+        const int64_t fj = first[j];
+        const int64_t k0 = std::max(fi, fj);
+        double s = Li[j - fi];
+        const double* a = Li + (k0 - fi);
+        const double* b = Lj + (k0 - fj);
+        const int64_t n = j - k0;
+        for (int64_t k = 0; k < n; k++) s -= a[k] * b[k];
+        Li[j - fi] = s / Lj[j - fj];
+      }
+      double d = Li[i - fi];
+      for (int64_t k = 0; k < i - fi; k++) d -= Li[k] * Li[k];
+      if (!(d > 0)) throw std::runtime_error("oracle: reduced system not positive definite");
+      Li[i - fi] = std::sqrt(d);
+    }
+    // solve L y = gr ; L^T z = y
+    std::vector<double> y(gr);
+    for (int64_t i = 0; i < nr; i++) {
+      const double* Li = &S[rowStart[i]];
+      double s = y[i];
+      for (int64_t k = first[i]; k < i; k++) s -= Li[k - first[i]] * y[k];
+      y[i] = s / Li[i - first[i]];
+    }
+    for (int64_t i = nr - 1; i >= 0; i--) {
+      const double* Li = &S[rowStart[i]];
+      y[i] /= Li[i - first[i]];
+      const double yi = y[i];
+      for (int64_t k = first[i]; k < i; k++) y[k] -= Li[k - first[i]] * yi;
+    }
+    for (int64_t c = 0; c < nC; c++)
+      for (int a = 0; a < e.P.blockSize[nP + c]; a++) x[e.paramStart[nP + c] + a] = y[cstart[c] + a];
+    (void)c0;
+    // back-substitute landmarks: x_p = Hpp^-1 (g_p - sum_a W_a^T x_a)
+    for (int64_t p = 0; p < nP; p++) {
+      double rhs[3] = {g[e.paramStart[p]], g[e.paramStart[p] + 1], g[e.paramStart[p] + 2]};
+      for (int64_t k : colBlocks[p]) {
+        const int64_t ba = rowOfEntry[k];
+        const int da = e.P.blockSize[ba];
+        const double* Wa = H + e.blkOff[k];
+        const double* xa = x + e.paramStart[ba];
+        for (int t = 0; t < da; t++) for (int c = 0; c < 3; c++) rhs[c] -= Wa[3 * t + c] * xa[t];
+      }
+      mat3vec(&HppInv[9 * p], rhs, x + e.paramStart[p]);
+    }
+  }
+};
+
+} // namespace orc

@@ -1,0 +1,229 @@
+// ORACLE (test infrastructure, CPU only) — see vmath.hpp header note.
+// C entry points over the oracle so that tests/ (ctypes) and bench.py's cpu_baseline /
+// --impl reference legs can drive it.  Never linked into the product library.
+#include <cstring>
+#include <string>
+#include <chrono>
+#include "lm.hpp"
+
+using namespace orc;
+
+struct OrcHandle {
+  Engine eng;
+  SchurSkylineSolver sol;
+  bool analyzed = false;
+  std::vector<double> hessF;
+  std::string err;
+};
+
+static thread_local std::string g_err;
+
+#define ORC_TRY try {
+#define ORC_CATCH                                   \
+  }                                                 \
+  catch (const std::exception& ex) {                \
+    g_err = ex.what();                              \
+    return 3;                                       \
+  }                                                 \
+  return 0;
+
+extern "C" {
+
+const char* orc_last_error() { return g_err.c_str(); }
+
+int orc_create(const vb_graph_desc* g, OrcHandle** out) {
+  ORC_TRY
+  auto* h = new OrcHandle();
+  h->eng.P.load(g);
+  h->eng.symbolic();
+  *out = h;
+  ORC_CATCH
+}
+int orc_destroy(OrcHandle* h) { delete h; return 0; }
+
+int64_t orc_order(OrcHandle* h) { return h->eng.order; }
+int64_t orc_data_size(OrcHandle* h) { return h->eng.dataSize; }
+int64_t orc_num_blocks(OrcHandle* h) { return h->eng.P.nblocks; }
+int64_t orc_nnz_blocks(OrcHandle* h) { return (int64_t)h->eng.colInd.size(); }
+// block CSR of Optimizer::initSolver (Optimizer.cpp:174-197): rowPtr[n+1], colInd[nnz], blkOff[nnz]
+int orc_get_structure(OrcHandle* h, int64_t* rowPtr, int64_t* colInd, int64_t* blkOff, int64_t* paramStart) {
+  const Engine& e = h->eng;
+  if (rowPtr) std::memcpy(rowPtr, e.rowPtr.data(), e.rowPtr.size() * 8);
+  if (colInd) std::memcpy(colInd, e.colInd.data(), e.colInd.size() * 8);
+  if (blkOff) std::memcpy(blkOff, e.blkOff.data(), e.blkOff.size() * 8);
+  if (paramStart) std::memcpy(paramStart, e.paramStart.data(), e.paramStart.size() * 8);
+  return 0;
+}
+
+int orc_eval_grad_hess(OrcHandle* h, int with_hess, int update_cache, int dont_retry, int which, double* cost) {
+  ORC_TRY
+  Engine& e = h->eng;
+  std::vector<double>& g = which == 0 ? e.grad : e.gradNew;
+  std::fill(g.begin(), g.end(), 0.0);
+  if (with_hess) std::fill(e.hess.begin(), e.hess.end(), 0.0);
+  const double c = e.computeGradHess(g.data(), with_hess ? e.hess.data() : nullptr, update_cache != 0, dont_retry != 0);
+  if (cost) *cost = c;
+  ORC_CATCH
+}
+int orc_eval_cost(OrcHandle* h, int comparable, double* cost, vb_cost_stats* stats) {
+  ORC_TRY
+  CostStats cs;
+  const double c = h->eng.computeCost(comparable != 0, &cs);
+  if (cost) *cost = c;
+  if (stats) { stats->num_total = cs.numTotal; stats->num_invalid = cs.numInvalid; stats->num_prev_invalid = cs.numPrevInvalid; }
+  ORC_CATCH
+}
+int orc_damp(OrcHandle* h, double lambda) { h->eng.addDamping(lambda); return 0; }
+
+// factor (on a private copy of hess) then step = H^-1 grad
+int orc_factor(OrcHandle* h) {
+  ORC_TRY
+  if (!h->analyzed) { h->sol.analyze(h->eng); h->analyzed = true; }
+  h->hessF = h->eng.hess;
+  h->sol.factor(h->hessF.data());
+  ORC_CATCH
+}
+int orc_solve(OrcHandle* h, int which) {
+  ORC_TRY
+  Engine& e = h->eng;
+  if (which == 0) h->sol.solveOnly(h->hessF.data(), e.grad.data(), e.step.data());
+  else { std::vector<double> g2 = e.gradNew; h->sol.solveOnly(h->hessF.data(), g2.data(), e.gradNew.data()); }
+  ORC_CATCH
+}
+int orc_scale_vec(OrcHandle* h, int which, double s) {
+  for (double& x : (which == 0 ? h->eng.step : h->eng.gradNew)) x *= s;
+  return 0;
+}
+int orc_apply_step(OrcHandle* h, int which, double* ratios) {
+  double r[3];
+  h->eng.applyStep(which == 0 ? h->eng.step.data() : h->eng.gradNew.data(), r);
+  if (ratios) { ratios[0] = r[0]; ratios[1] = r[1]; ratios[2] = r[2]; }
+  return 0;
+}
+int orc_backup(OrcHandle* h) { h->eng.backup(); return 0; }
+int orc_restore(OrcHandle* h) { h->eng.restore(); return 0; }
+
+// which: 0 grad, 1 step, 2 gradNew, 3 hess, 4 var data (registration order for vectors)
+int orc_get(OrcHandle* h, int which, double* out, int64_t n) {
+  Engine& e = h->eng;
+  const std::vector<double>* v = which == 0 ? &e.grad : which == 1 ? &e.step : which == 2 ? &e.gradNew : which == 3 ? &e.hess : &e.P.data;
+  if ((int64_t)v->size() != n) { g_err = "orc_get: size mismatch"; return 1; }
+  std::memcpy(out, v->data(), n * 8);
+  return 0;
+}
+int orc_set(OrcHandle* h, int which, const double* in, int64_t n) {
+  Engine& e = h->eng;
+  std::vector<double>* v = which == 0 ? &e.grad : which == 1 ? &e.step : which == 2 ? &e.gradNew : which == 3 ? &e.hess : &e.P.data;
+  if ((int64_t)v->size() != n) { g_err = "orc_set: size mismatch"; return 1; }
+  std::memcpy(v->data(), in, n * 8);
+  return 0;
+}
+int orc_get_cache(OrcHandle* h, int store, double* out, int64_t n) {
+  const auto& c = h->eng.P.stores[store].cache;
+  if ((int64_t)c.size() != n) return 1;
+  std::memcpy(out, c.data(), n * 8);
+  return 0;
+}
+int orc_set_store_aux(OrcHandle* h, int store, const double* aux, int64_t n) {
+  h->eng.P.stores[store].aux.assign(aux, aux + n);
+  return 0;
+}
+
+// per-factor residual + Jacobians: r[E], J = concatenated row-major E x d_i for every variable
+// (constants included, so numeric checks can cover them); returns validity in *valid
+int orc_eval_factor(OrcHandle* h, int store, int64_t k, double* r, double* J, int* valid) {
+  ORC_TRY
+  const Engine& e = h->eng;
+  const Store& st = e.P.stores[store];
+  const int E = factorErrorSize(st.type);
+  double* Jp[kMaxVars];
+  int64_t o = 0;
+  for (int i = 0; i < st.nvars; i++) {
+    Jp[i] = J ? J + o : nullptr;
+    o += (int64_t)E * e.P.tdim[st.vars[k * st.nvars + i]];
+  }
+  *valid = e.evalFactor(st, k, r, J ? Jp : nullptr) ? 1 : 0;
+  ORC_CATCH
+}
+
+int orc_optimize(OrcHandle* h, const vb_settings* s, vb_summary* out, double* tracePrev, double* traceNew, int traceCap) {
+  ORC_TRY
+  if (!h->analyzed) { h->sol.analyze(h->eng); h->analyzed = true; }
+  LmTrace tr;
+  optimize(h->eng, h->sol, *s, out, &tr);
+  for (int i = 0; i < traceCap && i < (int)tr.prevCost.size(); i++) {
+    if (tracePrev) tracePrev[i] = tr.prevCost[i];
+    if (traceNew) traceNew[i] = tr.newCost[i];
+  }
+  ORC_CATCH
+}
+
+// one accepted-path LM iteration, wall-clock split in ms: {gradhess, damp, factor, solve, apply, cost, total}
+int orc_lm_iteration_timed(OrcHandle* h, double lambda, double* ms, double* costBefore, double* costAfter) {
+  ORC_TRY
+  using clk = std::chrono::steady_clock;
+  auto ms_since = [](clk::time_point a) { return std::chrono::duration<double, std::milli>(clk::now() - a).count(); };
+  Engine& e = h->eng;
+  if (!h->analyzed) { h->sol.analyze(h->eng); h->analyzed = true; }
+  const auto t0 = clk::now();
+  std::fill(e.grad.begin(), e.grad.end(), 0.0);
+  std::fill(e.hess.begin(), e.hess.end(), 0.0);
+  const double c0 = e.computeGradHess(e.grad.data(), e.hess.data(), true, false);
+  ms[0] = ms_since(t0);
+  auto t1 = clk::now();
+  e.addDamping(lambda);
+  ms[1] = ms_since(t1);
+  t1 = clk::now();
+  h->sol.factor(e.hess.data());
+  ms[2] = ms_since(t1);
+  t1 = clk::now();
+  h->sol.solveOnly(e.hess.data(), e.grad.data(), e.step.data());
+  ms[3] = ms_since(t1);
+  t1 = clk::now();
+  for (double& s : e.step) s = -s;
+  e.backup();
+  double rr[3];
+  e.applyStep(e.step.data(), rr);
+  ms[4] = ms_since(t1);
+  t1 = clk::now();
+  CostStats cs;
+  const double c1 = e.computeCost(true, &cs);
+  ms[5] = ms_since(t1);
+  e.restore();
+  ms[6] = ms_since(t0);
+  if (costBefore) *costBefore = c0;
+  if (costAfter) *costAfter = c1;
+  ORC_CATCH
+}
+
+// Lie / camera unit entry points for tests/test_oracle_math.py
+// fn: 0 so3Exp(3->4) 1 so3Log(4->3) 2 se3Exp(6->7) 3 se3Log(7->6) 4 so3LeftJacobian(3->9)
+//     5 so3LeftJacobianInverse(3->9) 6 se3LeftJacobianInverse(6->36) 7 se3Adj(7->36) 8 se3Inv(7->7)
+//     9 se3Mul(14->7) 10 s2Ortho(3->6)
+int orc_lie(int fn, const double* in, double* out) {
+  switch (fn) {
+    case 0: so3Exp(in, out); break;
+    case 1: so3Log(in, out); break;
+    case 2: se3Exp(in, out); break;
+    case 3: se3Log(in, out); break;
+    case 4: so3LeftJacobian(in, out); break;
+    case 5: so3LeftJacobianInverse(in, out); break;
+    case 6: se3LeftJacobianInverse(in, out); break;
+    case 7: se3Adj(in, out); break;
+    case 8: se3Inv(in, out); break;
+    case 9: se3Mul(in, in + 7, out); break;
+    case 10: s2Ortho(in, out); break;
+    default: return 1;
+  }
+  return 0;
+}
+int orc_fisheye624(const double* p, const double* prm, double* uv, double* dPoint, double* dParam) {
+  return fisheye624Project(p, prm, uv, dPoint, dParam) ? 1 : 0;
+}
+int orc_boxplus(int kind, uint32_t flags, double aux, double* x, const double* s, int tdim, double* ratio) {
+  const double r = applyBoxPlus(kind, flags, aux, x, s, tdim);
+  if (ratio) *ratio = r;
+  return 0;
+}
+
+} // extern "C"

@@ -122,18 +122,18 @@ struct SchurSkylineSolver {
   }
 
   // factor(hess) + solve(hess, g) : x = H^-1 g, all in registration order
-  void factorAndSolve(const double* H, const double* g, double* x) {
+  void factorAndSolve(const double* H, const double* g, double* x) { factor(H); solveOnly(H, g, x); }
+
+  // Solver::factor (Optimizer.cpp:223): H is read-only here; the factor lives in S / HppInv
+  void factor(const double* H) {
     const Engine& e = *E;
     std::fill(S.begin(), S.end(), 0.0);
-    const int64_t c0 = e.paramStart[nP];
     // camera-side blocks
     for (int64_t i = nP; i < nB; i++)
       for (int64_t k = e.rowPtr[i]; k < e.rowPtr[i + 1]; k++) {
         const int64_t j = e.colInd[k];
         if (j >= nP) addBlock(i, j, H + e.blkOff[k], 1.0);
       }
-    for (int64_t c = 0; c < nC; c++)
-      for (int a = 0; a < e.P.blockSize[nP + c]; a++) gr[cstart[c] + a] = g[e.paramStart[nP + c] + a];
     // landmark elimination
     flopsSchur = 0;
     std::vector<double> Y;
@@ -141,9 +141,6 @@ struct SchurSkylineSolver {
       const double* Hpp = H + e.blkOff[e.rowPtr[p + 1] - 1];
       double* Hi = &HppInv[9 * p];
       inv3sym(Hpp, Hi);
-      const double* gp = g + e.paramStart[p];
-      double hg[3];
-      mat3vec(Hi, gp, hg);
       const auto& cb = colBlocks[p];
       int64_t m = 0;
       for (int64_t k : cb) m += e.P.blockSize[rowOfEntry[k]];
@@ -162,7 +159,7 @@ struct SchurSkylineSolver {
         const int64_t ba = rowOfEntry[cb[a]];
         const int da = e.P.blockSize[ba];
         const double* Wa = H + e.blkOff[cb[a]];
-        for (int t = 0; t < da; t++) gr[cstart[ba - nP] + t] -= dot3(Wa + 3 * t, hg);
+        (void)Wa;
         int64_t ob = 0;
         for (size_t b = 0; b <= a; b++) {
           const int64_t bb = rowOfEntry[cb[b]];
@@ -196,6 +193,23 @@ struct SchurSkylineSolver {
       if (!(d > 0)) throw std::runtime_error("oracle: reduced system not positive definite");
       Li[i - fi] = std::sqrt(d);
     }
+  }
+
+  // Solver::solve (Optimizer.cpp:228) with the factor computed by factor(H)
+  void solveOnly(const double* H, const double* g, double* x) {
+    const Engine& e = *E;
+    for (int64_t c = 0; c < nC; c++)
+      for (int a = 0; a < e.P.blockSize[nP + c]; a++) gr[cstart[c] + a] = g[e.paramStart[nP + c] + a];
+    for (int64_t p = 0; p < nP; p++) {
+      double hg[3];
+      mat3vec(&HppInv[9 * p], g + e.paramStart[p], hg);
+      for (int64_t k : colBlocks[p]) {
+        const int64_t ba = rowOfEntry[k];
+        const int da = e.P.blockSize[ba];
+        const double* Wa = H + e.blkOff[k];
+        for (int t = 0; t < da; t++) gr[cstart[ba - nP] + t] -= dot3(Wa + 3 * t, hg);
+      }
+    }
     // solve L y = gr ; L^T z = y
     std::vector<double> y(gr);
     for (int64_t i = 0; i < nr; i++) {
@@ -212,7 +226,6 @@ struct SchurSkylineSolver {
     }
     for (int64_t c = 0; c < nC; c++)
       for (int a = 0; a < e.P.blockSize[nP + c]; a++) x[e.paramStart[nP + c] + a] = y[cstart[c] + a];
-    (void)c0;
     // back-substitute landmarks: x_p = Hpp^-1 (g_p - sum_a W_a^T x_a)
     for (int64_t p = 0; p < nP; p++) {
       double rhs[3] = {g[e.paramStart[p]], g[e.paramStart[p] + 1], g[e.paramStart[p] + 2]};

@@ -1,0 +1,134 @@
+"""ctypes binding of oracle/liboracle.so (the CPU checker).  Test infrastructure only."""
+import ctypes as C
+import os, subprocess
+import numpy as np
+from visual_inertial_bundle_adjustment_b200 import graph as G
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int64)
+
+
+def load_oracle():
+    so = os.path.join(ROOT, "oracle", "liboracle.so")
+    if not os.path.exists(so):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")])
+    lib = C.CDLL(so)
+    lib.orc_last_error.restype = C.c_char_p
+    for f in ("orc_order", "orc_data_size", "orc_num_blocks", "orc_nnz_blocks"):
+        getattr(lib, f).restype = C.c_int64
+        getattr(lib, f).argtypes = [C.c_void_p]
+    lib.orc_damp.argtypes = [C.c_void_p, C.c_double]
+    lib.orc_scale_vec.argtypes = [C.c_void_p, C.c_int, C.c_double]
+    lib.orc_boxplus.argtypes = [C.c_int, C.c_uint32, C.c_double, _dp, _dp, C.c_int, _dp]
+    lib.orc_lm_iteration_timed.argtypes = [C.c_void_p, C.c_double, _dp, _dp, _dp]
+    lib.orc_eval_factor.argtypes = [C.c_void_p, C.c_int, C.c_int64, _dp, _dp, C.POINTER(C.c_int)]
+    return lib
+
+
+def dptr(a):
+    return a.ctypes.data_as(_dp)
+
+
+class Oracle:
+    def __init__(self, lib, graph):
+        self.lib, self.g = lib, graph
+        self.h = C.c_void_p()
+        self._desc = graph.desc()
+        self._ck(lib.orc_create(C.byref(self._desc), C.byref(self.h)))
+        self.order = lib.orc_order(self.h)
+        self.data_size = lib.orc_data_size(self.h)
+        self.nblocks = lib.orc_num_blocks(self.h)
+        self.nnz = lib.orc_nnz_blocks(self.h)
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise RuntimeError(self.lib.orc_last_error().decode())
+
+    def __del__(self):
+        try:
+            self.lib.orc_destroy(self.h)
+        except Exception:
+            pass
+
+    def structure(self):
+        rp = np.zeros(self.nblocks + 1, np.int64); ci = np.zeros(self.nnz, np.int64)
+        bo = np.zeros(self.nnz, np.int64); ps = np.zeros(self.nblocks + 1, np.int64)
+        self.lib.orc_get_structure(self.h, rp.ctypes.data_as(_ip), ci.ctypes.data_as(_ip), bo.ctypes.data_as(_ip), ps.ctypes.data_as(_ip))
+        return rp, ci, bo, ps
+
+    def eval_grad_hess(self, with_hess=True, update_cache=True, dont_retry=False, which=0):
+        c = C.c_double()
+        self._ck(self.lib.orc_eval_grad_hess(self.h, int(with_hess), int(update_cache), int(dont_retry), which, C.byref(c)))
+        return c.value
+
+    def eval_cost(self, comparable=True):
+        c = C.c_double(); st = G.vb_cost_stats()
+        self._ck(self.lib.orc_eval_cost(self.h, int(comparable), C.byref(c), C.byref(st)))
+        return c.value, (st.num_total, st.num_invalid, st.num_prev_invalid)
+
+    def damp(self, lam): self.lib.orc_damp(self.h, lam)
+    def factor(self): self._ck(self.lib.orc_factor(self.h))
+    def solve(self, which=0): self._ck(self.lib.orc_solve(self.h, which))
+    def scale(self, which, s): self.lib.orc_scale_vec(self.h, which, s)
+    def backup(self): self.lib.orc_backup(self.h)
+    def restore(self): self.lib.orc_restore(self.h)
+
+    def apply_step(self, which=0):
+        r = np.zeros(3)
+        self.lib.orc_apply_step(self.h, which, dptr(r))
+        return r
+
+    def get(self, which):
+        n = {0: self.order, 1: self.order, 2: self.order, 3: self.data_size, 4: self.g.var_data.size}[which]
+        out = np.zeros(n)
+        self._ck(self.lib.orc_get(self.h, which, dptr(out), n))
+        return out
+
+    def set(self, which, a):
+        a = np.ascontiguousarray(a, np.float64)
+        self._ck(self.lib.orc_set(self.h, which, dptr(a), a.size))
+
+    grad = property(lambda s: s.get(0)); step = property(lambda s: s.get(1))
+    hess = property(lambda s: s.get(3)); vars = property(lambda s: s.get(4))
+
+    def cache(self, store):
+        out = np.zeros(self.g.stores[store].count)
+        self.lib.orc_get_cache(self.h, store, dptr(out), out.size)
+        return out
+
+    def eval_factor(self, store, k, jac=True):
+        st = self.g.stores[store]
+        E = G.ERR_SIZE[st.type]
+        dims = self.g.var_tdim[st.vars[k]]
+        r = np.zeros(E); J = np.zeros(E * int(dims.sum())); valid = C.c_int()
+        self._ck(self.lib.orc_eval_factor(self.h, store, k, dptr(r), dptr(J) if jac else None, C.byref(valid)))
+        Js, o = [], 0
+        for d in dims:
+            Js.append(J[o:o + E * d].reshape(E, d)); o += E * d
+        return r, Js, bool(valid.value)
+
+    def optimize(self, settings, trace_cap=300):
+        summ = G.vb_summary(); tp = np.zeros(trace_cap); tn = np.zeros(trace_cap)
+        self._ck(self.lib.orc_optimize(self.h, C.byref(settings), C.byref(summ), dptr(tp), dptr(tn), trace_cap))
+        n = summ.num_iterations
+        return summ, tp[:n], tn[:n]
+
+    def lm_iteration_timed(self, lam):
+        ms = np.zeros(7); c0 = C.c_double(); c1 = C.c_double()
+        self._ck(self.lib.orc_lm_iteration_timed(self.h, lam, dptr(ms), C.byref(c0), C.byref(c1)))
+        return ms, c0.value, c1.value
+
+    def dense_hessian(self):
+        """Symmetric dense H in registration order from the block CSR (small problems only)."""
+        rp, ci, bo, ps = self.structure()
+        H = np.zeros((self.order, self.order)); h = self.hess
+        for i in range(self.nblocks):
+            di = ps[i + 1] - ps[i]
+            for k in range(rp[i], rp[i + 1]):
+                j = ci[k]; dj = ps[j + 1] - ps[j]
+                B = h[bo[k]:bo[k] + di * dj].reshape(di, dj)
+                H[ps[i]:ps[i + 1], ps[j]:ps[j + 1]] = B
+                if i != j:
+                    H[ps[j]:ps[j + 1], ps[i]:ps[i + 1]] = B.T
+        return H

@@ -17,9 +17,9 @@ def lie(lib, fn, x, n):
 def test_so3_se3_roundtrip(oracle):
     rng = np.random.default_rng(42)
     for _ in range(50):
-        w = rng.normal(0, 1, 3)
+        w = rng.normal(0, 0.6, 3)
         assert np.allclose(lie(oracle, 1, lie(oracle, 0, w, 4), 3), w, atol=1e-12)
-        d = rng.normal(0, 1, 6)
+        d = rng.normal(0, 0.6, 6)
         assert np.allclose(lie(oracle, 3, lie(oracle, 2, d, 7), 6), d, atol=1e-11)
     assert np.allclose(lie(oracle, 1, lie(oracle, 0, np.zeros(3), 4), 3), 0)
     w = np.array([1e-12, -2e-12, 3e-13])

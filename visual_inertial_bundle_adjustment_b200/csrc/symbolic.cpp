@@ -1,0 +1,338 @@
+// See symbolic.hpp.  Pure host C++17; no CUDA here.
+#include "symbolic.hpp"
+#include <algorithm>
+#include <numeric>
+#include <stdexcept>
+#include <queue>
+#include <cstring>
+
+namespace vb {
+
+void HostGraph::load(const vb_graph_desc* g) {
+  if (!g || g->num_vars <= 0 || !g->var_kind || !g->var_tdim || !g->var_index || !g->var_off || !g->var_data)
+    throw std::runtime_error("vb_graph_desc: missing variable arrays");
+  nv = g->num_vars;
+  nP = g->num_points;
+  kind.assign(g->var_kind, g->var_kind + nv);
+  tdim.assign(g->var_tdim, g->var_tdim + nv);
+  flags.assign(nv, 0u);
+  if (g->var_flags) flags.assign(g->var_flags, g->var_flags + nv);
+  index.assign(g->var_index, g->var_index + nv);
+  off.assign(g->var_off, g->var_off + nv);
+  aux.assign(nv, 0.0);
+  if (g->var_aux) aux.assign(g->var_aux, g->var_aux + nv);
+  data.assign(g->var_data, g->var_data + g->var_data_len);
+  stores.resize(g->num_stores);
+  for (int s = 0; s < g->num_stores; s++) {
+    const vb_factor_store& fs = g->stores[s];
+    Store& st = stores[s];
+    st.type = fs.type; st.nvars = fs.nvars; st.cpf = fs.consts_per_factor; st.count = fs.count;
+    if (fs.count > 0 && (!fs.vars || (fs.consts_per_factor > 0 && !fs.consts)))
+      throw std::runtime_error("vb_factor_store: null table");
+    st.vars.assign(fs.vars, fs.vars + fs.count * fs.nvars);
+    for (int32_t v : st.vars)
+      if (v < 0 || v >= nv) throw std::runtime_error("vb_factor_store: variable id out of range");
+    st.consts.assign(fs.consts, fs.consts + fs.count * (int64_t)fs.consts_per_factor);
+    if (fs.aux && fs.aux_len > 0) st.aux.assign(fs.aux, fs.aux + fs.aux_len);
+    st.loss_a = fs.loss_a; st.loss_k = fs.loss_k;
+  }
+}
+
+static void sortUnique(std::vector<int64_t>& v) {
+  std::sort(v.begin(), v.end());
+  v.erase(std::unique(v.begin(), v.end()), v.end());
+}
+
+int32_t Symbolic::rowInLump(int32_t L, int32_t c) const {
+  if (camLump[c] == L) return camStart[c] - camStart[lumpFirst[L]];
+  const int32_t* b = lumpRowCam.data() + lumpRowPtr[L];
+  const int32_t* e = lumpRowCam.data() + lumpRowPtr[L + 1];
+  const int32_t* p = std::lower_bound(b, e, c);
+  if (p == e || *p != c) return -1;
+  return lumpRowOff[p - lumpRowCam.data()];
+}
+
+bool Symbolic::block(int64_t ri, int64_t rj, BlockRef* out) const {
+  int64_t pi = pos[ri], pj = pos[rj];
+  int32_t tr = 0;
+  if (pi < pj) { std::swap(pi, pj); tr = 1; }
+  if (pj < nP) { // landmark column
+    if (pi == pj) { *out = {lmOff[pj], 3, 0}; return true; }
+    if (pi < nP) return false;
+    const int32_t c = (int32_t)(pi - nP);
+    const int32_t* b = lmRowCam.data() + lmRowPtr[pj];
+    const int32_t* e = lmRowCam.data() + lmRowPtr[pj + 1];
+    const int32_t* p = std::lower_bound(b, e, c);
+    if (p == e || *p != c) return false;
+    *out = {lmOff[pj] + (int64_t)lmRowOff[p - lmRowCam.data()] * 3, 3, tr};
+    return true;
+  }
+  const int32_t cj = (int32_t)(pj - nP), ci = (int32_t)(pi - nP);
+  const int32_t L = camLump[cj];
+  const int32_t row = rowInLump(L, ci);
+  if (row < 0) return false;
+  const int32_t col = camStart[cj] - camStart[lumpFirst[L]];
+  *out = {lumpOff[L] + (int64_t)row * lumpWidth[L] + col, lumpWidth[L], tr};
+  return true;
+}
+
+void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp) {
+  Symbolic& S = *Sp;
+  const int64_t nP = g.nP;
+  int64_t nB = 0;
+  for (int64_t v = 0; v < g.nv; v++) if (g.index[v] >= 0) nB = std::max(nB, g.index[v] + 1);
+  if (nP < 0 || nP > nB) throw std::runtime_error("num_points out of range");
+  const int64_t nC = nB - nP;
+  if (nC >= (1ll << 31) || nP >= (1ll << 31)) throw std::runtime_error("too many blocks");
+  S.nB = nB; S.nP = nP; S.nC = nC;
+  S.bsize.assign(nB, 0);
+  for (int64_t v = 0; v < g.nv; v++)
+    if (g.index[v] >= 0) {
+      if (S.bsize[g.index[v]] != 0) throw std::runtime_error("duplicate registration index");
+      if (g.tdim[v] <= 0 || g.tdim[v] > 23) throw std::runtime_error("tangent dim out of range");
+      S.bsize[g.index[v]] = g.tdim[v];
+    }
+  for (int64_t b = 0; b < nB; b++) if (S.bsize[b] == 0) throw std::runtime_error("registration indices not contiguous");
+  for (int64_t p = 0; p < nP; p++) if (S.bsize[p] != 3) throw std::runtime_error("elimination range must hold 3-dim landmarks");
+
+  // ---- adjacency: landmark -> camera blocks, camera <-> camera (direct) --------------------
+  std::vector<int64_t> lmKeys, ccKeys;
+  for (const auto& st : g.stores) {
+    int64_t last = -1;
+    for (int64_t k = 0; k < st.count; k++) {
+      const int32_t* v = &st.vars[k * st.nvars];
+      int64_t lm = -1;
+      int64_t cams[16]; int nc = 0;
+      for (int i = 0; i < st.nvars; i++) {
+        const int64_t ii = g.index[v[i]];
+        if (ii < 0) continue;
+        if (ii < nP) { if (lm >= 0 && lm != ii) throw std::runtime_error("factor couples two landmarks"); lm = ii; }
+        else cams[nc++] = ii - nP;
+      }
+      if (lm >= 0)
+        for (int a = 0; a < nc; a++) {
+          const int64_t key = lm * nC + cams[a];
+          if (key != last) lmKeys.push_back(key);
+          last = key;
+        }
+      for (int a = 0; a < nc; a++)
+        for (int b = 0; b < a; b++)
+          if (cams[a] != cams[b]) ccKeys.push_back(std::max(cams[a], cams[b]) * nC + std::min(cams[a], cams[b]));
+      if (ccKeys.size() > (size_t)(1 << 24)) sortUnique(ccKeys);
+    }
+  }
+  sortUnique(lmKeys);
+  sortUnique(ccKeys);
+  // landmark -> cams CSR (camera registration order c = reg - nP)
+  std::vector<int64_t> lmPtr(nP + 1, 0);
+  std::vector<int32_t> lmCam(lmKeys.size());
+  for (size_t i = 0; i < lmKeys.size(); i++) { lmPtr[lmKeys[i] / nC + 1]++; lmCam[i] = (int32_t)(lmKeys[i] % nC); }
+  for (int64_t p = 0; p < nP; p++) lmPtr[p + 1] += lmPtr[p];
+  std::vector<int64_t>().swap(lmKeys);
+  // cam -> landmarks CSR
+  std::vector<int64_t> clPtr(nC + 1, 0);
+  for (int32_t c : lmCam) clPtr[c + 1]++;
+  for (int64_t c = 0; c < nC; c++) clPtr[c + 1] += clPtr[c];
+  std::vector<int32_t> clLm(lmCam.size());
+  {
+    std::vector<int64_t> fill(clPtr.begin(), clPtr.end() - 1);
+    for (int64_t p = 0; p < nP; p++)
+      for (int64_t k = lmPtr[p]; k < lmPtr[p + 1]; k++) clLm[fill[lmCam[k]]++] = (int32_t)p;
+  }
+  // cam <-> cam direct CSR (symmetric)
+  std::vector<int64_t> ccPtr(nC + 1, 0);
+  for (int64_t key : ccKeys) { ccPtr[key / nC + 1]++; ccPtr[key % nC + 1]++; }
+  for (int64_t c = 0; c < nC; c++) ccPtr[c + 1] += ccPtr[c];
+  std::vector<int32_t> ccAdj(ccPtr[nC]);
+  {
+    std::vector<int64_t> fill(ccPtr.begin(), ccPtr.end() - 1);
+    for (int64_t key : ccKeys) {
+      const int32_t a = (int32_t)(key / nC), b = (int32_t)(key % nC);
+      ccAdj[fill[a]++] = b; ccAdj[fill[b]++] = a;
+    }
+  }
+
+  // ---- ordering of the camera side: reverse Cuthill-McKee on the Schur-filled graph, walked
+  // through the landmark adjacency without materialising the fill ---------------------------
+  std::vector<int32_t> orderC; orderC.reserve(nC);
+  {
+    std::vector<char> vis(nC, 0), lmDone(nP, 0);
+    std::vector<int32_t> deg(nC);
+    for (int64_t c = 0; c < nC; c++) deg[c] = (int32_t)((ccPtr[c + 1] - ccPtr[c]) + (clPtr[c + 1] - clPtr[c]));
+    auto bfs = [&](int32_t root, std::vector<int32_t>& out, std::vector<char>& visited, std::vector<char>& lmd) {
+      size_t head = out.size();
+      out.push_back(root); visited[root] = 1;
+      std::vector<int32_t> nb;
+      while (head < out.size()) {
+        const int32_t u = out[head++];
+        nb.clear();
+        for (int64_t k = ccPtr[u]; k < ccPtr[u + 1]; k++) { const int32_t w = ccAdj[k]; if (!visited[w]) { visited[w] = 1; nb.push_back(w); } }
+        for (int64_t k = clPtr[u]; k < clPtr[u + 1]; k++) {
+          const int32_t p = clLm[k];
+          if (lmd[p]) continue;
+          lmd[p] = 1;
+          for (int64_t q = lmPtr[p]; q < lmPtr[p + 1]; q++) { const int32_t w = lmCam[q]; if (!visited[w]) { visited[w] = 1; nb.push_back(w); } }
+        }
+        std::sort(nb.begin(), nb.end(), [&](int32_t a, int32_t b) { return deg[a] != deg[b] ? deg[a] < deg[b] : a < b; });
+        out.insert(out.end(), nb.begin(), nb.end());
+      }
+    };
+    std::vector<int32_t> byDeg(nC);
+    std::iota(byDeg.begin(), byDeg.end(), 0);
+    std::stable_sort(byDeg.begin(), byDeg.end(), [&](int32_t a, int32_t b) { return deg[a] < deg[b]; });
+    int nComponents = 0;
+    for (int32_t seed : byDeg) {
+      if (vis[seed]) continue;
+      // pseudo-peripheral root: two BFS sweeps on scratch marks restricted to this component
+      int32_t root = seed;
+      for (int sweep = 0; sweep < 2 && nComponents < 4; sweep++) {
+        std::vector<char> v2(vis), l2(lmDone);
+        std::vector<int32_t> tmp;
+        bfs(root, tmp, v2, l2);
+        root = tmp.back();
+        if (tmp.size() > 200000) break; // one sweep is enough on very large components
+      }
+      bfs(root, orderC, vis, lmDone);
+      nComponents++;
+    }
+    std::reverse(orderC.begin(), orderC.end());
+  }
+  std::vector<int32_t> cpos(nC); // camera registration c -> camera position
+  for (int64_t i = 0; i < nC; i++) cpos[orderC[i]] = (int32_t)i;
+
+  S.pos.assign(nB, 0); S.posToReg.assign(nB, 0);
+  for (int64_t p = 0; p < nP; p++) { S.pos[p] = p; S.posToReg[p] = p; }
+  for (int64_t c = 0; c < nC; c++) { S.pos[nP + c] = nP + cpos[c]; S.posToReg[nP + cpos[c]] = nP + c; }
+  S.vecStart.assign(nB + 1, 0);
+  for (int64_t q = 0; q < nB; q++) S.vecStart[q + 1] = S.vecStart[q] + S.bsize[S.posToReg[q]];
+  S.order = S.vecStart[nB];
+  S.camStart.assign(nC + 1, 0);
+  for (int64_t q = 0; q < nC; q++) S.camStart[q + 1] = S.camStart[q] + S.bsize[S.posToReg[nP + q]];
+
+  // ---- landmark panels ------------------------------------------------------------------------
+  S.lmOff.assign(nP + 1, 0); S.lmRowPtr = lmPtr;
+  S.lmRowCam.resize(lmCam.size()); S.lmRowOff.resize(lmCam.size());
+  S.schurFlops = 0;
+  {
+    int64_t off = 0;
+    for (int64_t p = 0; p < nP; p++) {
+      S.lmOff[p] = off;
+      const int64_t b = lmPtr[p], e = lmPtr[p + 1];
+      for (int64_t k = b; k < e; k++) S.lmRowCam[k] = cpos[lmCam[k]];
+      std::sort(S.lmRowCam.begin() + b, S.lmRowCam.begin() + e);
+      int32_t row = 3;
+      for (int64_t k = b; k < e; k++) { S.lmRowOff[k] = row; row += S.camStart[S.lmRowCam[k] + 1] - S.camStart[S.lmRowCam[k]]; }
+      off += (int64_t)row * 3;
+      const double m = row - 3;
+      S.schurFlops += 3.0 * m * m + 9.0 * m + 9.0;
+    }
+    S.lmOff[nP] = off;
+    S.lmDataSize = off;
+  }
+
+  // ---- symbolic Cholesky of the reduced camera system (column structures via the etree) ------
+  std::vector<std::vector<int32_t>> cstruct(nC);
+  std::vector<int32_t> parent(nC, -1);
+  {
+    // landmarks bucketed by their first (minimum-position) neighbour
+    std::vector<int64_t> byMinPtr(nC + 1, 0);
+    for (int64_t p = 0; p < nP; p++) if (lmPtr[p + 1] > lmPtr[p]) byMinPtr[S.lmRowCam[lmPtr[p]] + 1]++;
+    for (int64_t c = 0; c < nC; c++) byMinPtr[c + 1] += byMinPtr[c];
+    std::vector<int32_t> byMin(byMinPtr[nC]);
+    {
+      std::vector<int64_t> fill(byMinPtr.begin(), byMinPtr.end() - 1);
+      for (int64_t p = 0; p < nP; p++) if (lmPtr[p + 1] > lmPtr[p]) byMin[fill[S.lmRowCam[lmPtr[p]]]++] = (int32_t)p;
+    }
+    std::vector<std::vector<int32_t>> children(nC);
+    std::vector<int32_t> mark(nC, -1);
+    for (int32_t j = 0; j < (int32_t)nC; j++) {
+      std::vector<int32_t>& st = cstruct[j];
+      auto add = [&](int32_t w) { if (w > j && mark[w] != j) { mark[w] = j; st.push_back(w); } };
+      const int32_t cj = orderC[j];
+      for (int64_t k = ccPtr[cj]; k < ccPtr[cj + 1]; k++) add(cpos[ccAdj[k]]);
+      for (int64_t k = byMinPtr[j]; k < byMinPtr[j + 1]; k++) {
+        const int32_t p = byMin[k];
+        for (int64_t q = lmPtr[p] + 1; q < lmPtr[p + 1]; q++) add(S.lmRowCam[q]);
+      }
+      for (int32_t c : children[j]) {
+        for (int32_t w : cstruct[c]) add(w);
+      }
+      std::vector<int32_t>().swap(children[j]);
+      std::sort(st.begin(), st.end());
+      if (!st.empty()) { parent[j] = st[0]; children[st[0]].push_back(j); }
+    }
+  }
+
+  // ---- supernodes ("lumps"): chains of columns merged under a width cap and a fill budget ----
+  auto csize = [&](int32_t c) { return S.camStart[c + 1] - S.camStart[c]; };
+  S.camLump.assign(nC, 0);
+  S.lumpFirst.clear(); S.lumpWidth.clear(); S.lumpRows.clear(); S.lumpOff.clear();
+  S.lumpRowPtr.assign(1, 0); S.lumpRowCam.clear(); S.lumpRowOff.clear();
+  {
+    int32_t j = 0;
+    std::vector<int32_t> cur, merged;
+    while (j < (int32_t)nC) {
+      const int32_t j0 = j;
+      cur = cstruct[j];
+      int32_t width = csize(j);
+      auto scal = [&](const std::vector<int32_t>& v) { int64_t s = 0; for (int32_t c : v) s += csize(c); return s; };
+      double exact = (double)csize(j) * (csize(j) + scal(cur));
+      while (j + 1 < (int32_t)nC && parent[j] == j + 1 && width + csize(j + 1) <= opt.maxLumpWidth) {
+        const int32_t n = j + 1;
+        merged.clear();
+        // (cur \ {n}) U struct(n)
+        std::set_union(cur.begin() + (cur.size() && cur[0] == n ? 1 : 0), cur.end(), cstruct[n].begin(), cstruct[n].end(), std::back_inserter(merged));
+        const double exactN = exact + (double)csize(n) * (csize(n) + scal(cstruct[n]));
+        // lower-trapezoid area of the merged panel
+        const int64_t rowsBelow = scal(merged);
+        double area = 0;
+        int32_t rem = width + csize(n);
+        for (int32_t c = j0; c <= n; c++) { area += (double)csize(c) * (rem + rowsBelow); rem -= csize(c); }
+        if (area - exactN > opt.relaxFill * area) break;
+        cur.swap(merged);
+        exact = exactN;
+        width += csize(n);
+        j = n;
+      }
+      const int32_t L = (int32_t)S.lumpFirst.size();
+      S.lumpFirst.push_back(j0);
+      for (int32_t c = j0; c <= j; c++) S.camLump[c] = L;
+      S.lumpWidth.push_back(width);
+      int32_t row = width;
+      for (int32_t c : cur) { S.lumpRowCam.push_back(c); S.lumpRowOff.push_back(row); row += csize(c); }
+      S.lumpRowPtr.push_back((int64_t)S.lumpRowCam.size());
+      S.lumpRows.push_back(row);
+      j++;
+    }
+    S.nL = (int64_t)S.lumpFirst.size();
+    S.lumpFirst.push_back((int32_t)nC);
+  }
+  std::vector<std::vector<int32_t>>().swap(cstruct);
+
+  // ---- storage offsets, etree over lumps, levels, work estimates ------------------------------
+  S.lumpOff.assign(S.nL, 0);
+  S.lumpParent.assign(S.nL, -1);
+  S.lumpLevel.assign(S.nL, 0);
+  S.cholFlops = 0; S.maxLumpWidth = 0; S.maxLumpRows = 0;
+  int64_t off = S.lmDataSize;
+  for (int64_t L = 0; L < S.nL; L++) {
+    S.lumpOff[L] = off;
+    off += (int64_t)S.lumpRows[L] * S.lumpWidth[L];
+    const double w = S.lumpWidth[L], r = S.lumpRows[L] - S.lumpWidth[L];
+    S.cholFlops += w * w * w / 3.0 + w * w * r + w * r * r;
+    S.maxLumpWidth = std::max(S.maxLumpWidth, S.lumpWidth[L]);
+    S.maxLumpRows = std::max(S.maxLumpRows, S.lumpRows[L]);
+    if (S.lumpRowPtr[L + 1] > S.lumpRowPtr[L]) S.lumpParent[L] = S.camLump[S.lumpRowCam[S.lumpRowPtr[L]]];
+  }
+  S.dataSize = off;
+  int32_t maxLevel = 0;
+  for (int64_t L = 0; L < S.nL; L++) {
+    const int32_t p = S.lumpParent[L];
+    if (p >= 0) S.lumpLevel[p] = std::max(S.lumpLevel[p], S.lumpLevel[L] + 1);
+    maxLevel = std::max(maxLevel, S.lumpLevel[L]);
+  }
+  S.levels.assign(S.nL ? maxLevel + 1 : 0, {});
+  for (int64_t L = 0; L < S.nL; L++) S.levels[S.lumpLevel[L]].push_back((int32_t)L);
+}
+
+} // namespace vb

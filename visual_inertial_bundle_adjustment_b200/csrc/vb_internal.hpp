@@ -1,0 +1,88 @@
+// Internal definitions shared by the translation units of libviba_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "symbolic.hpp"
+
+namespace vb {
+
+#define VB_CUDA(x)                                                                          \
+  do {                                                                                      \
+    cudaError_t e_ = (x);                                                                   \
+    if (e_ != cudaSuccess) throw std::runtime_error(std::string(#x) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+constexpr int kPreintStride = 250; // R(4) dV(3) dP(3) dt(1) J(9x23) evalPoint(32)
+constexpr int kMaxVars = 10;
+
+// device view of one factor store (SoA tables + scatter map)
+struct DevStore {
+  int32_t type, nvars, cpf, npairs;
+  int64_t count;
+  const int32_t* vars;   // [count*nvars] variable ids
+  const double* consts;  // [count*cpf]
+  const double* aux;     // store-level (preintegration records)
+  double* cache;         // ResultCache (Factor.h:92-94): last valid 0.5*rho or -1
+  double loss_a, loss_k;
+  const int64_t* gOff;    // [count*nvars] scalar offset in the permuted vectors, -1 for constants
+  const int64_t* hOff;    // [count*npairs] pair (i,j<=i) at i*(i+1)/2+j ; -1 if absent
+  const int32_t* hStride; // [count*npairs] row stride | (transposed << 30)
+};
+
+// device view of the variables
+struct DevVars {
+  int64_t nv;
+  const int32_t* kind;
+  const int32_t* tdim;
+  const uint32_t* flags;
+  const int64_t* off;    // offset of the variable's data
+  const int64_t* vecOff; // permuted scalar offset or -1
+  const double* aux;
+  double* data;
+};
+
+// device view of the solver structure
+struct DevSolver {
+  int64_t nP, nC, nL;
+  const int64_t* lmOff; const int64_t* lmRowPtr; const int32_t* lmRowCam; const int32_t* lmRowOff;
+  const int32_t* camLump; const int32_t* camStart; const int32_t* lumpFirst;
+  const int32_t* lumpWidth; const int32_t* lumpRows; const int64_t* lumpOff;
+  const int64_t* lumpRowPtr; const int32_t* lumpRowCam; const int32_t* lumpRowOff;
+  const int64_t* diagLOff;  // [nL] offset of the factored diagonal block in diagL
+  double* diagL;
+  // update tables (per lump, indexed by below-row scalar q)
+  const int64_t* updPtr;    // [nL+1] start of the lump's below rows in the per-row arrays
+  const int64_t* updColOff; // target address of column role: lumpOff[T] + col
+  const int32_t* updStride; // width of T
+  const int32_t* updTgt;    // target index t among the lump's distinct targets
+  const int32_t* updGlobal; // reduced-system scalar index of the row
+  const int64_t* relPtr;    // [nL+1] start of rel table (nT * r ints)
+  const int32_t* rel;       // rel[t*r + q] = row of q inside T's panel
+  int64_t camVec0;          // scalar offset of the camera section in the permuted vectors (= 3 nP)
+};
+
+struct LevelTask { int32_t lump, ti, tj; };
+
+// kernels_factors.cu
+void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
+                    double* costAcc, cudaStream_t s);
+void launchCost(const DevStore& st, const DevVars& v, int comparable, double* acc /* cost,total,invalid,prevInvalid */, cudaStream_t s);
+void launchApplyStep(const DevVars& v, const int64_t* blockVar, int64_t nB, const double* step, double* ratioAcc, cudaStream_t s);
+void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize, int64_t nB,
+                   double lambda, cudaStream_t s);
+// kernels_solver.cu
+void launchSchur(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
+void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s);
+void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s);
+void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);
+void launchSolveLandmarksBwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);
+void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int useAtomics, cudaStream_t s);
+void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, cudaStream_t s);
+// op: 0 a=b ; 1 a*=s ; 2 out[0]+=a.b ; 3 a=0
+void launchVecOp(int op, double* a, const double* b, double s, int64_t n, double* out, cudaStream_t st);
+double measureDmmaPeak(cudaStream_t s);
+
+} // namespace vb

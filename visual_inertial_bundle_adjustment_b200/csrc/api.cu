@@ -1,0 +1,706 @@
+// C ABI of libviba_b200.so (include/viba_b200.h).  Host control in C++17, all arithmetic of the LM
+// iteration on the device; there is no CPU fallback: every compute entry point needs an sm_100 GPU.
+#include <cstring>
+#include <cstdio>
+#include <cmath>
+#include <algorithm>
+#include <memory>
+#include "vb_internal.hpp"
+
+using namespace vb;
+
+static thread_local std::string g_err;
+
+struct vb_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+};
+
+struct vb_problem {
+  vb_ctx* ctx = nullptr;
+  HostGraph g;
+  Symbolic S;
+  std::vector<void*> allocs;
+  DevVars dv{};
+  std::vector<DevStore> ds;
+  DevSolver sol{};
+  double *hess = nullptr, *grad = nullptr, *step = nullptr, *gradNew = nullptr, *backup = nullptr, *acc = nullptr;
+  double* accHost = nullptr; // pinned
+  int* errFlag = nullptr;
+  int64_t* blockVar = nullptr;
+  int64_t* diagOff = nullptr; int32_t* diagStride = nullptr; int32_t* diagSize = nullptr;
+  int32_t* levelLumps = nullptr; LevelTask* levelTasks = nullptr;
+  std::vector<int64_t> levelLumpOff, levelTaskOff;
+  std::vector<int32_t> levelMaxBelow, levelMaxWidth;
+  int64_t varDataLen = 0;
+  double visualBytes = 0;
+  cudaEvent_t ev[10];
+
+  template <typename T>
+  T* alloc(size_t n) {
+    void* p = nullptr;
+    VB_CUDA(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+    allocs.push_back(p);
+    return (T*)p;
+  }
+  template <typename T>
+  T* upload(const std::vector<T>& v) {
+    T* p = alloc<T>(v.size());
+    if (!v.empty()) VB_CUDA(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return p;
+  }
+  ~vb_problem() {
+    for (void* p : allocs) cudaFree(p);
+    if (accHost) cudaFreeHost(accHost);
+  }
+};
+
+#define VB_TRY try {
+#define VB_CATCH                                                  \
+  }                                                               \
+  catch (const std::bad_alloc&) { g_err = "out of host memory"; return VB_ERR_STATE; } \
+  catch (const std::invalid_argument& ex) { g_err = ex.what(); return VB_ERR_ARG; }     \
+  catch (const std::exception& ex) {                              \
+    g_err = ex.what();                                            \
+    return (g_err.find("cuda") != std::string::npos || g_err.find("CUDA") != std::string::npos) ? VB_ERR_CUDA : VB_ERR_ARG; \
+  }                                                               \
+  return VB_OK;
+
+static void buildDeviceProblem(vb_problem& P) {
+  const HostGraph& g = P.g;
+  const Symbolic& S = P.S;
+  // variables
+  std::vector<int64_t> vecOff(g.nv, -1);
+  std::vector<int64_t> blockVar(S.nB, -1);
+  for (int64_t v = 0; v < g.nv; v++)
+    if (g.index[v] >= 0) { vecOff[v] = S.vecStart[S.pos[g.index[v]]]; blockVar[g.index[v]] = v; }
+  P.dv.nv = g.nv;
+  P.dv.kind = P.upload(g.kind); P.dv.tdim = P.upload(g.tdim); P.dv.flags = P.upload(g.flags);
+  P.dv.off = P.upload(g.off); P.dv.vecOff = P.upload(vecOff); P.dv.aux = P.upload(g.aux);
+  P.dv.data = P.upload(g.data);
+  P.varDataLen = (int64_t)g.data.size();
+  P.backup = P.alloc<double>(g.data.size());
+  P.blockVar = P.upload(blockVar);
+  // diagonal blocks for damping
+  {
+    std::vector<int64_t> off(S.nB); std::vector<int32_t> st(S.nB), sz(S.nB);
+    for (int64_t b = 0; b < S.nB; b++) {
+      BlockRef br;
+      if (!S.block(b, b, &br)) throw std::runtime_error("diagonal block missing");
+      off[b] = br.off; st[b] = br.stride; sz[b] = S.bsize[b];
+    }
+    P.diagOff = P.upload(off); P.diagStride = P.upload(st); P.diagSize = P.upload(sz);
+  }
+  // factor stores + scatter maps
+  P.ds.resize(g.stores.size());
+  for (size_t s = 0; s < g.stores.size(); s++) {
+    const HostGraph::Store& hs = g.stores[s];
+    DevStore& d = P.ds[s];
+    const int nv = hs.nvars, np = nv * (nv + 1) / 2;
+    d.type = hs.type; d.nvars = nv; d.cpf = hs.cpf; d.npairs = np; d.count = hs.count;
+    d.loss_a = hs.loss_a; d.loss_k = hs.loss_k;
+    d.vars = P.upload(hs.vars); d.consts = P.upload(hs.consts); d.aux = P.upload(hs.aux);
+    std::vector<double> cache(hs.count, 0.0);
+    d.cache = P.upload(cache);
+    std::vector<int64_t> gOff((size_t)hs.count * nv), hOff((size_t)hs.count * np);
+    std::vector<int32_t> hStride((size_t)hs.count * np);
+    int bad = 0;
+#pragma omp parallel for schedule(static) reduction(+ : bad)
+    for (int64_t k = 0; k < hs.count; k++) {
+      const int32_t* v = &hs.vars[k * nv];
+      for (int i = 0; i < nv; i++) {
+        const int64_t ii = g.index[v[i]];
+        gOff[k * nv + i] = ii < 0 ? -1 : S.vecStart[S.pos[ii]];
+        for (int j = 0; j <= i; j++) {
+          const int64_t jj = g.index[v[j]];
+          const int64_t pi = k * np + i * (i + 1) / 2 + j;
+          hOff[pi] = -1; hStride[pi] = 0;
+          if (ii < 0 || jj < 0) continue;
+          BlockRef br;
+          if (!S.block(ii, jj, &br)) { bad++; continue; }
+          hOff[pi] = br.off;
+          hStride[pi] = br.stride | ((i != j && ii != jj && br.transposed) ? (1 << 30) : 0);
+        }
+      }
+    }
+    if (bad) throw std::runtime_error("scatter map: block missing from the structure");
+    d.gOff = P.upload(gOff); d.hOff = P.upload(hOff); d.hStride = P.upload(hStride);
+    if (hs.type == VB_F_VISUAL) P.visualBytes += 224.0 * hs.count; // SURVEY.md §8d algorithmic bytes/obs
+    if (hs.type == VB_F_VISUAL_RS) P.visualBytes += 296.0 * hs.count;
+  }
+  // solver structure
+  DevSolver& d = P.sol;
+  d.nP = S.nP; d.nC = S.nC; d.nL = S.nL;
+  d.lmOff = P.upload(S.lmOff); d.lmRowPtr = P.upload(S.lmRowPtr); d.lmRowCam = P.upload(S.lmRowCam); d.lmRowOff = P.upload(S.lmRowOff);
+  d.camLump = P.upload(S.camLump); d.camStart = P.upload(S.camStart); d.lumpFirst = P.upload(S.lumpFirst);
+  d.lumpWidth = P.upload(S.lumpWidth); d.lumpRows = P.upload(S.lumpRows); d.lumpOff = P.upload(S.lumpOff);
+  d.lumpRowPtr = P.upload(S.lumpRowPtr); d.lumpRowCam = P.upload(S.lumpRowCam); d.lumpRowOff = P.upload(S.lumpRowOff);
+  d.camVec0 = S.vecStart[S.nP];
+  {
+    std::vector<int64_t> diagLOff(S.nL), updPtr(S.nL + 1, 0), relPtr(S.nL + 1, 0), colOff;
+    std::vector<int32_t> stride, tgt, glob, rel;
+    int64_t dl = 0;
+    for (int64_t L = 0; L < S.nL; L++) {
+      diagLOff[L] = dl; dl += (int64_t)S.lumpWidth[L] * S.lumpWidth[L];
+      const int r = S.lumpRows[L] - S.lumpWidth[L];
+      updPtr[L] = (int64_t)colOff.size();
+      relPtr[L] = (int64_t)rel.size();
+      std::vector<int32_t> targets;
+      for (int64_t k = S.lumpRowPtr[L]; k < S.lumpRowPtr[L + 1]; k++) {
+        const int32_t c = S.lumpRowCam[k];
+        const int32_t T = S.camLump[c];
+        if (targets.empty() || targets.back() != T) targets.push_back(T);
+        const int32_t t = (int32_t)targets.size() - 1;
+        const int32_t dc = S.camStart[c + 1] - S.camStart[c];
+        for (int32_t s = 0; s < dc; s++) {
+          colOff.push_back(S.lumpOff[T] + (S.camStart[c] + s - S.camStart[S.lumpFirst[T]]));
+          stride.push_back(S.lumpWidth[T]); tgt.push_back(t); glob.push_back(S.camStart[c] + s);
+        }
+      }
+      rel.resize(rel.size() + targets.size() * (size_t)r, -1);
+      for (size_t t = 0; t < targets.size(); t++) {
+        const int32_t T = targets[t];
+        int32_t q = 0;
+        for (int64_t k = S.lumpRowPtr[L]; k < S.lumpRowPtr[L + 1]; k++) {
+          const int32_t c = S.lumpRowCam[k];
+          const int32_t dc = S.camStart[c + 1] - S.camStart[c];
+          if (c >= S.lumpFirst[T]) {
+            const int32_t row = S.rowInLump(T, c);
+            if (row < 0) throw std::runtime_error("symbolic: ancestor structure does not contain a descendant row");
+            for (int32_t s = 0; s < dc; s++) rel[relPtr[L] + t * (size_t)r + q + s] = row + s;
+          }
+          q += dc;
+        }
+      }
+    }
+    updPtr[S.nL] = (int64_t)colOff.size(); relPtr[S.nL] = (int64_t)rel.size();
+    d.diagLOff = P.upload(diagLOff); d.diagL = P.alloc<double>(dl);
+    d.updPtr = P.upload(updPtr); d.updColOff = P.upload(colOff); d.updStride = P.upload(stride);
+    d.updTgt = P.upload(tgt); d.updGlobal = P.upload(glob); d.relPtr = P.upload(relPtr); d.rel = P.upload(rel);
+  }
+  // level schedules
+  {
+    std::vector<int32_t> lumps; std::vector<LevelTask> tasks;
+    for (const auto& lv : S.levels) {
+      P.levelLumpOff.push_back((int64_t)lumps.size());
+      P.levelTaskOff.push_back((int64_t)tasks.size());
+      int32_t mb = 0, mw = 0;
+      for (int32_t L : lv) {
+        lumps.push_back(L);
+        const int r = S.lumpRows[L] - S.lumpWidth[L];
+        mb = std::max(mb, r); mw = std::max(mw, S.lumpWidth[L]);
+        const int nt = (r + 63) / 64;
+        for (int ti = 0; ti < nt; ti++) for (int tj = 0; tj <= ti; tj++) tasks.push_back({L, ti, tj});
+      }
+      P.levelMaxBelow.push_back(mb); P.levelMaxWidth.push_back(mw);
+    }
+    P.levelLumpOff.push_back((int64_t)lumps.size());
+    P.levelTaskOff.push_back((int64_t)tasks.size());
+    P.levelLumps = P.upload(lumps); P.levelTasks = P.upload(tasks);
+  }
+  P.hess = P.alloc<double>(S.dataSize);
+  P.grad = P.alloc<double>(S.order); P.step = P.alloc<double>(S.order); P.gradNew = P.alloc<double>(S.order);
+  P.acc = P.alloc<double>(64 + 4 * g.stores.size());
+  P.errFlag = P.alloc<int>(1);
+  VB_CUDA(cudaMallocHost(&P.accHost, (64 + 4 * g.stores.size()) * sizeof(double)));
+  VB_CUDA(cudaMemset(P.hess, 0, S.dataSize * sizeof(double)));
+  VB_CUDA(cudaMemset(P.grad, 0, S.order * sizeof(double)));
+  VB_CUDA(cudaMemset(P.step, 0, S.order * sizeof(double)));
+  VB_CUDA(cudaMemset(P.gradNew, 0, S.order * sizeof(double)));
+  VB_CUDA(cudaMemset(P.errFlag, 0, sizeof(int)));
+  for (auto& e : P.ev) VB_CUDA(cudaEventCreate(&e));
+}
+
+static double* vecOf(vb_problem* p, int which) { return which == 0 ? p->step : which == 1 ? p->gradNew : p->grad; }
+static void requireProblem(const vb_problem* p) { if (!p) throw std::invalid_argument("null problem"); }
+static void syncCheck(vb_problem* p) { VB_CUDA(cudaStreamSynchronize(p->ctx->stream)); }
+
+extern "C" {
+
+int vb_version(void) { return 100; }
+const char* vb_last_error(void) { return g_err.c_str(); }
+
+void vb_settings_default(vb_settings* s) { // lib/small_thing/Optimizer.h:40-78
+  if (!s) return;
+  s->damping = 1e-5; s->damping_adjust_on_fail = 2.5; s->damping_adjust_on_good = 0.7; s->damping_adjust_on_average = 1.5;
+  s->damping_min = 1e-9; s->damping_max = 1e8;
+  s->min_relative_cost_reduction = 0.3; s->step_factor_decrease = 0.3; s->min_step_factor_for_good = 0.7;
+  s->absolute_cost_tolerance = 1e-8; s->relative_cost_tolerance = 1e-10; s->variables_tolerance = 1e-5;
+  s->max_step_factor_attempts = 2; s->try_sub_step = 1;
+  s->stop_if_no_improvement_for = 3; s->distance_from_troubled_iteration = 3; s->max_num_iterations = 50;
+  s->verbose = 0;
+}
+
+int vb_ctx_create(int device, vb_ctx** out) {
+  VB_TRY
+  if (!out) throw std::invalid_argument("null out");
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) throw std::runtime_error("CUDA: no device available (this library has no CPU fallback)");
+  if (device < 0 || device >= n) throw std::invalid_argument("device index out of range");
+  cudaDeviceProp prop;
+  VB_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) throw std::runtime_error("CUDA: device is not sm_100 (Blackwell) — kernels are built for sm_100a only");
+  VB_CUDA(cudaSetDevice(device));
+  auto* c = new vb_ctx();
+  c->device = device;
+  VB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  *out = c;
+  VB_CATCH
+}
+int vb_ctx_destroy(vb_ctx* ctx) {
+  if (!ctx) return VB_OK;
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return VB_OK;
+}
+
+int vb_problem_create(vb_ctx* ctx, const vb_graph_desc* g, vb_problem** out) {
+  VB_TRY
+  if (!ctx || !g || !out) throw std::invalid_argument("null argument");
+  VB_CUDA(cudaSetDevice(ctx->device));
+  std::unique_ptr<vb_problem> P(new vb_problem());
+  P->ctx = ctx;
+  P->g.load(g);
+  SymbolicOptions opt;
+  if (const char* e = getenv("VB_MAX_LUMP_WIDTH")) opt.maxLumpWidth = std::max(8, std::min(128, atoi(e)));
+  buildSymbolic(P->g, opt, &P->S);
+  buildDeviceProblem(*P);
+  *out = P.release();
+  VB_CATCH
+}
+int vb_problem_destroy(vb_problem* p) { delete p; return VB_OK; }
+
+// symbolic-only entry (host): lets CPU-side tests check the structure without a GPU
+int vb_symbolic_only(const vb_graph_desc* g, int64_t* order, int64_t* dataSize, int64_t* nLumps, int64_t* perm, int64_t permLen) {
+  VB_TRY
+  HostGraph hg; hg.load(g);
+  Symbolic S; buildSymbolic(hg, SymbolicOptions(), &S);
+  if (order) *order = S.order;
+  if (dataSize) *dataSize = S.dataSize;
+  if (nLumps) *nLumps = S.nL;
+  if (perm) { if (permLen != S.nB) throw std::invalid_argument("perm length"); std::copy(S.pos.begin(), S.pos.end(), perm); }
+  VB_CATCH
+}
+
+int64_t vb_order(const vb_problem* p) { return p ? p->S.order : -1; }
+int64_t vb_data_size(const vb_problem* p) { return p ? p->S.dataSize : -1; }
+int64_t vb_num_blocks(const vb_problem* p) { return p ? p->S.nB : -1; }
+int64_t vb_num_lumps(const vb_problem* p) { return p ? p->S.nL : -1; }
+int vb_get_param_start(const vb_problem* p, int64_t* out, int64_t n) {
+  VB_TRY
+  requireProblem(p);
+  if (n != p->S.nB) throw std::invalid_argument("length must be vb_num_blocks");
+  for (int64_t i = 0; i < n; i++) out[i] = p->S.vecStart[p->S.pos[i]];
+  VB_CATCH
+}
+int vb_get_perm(const vb_problem* p, int64_t* out, int64_t n) {
+  VB_TRY
+  requireProblem(p);
+  if (n != p->S.nB) throw std::invalid_argument("length must be vb_num_blocks");
+  std::copy(p->S.pos.begin(), p->S.pos.end(), out);
+  VB_CATCH
+}
+int vb_get_lump_start(const vb_problem* p, int64_t* out, int64_t n) {
+  VB_TRY
+  requireProblem(p);
+  if (n != p->S.nL + 1) throw std::invalid_argument("length must be vb_num_lumps + 1");
+  for (int64_t i = 0; i < n; i++) out[i] = p->S.nP + p->S.lumpFirst[i];
+  VB_CATCH
+}
+int vb_block_offset(const vb_problem* p, int64_t i, int64_t j, int64_t* offset, int64_t* stride, int32_t* transposed) {
+  VB_TRY
+  requireProblem(p);
+  if (i < 0 || j < 0 || i >= p->S.nB || j >= p->S.nB) throw std::invalid_argument("block index out of range");
+  BlockRef br;
+  if (!p->S.block(i, j, &br)) { *offset = -1; *stride = 0; *transposed = 0; }
+  else { *offset = br.off; *stride = br.stride; *transposed = br.transposed; }
+  VB_CATCH
+}
+int vb_get_work(const vb_problem* p, double* schur_flops, double* chol_flops, double* visual_bytes) {
+  VB_TRY
+  requireProblem(p);
+  if (schur_flops) *schur_flops = p->S.schurFlops;
+  if (chol_flops) *chol_flops = p->S.cholFlops;
+  if (visual_bytes) *visual_bytes = p->visualBytes;
+  VB_CATCH
+}
+
+static double evalGradHess(vb_problem* p, double* gvec, int with_hess, int update_cache, int dont_retry, bool sync) {
+  cudaStream_t s = p->ctx->stream;
+  VB_CUDA(cudaMemsetAsync(gvec, 0, p->S.order * sizeof(double), s));
+  if (with_hess) VB_CUDA(cudaMemsetAsync(p->hess, 0, p->S.dataSize * sizeof(double), s));
+  VB_CUDA(cudaMemsetAsync(p->acc, 0, sizeof(double), s));
+  for (const DevStore& st : p->ds) launchGradHess(st, p->dv, gvec, with_hess ? p->hess : nullptr, update_cache, dont_retry, p->acc, s);
+  if (!sync) return 0.0;
+  VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  return p->accHost[0];
+}
+int vb_eval_grad_hess(vb_problem* p, int with_hess, int update_cache, int dont_retry_failed, double* cost) {
+  VB_TRY
+  requireProblem(p);
+  const double c = evalGradHess(p, p->grad, with_hess, update_cache, dont_retry_failed, true);
+  if (cost) *cost = c;
+  VB_CATCH
+}
+int vb_eval_grad_new(vb_problem* p, int dont_retry_failed) {
+  VB_TRY
+  requireProblem(p);
+  evalGradHess(p, p->gradNew, 0, 0, dont_retry_failed, true);
+  VB_CATCH
+}
+static double evalCost(vb_problem* p, int comparable, vb_cost_stats* stats) {
+  cudaStream_t s = p->ctx->stream;
+  const size_t n = p->ds.size();
+  double* acc = p->acc + 64;
+  VB_CUDA(cudaMemsetAsync(acc, 0, 4 * n * sizeof(double), s));
+  for (size_t i = 0; i < n; i++) launchCost(p->ds[i], p->dv, comparable, acc + 4 * i, s);
+  VB_CUDA(cudaMemcpyAsync(p->accHost + 64, acc, 4 * n * sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  double tot = 0;
+  for (size_t i = 0; i < n; i++) tot += p->accHost[64 + 4 * i];
+  if (stats && n) { // Q3: CostStats of the last store only (Factor.h:686-688, Optimizer.cpp:93-95)
+    const double* a = p->accHost + 64 + 4 * (n - 1);
+    stats->num_total = (int64_t)a[1]; stats->num_invalid = (int64_t)a[2]; stats->num_prev_invalid = (int64_t)a[3];
+  }
+  return tot;
+}
+int vb_eval_cost(vb_problem* p, int comparable, double* cost, vb_cost_stats* stats) {
+  VB_TRY
+  requireProblem(p);
+  const double c = evalCost(p, comparable, stats);
+  if (cost) *cost = c;
+  VB_CATCH
+}
+int vb_damp(vb_problem* p, double lambda) {
+  VB_TRY
+  requireProblem(p);
+  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->ctx->stream);
+  VB_CATCH
+}
+int vb_step_from_grad(vb_problem* p) {
+  VB_TRY
+  requireProblem(p);
+  launchVecOp(0, p->step, p->grad, 0, p->S.order, nullptr, p->ctx->stream);
+  VB_CATCH
+}
+
+static void factorAsync(vb_problem* p, cudaEvent_t afterSchur) {
+  cudaStream_t s = p->ctx->stream;
+  VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
+  launchSchur(p->sol, p->hess, p->errFlag, s);
+  if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
+  for (size_t lv = 0; lv + 1 < p->levelLumpOff.size(); lv++) {
+    const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
+    const int nt = (int)(p->levelTaskOff[lv + 1] - p->levelTaskOff[lv]);
+    launchLumpFactor(p->sol, p->hess, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxBelow[lv], p->levelMaxWidth[lv], p->errFlag, s);
+    launchLumpUpdate(p->sol, p->hess, p->levelTasks + p->levelTaskOff[lv], nt, p->levelMaxWidth[lv], nl > 1, s);
+  }
+}
+static void checkNumeric(vb_problem* p) {
+  int flag = 0;
+  VB_CUDA(cudaMemcpyAsync(&flag, p->errFlag, sizeof(int), cudaMemcpyDeviceToHost, p->ctx->stream));
+  syncCheck(p);
+  if (flag == 1) throw std::domain_error("factor: landmark block not positive definite");
+  if (flag == 2) throw std::domain_error("factor: reduced camera system not positive definite");
+}
+static void solveAsync(vb_problem* p, double* vec) {
+  cudaStream_t s = p->ctx->stream;
+  const int nLv = (int)p->levelLumpOff.size() - 1;
+  launchSolveLandmarksFwd(p->sol, p->hess, vec, s);
+  for (int lv = 0; lv < nLv; lv++) {
+    const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
+    launchSolveLumpsFwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], nl > 1, s);
+  }
+  for (int lv = nLv - 1; lv >= 0; lv--) {
+    const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
+    launchSolveLumpsBwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv] + p->levelMaxBelow[lv], s);
+  }
+  launchSolveLandmarksBwd(p->sol, p->hess, vec, s);
+}
+#define VB_CATCH_NUMERIC                                                             \
+  }                                                                                  \
+  catch (const std::domain_error& ex) { g_err = ex.what(); return VB_ERR_NUMERIC; } \
+  catch (const std::invalid_argument& ex) { g_err = ex.what(); return VB_ERR_ARG; }  \
+  catch (const std::exception& ex) { g_err = ex.what(); return VB_ERR_CUDA; }        \
+  return VB_OK;
+
+int vb_factor(vb_problem* p) {
+  VB_TRY
+  requireProblem(p);
+  factorAsync(p, nullptr);
+  checkNumeric(p);
+  VB_CATCH_NUMERIC
+}
+int vb_solve(vb_problem* p, int which) {
+  VB_TRY
+  requireProblem(p);
+  solveAsync(p, vecOf(p, which));
+  syncCheck(p);
+  VB_CATCH_NUMERIC
+}
+static double dotVec(vb_problem* p, const double* a, const double* b) {
+  cudaStream_t s = p->ctx->stream;
+  VB_CUDA(cudaMemsetAsync(p->acc + 8, 0, sizeof(double), s));
+  launchVecOp(2, const_cast<double*>(a), b, 0, p->S.order, p->acc + 8, s);
+  VB_CUDA(cudaMemcpyAsync(p->accHost + 8, p->acc + 8, sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  return p->accHost[8];
+}
+int vb_step_stats(vb_problem* p, double* step_dot_grad, double* grad_norm, double* step_norm) {
+  VB_TRY
+  requireProblem(p);
+  if (step_dot_grad) *step_dot_grad = dotVec(p, p->step, p->grad);
+  if (grad_norm) *grad_norm = std::sqrt(dotVec(p, p->grad, p->grad));
+  if (step_norm) *step_norm = std::sqrt(dotVec(p, p->step, p->step));
+  VB_CATCH
+}
+int vb_scale_vec(vb_problem* p, int which, double sc) {
+  VB_TRY
+  requireProblem(p);
+  launchVecOp(1, vecOf(p, which), nullptr, sc, p->S.order, nullptr, p->ctx->stream);
+  VB_CATCH
+}
+int vb_dot(vb_problem* p, int a, int b, double* out) {
+  VB_TRY
+  requireProblem(p);
+  if (!out) throw std::invalid_argument("null out");
+  *out = dotVec(p, vecOf(p, a), vecOf(p, b));
+  VB_CATCH
+}
+static void applyStep(vb_problem* p, const double* vec, double ratios[3]) {
+  cudaStream_t s = p->ctx->stream;
+  VB_CUDA(cudaMemsetAsync(p->acc + 16, 0, 4 * sizeof(double), s));
+  launchApplyStep(p->dv, p->blockVar, p->S.nB, vec, p->acc + 16, s);
+  if (!ratios) return;
+  VB_CUDA(cudaMemcpyAsync(p->accHost + 16, p->acc + 16, 4 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  const double n = p->accHost[19];
+  ratios[0] = p->accHost[16]; ratios[1] = std::sqrt(p->accHost[17] / n); ratios[2] = p->accHost[18] / n;
+}
+int vb_apply_step(vb_problem* p, int which, double ratios[3]) {
+  VB_TRY
+  requireProblem(p);
+  double r[3];
+  applyStep(p, vecOf(p, which), r);
+  if (ratios) { ratios[0] = r[0]; ratios[1] = r[1]; ratios[2] = r[2]; }
+  VB_CATCH
+}
+int vb_backup(vb_problem* p) {
+  VB_TRY
+  requireProblem(p);
+  VB_CUDA(cudaMemcpyAsync(p->backup, p->dv.data, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, p->ctx->stream));
+  VB_CATCH
+}
+int vb_restore(vb_problem* p) {
+  VB_TRY
+  requireProblem(p);
+  VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, p->ctx->stream));
+  VB_CATCH
+}
+
+// Optimizer::optimize — lib/small_thing/Optimizer.cpp:768-1106, host control over device state.
+// Quirks Q1-Q5 of SURVEY.md App. A are kept (see the inline notes).
+int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) {
+  VB_TRY
+  requireProblem(p);
+  if (!st) throw std::invalid_argument("null settings");
+  cudaStream_t s = p->ctx->stream;
+  const int64_t n = p->S.order;
+  double damping = st->damping;
+  int iterationNum = 0, lastImprovementIteration = 0, lastTroubledIteration = -10;
+  double initialCost = 0, finalCost = 0, troubledSeqStartDamping = damping;
+  int troubledSeqStart = 0, numTroubledSeqs = 0, largestTroubledSeq = 0, stopReason = 1;
+  bool dontRetryFailed = false;
+  auto acceptable = [](const vb_cost_stats& c) {
+    const double rate = c.num_invalid / (c.num_total + 1.0);
+    return rate < 0.03 && (c.num_invalid < c.num_prev_invalid * 2.0 + 50);
+  };
+  while (true) {
+    const double prevCost = evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
+    finalCost = prevCost;
+    if (iterationNum == 0) initialCost = prevCost;
+    launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, damping, s);
+    launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
+    factorAsync(p, nullptr);
+    checkNumeric(p);
+    solveAsync(p, p->step);
+    const double modelCostReduction = dotVec(p, p->step, p->grad) * 0.5;
+    if (modelCostReduction < 0) { // Q1: recompute, bump damping, fall through with the bad step
+      evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
+      damping *= st->damping_adjust_on_fail;
+    }
+    launchVecOp(1, p->step, nullptr, -1.0, n, nullptr, s);
+    VB_CUDA(cudaMemcpyAsync(p->backup, p->dv.data, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    double ratios[3];
+    applyStep(p, p->step, ratios);
+    vb_cost_stats stats{};
+    double newCost = evalCost(p, 1, &stats);
+    double costReduction = prevCost - newCost;
+    const double ratioReductionToCost = costReduction / newCost;
+    double ratioReductionToExpected = costReduction / modelCostReduction;
+    double appliedStepFactor = 1.0;
+    bool failureRateIsAcceptable = acceptable(stats);
+    if (st->max_step_factor_attempts > 0 &&
+        (ratioReductionToExpected < st->min_relative_cost_reduction || !failureRateIsAcceptable)) {
+      evalGradHess(p, p->gradNew, 0, 0, dontRetryFailed, false);
+      const double backRed = -dotVec(p, p->gradNew, p->step) * 0.5;
+      double stepFactor = backRed > 0 ? (modelCostReduction / (modelCostReduction + backRed)) : st->step_factor_decrease;
+      for (int i = 0; i < st->max_step_factor_attempts; i++) {
+        appliedStepFactor *= stepFactor;
+        launchVecOp(1, p->step, nullptr, stepFactor, n, nullptr, s);
+        VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
+        applyStep(p, p->step, nullptr);
+        vb_cost_stats statsAtF{};
+        const double newCostAtF = evalCost(p, 1, &statsAtF);
+        const double costReductionAtF = prevCost - newCost; // Q2: stale newCost, as in the reference
+        const double ratioAtF = costReductionAtF / (modelCostReduction * appliedStepFactor);
+        if (ratioAtF >= st->min_relative_cost_reduction && acceptable(statsAtF)) {
+          newCost = newCostAtF; stats = statsAtF; costReduction = costReductionAtF;
+          ratioReductionToExpected = ratioAtF; failureRateIsAcceptable = true;
+          break;
+        }
+        if (st->try_sub_step) {
+          evalGradHess(p, p->gradNew, 0, 0, dontRetryFailed, false);
+          solveAsync(p, p->gradNew);
+          launchVecOp(1, p->gradNew, nullptr, -1.0, n, nullptr, s);
+          applyStep(p, p->gradNew, nullptr);
+          vb_cost_stats statsAtSub{};
+          const double newCostAtSub = evalCost(p, 1, &statsAtSub);
+          const double costReductionAtSub = prevCost - newCostAtSub;
+          const double ratioAtSub = costReductionAtSub / (modelCostReduction * appliedStepFactor);
+          if (ratioAtSub >= st->min_relative_cost_reduction && acceptable(statsAtSub)) {
+            newCost = newCostAtSub; stats = statsAtSub; costReduction = costReductionAtSub;
+            ratioReductionToExpected = ratioAtSub; failureRateIsAcceptable = true;
+            break;
+          }
+        }
+        dontRetryFailed = true; // Q5 latch
+        stepFactor = st->step_factor_decrease;
+      }
+    }
+    const bool toleranceHit = ratioReductionToCost < st->relative_cost_tolerance ||
+        costReduction < st->absolute_cost_tolerance || ratios[1] < st->variables_tolerance;
+    if (st->verbose)
+      std::printf("[viba_b200] it %d cost %.12g -> %.12g lambda %.3g model %.6g\n", iterationNum, prevCost, newCost, damping, modelCostReduction);
+    if (newCost > prevCost || !failureRateIsAcceptable) {
+      if (lastTroubledIteration != iterationNum - 1) { troubledSeqStartDamping = damping; troubledSeqStart = iterationNum; }
+      damping *= st->damping_adjust_on_fail;
+      VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
+      if (damping > st->damping_max) { stopReason = 2; break; }
+      lastTroubledIteration = iterationNum;
+    } else {
+      if (lastTroubledIteration == iterationNum - 1) {
+        if (troubledSeqStartDamping < 1e1 && damping > 1e-3) {
+          numTroubledSeqs++;
+          largestTroubledSeq = std::max(largestTroubledSeq, iterationNum - troubledSeqStart);
+        }
+      }
+      if (ratioReductionToExpected >= st->min_relative_cost_reduction && appliedStepFactor > st->min_step_factor_for_good) {
+        damping *= st->damping_adjust_on_good;
+        damping = std::max(damping, st->damping_min);
+      } else {
+        damping *= st->damping_adjust_on_average;
+      }
+      finalCost = newCost;
+    }
+    iterationNum++;
+    if (!toleranceHit) lastImprovementIteration = iterationNum;
+    if (iterationNum >= lastImprovementIteration + st->stop_if_no_improvement_for &&
+        iterationNum >= lastTroubledIteration + st->distance_from_troubled_iteration) { stopReason = 0; break; }
+    else if (iterationNum >= st->max_num_iterations) { stopReason = 1; break; }
+  }
+  syncCheck(p);
+  if (out) {
+    out->initial_cost = initialCost; out->final_cost = finalCost;
+    out->num_troubled_seqs = numTroubledSeqs; out->largest_troubled_seq = largestTroubledSeq;
+    out->num_iterations = iterationNum; out->stop_reason = stopReason;
+  }
+  VB_CATCH_NUMERIC
+}
+
+// one accepted-path LM iteration (Optimizer.cpp:800-1076 on the good-step path) with CUDA-event
+// timing of the phases the reference logs (g/H, factor, solve: Optimizer.cpp:1062-1067).
+int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times* t, double* cost_before, double* cost_after) {
+  VB_TRY
+  requireProblem(p);
+  cudaStream_t s = p->ctx->stream;
+  cudaEvent_t* e = p->ev;
+  const int64_t n = p->S.order;
+  VB_CUDA(cudaEventRecord(e[0], s));
+  evalGradHess(p, p->grad, 1, 1, 0, false);
+  VB_CUDA(cudaEventRecord(e[1], s));
+  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, s);
+  launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
+  VB_CUDA(cudaEventRecord(e[2], s));
+  factorAsync(p, e[3]);
+  VB_CUDA(cudaEventRecord(e[4], s));
+  solveAsync(p, p->step);
+  VB_CUDA(cudaMemsetAsync(p->acc + 8, 0, sizeof(double), s));
+  launchVecOp(2, p->step, p->grad, 0, n, p->acc + 8, s);
+  launchVecOp(1, p->step, nullptr, -1.0, n, nullptr, s);
+  VB_CUDA(cudaEventRecord(e[5], s));
+  VB_CUDA(cudaMemcpyAsync(p->backup, p->dv.data, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  applyStep(p, p->step, nullptr);
+  VB_CUDA(cudaEventRecord(e[6], s));
+  const size_t ns = p->ds.size();
+  VB_CUDA(cudaMemsetAsync(p->acc + 64, 0, 4 * ns * sizeof(double), s));
+  for (size_t i = 0; i < ns; i++) launchCost(p->ds[i], p->dv, 1, p->acc + 64 + 4 * i, s);
+  VB_CUDA(cudaEventRecord(e[7], s));
+  if (!apply) VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, (64 + 4 * ns) * sizeof(double), cudaMemcpyDeviceToHost, s));
+  checkNumeric(p);
+  auto ms = [&](int a, int b) { float f = 0; cudaEventElapsedTime(&f, e[a], e[b]); return (double)f; };
+  if (t) {
+    t->grad_hess = ms(0, 1); t->damping = ms(1, 2); t->factor_schur = ms(2, 3); t->factor_chol = ms(3, 4);
+    t->solve = ms(4, 5); t->apply = ms(5, 6); t->cost = ms(6, 7); t->total = ms(0, 7);
+  }
+  if (cost_before) *cost_before = p->accHost[0];
+  if (cost_after) { double c = 0; for (size_t i = 0; i < ns; i++) c += p->accHost[64 + 4 * i]; *cost_after = c; }
+  VB_CATCH_NUMERIC
+}
+
+static int copyOut(vb_problem* p, const double* src, int64_t len, double* out, int64_t n) {
+  VB_TRY
+  requireProblem(p);
+  if (!out || n != len) throw std::invalid_argument("buffer length mismatch");
+  syncCheck(p);
+  VB_CUDA(cudaMemcpy(out, src, len * sizeof(double), cudaMemcpyDeviceToHost));
+  VB_CATCH
+}
+static int copyIn(vb_problem* p, double* dst, int64_t len, const double* in, int64_t n) {
+  VB_TRY
+  requireProblem(p);
+  if (!in || n != len) throw std::invalid_argument("buffer length mismatch");
+  syncCheck(p);
+  VB_CUDA(cudaMemcpy(dst, in, len * sizeof(double), cudaMemcpyHostToDevice));
+  VB_CATCH
+}
+int vb_download_vars(vb_problem* p, double* o, int64_t n) { return p ? copyOut(p, p->dv.data, p->varDataLen, o, n) : VB_ERR_ARG; }
+int vb_upload_vars(vb_problem* p, const double* i, int64_t n) { return p ? copyIn(p, p->dv.data, p->varDataLen, i, n) : VB_ERR_ARG; }
+int vb_download_grad(vb_problem* p, double* o, int64_t n) { return p ? copyOut(p, p->grad, p->S.order, o, n) : VB_ERR_ARG; }
+int vb_download_step(vb_problem* p, double* o, int64_t n) { return p ? copyOut(p, p->step, p->S.order, o, n) : VB_ERR_ARG; }
+int vb_download_hess(vb_problem* p, double* o, int64_t n) { return p ? copyOut(p, p->hess, p->S.dataSize, o, n) : VB_ERR_ARG; }
+int vb_upload_hess(vb_problem* p, const double* i, int64_t n) { return p ? copyIn(p, p->hess, p->S.dataSize, i, n) : VB_ERR_ARG; }
+int vb_upload_grad(vb_problem* p, const double* i, int64_t n) { return p ? copyIn(p, p->grad, p->S.order, i, n) : VB_ERR_ARG; }
+int vb_download_factor_cache(vb_problem* p, int32_t store, double* o, int64_t n) {
+  if (!p || store < 0 || store >= (int)p->ds.size()) { g_err = "store index out of range"; return VB_ERR_ARG; }
+  return copyOut(p, p->ds[store].cache, p->ds[store].count, o, n);
+}
+int vb_upload_store_aux(vb_problem* p, int32_t store, const double* aux, int64_t n) {
+  if (!p || store < 0 || store >= (int)p->ds.size()) { g_err = "store index out of range"; return VB_ERR_ARG; }
+  return copyIn(p, const_cast<double*>(p->ds[store].aux), (int64_t)p->g.stores[store].aux.size(), aux, n);
+}
+int vb_upload_store_consts(vb_problem* p, int32_t store, const double* c, int64_t n) {
+  if (!p || store < 0 || store >= (int)p->ds.size()) { g_err = "store index out of range"; return VB_ERR_ARG; }
+  return copyIn(p, const_cast<double*>(p->ds[store].consts), (int64_t)p->g.stores[store].consts.size(), c, n);
+}
+int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops) {
+  VB_TRY
+  if (!ctx || !tflops) throw std::invalid_argument("null argument");
+  VB_CUDA(cudaSetDevice(ctx->device));
+  *tflops = measureDmmaPeak(ctx->stream);
+  VB_CATCH
+}
+
+} // extern "C"

@@ -1,0 +1,171 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same seeded
+synthetic sessions.  Tolerances (FP64): cost rel 1e-12 per evaluation, gradient/Hessian 1e-10 of
+scale, step vector 1e-7 (conditioning of the damped system), per-iteration LM cost rel 1e-9, final
+state 1e-6 — the gates of BASELINE.json's north_star."""
+import numpy as np
+import pytest
+from tests.oracle_lib import Oracle
+from visual_inertial_bundle_adjustment_b200 import synth, capi, graph as G
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+def to_reg(p, o, vec):
+    """permuted GPU vector -> oracle registration order"""
+    ps_g = p.param_start(); _, _, _, ps_o = o.structure()
+    out = np.zeros(o.order)
+    d = np.diff(ps_o)
+    for b in range(o.nblocks):
+        out[ps_o[b]:ps_o[b] + d[b]] = vec[ps_g[b]:ps_g[b] + d[b]]
+    return out
+
+
+def gpu_dense_hessian(p, o):
+    """lower-triangular blocks of the GPU Hessian gathered into a dense registration-order matrix"""
+    rp, ci, bo, ps = o.structure()
+    h = p.hess
+    H = np.zeros((o.order, o.order))
+    for i in range(o.nblocks):
+        di = ps[i + 1] - ps[i]
+        for k in range(rp[i], rp[i + 1]):
+            j = ci[k]; dj = ps[j + 1] - ps[j]
+            off, stride, tr = p.block_offset(i, j)
+            assert off >= 0
+            if tr:
+                B = np.array([[h[off + b * stride + a] for b in range(dj)] for a in range(di)])
+            else:
+                B = np.array([[h[off + a * stride + b] for b in range(dj)] for a in range(di)])
+            if i == j:
+                B = np.tril(B) + np.tril(B, -1).T
+            H[ps[i]:ps[i + 1], ps[j]:ps[j + 1]] = B
+            if i != j:
+                H[ps[j]:ps[j + 1], ps[i]:ps[i + 1]] = B.T
+    return H
+
+
+@pytest.fixture(scope="module", params=["tiny", "small"])
+def pair(request, ctx, oracle):
+    s = synth.make_session(**synth.CONFIGS[request.param])
+    o = Oracle(oracle, s.graph)
+    p = capi.Problem(ctx, s.graph)
+    yield s, o, p
+    p.close()
+
+
+def test_structure(pair):
+    s, o, p = pair
+    assert p.order == o.order and p.num_blocks == o.nblocks
+    perm = p.perm()
+    assert sorted(perm) == list(range(o.nblocks))
+    assert np.array_equal(perm[:s.n_points], np.arange(s.n_points))  # elimination range first, in order
+
+
+def test_grad_hess_cost(pair):
+    s, o, p = pair
+    co = o.eval_grad_hess()
+    cg = p.compute_grad_hess()
+    assert abs(cg - co) <= 1e-12 * abs(co)
+    go = o.grad; gg = to_reg(p, o, p.grad)
+    assert np.abs(gg - go).max() <= 1e-10 * np.abs(go).max()
+    if o.order <= 1000:
+        Ho = o.dense_hessian(); Hg = gpu_dense_hessian(p, o)
+        assert np.abs(Hg - Ho).max() <= 1e-10 * np.abs(Ho).max()
+    c1, st1 = o.eval_cost(True); c2, st2 = p.compute_cost(True)
+    assert abs(c1 - c2) <= 1e-12 * abs(c1) and st1 == st2
+    assert np.allclose(p.factor_cache(0), o.cache(0), rtol=1e-12, atol=0)
+
+
+def test_factor_solve_step(pair):
+    s, o, p = pair
+    o.eval_grad_hess(); p.compute_grad_hess()
+    o.damp(1e-4); p.add_damping(1e-4)
+    o.factor(); o.solve()
+    p.step_from_grad(); p.factor(); p.solve(0)
+    so = o.step; sg = to_reg(p, o, p.step)
+    assert np.abs(sg - so).max() <= 1e-7 * np.abs(so).max()
+    md_o = 0.5 * so @ o.grad; md_g = 0.5 * p.dot(0, 2)
+    assert abs(md_o - md_g) <= 1e-9 * abs(md_o)
+
+
+def test_apply_step_backup_restore(pair):
+    s, o, p = pair
+    v0 = p.vars
+    assert np.array_equal(v0, o.vars)
+    rng = np.random.default_rng(5)
+    step_reg = rng.normal(0, 1e-3, o.order)
+    o.set(1, step_reg)
+    # permuted copy for the GPU: upload through the gradient vector, then step = grad
+    ps_g = p.param_start(); _, _, _, ps_o = o.structure()
+    perm_step = np.zeros(o.order); d = np.diff(ps_o)
+    for b in range(o.nblocks):
+        perm_step[ps_g[b]:ps_g[b] + d[b]] = step_reg[ps_o[b]:ps_o[b] + d[b]]
+    p.set_grad(perm_step); p.step_from_grad()
+    o.backup(); p.backup_variables()
+    ro = o.apply_step(0); rg = p.apply_step(0)
+    assert np.allclose(ro, rg, rtol=1e-12)
+    assert np.abs(p.vars - o.vars).max() <= 1e-13
+    o.restore(); p.restore_variables()
+    assert np.array_equal(p.vars, v0) and np.array_equal(o.vars, v0)
+
+
+def test_lm_iteration_parity(ctx, oracle):
+    s = synth.make_session(**synth.CONFIGS["small"])
+    o = Oracle(oracle, s.graph); p = capi.Problem(ctx, s.graph)
+    st = G.default_settings(8)
+    so, tp, tn = o.optimize(st)
+    sg = p.optimize(st)
+    assert sg.num_iterations == so.num_iterations
+    assert abs(sg.initial_cost - so.initial_cost) <= 1e-12 * so.initial_cost
+    assert abs(sg.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert np.abs(p.vars - o.vars).max() <= 1e-6
+    p.close()
+
+
+def test_lm_converges_tiny(ctx, oracle):
+    s = synth.make_session(**synth.CONFIGS["tiny"])
+    o = Oracle(oracle, s.graph); p = capi.Problem(ctx, s.graph)
+    st = G.default_settings(40)
+    so, _, _ = o.optimize(st); sg = p.optimize(st)
+    assert sg.stop_reason == so.stop_reason == 0
+    assert abs(sg.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert np.abs(p.vars - o.vars).max() <= 1e-6
+    p.close()
+
+
+def test_invalid_factor_cache_semantics(ctx, oracle):
+    """a landmark pushed behind its cameras makes visual factors invalid (optional residual):
+    cached -1, comparable cost skips them, stats count them (Factor.h:390-417,576-583)."""
+    s = synth.make_session(**synth.CONFIGS["tiny"])
+    g = s.graph
+    data = g.var_data.copy()
+    v = s.ids["point"][0]
+    g.var_data[g.var_off[v]:g.var_off[v] + 3] = s.gt["X"][0] + np.array([0.0, -40.0, 0.0])
+    o = Oracle(oracle, g); p = capi.Problem(ctx, g)
+    g.var_data[:] = data
+    co = o.eval_grad_hess(); cg = p.compute_grad_hess()
+    assert abs(co - cg) <= 1e-12 * co
+    assert np.array_equal(p.factor_cache(0) < 0, o.cache(0) < 0) and (o.cache(0) < 0).sum() > 0
+    for comparable in (True, False):
+        c1, st1 = o.eval_cost(comparable); c2, st2 = p.compute_cost(comparable)
+        assert abs(c1 - c2) <= 1e-12 * c1 and st1 == st2
+    p.close()
+
+
+def test_full_size_properties_c1(ctx):
+    """BASELINE config C1 (60 s, 20k landmarks, 1M observations): size-independent properties —
+    H step solves the damped normal equations (residual check through a second gradient-only
+    product is not available, so: model reduction positive, cost decreases, iteration idempotent)."""
+    s = synth.make_session(**synth.CONFIGS["c1_60s"])
+    p = capi.Problem(ctx, s.graph)
+    t1, c0, c1 = p.lm_iteration_timed(1e-5, apply=False)
+    t2, d0, d1 = p.lm_iteration_timed(1e-5, apply=False)
+    assert c1 < c0 and abs(c0 - d0) <= 1e-12 * c0 and abs(c1 - d1) <= 1e-9 * c1
+    assert p.dot(0, 2) < 0  # step (negated) . grad < 0: descent direction
+    p.close()

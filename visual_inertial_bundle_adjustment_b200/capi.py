@@ -1,0 +1,234 @@
+"""ctypes binding of libviba_b200.so — the C ABI declared in include/viba_b200.h.
+
+This is the same stub a reference maintainer would bind; it holds no
+arithmetic.  Loading fails loudly if the CUDA library has not been built: there is no fallback.
+"""
+import ctypes as C
+import os
+import numpy as np
+from . import graph as G
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libviba_b200.so")
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int64)
+
+EXPORTS = [
+    "vb_version", "vb_last_error", "vb_settings_default", "vb_ctx_create", "vb_ctx_destroy",
+    "vb_problem_create", "vb_problem_destroy", "vb_order", "vb_data_size", "vb_num_blocks", "vb_num_lumps",
+    "vb_get_param_start", "vb_get_perm", "vb_get_lump_start", "vb_block_offset", "vb_get_work",
+    "vb_eval_grad_hess", "vb_eval_cost", "vb_damp", "vb_step_from_grad", "vb_factor", "vb_solve",
+    "vb_step_stats", "vb_scale_vec", "vb_dot", "vb_apply_step", "vb_backup", "vb_restore", "vb_eval_grad_new",
+    "vb_optimize", "vb_lm_iteration_timed", "vb_download_vars", "vb_upload_vars", "vb_download_grad",
+    "vb_download_step", "vb_download_hess", "vb_upload_hess", "vb_upload_grad", "vb_download_factor_cache",
+    "vb_upload_store_aux", "vb_upload_store_consts", "vb_measure_dmma_peak",
+]
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(make -C visual_inertial_bundle_adjustment_b200/csrc). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.vb_last_error.restype = C.c_char_p
+    for f in ("vb_order", "vb_data_size", "vb_num_blocks", "vb_num_lumps"):
+        getattr(lib, f).restype = C.c_int64
+        getattr(lib, f).argtypes = [C.c_void_p]
+    lib.vb_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.vb_ctx_destroy.argtypes = [C.c_void_p]
+    lib.vb_problem_create.argtypes = [C.c_void_p, C.POINTER(G.vb_graph_desc), C.POINTER(C.c_void_p)]
+    lib.vb_problem_destroy.argtypes = [C.c_void_p]
+    lib.vb_get_param_start.argtypes = [C.c_void_p, _ip, C.c_int64]
+    lib.vb_get_perm.argtypes = [C.c_void_p, _ip, C.c_int64]
+    lib.vb_get_lump_start.argtypes = [C.c_void_p, _ip, C.c_int64]
+    lib.vb_block_offset.argtypes = [C.c_void_p, C.c_int64, C.c_int64, _ip, _ip, C.POINTER(C.c_int32)]
+    lib.vb_get_work.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    lib.vb_eval_grad_hess.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp]
+    lib.vb_eval_cost.argtypes = [C.c_void_p, C.c_int, _dp, C.POINTER(G.vb_cost_stats)]
+    lib.vb_damp.argtypes = [C.c_void_p, C.c_double]
+    lib.vb_step_from_grad.argtypes = [C.c_void_p]
+    lib.vb_factor.argtypes = [C.c_void_p]
+    lib.vb_solve.argtypes = [C.c_void_p, C.c_int]
+    lib.vb_step_stats.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    lib.vb_scale_vec.argtypes = [C.c_void_p, C.c_int, C.c_double]
+    lib.vb_dot.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
+    lib.vb_apply_step.argtypes = [C.c_void_p, C.c_int, _dp]
+    lib.vb_backup.argtypes = [C.c_void_p]
+    lib.vb_restore.argtypes = [C.c_void_p]
+    lib.vb_eval_grad_new.argtypes = [C.c_void_p, C.c_int]
+    lib.vb_optimize.argtypes = [C.c_void_p, C.POINTER(G.vb_settings), C.POINTER(G.vb_summary)]
+    lib.vb_lm_iteration_timed.argtypes = [C.c_void_p, C.c_double, C.c_int, C.POINTER(G.vb_iter_times), _dp, _dp]
+    for f in ("vb_download_vars", "vb_upload_vars", "vb_download_grad", "vb_download_step", "vb_download_hess",
+              "vb_upload_hess", "vb_upload_grad"):
+        getattr(lib, f).argtypes = [C.c_void_p, _dp, C.c_int64]
+    for f in ("vb_download_factor_cache", "vb_upload_store_aux", "vb_upload_store_consts"):
+        getattr(lib, f).argtypes = [C.c_void_p, C.c_int32, _dp, C.c_int64]
+    lib.vb_measure_dmma_peak.argtypes = [C.c_void_p, _dp]
+    lib.vb_symbolic_only.argtypes = [C.POINTER(G.vb_graph_desc), _ip, _ip, _ip, _ip, C.c_int64]
+    _lib = lib
+    return lib
+
+
+class VbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"viba_b200 error {code}: {msg}")
+        self.code = code
+
+
+def _ck(lib, rc):
+    if rc != 0:
+        raise VbError(rc, lib.vb_last_error().decode())
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+def symbolic_only(graph):
+    """Host-only symbolic phase (no GPU needed): order, dataSize, number of lumps, permutation."""
+    lib = load()
+    desc = graph.desc()
+    o, ds, nl = C.c_int64(), C.c_int64(), C.c_int64()
+    perm = np.zeros(graph.num_blocks, np.int64)
+    _ck(lib, lib.vb_symbolic_only(C.byref(desc), C.byref(o), C.byref(ds), C.byref(nl), perm.ctypes.data_as(_ip), perm.size))
+    return o.value, ds.value, nl.value, perm
+
+
+class Context:
+    def __init__(self, device=0):
+        self.lib = load()
+        self.h = C.c_void_p()
+        _ck(self.lib, self.lib.vb_ctx_create(device, C.byref(self.h)))
+
+    def dmma_peak_tflops(self):
+        t = C.c_double()
+        _ck(self.lib, self.lib.vb_measure_dmma_peak(self.h, C.byref(t)))
+        return t.value
+
+    def close(self):
+        if self.h:
+            self.lib.vb_ctx_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class Problem:
+    """Thin object wrapper over vb_problem; method names follow small_thing::Optimizer
+    (lib/small_thing/Optimizer.h:115-335) where one exists."""
+
+    def __init__(self, ctx, graph):
+        self.ctx, self.lib, self.g = ctx, ctx.lib, graph
+        self.h = C.c_void_p()
+        desc = graph.desc()
+        _ck(self.lib, self.lib.vb_problem_create(ctx.h, C.byref(desc), C.byref(self.h)))
+        self.order = self.lib.vb_order(self.h)
+        self.data_size = self.lib.vb_data_size(self.h)
+        self.num_blocks = self.lib.vb_num_blocks(self.h)
+        self.num_lumps = self.lib.vb_num_lumps(self.h)
+
+    def close(self):
+        if self.h:
+            self.lib.vb_problem_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def param_start(self):
+        out = np.zeros(self.num_blocks, np.int64)
+        _ck(self.lib, self.lib.vb_get_param_start(self.h, out.ctypes.data_as(_ip), out.size))
+        return out
+
+    def perm(self):
+        out = np.zeros(self.num_blocks, np.int64)
+        _ck(self.lib, self.lib.vb_get_perm(self.h, out.ctypes.data_as(_ip), out.size))
+        return out
+
+    def lump_start(self):
+        out = np.zeros(self.num_lumps + 1, np.int64)
+        _ck(self.lib, self.lib.vb_get_lump_start(self.h, out.ctypes.data_as(_ip), out.size))
+        return out
+
+    def block_offset(self, i, j):
+        o, s, t = C.c_int64(), C.c_int64(), C.c_int32()
+        _ck(self.lib, self.lib.vb_block_offset(self.h, i, j, C.byref(o), C.byref(s), C.byref(t)))
+        return o.value, s.value, t.value
+
+    def work(self):
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        _ck(self.lib, self.lib.vb_get_work(self.h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(schur_flops=a.value, chol_flops=b.value, visual_bytes=c.value)
+
+    def compute_grad_hess(self, with_hess=True, update_cache=True, dont_retry_failed=False):
+        c = C.c_double()
+        _ck(self.lib, self.lib.vb_eval_grad_hess(self.h, int(with_hess), int(update_cache), int(dont_retry_failed), C.byref(c)))
+        return c.value
+
+    def compute_grad_new(self, dont_retry_failed=False):
+        _ck(self.lib, self.lib.vb_eval_grad_new(self.h, int(dont_retry_failed)))
+
+    def compute_cost(self, comparable=True):
+        c, st = C.c_double(), G.vb_cost_stats()
+        _ck(self.lib, self.lib.vb_eval_cost(self.h, int(comparable), C.byref(c), C.byref(st)))
+        return c.value, (st.num_total, st.num_invalid, st.num_prev_invalid)
+
+    def add_damping(self, lam): _ck(self.lib, self.lib.vb_damp(self.h, lam))
+    def step_from_grad(self): _ck(self.lib, self.lib.vb_step_from_grad(self.h))
+    def factor(self): _ck(self.lib, self.lib.vb_factor(self.h))
+    def solve(self, which=0): _ck(self.lib, self.lib.vb_solve(self.h, which))
+    def scale(self, which, s): _ck(self.lib, self.lib.vb_scale_vec(self.h, which, s))
+    def backup_variables(self): _ck(self.lib, self.lib.vb_backup(self.h))
+    def restore_variables(self): _ck(self.lib, self.lib.vb_restore(self.h))
+
+    def dot(self, a, b):
+        o = C.c_double()
+        _ck(self.lib, self.lib.vb_dot(self.h, a, b, C.byref(o)))
+        return o.value
+
+    def apply_step(self, which=0):
+        r = np.zeros(3)
+        _ck(self.lib, self.lib.vb_apply_step(self.h, which, _d(r)))
+        return r
+
+    def optimize(self, settings):
+        s = G.vb_summary()
+        _ck(self.lib, self.lib.vb_optimize(self.h, C.byref(settings), C.byref(s)))
+        return s
+
+    def lm_iteration_timed(self, lam, apply=False):
+        t, c0, c1 = G.vb_iter_times(), C.c_double(), C.c_double()
+        _ck(self.lib, self.lib.vb_lm_iteration_timed(self.h, lam, int(apply), C.byref(t), C.byref(c0), C.byref(c1)))
+        return {n: getattr(t, n) for n, _ in G.vb_iter_times._fields_}, c0.value, c1.value
+
+    def _get(self, fn, n):
+        out = np.zeros(n)
+        _ck(self.lib, fn(self.h, _d(out), n))
+        return out
+
+    def _put(self, fn, a):
+        a = np.ascontiguousarray(a, np.float64)
+        _ck(self.lib, fn(self.h, _d(a), a.size))
+
+    vars = property(lambda s: s._get(s.lib.vb_download_vars, s.g.var_data.size))
+    grad = property(lambda s: s._get(s.lib.vb_download_grad, s.order))
+    step = property(lambda s: s._get(s.lib.vb_download_step, s.order))
+    hess = property(lambda s: s._get(s.lib.vb_download_hess, s.data_size))
+    def set_vars(self, a): self._put(self.lib.vb_upload_vars, a)
+    def set_hess(self, a): self._put(self.lib.vb_upload_hess, a)
+    def set_grad(self, a): self._put(self.lib.vb_upload_grad, a)
+
+    def factor_cache(self, store):
+        out = np.zeros(self.g.stores[store].count)
+        _ck(self.lib, self.lib.vb_download_factor_cache(self.h, store, _d(out), out.size))
+        return out
+
+    def upload_store_aux(self, store, aux):
+        aux = np.ascontiguousarray(aux, np.float64)
+        _ck(self.lib, self.lib.vb_upload_store_aux(self.h, store, _d(aux), aux.size))

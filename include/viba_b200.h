@@ -138,6 +138,10 @@ int64_t vb_order(const vb_problem* p);
 int64_t vb_data_size(const vb_problem* p);
 int64_t vb_num_blocks(const vb_problem* p);
 int64_t vb_num_lumps(const vb_problem* p);
+int64_t vb_num_levels(const vb_problem* p);                 /* depth of the supernodal elimination tree */
+int64_t vb_num_launches_per_iteration(const vb_problem* p); /* kernels launched by vb_lm_iteration_timed */
+/* host-only symbolic phase (no device needed): order, dataSize, lumps, permutation[vb_num_blocks] */
+int vb_symbolic_only(const vb_graph_desc* g, int64_t* order, int64_t* data_size, int64_t* num_lumps, int64_t* perm, int64_t perm_len);
 /* accessor().paramStart(i) for every registration index (Factor.h:612) */
 int vb_get_param_start(const vb_problem* p, int64_t* out, int64_t n);
 /* elimination position of every registration index (the permutation) */

@@ -16,6 +16,7 @@ _ip = C.POINTER(C.c_int64)
 EXPORTS = [
     "vb_version", "vb_last_error", "vb_settings_default", "vb_ctx_create", "vb_ctx_destroy",
     "vb_problem_create", "vb_problem_destroy", "vb_order", "vb_data_size", "vb_num_blocks", "vb_num_lumps",
+    "vb_num_levels", "vb_num_launches_per_iteration", "vb_symbolic_only",
     "vb_get_param_start", "vb_get_perm", "vb_get_lump_start", "vb_block_offset", "vb_get_work",
     "vb_eval_grad_hess", "vb_eval_cost", "vb_damp", "vb_step_from_grad", "vb_factor", "vb_solve",
     "vb_step_stats", "vb_scale_vec", "vb_dot", "vb_apply_step", "vb_backup", "vb_restore", "vb_eval_grad_new",
@@ -36,7 +37,7 @@ def load():
                            "(make -C visual_inertial_bundle_adjustment_b200/csrc). There is no CPU fallback.")
     lib = C.CDLL(LIB_PATH)
     lib.vb_last_error.restype = C.c_char_p
-    for f in ("vb_order", "vb_data_size", "vb_num_blocks", "vb_num_lumps"):
+    for f in ("vb_order", "vb_data_size", "vb_num_blocks", "vb_num_lumps", "vb_num_levels", "vb_num_launches_per_iteration"):
         getattr(lib, f).restype = C.c_int64
         getattr(lib, f).argtypes = [C.c_void_p]
     lib.vb_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
@@ -129,6 +130,8 @@ class Problem:
         self.data_size = self.lib.vb_data_size(self.h)
         self.num_blocks = self.lib.vb_num_blocks(self.h)
         self.num_lumps = self.lib.vb_num_lumps(self.h)
+        self.num_levels = self.lib.vb_num_levels(self.h)
+        self.launches_per_iteration = self.lib.vb_num_launches_per_iteration(self.h)
 
     def close(self):
         if self.h:

@@ -286,6 +286,14 @@ int64_t vb_order(const vb_problem* p) { return p ? p->S.order : -1; }
 int64_t vb_data_size(const vb_problem* p) { return p ? p->S.dataSize : -1; }
 int64_t vb_num_blocks(const vb_problem* p) { return p ? p->S.nB : -1; }
 int64_t vb_num_lumps(const vb_problem* p) { return p ? p->S.nL : -1; }
+int64_t vb_num_levels(const vb_problem* p) { return p ? (int64_t)p->S.levels.size() : -1; }
+int64_t vb_num_launches_per_iteration(const vb_problem* p) { // kernels one vb_lm_iteration_timed launches
+  if (!p) return -1;
+  int64_t n = 0;
+  for (const auto& st : p->ds) n += st.count > 0 ? 2 : 0;     // grad/Hess + cost
+  const int64_t lv = (int64_t)p->S.levels.size();
+  return n + 2 /*damp, step=grad*/ + 1 + 2 * lv /*factor*/ + 2 + 2 * lv /*solve*/ + 2 /*dot, negate*/ + 1 /*apply*/;
+}
 int vb_get_param_start(const vb_problem* p, int64_t* out, int64_t n) {
   VB_TRY
   requireProblem(p);

@@ -134,6 +134,9 @@ int vb_problem_create(vb_ctx* ctx, const vb_graph_desc* g, vb_problem** out);
 int vb_problem_destroy(vb_problem* p);
 
 /* Solver::order(), dataSize() (Optimizer.cpp:339-340,777,783-784) and symbolic-phase outputs */
+/* host-only symbolic statistics for a given supernode width cap / nested-dissection leaf size:
+ * out8 = {order, dataSize, lumps, levels, maxLumpRows, cholFlops, schurFlops, widest level} */
+int vb_symbolic_stats(const vb_graph_desc* g, int max_lump_width, int nd_leaf_blocks, double* out8);
 int64_t vb_order(const vb_problem* p);
 int64_t vb_data_size(const vb_problem* p);
 int64_t vb_num_blocks(const vb_problem* p);

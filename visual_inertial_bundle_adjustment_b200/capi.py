@@ -16,7 +16,7 @@ _ip = C.POINTER(C.c_int64)
 EXPORTS = [
     "vb_version", "vb_last_error", "vb_settings_default", "vb_ctx_create", "vb_ctx_destroy",
     "vb_problem_create", "vb_problem_destroy", "vb_order", "vb_data_size", "vb_num_blocks", "vb_num_lumps",
-    "vb_num_levels", "vb_num_launches_per_iteration", "vb_symbolic_only",
+    "vb_num_levels", "vb_num_launches_per_iteration", "vb_symbolic_only", "vb_symbolic_stats",
     "vb_get_param_start", "vb_get_perm", "vb_get_lump_start", "vb_block_offset", "vb_get_work",
     "vb_eval_grad_hess", "vb_eval_cost", "vb_damp", "vb_step_from_grad", "vb_factor", "vb_solve",
     "vb_step_stats", "vb_scale_vec", "vb_dot", "vb_apply_step", "vb_backup", "vb_restore", "vb_eval_grad_new",
@@ -71,6 +71,7 @@ def load():
         getattr(lib, f).argtypes = [C.c_void_p, C.c_int32, _dp, C.c_int64]
     lib.vb_measure_dmma_peak.argtypes = [C.c_void_p, _dp]
     lib.vb_symbolic_only.argtypes = [C.POINTER(G.vb_graph_desc), _ip, _ip, _ip, _ip, C.c_int64]
+    lib.vb_symbolic_stats.argtypes = [C.POINTER(G.vb_graph_desc), C.c_int, C.c_int, _dp]
     _lib = lib
     return lib
 
@@ -98,6 +99,14 @@ def symbolic_only(graph):
     perm = np.zeros(graph.num_blocks, np.int64)
     _ck(lib, lib.vb_symbolic_only(C.byref(desc), C.byref(o), C.byref(ds), C.byref(nl), perm.ctypes.data_as(_ip), perm.size))
     return o.value, ds.value, nl.value, perm
+
+
+def symbolic_stats(graph, max_lump_width=0, nd_leaf_blocks=600):
+    lib = load()
+    desc = graph.desc()
+    out = np.zeros(8)
+    _ck(lib, lib.vb_symbolic_stats(C.byref(desc), max_lump_width, nd_leaf_blocks, _d(out)))
+    return dict(zip(["order", "data_size", "lumps", "levels", "max_lump_rows", "chol_flops", "schur_flops", "widest_level"], out))
 
 
 class Context:

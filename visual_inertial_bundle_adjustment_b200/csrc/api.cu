@@ -263,6 +263,7 @@ int vb_problem_create(vb_ctx* ctx, const vb_graph_desc* g, vb_problem** out) {
   P->g.load(g);
   SymbolicOptions opt;
   if (const char* e = getenv("VB_MAX_LUMP_WIDTH")) opt.maxLumpWidth = std::max(8, std::min(128, atoi(e)));
+  if (const char* e = getenv("VB_ND_LEAF_BLOCKS")) opt.ndLeafBlocks = atoi(e);
   buildSymbolic(P->g, opt, &P->S);
   buildDeviceProblem(*P);
   *out = P.release();
@@ -279,6 +280,21 @@ int vb_symbolic_only(const vb_graph_desc* g, int64_t* order, int64_t* dataSize, 
   if (dataSize) *dataSize = S.dataSize;
   if (nLumps) *nLumps = S.nL;
   if (perm) { if (permLen != S.nB) throw std::invalid_argument("perm length"); std::copy(S.pos.begin(), S.pos.end(), perm); }
+  VB_CATCH
+}
+
+// host-only: {order, dataSize, lumps, levels, maxLumpRows, cholFlops, schurFlops, widest level (lumps)}
+int vb_symbolic_stats(const vb_graph_desc* g, int max_lump_width, int nd_leaf_blocks, double* out8) {
+  VB_TRY
+  HostGraph hg; hg.load(g);
+  SymbolicOptions opt;
+  if (max_lump_width > 0) opt.maxLumpWidth = max_lump_width;
+  opt.ndLeafBlocks = nd_leaf_blocks;
+  Symbolic S; buildSymbolic(hg, opt, &S);
+  size_t widest = 0;
+  for (const auto& lv : S.levels) widest = std::max(widest, lv.size());
+  out8[0] = (double)S.order; out8[1] = (double)S.dataSize; out8[2] = (double)S.nL; out8[3] = (double)S.levels.size();
+  out8[4] = S.maxLumpRows; out8[5] = S.cholFlops; out8[6] = S.schurFlops; out8[7] = (double)widest;
   VB_CATCH
 }
 

@@ -1,0 +1,332 @@
+// Supernodal Cholesky of the reduced camera system and the supernode part of the
+// solves (K11), level-scheduled over the elimination tree.  The dense contractions — panel trsm
+// updates and the supernode outer product B B^T — run on the FP64 tensor pipe through
+// mma.sync.aligned.m8n8k4.f64 (DMMA; tcgen05 has no f64 kind), operands staged in shared memory.
+#include "vb_internal.hpp"
+#include "dev_math.cuh"
+
+namespace vb {
+
+// D(8x8) += A(8x4, row) * B(4x8, col).  Lane l holds a = A[l/4][l%4], b = B[l%4][l/4],
+// c = C[l/4][2*(l%4) + {0,1}].
+VB_DEV void dmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+// shared-memory leading dimension: >= n rounded up to the 8-wide MMA tiles, == 4 mod 8 so that the
+// 4-row x 4-column fragment loads of a half warp hit 16 distinct 8-byte banks
+__host__ __device__ inline int ldFor(int n) { return ((n + 7) & ~7) + 4; }
+
+// acc[mt][nt] (8x8 tiles) += A[rowBase + 8 mt .., :K] * B[colBase + 8 nt .., :K]^T, A/B row-major in smem
+template <int MT, int NT>
+VB_DEV void dmmaABt(const double* As, int lda, const double* Bs, int ldb, int K4, int rowBase, int colBase, double (&acc)[MT][NT][2]) {
+  const int lane = threadIdx.x & 31;
+  const double* ap = As + (rowBase + (lane >> 2)) * lda + (lane & 3);
+  const double* bp = Bs + (colBase + (lane >> 2)) * ldb + (lane & 3);
+  for (int k = 0; k < K4; k += 4) {
+    double a[MT], b[NT];
+#pragma unroll
+    for (int m = 0; m < MT; m++) a[m] = ap[m * 8 * lda + k];
+#pragma unroll
+    for (int n = 0; n < NT; n++) b[n] = bp[n * 8 * ldb + k];
+#pragma unroll
+    for (int m = 0; m < MT; m++)
+#pragma unroll
+      for (int n = 0; n < NT; n++) dmma(acc[m][n][0], acc[m][n][1], a[m], b[n]);
+  }
+}
+
+constexpr int kPanelRows = 64;  // panel rows per CTA in the factor kernel
+constexpr int kNB = 8;          // column block of the blocked potrf / trsm
+
+// ---- K10a: diagonal potrf + panel trsm -------------------------------------------------------------
+// grid = (row tiles, lumps of the level), 256 threads.  Every CTA factors the w x w diagonal block
+// redundantly in shared memory (no inter-CTA dependency), CTA x==0 publishes L into diagL, each CTA
+// solves X L^T = B for its 64 panel rows.  Both are blocked by 8 columns: the bulk is
+// [rows x 8] -= [rows x k] [8 x k]^T on DMMA, the 8x8 triangles are solved per row in registers.
+__global__ void __launch_bounds__(256) lumpFactorKernel(DevSolver d, double* hess, const int32_t* lumps, int* errFlag) {
+  extern __shared__ double sm[];
+  __shared__ int bad;
+  const int L = lumps[blockIdx.y];
+  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const int tile = blockIdx.x;
+  if (tile > 0 && tile * kPanelRows >= r) return;
+  const int ld = ldFor(w);
+  const int wp = (w + 7) & ~7;          // rows padded to the 8-row MMA tiles
+  double* A = sm;                        // wp x ld   (diagonal block -> L)
+  double* X = sm + (size_t)wp * ld;      // 64 x ld   (panel rows)
+  double* panel = hess + d.lumpOff[L];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) bad = 0;
+  for (int i = tid; i < wp * ld; i += 256) { const int a = i / ld, b = i % ld; A[i] = (a < w && b <= a) ? panel[(int64_t)a * w + b] : 0.0; }
+  const int row0 = tile * kPanelRows;
+  const int nrows = max(0, min(kPanelRows, r - row0));
+  const double* below = panel + (int64_t)(w + row0) * w;
+  for (int i = tid; i < kPanelRows * ld; i += 256) { const int a = i / ld, b = i % ld; X[i] = (a < nrows && b < w) ? below[(int64_t)a * w + b] : 0.0; }
+  __syncthreads();
+  // ---- blocked left-looking Cholesky of A (lower), 8 columns at a time
+  for (int j0 = 0; j0 < w; j0 += kNB) {
+    const int nb = min(kNB, w - j0);
+    // (1) A[j0:, j0:j0+8] -= A[j0:, :j0] A[j0:j0+8, :j0]^T   (DMMA, one 8-row tile per warp iteration)
+    if (j0 > 0) {
+      for (int rt = (j0 >> 3) + warp; rt * 8 < w; rt += 8) {
+        double acc[1][1][2] = {{{0.0, 0.0}}};
+        dmmaABt<1, 1>(A, ld, A, ld, j0, rt * 8, j0, acc);
+        const int rr = rt * 8 + (lane >> 2), cc = j0 + 2 * (lane & 3);
+        A[rr * ld + cc] -= acc[0][0][0];
+        A[rr * ld + cc + 1] -= acc[0][0][1];
+      }
+    }
+    __syncthreads();
+    // (2) 8x8 diagonal block: unblocked Cholesky by warp 0 (lane i owns row j0+i)
+    if (warp == 0) {
+      for (int j = 0; j < nb; j++) {
+        const double djj = A[(j0 + j) * ld + j0 + j];
+        if (!(djj > 0.0)) { if (lane == 0) bad = 1; break; }
+        const double ljj = sqrt(djj);
+        __syncwarp();
+        if (lane == j) A[(j0 + j) * ld + j0 + j] = ljj;
+        else if (lane > j && lane < nb) A[(j0 + lane) * ld + j0 + j] /= ljj;
+        __syncwarp();
+        if (lane > j && lane < nb) {
+          const double lij = A[(j0 + lane) * ld + j0 + j];
+          for (int k = j + 1; k <= lane; k++) A[(j0 + lane) * ld + j0 + k] -= lij * A[(j0 + k) * ld + j0 + j];
+        }
+        __syncwarp();
+      }
+      // zero the strict upper part of the diagonal block (it received the symmetric DMMA update)
+      if (lane < nb) for (int k = lane + 1; k < kNB; k++) A[(j0 + lane) * ld + j0 + k] = 0.0;
+    }
+    __syncthreads();
+    if (bad) { if (tid == 0) atomicExch(errFlag, 2); return; }
+    // (3) rows below the diagonal block: A[i, j0:j0+8] <- A[i, j0:j0+8] L_jj^-T, one thread per row
+    for (int i = j0 + nb + tid; i < w; i += 256) {
+      double x[kNB];
+#pragma unroll
+      for (int c = 0; c < kNB; c++) x[c] = A[i * ld + j0 + c];
+#pragma unroll
+      for (int c = 0; c < kNB; c++) {
+        if (c < nb) {
+          double s = x[c];
+#pragma unroll
+          for (int k = 0; k < c; k++) s = fma(-x[k], A[(j0 + c) * ld + j0 + k], s);
+          x[c] = s / A[(j0 + c) * ld + j0 + c];
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < kNB; c++) if (c < nb) A[i * ld + j0 + c] = x[c];
+    }
+    __syncthreads();
+  }
+  if (tile == 0) {
+    double* out = d.diagL + d.diagLOff[L];
+    for (int i = tid; i < w * w; i += 256) { const int a = i / w, b = i % w; out[i] = b <= a ? A[a * ld + b] : 0.0; }
+  }
+  if (nrows == 0) return;
+  // ---- panel trsm X L^T = B, blocked the same way (8 warps = 8 row tiles of the 64 rows)
+  for (int j0 = 0; j0 < w; j0 += kNB) {
+    const int nb = min(kNB, w - j0);
+    if (j0 > 0) {
+      double acc[1][1][2] = {{{0.0, 0.0}}};
+      dmmaABt<1, 1>(X, ld, A, ld, j0, warp * 8, j0, acc);
+      const int rr = warp * 8 + (lane >> 2), cc = j0 + 2 * (lane & 3);
+      X[rr * ld + cc] -= acc[0][0][0];
+      X[rr * ld + cc + 1] -= acc[0][0][1];
+    }
+    __syncthreads();
+    if (tid < kPanelRows) {
+      double x[kNB];
+#pragma unroll
+      for (int c = 0; c < kNB; c++) x[c] = X[tid * ld + j0 + c];
+#pragma unroll
+      for (int c = 0; c < kNB; c++) {
+        if (c < nb) {
+          double s = x[c];
+#pragma unroll
+          for (int k = 0; k < c; k++) s = fma(-x[k], A[(j0 + c) * ld + j0 + k], s);
+          x[c] = s / A[(j0 + c) * ld + j0 + c];
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < kNB; c++) if (c < nb) X[tid * ld + j0 + c] = x[c];
+    }
+    __syncthreads();
+  }
+  double* belowW = panel + (int64_t)(w + row0) * w;
+  for (int i = tid; i < nrows * w; i += 256) belowW[i] = X[(i / w) * ld + (i % w)];
+}
+
+// ---- K10b: supernode update  C = B B^T  (B = factored panel rows), scattered into the ancestors ----
+// One CTA per 64x64 tile pair of the lump's below-diagonal rows; 8 warps, each a 16x32 sub-tile
+// (2x4 DMMA tiles).  The scatter uses the per-lump relative-index tables built by the symbolic phase.
+constexpr int kUpdTile = 64;
+__global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hess, const LevelTask* tasks, int useAtomics) {
+  extern __shared__ double sm[];
+  const LevelTask t = tasks[blockIdx.x];
+  const int L = t.lump;
+  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const int ld = ldFor(w);
+  double* As = sm;
+  double* Bs = (t.ti == t.tj) ? sm : sm + (size_t)kUpdTile * ld;
+  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
+  const int i0 = t.ti * kUpdTile, j0 = t.tj * kUpdTile;
+  const int ni = min(kUpdTile, r - i0), nj = min(kUpdTile, r - j0);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < kUpdTile * ld; i += 256) {
+    const int a = i / ld, b = i % ld;
+    As[i] = (a < ni && b < w) ? below[(int64_t)(i0 + a) * w + b] : 0.0;
+    if (t.ti != t.tj) Bs[i] = (a < nj && b < w) ? below[(int64_t)(j0 + a) * w + b] : 0.0;
+  }
+  __syncthreads();
+  const int rowBase = (warp >> 1) * 16, colBase = (warp & 1) * 32;
+  double acc[2][4][2];
+#pragma unroll
+  for (int m = 0; m < 2; m++)
+#pragma unroll
+    for (int n = 0; n < 4; n++) acc[m][n][0] = acc[m][n][1] = 0.0;
+  dmmaABt<2, 4>(As, ld, Bs, ld, (w + 3) & ~3, rowBase, colBase, acc);
+  const int64_t q0 = d.updPtr[L];
+  const int32_t* rel = d.rel + d.relPtr[L];
+#pragma unroll
+  for (int n = 0; n < 4; n++)
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+      const int qj = j0 + colBase + n * 8 + 2 * (lane & 3) + e;
+      if (qj >= r) continue;
+      const int64_t colOff = d.updColOff[q0 + qj];
+      const int stride = d.updStride[q0 + qj];
+      const int32_t* relT = rel + (int64_t)d.updTgt[q0 + qj] * r;
+#pragma unroll
+      for (int m = 0; m < 2; m++) {
+        const int qi = i0 + rowBase + m * 8 + (lane >> 2);
+        if (qi >= r || qi < qj) continue;
+        double* p = hess + colOff + (int64_t)relT[qi] * stride;
+        if (useAtomics) red_add(p, -acc[m][n][e]); else *p -= acc[m][n][e];
+      }
+    }
+}
+
+// ---- K11 (supernode part) ---------------------------------------------------------------------------
+// warp-level triangular solves with L (w x w, lower, row-major with leading dimension ld) in shared
+// memory and x in shared memory; called by warp 0 only
+VB_DEV void warpSolveL(const double* Ls, int ld, double* x, int w) {  // L y = x
+  const int lane = threadIdx.x & 31;
+  for (int c = 0; c < w; c++) {
+    const double xc = x[c] / Ls[c * ld + c];
+    __syncwarp();
+    if (lane == 0) x[c] = xc;
+    for (int k = c + 1 + lane; k < w; k += 32) x[k] = fma(-Ls[k * ld + c], xc, x[k]);
+    __syncwarp();
+  }
+}
+VB_DEV void warpSolveLt(const double* Ls, int ld, double* x, int w) { // L^T y = x
+  const int lane = threadIdx.x & 31;
+  for (int c = w - 1; c >= 0; c--) {
+    const double xc = x[c] / Ls[c * ld + c];
+    __syncwarp();
+    if (lane == 0) x[c] = xc;
+    for (int k = lane; k < c; k += 32) x[k] = fma(-Ls[c * ld + k], xc, x[k]);
+    __syncwarp();
+  }
+}
+
+// forward over the lumps of one level: x_L = L^-1 b_L ; b_below -= P x_L.  One CTA per lump.
+__global__ void __launch_bounds__(512) solveLumpFwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps, int useAtomics) {
+  extern __shared__ double sm[];
+  const int L = lumps[blockIdx.x];
+  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const int ld = w | 1;
+  double* Ls = sm;
+  double* x = sm + (size_t)w * ld;
+  double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
+  const double* Ld = d.diagL + d.diagLOff[L];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < w * w; i += 512) Ls[(i / w) * ld + (i % w)] = Ld[i];
+  for (int i = tid; i < w; i += 512) x[i] = vL[i];
+  __syncthreads();
+  if (tid < 32) warpSolveL(Ls, ld, x, w);
+  __syncthreads();
+  for (int i = tid; i < w; i += 512) vL[i] = x[i];
+  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
+  const int64_t q0 = d.updPtr[L];
+  // one warp per panel row: coalesced row read, shuffle reduction
+  const int warp = tid >> 5, lane = tid & 31;
+  for (int row = warp; row < r; row += 16) {
+    const double* P = below + (int64_t)row * w;
+    double s = 0;
+    for (int c = lane; c < w; c += 32) s = fma(P[c], x[c], s);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+      double* out = vec + d.camVec0 + d.updGlobal[q0 + row];
+      if (useAtomics) red_add(out, -s); else *out -= s;
+    }
+  }
+}
+// backward: x_L = L^-T (b_L - P^T x_below)
+__global__ void __launch_bounds__(512) solveLumpBwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps) {
+  extern __shared__ double sm[];
+  const int L = lumps[blockIdx.x];
+  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const int ld = w | 1;
+  double* Ls = sm;
+  double* x = sm + (size_t)w * ld;   // w
+  double* part = x + w;              // 4 x w partial sums
+  double* xb = part + 4 * w;         // r
+  double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
+  const double* Ld = d.diagL + d.diagLOff[L];
+  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
+  const int64_t q0 = d.updPtr[L];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < w * w; i += 512) Ls[(i / w) * ld + (i % w)] = Ld[i];
+  for (int row = tid; row < r; row += 512) xb[row] = vec[d.camVec0 + d.updGlobal[q0 + row]];
+  __syncthreads();
+  // 4 row slices x 128 column lanes: coalesced along the columns of the row-major panel
+  const int slice = tid >> 7, cl = tid & 127;
+  for (int c = cl; c < w; c += 128) {
+    double s = 0;
+    for (int row = slice; row < r; row += 4) s = fma(below[(int64_t)row * w + c], xb[row], s);
+    part[slice * w + c] = s;
+  }
+  __syncthreads();
+  for (int c = tid; c < w; c += 512) x[c] = vL[c] - (part[c] + part[w + c] + part[2 * w + c] + part[3 * w + c]);
+  __syncthreads();
+  if (tid < 32) warpSolveLt(Ls, ld, x, w);
+  __syncthreads();
+  for (int i = tid; i < w; i += 512) vL[i] = x[i];
+}
+
+// ---- launchers ----------------------------------------------------------------------------------------
+static void ensureSmem(const void* fn, size_t bytes) {
+  if (bytes > 48 * 1024) VB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+}
+void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s) {
+  const size_t smem = (size_t)(((maxWidth + 7) & ~7) + kPanelRows) * ldFor(maxWidth) * sizeof(double);
+  ensureSmem((const void*)lumpFactorKernel, smem);
+  const int tiles = std::max(1, (maxRows + kPanelRows - 1) / kPanelRows);
+  lumpFactorKernel<<<dim3(tiles, nLumps), 256, smem, s>>>(d, hess, lumps, errFlag);
+  VB_CUDA(cudaGetLastError());
+}
+void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s) {
+  if (nTasks == 0) return;
+  const size_t smem = (size_t)2 * kUpdTile * ldFor(maxWidth) * sizeof(double);
+  ensureSmem((const void*)lumpUpdateKernel, smem);
+  lumpUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks, useAtomics);
+  VB_CUDA(cudaGetLastError());
+}
+void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int useAtomics, cudaStream_t s) {
+  const size_t smem = ((size_t)maxWidth * (maxWidth | 1) + maxWidth) * sizeof(double);
+  ensureSmem((const void*)solveLumpFwdKernel, smem);
+  solveLumpFwdKernel<<<nLumps, 512, smem, s>>>(d, hess, vec, lumps, useAtomics);
+  VB_CUDA(cudaGetLastError());
+}
+// maxWidthPlusBelow = widest lump of the level + its longest below-row list
+void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidthPlusBelow, cudaStream_t s) {
+  // the width is not passed separately: bound w by 128 (the supernode cap) for the L tile
+  const int wMax = std::min(maxWidthPlusBelow, 128);
+  const size_t smem = ((size_t)wMax * (wMax | 1) + 5 * (size_t)wMax + maxWidthPlusBelow) * sizeof(double);
+  ensureSmem((const void*)solveLumpBwdKernel, smem);
+  solveLumpBwdKernel<<<nLumps, 512, smem, s>>>(d, hess, vec, lumps);
+  VB_CUDA(cudaGetLastError());
+}
+
+} // namespace vb

@@ -71,113 +71,6 @@ __global__ void __launch_bounds__(256) schurKernel(DevSolver d, double* hess, in
   }
 }
 
-// ---- K10a: diagonal potrf (in shared memory) + panel trsm ------------------------------------------
-// grid = (row tiles, lumps of the level); every CTA factors the diagonal block redundantly (no
-// inter-CTA dependency), CTA x==0 publishes L into diagL, each CTA solves its 64 panel rows.
-constexpr int kTrsmRows = 64;
-__global__ void __launch_bounds__(128) lumpFactorKernel(DevSolver d, double* hess, const int32_t* lumps, int* errFlag) {
-  extern __shared__ double sm[];
-  const int L = lumps[blockIdx.y];
-  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
-  const int tile = blockIdx.x;
-  if (tile > 0 && tile * kTrsmRows >= r) return;
-  const int ld = w + 1;
-  double* A = sm;                 // w x ld
-  double* X = sm + (size_t)w * ld; // kTrsmRows x ld
-  double* panel = hess + d.lumpOff[L];
-  const int tid = threadIdx.x, nt = blockDim.x;
-  for (int i = tid; i < w * w; i += nt) A[(i / w) * ld + (i % w)] = panel[i];
-  const int row0 = tile * kTrsmRows;
-  const int nrows = min(kTrsmRows, r - row0);
-  const double* below = panel + (int64_t)(w + row0) * w;
-  for (int i = tid; i < nrows * w; i += nt) X[(i / w) * ld + (i % w)] = below[i];
-  __syncthreads();
-  for (int j = 0; j < w; j++) {
-    const double djj = A[j * ld + j];
-    if (!(djj > 0.0)) { if (tid == 0) atomicExch(errFlag, 2); return; } // uniform: every thread reads the same value
-    const double ljj = sqrt(djj), inv = 1.0 / ljj;
-    __syncthreads();
-    for (int i = j + tid; i < w; i += nt) A[i * ld + j] = (i == j) ? ljj : A[i * ld + j] * inv;
-    __syncthreads();
-    // trailing update of the lower triangle: row i, columns j+1..i
-    for (int i = j + 1 + tid; i < w; i += nt) {
-      const double lij = A[i * ld + j];
-      for (int k = j + 1; k <= i; k++) A[i * ld + k] -= lij * A[k * ld + j];
-    }
-    __syncthreads();
-  }
-  if (tile == 0) {
-    double* out = d.diagL + d.diagLOff[L];
-    for (int i = tid; i < w * w; i += nt) { const int a = i / w, b = i % w; out[i] = b <= a ? A[a * ld + b] : 0.0; }
-  }
-  if (tid < nrows) { // x L^T = b, one thread per panel row
-    double* x = X + tid * ld;
-    for (int c = 0; c < w; c++) {
-      double s = x[c];
-      const double* Lc = A + c * ld;
-      for (int k = 0; k < c; k++) s = fma(-x[k], Lc[k], s);
-      x[c] = s / Lc[c];
-    }
-  }
-  __syncthreads();
-  double* belowW = panel + (int64_t)(w + row0) * w;
-  for (int i = tid; i < nrows * w; i += nt) belowW[i] = X[(i / w) * ld + (i % w)];
-}
-
-// ---- K10b: supernode update C = B B^T scattered into the ancestors (v0: SIMT 64x64 tiles) ----------
-constexpr int kUpdTile = 64;
-__global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hess, const LevelTask* tasks, int useAtomics) {
-  extern __shared__ double sm[];
-  const LevelTask t = tasks[blockIdx.x];
-  const int L = t.lump;
-  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
-  const int ld = w + 1;
-  double* As = sm;                            // rows of tile ti
-  double* Bs = sm + (size_t)kUpdTile * ld;    // rows of tile tj
-  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
-  const int i0 = t.ti * kUpdTile, j0 = t.tj * kUpdTile;
-  const int ni = min(kUpdTile, r - i0), nj = min(kUpdTile, r - j0);
-  const int tid = threadIdx.x;
-  for (int i = tid; i < kUpdTile * w; i += 256) {
-    const int a = i / w, b = i % w;
-    As[a * ld + b] = a < ni ? below[(int64_t)(i0 + a) * w + b] : 0.0;
-    Bs[a * ld + b] = a < nj ? below[(int64_t)(j0 + a) * w + b] : 0.0;
-  }
-  __syncthreads();
-  const int ty = tid >> 4, tx = tid & 15; // 16x16 threads, 4x4 micro-tiles
-  double acc[4][4];
-#pragma unroll
-  for (int a = 0; a < 4; a++)
-#pragma unroll
-    for (int b = 0; b < 4; b++) acc[a][b] = 0.0;
-  for (int k = 0; k < w; k++) {
-    double av[4], bv[4];
-#pragma unroll
-    for (int a = 0; a < 4; a++) { av[a] = As[(ty + 16 * a) * ld + k]; bv[a] = Bs[(tx + 16 * a) * ld + k]; }
-#pragma unroll
-    for (int a = 0; a < 4; a++)
-#pragma unroll
-      for (int b = 0; b < 4; b++) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
-  }
-  const int64_t q0 = d.updPtr[L];
-  const int32_t* rel = d.rel + d.relPtr[L];
-#pragma unroll
-  for (int b = 0; b < 4; b++) {
-    const int qj = j0 + tx + 16 * b;
-    if (qj >= r) continue;
-    const int64_t colOff = d.updColOff[q0 + qj];
-    const int stride = d.updStride[q0 + qj];
-    const int32_t* relT = rel + (int64_t)d.updTgt[q0 + qj] * r;
-#pragma unroll
-    for (int a = 0; a < 4; a++) {
-      const int qi = i0 + ty + 16 * a;
-      if (qi >= r || qi < qj) continue;
-      double* p = hess + colOff + (int64_t)relT[qi] * stride;
-      if (useAtomics) red_add(p, -acc[a][b]); else *p -= acc[a][b];
-    }
-  }
-}
-
 // ---- K11: solves -------------------------------------------------------------------------------------
 // forward over landmarks: y_p = L_pp^-1 g_p ; g_cam -= W'_p y_p
 __global__ void __launch_bounds__(256) solveLmFwdKernel(DevSolver d, const double* hess, double* vec) {
@@ -230,65 +123,6 @@ __global__ void __launch_bounds__(256) solveLmBwdKernel(DevSolver d, const doubl
     g[0] = x0; g[1] = x1; g[2] = x2;
   }
 }
-// forward over the lumps of one level: x_L = L^-1 b_L ; b_below -= P x_L.  One CTA per lump.
-__global__ void __launch_bounds__(128) solveLumpFwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps, int useAtomics) {
-  extern __shared__ double sm[];
-  const int L = lumps[blockIdx.x];
-  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
-  double* x = sm;
-  double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
-  const double* Ld = d.diagL + d.diagLOff[L];
-  const int tid = threadIdx.x;
-  for (int i = tid; i < w; i += 128) x[i] = vL[i];
-  __syncthreads();
-  for (int c = 0; c < w; c++) {
-    if (tid == 0) x[c] /= Ld[c * w + c];
-    __syncthreads();
-    const double xc = x[c];
-    for (int k = c + 1 + tid; k < w; k += 128) x[k] = fma(-Ld[k * w + c], xc, x[k]);
-    __syncthreads();
-  }
-  for (int i = tid; i < w; i += 128) vL[i] = x[i];
-  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
-  const int64_t q0 = d.updPtr[L];
-  for (int row = tid; row < r; row += 128) {
-    const double* P = below + (int64_t)row * w;
-    double s = 0;
-    for (int c = 0; c < w; c++) s = fma(P[c], x[c], s);
-    double* out = vec + d.camVec0 + d.updGlobal[q0 + row];
-    if (useAtomics) red_add(out, -s); else *out -= s;
-  }
-}
-// backward: x_L = L^-T (b_L - P^T x_below)
-__global__ void __launch_bounds__(128) solveLumpBwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps) {
-  extern __shared__ double sm[];
-  const int L = lumps[blockIdx.x];
-  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
-  double* x = sm;       // w
-  double* xb = sm + w;  // r
-  double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
-  const double* Ld = d.diagL + d.diagLOff[L];
-  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
-  const int64_t q0 = d.updPtr[L];
-  const int tid = threadIdx.x;
-  for (int row = tid; row < r; row += 128) xb[row] = vec[d.camVec0 + d.updGlobal[q0 + row]];
-  __syncthreads();
-  for (int c = tid; c < w; c += 128) {
-    double s = vL[c];
-    for (int row = 0; row < r; row++) s = fma(-below[(int64_t)row * w + c], xb[row], s);
-    x[c] = s;
-  }
-  __syncthreads();
-  for (int c = w - 1; c >= 0; c--) {
-    if (tid == 0) x[c] /= Ld[c * w + c];
-    __syncthreads();
-    const double xc = x[c];
-    for (int k = tid; k < c; k += 128) x[k] = fma(-Ld[c * w + k], xc, x[k]);
-    __syncthreads();
-  }
-  for (int i = tid; i < w; i += 128) vL[i] = x[i];
-}
-
 // ---- FP64 tensor-pipe probe: mma.sync.m8n8k4.f64 issue-bound loop, returns TFLOP/s -------------------
 __global__ void dmmaProbeKernel(double* out, int iters) {
   double c0[2] = {0, 0}, c1[2] = {0, 0}, c2[2] = {0, 0}, c3[2] = {0, 0};
@@ -325,23 +159,6 @@ void launchSchur(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s)
   schurKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, errFlag);
   VB_CUDA(cudaGetLastError());
 }
-static void ensureSmem(const void* fn, size_t bytes) {
-  if (bytes > 48 * 1024) VB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-}
-void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s) {
-  const size_t smem = (size_t)(maxWidth + kTrsmRows) * (maxWidth + 1) * sizeof(double);
-  ensureSmem((const void*)lumpFactorKernel, smem);
-  const int tiles = std::max(1, (maxRows + kTrsmRows - 1) / kTrsmRows);
-  lumpFactorKernel<<<dim3(tiles, nLumps), 128, smem, s>>>(d, hess, lumps, errFlag);
-  VB_CUDA(cudaGetLastError());
-}
-void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s) {
-  if (nTasks == 0) return;
-  const size_t smem = (size_t)2 * kUpdTile * (maxWidth + 1) * sizeof(double);
-  ensureSmem((const void*)lumpUpdateKernel, smem);
-  lumpUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks, useAtomics);
-  VB_CUDA(cudaGetLastError());
-}
 void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s) {
   if (d.nP == 0) return;
   solveLmFwdKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, vec);
@@ -352,16 +169,4 @@ void launchSolveLandmarksBwd(const DevSolver& d, const double* hess, double* vec
   solveLmBwdKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, vec);
   VB_CUDA(cudaGetLastError());
 }
-void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int useAtomics, cudaStream_t s) {
-  solveLumpFwdKernel<<<nLumps, 128, maxWidth * sizeof(double), s>>>(d, hess, vec, lumps, useAtomics);
-  VB_CUDA(cudaGetLastError());
-}
-void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, cudaStream_t s) {
-  // dynamic smem = width + below rows of the widest lump of the problem (passed as maxWidth = w + r bound)
-  const size_t smem = (size_t)maxWidth * sizeof(double);
-  ensureSmem((const void*)solveLumpBwdKernel, smem);
-  solveLumpBwdKernel<<<nLumps, 128, smem, s>>>(d, hess, vec, lumps);
-  VB_CUDA(cudaGetLastError());
-}
-
 } // namespace vb

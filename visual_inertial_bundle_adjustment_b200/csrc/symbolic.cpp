@@ -152,50 +152,102 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
     }
   }
 
-  // ---- ordering of the camera side: reverse Cuthill-McKee on the Schur-filled graph, walked
-  // through the landmark adjacency without materialising the fill ---------------------------
+  // ---- ordering of the camera side -----------------------------------------------------------
+  // Nested dissection by BFS level structures on the Schur-filled graph (walked through the
+  // landmark adjacency, never materialised): the visual-inertial graph is a chain in time, so a
+  // BFS level is a time slab and makes a vertex separator; the two halves become independent
+  // subtrees of the elimination tree (parallel on one GPU, the shard boundary across GPUs).
+  // Leaves and separators are ordered by (reverse) Cuthill-McKee.  opt.ndLeafBlocks <= 0 gives
+  // plain RCM (a single chain).
   std::vector<int32_t> orderC; orderC.reserve(nC);
   {
-    std::vector<char> vis(nC, 0), lmDone(nP, 0);
     std::vector<int32_t> deg(nC);
     for (int64_t c = 0; c < nC; c++) deg[c] = (int32_t)((ccPtr[c + 1] - ccPtr[c]) + (clPtr[c + 1] - clPtr[c]));
-    auto bfs = [&](int32_t root, std::vector<int32_t>& out, std::vector<char>& visited, std::vector<char>& lmd) {
-      size_t head = out.size();
-      out.push_back(root); visited[root] = 1;
+    std::vector<int32_t> inSet(nC, -1), seen(nC, -1), lmSeen(nP, -1);
+    int32_t bfsStamp = 0, setStamp = 0;
+    // BFS inside the node set stamped `set`; appends discovery order to out, level starts to lv
+    auto bfs = [&](int32_t root, int32_t set, std::vector<int32_t>& out, std::vector<int32_t>* lv) {
+      const int32_t stamp = ++bfsStamp;
+      size_t head = out.size(), levelEnd;
+      out.push_back(root); seen[root] = stamp;
       std::vector<int32_t> nb;
+      if (lv) lv->push_back((int32_t)head);
+      levelEnd = out.size();
       while (head < out.size()) {
+        if (head == levelEnd) { if (lv) lv->push_back((int32_t)head); levelEnd = out.size(); }
         const int32_t u = out[head++];
         nb.clear();
-        for (int64_t k = ccPtr[u]; k < ccPtr[u + 1]; k++) { const int32_t w = ccAdj[k]; if (!visited[w]) { visited[w] = 1; nb.push_back(w); } }
+        for (int64_t k = ccPtr[u]; k < ccPtr[u + 1]; k++) {
+          const int32_t w = ccAdj[k];
+          if (inSet[w] == set && seen[w] != stamp) { seen[w] = stamp; nb.push_back(w); }
+        }
         for (int64_t k = clPtr[u]; k < clPtr[u + 1]; k++) {
           const int32_t p = clLm[k];
-          if (lmd[p]) continue;
-          lmd[p] = 1;
-          for (int64_t q = lmPtr[p]; q < lmPtr[p + 1]; q++) { const int32_t w = lmCam[q]; if (!visited[w]) { visited[w] = 1; nb.push_back(w); } }
+          if (lmSeen[p] == stamp) continue;
+          lmSeen[p] = stamp;
+          for (int64_t q = lmPtr[p]; q < lmPtr[p + 1]; q++) {
+            const int32_t w = lmCam[q];
+            if (inSet[w] == set && seen[w] != stamp) { seen[w] = stamp; nb.push_back(w); }
+          }
         }
         std::sort(nb.begin(), nb.end(), [&](int32_t a, int32_t b) { return deg[a] != deg[b] ? deg[a] < deg[b] : a < b; });
         out.insert(out.end(), nb.begin(), nb.end());
       }
+      if (lv) lv->push_back((int32_t)out.size());
     };
-    std::vector<int32_t> byDeg(nC);
-    std::iota(byDeg.begin(), byDeg.end(), 0);
-    std::stable_sort(byDeg.begin(), byDeg.end(), [&](int32_t a, int32_t b) { return deg[a] < deg[b]; });
-    int nComponents = 0;
-    for (int32_t seed : byDeg) {
-      if (vis[seed]) continue;
-      // pseudo-peripheral root: two BFS sweeps on scratch marks restricted to this component
-      int32_t root = seed;
-      for (int sweep = 0; sweep < 2 && nComponents < 4; sweep++) {
-        std::vector<char> v2(vis), l2(lmDone);
-        std::vector<int32_t> tmp;
-        bfs(root, tmp, v2, l2);
-        root = tmp.back();
-        if (tmp.size() > 200000) break; // one sweep is enough on very large components
-      }
-      bfs(root, orderC, vis, lmDone);
-      nComponents++;
+    auto weight = [&](int32_t c) { return (int64_t)S.bsize[nP + c]; };
+    struct Job { std::vector<int32_t> nodes; bool dissect; };
+    // explicit stack; emitted segments are appended to orderC in elimination order
+    std::vector<Job> stack;
+    {
+      Job all; all.nodes.resize(nC); std::iota(all.nodes.begin(), all.nodes.end(), 0); all.dissect = true;
+      stack.push_back(std::move(all));
     }
-    std::reverse(orderC.begin(), orderC.end());
+    while (!stack.empty()) {
+      Job job = std::move(stack.back());
+      stack.pop_back();
+      if (job.nodes.empty()) continue;
+      const int32_t set = ++setStamp;
+      for (int32_t c : job.nodes) inSet[c] = set;
+      // min-degree start, then one sweep to a pseudo-peripheral root
+      int32_t start = job.nodes[0];
+      for (int32_t c : job.nodes) if (deg[c] < deg[start] || (deg[c] == deg[start] && c < start)) start = c;
+      std::vector<int32_t> comp, lv;
+      bfs(start, set, comp, nullptr);
+      const int32_t root = comp.back();
+      comp.clear();
+      bfs(root, set, comp, &lv);
+      if (comp.size() < job.nodes.size()) { // disconnected: the rest is an independent job (no separator)
+        Job rest; rest.dissect = job.dissect;
+        for (int32_t c : job.nodes) if (seen[c] != bfsStamp) rest.nodes.push_back(c);
+        stack.push_back(std::move(rest));
+      }
+      const int nlev = (int)lv.size() - 1;
+      if (!job.dissect || opt.ndLeafBlocks <= 0 || (int64_t)comp.size() <= opt.ndLeafBlocks || nlev < 5) {
+        orderC.insert(orderC.end(), comp.rbegin(), comp.rend()); // reverse Cuthill-McKee
+        continue;
+      }
+      // separator = the lightest level among those keeping both sides within 35..65 % of the weight
+      std::vector<int64_t> cum(nlev + 1, 0);
+      for (int l = 0; l < nlev; l++) { int64_t w = 0; for (int32_t i = lv[l]; i < lv[l + 1]; i++) w += weight(comp[i]); cum[l + 1] = cum[l] + w; }
+      int best = -1;
+      for (int l = 1; l + 1 < nlev; l++) {
+        const double left = (double)cum[l] / cum[nlev], right = (double)(cum[nlev] - cum[l + 1]) / cum[nlev];
+        if (left < 0.3 || right < 0.3) continue;
+        if (best < 0 || cum[l + 1] - cum[l] < cum[best + 1] - cum[best]) best = l;
+      }
+      if (best < 0) best = nlev / 2;
+      Job A, B, Sep;
+      A.dissect = B.dissect = true; Sep.dissect = false;
+      A.nodes.assign(comp.begin(), comp.begin() + lv[best]);
+      Sep.nodes.assign(comp.begin() + lv[best], comp.begin() + lv[best + 1]);
+      B.nodes.assign(comp.begin() + lv[best + 1], comp.end());
+      // LIFO: A is processed (and emitted) first, then B, then the separator
+      stack.push_back(std::move(Sep));
+      stack.push_back(std::move(B));
+      stack.push_back(std::move(A));
+    }
+    if ((int64_t)orderC.size() != nC) throw std::runtime_error("ordering lost camera blocks");
   }
   std::vector<int32_t> cpos(nC); // camera registration c -> camera position
   for (int64_t i = 0; i < nC; i++) cpos[orderC[i]] = (int32_t)i;

@@ -72,6 +72,7 @@ struct HostGraph { // owning copy of a vb_graph_desc
 struct SymbolicOptions {
   int maxLumpWidth = 96;     // scalar columns per supernode
   double relaxFill = 0.35;   // admissible fraction of explicit zeros when merging columns
+  int ndLeafBlocks = 300;    // nested-dissection leaf size in camera blocks (<= 0: plain RCM chain)
 };
 
 // throws std::runtime_error on malformed graphs

@@ -125,6 +125,31 @@ static void buildDeviceProblem(vb_problem& P) {
     }
     if (bad) throw std::runtime_error("scatter map: block missing from the structure");
     d.gOff = P.upload(gOff); d.hOff = P.upload(hOff); d.hStride = P.upload(hStride);
+    d.order = nullptr; d.chunkStart = nullptr; d.nChunks = 0;
+    if (hs.type == VB_F_VISUAL && hs.count > 0) {
+      if (hs.count >= (1ll << 31)) throw std::runtime_error("visual store too large for 32-bit factor indices");
+      std::vector<int32_t> order(hs.count);
+      for (int64_t k = 0; k < hs.count; k++) order[k] = (int32_t)k;
+      auto key = [&](int32_t k, int a) { return hs.vars[(int64_t)k * 4 + a]; };
+      std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
+        if (key(x, 1) != key(y, 1)) return key(x, 1) < key(y, 1);
+        if (key(x, 2) != key(y, 2)) return key(x, 2) < key(y, 2);
+        return key(x, 3) < key(y, 3);
+      });
+      std::vector<int32_t> chunkStart;
+      int64_t groupStart = 0;
+      for (int64_t i = 0; i <= hs.count; i++) {
+        const bool boundary = i == hs.count || (i > 0 && (key(order[i], 1) != key(order[i - 1], 1) ||
+                              key(order[i], 2) != key(order[i - 1], 2) || key(order[i], 3) != key(order[i - 1], 3)));
+        if (boundary || i - groupStart == 128) {
+          if (i > groupStart) chunkStart.push_back((int32_t)groupStart);
+          groupStart = i;
+        }
+      }
+      chunkStart.push_back((int32_t)hs.count);
+      d.nChunks = (int32_t)chunkStart.size() - 1;
+      d.order = P.upload(order); d.chunkStart = P.upload(chunkStart);
+    }
     if (hs.type == VB_F_VISUAL) P.visualBytes += 224.0 * hs.count; // SURVEY.md §8d algorithmic bytes/obs
     if (hs.type == VB_F_VISUAL_RS) P.visualBytes += 296.0 * hs.count;
   }

@@ -257,6 +257,12 @@ VB_DEV void loss_jet2(double a, double k, double s, double& val, double& der) {
   else { val = s; der = 1.0; }
 }
 
+// D(8x8) += A(8x4, row) * B(4x8, col).  Lane l holds a = A[l/4][l%4], b = B[l%4][l/4],
+// c = C[l/4][2*(l%4) + {0,1}].
+VB_DEV void dmma(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
 // fp64 reduction without return value (REDG.E.ADD.F64)
 VB_DEV void red_add(double* addr, double v) { atomicAdd(addr, v); }
 

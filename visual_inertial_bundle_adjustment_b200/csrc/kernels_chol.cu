@@ -7,11 +7,6 @@
 
 namespace vb {
 
-// D(8x8) += A(8x4, row) * B(4x8, col).  Lane l holds a = A[l/4][l%4], b = B[l%4][l/4],
-// c = C[l/4][2*(l%4) + {0,1}].
-VB_DEV void dmma(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 // shared-memory leading dimension: >= n rounded up to the 8-wide MMA tiles, == 4 mod 8 so that the
 // 4-row x 4-column fragment loads of a half warp hit 16 distinct 8-byte banks
 __host__ __device__ inline int ldFor(int n) { return ((n + 7) & ~7) + 4; }

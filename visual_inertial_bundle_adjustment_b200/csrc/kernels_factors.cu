@@ -237,6 +237,145 @@ done:
   blockReduceAdd<1>(acc, costAcc);
 }
 
+// ---- visual factors v1 (K1): one CTA per chunk of <= 128 observations sharing rig pose,
+// extrinsics and intrinsics.  Thread t evaluates observation t (residual + Jacobians in registers),
+// scatters the landmark-side blocks (H_pp, g_p, W_r, W_e, W_c: distinct addresses per landmark)
+// with fp64 reductions, and stores its two camera-side Jacobian rows, scaled by sqrt(rho'), plus
+// the scaled residual as a 28th column into shared memory:  M = [ sqrt(rho') J_cam | sqrt(rho') r ].
+// The camera-side Hessian blocks and gradients of the whole chunk are then ONE contraction
+// M^T M (27 x 28, K = 256) on the FP64 tensor pipe, written with one reduction per entry per chunk.
+constexpr int kVisChunk = 128, kVisLd = 36;
+__global__ void __launch_bounds__(128) gradHessVisualChunkKernel(DevStore st, DevVars V, double* grad, double* hess, int updateCache,
+                                                                  int dontRetry, double* costAcc) {
+  extern __shared__ double M[];          // 256 x 36
+  __shared__ double camv[32];            // pose(7) extr(7) intr(15 used of 17)
+  const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int s0 = st.chunkStart[c], n = st.chunkStart[c + 1] - s0;
+  const int f0 = st.order[s0];
+  {
+    const int32_t* v0 = st.vars + (int64_t)f0 * 4;
+    if (tid < 7) camv[tid] = V.data[V.off[v0[1]] + tid];
+    else if (tid < 14) camv[tid] = V.data[V.off[v0[2]] + tid - 7];
+    else if (tid < 29) camv[tid] = V.data[V.off[v0[3]] + tid - 14];
+  }
+  __syncthreads();
+  double acc[1] = {0.0};
+  double* row0 = M + (2 * tid) * kVisLd;
+  double* row1 = row0 + kVisLd;
+  bool live = false;
+  if (tid < n) {
+    const int f = st.order[s0 + tid];
+    if (!(dontRetry && st.cache[f] < 0.0)) {
+      double r[2], JX[6], JT[12], JE[12], JC[30];
+      const bool ok = visual_factor<true>(V.data + V.off[st.vars[(int64_t)f * 4]], camv, camv + 7, camv + 14,
+                                          st.consts + (int64_t)f * 6, r, JX, JT, JE, JC);
+      if (!ok) {
+        if (updateCache || dontRetry) st.cache[f] = -1.0;
+      } else {
+        live = true;
+        double soft, w;
+        loss_jet2(st.loss_a, st.loss_k, r[0] * r[0] + r[1] * r[1], soft, w);
+        acc[0] = 0.5 * soft;
+        if (updateCache) st.cache[f] = acc[0];
+        const double sw = sqrt(w);
+#pragma unroll
+        for (int j = 0; j < 6; j++) { row0[j] = sw * JT[j]; row1[j] = sw * JT[6 + j]; row0[6 + j] = sw * JE[j]; row1[6 + j] = sw * JE[6 + j]; }
+#pragma unroll
+        for (int j = 0; j < 15; j++) { row0[12 + j] = sw * JC[j]; row1[12 + j] = sw * JC[15 + j]; }
+        row0[27] = sw * r[0]; row1[27] = sw * r[1];
+#pragma unroll
+        for (int j = 28; j < kVisLd; j++) { row0[j] = 0.0; row1[j] = 0.0; }
+        // landmark side: weighted J_X
+        const int64_t gp = st.gOff[(int64_t)f * 4];
+        if (gp >= 0) {
+          double X0[3], X1[3];
+#pragma unroll
+          for (int a = 0; a < 3; a++) { X0[a] = w * JX[a]; X1[a] = w * JX[3 + a]; }
+#pragma unroll
+          for (int a = 0; a < 3; a++) red_add(grad + gp + a, r[0] * X0[a] + r[1] * X1[a]);
+          if (hess) {
+            const int64_t* ho = st.hOff + (int64_t)f * 10;
+            double* Hpp = hess + ho[0];
+#pragma unroll
+            for (int a = 0; a < 3; a++)
+#pragma unroll
+              for (int b = 0; b <= a; b++) red_add(Hpp + a * 3 + b, X0[a] * JX[b] + X1[a] * JX[3 + b]);
+            if (ho[1] >= 0) {
+              double* W = hess + ho[1];
+#pragma unroll
+              for (int s_ = 0; s_ < 6; s_++)
+#pragma unroll
+                for (int a = 0; a < 3; a++) red_add(W + s_ * 3 + a, JT[s_] * X0[a] + JT[6 + s_] * X1[a]);
+            }
+            if (ho[3] >= 0) {
+              double* W = hess + ho[3];
+#pragma unroll
+              for (int s_ = 0; s_ < 6; s_++)
+#pragma unroll
+                for (int a = 0; a < 3; a++) red_add(W + s_ * 3 + a, JE[s_] * X0[a] + JE[6 + s_] * X1[a]);
+            }
+            if (ho[6] >= 0) {
+              double* W = hess + ho[6];
+#pragma unroll
+              for (int s_ = 0; s_ < 15; s_++)
+#pragma unroll
+                for (int a = 0; a < 3; a++) red_add(W + s_ * 3 + a, JC[s_] * X0[a] + JC[15 + s_] * X1[a]);
+            }
+          }
+        }
+      }
+    }
+  }
+  if (!live) {
+#pragma unroll
+    for (int j = 0; j < kVisLd; j++) { row0[j] = 0.0; row1[j] = 0.0; }
+  }
+  __syncthreads();
+  // M^T M on DMMA: warp = 8-row tile of the output, 4 column tiles
+  double C[4][2];
+#pragma unroll
+  for (int t = 0; t < 4; t++) C[t][0] = C[t][1] = 0.0;
+  {
+    const double* ap = M + (lane & 3) * kVisLd + warp * 8 + (lane >> 2);
+    const double* bp = M + (lane & 3) * kVisLd + (lane >> 2);
+    for (int k = 0; k < 2 * kVisChunk; k += 4) {
+      const double a = ap[k * kVisLd];
+#pragma unroll
+      for (int t = 0; t < 4; t++) dmma(C[t][0], C[t][1], a, bp[k * kVisLd + 8 * t]);
+    }
+  }
+  // epilogue: entry (i, j) of [H_cam | g_cam]; rows/cols 0-5 pose, 6-11 extrinsics, 12-26 intrinsics
+  {
+    const int i = warp * 8 + (lane >> 2);
+    if (i < 27) {
+      const int bi = i < 6 ? 0 : (i < 12 ? 1 : 2);
+      const int ai = i - (bi == 0 ? 0 : (bi == 1 ? 6 : 12));
+      const int64_t gi = st.gOff[(int64_t)f0 * 4 + 1 + bi];
+      if (gi >= 0) {
+#pragma unroll
+        for (int t = 0; t < 4; t++)
+#pragma unroll
+          for (int e = 0; e < 2; e++) {
+            const int j = 8 * t + 2 * (lane & 3) + e;
+            const double val = C[t][e];
+            if (j == 27) { if (val != 0.0) red_add(grad + gi + ai, val); continue; }
+            if (!hess || j > i || j >= 27) continue;
+            const int bj = j < 6 ? 0 : (j < 12 ? 1 : 2);
+            const int aj = j - (bj == 0 ? 0 : (bj == 1 ? 6 : 12));
+            const int pi = (bi + 1) * (bi + 2) / 2 + (bj + 1);
+            const int64_t ho = st.hOff[(int64_t)f0 * 10 + pi];
+            if (ho < 0) continue;
+            const int sw_ = st.hStride[(int64_t)f0 * 10 + pi];
+            const int stride = sw_ & 0x3fffffff;
+            const bool tr = (sw_ >> 30) & 1;
+            red_add(hess + ho + (tr ? (int64_t)aj * stride + ai : (int64_t)ai * stride + aj), val);
+          }
+      }
+    }
+  }
+  blockReduceAdd<1>(acc, costAcc);
+}
+
 // ---- cost-only kernel: computeSingleCost (Factor.h:390-417) + CostStats ---------------------------
 // acc = {cost, numTotal, numInvalid, numPrevInvalid}
 template <int E>
@@ -377,7 +516,16 @@ void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* 
   if (st.count == 0) return;
 #define SMALL(E, TOT) gradHessSmallKernel<E, TOT><<<gridFor(st.count, 64), 64, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc)
   switch (st.type) {
-    case VB_F_VISUAL: gradHessVisualKernel<<<gridFor(st.count, 128), 128, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc); break;
+    case VB_F_VISUAL:
+      if (st.order) {
+        const size_t smem = (size_t)2 * kVisChunk * kVisLd * sizeof(double);
+        static bool attr = false;
+        if (!attr) { VB_CUDA(cudaFuncSetAttribute(gradHessVisualChunkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+        gradHessVisualChunkKernel<<<st.nChunks, 128, smem, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc);
+      } else {
+        gradHessVisualKernel<<<gridFor(st.count, 128), 128, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc);
+      }
+      break;
     case VB_F_INERTIAL: SMALL(9, 43); break;
     case VB_F_RW_IMUCALIB: SMALL(23, 46); break;
     case VB_F_PRIOR_IMUCALIB: SMALL(23, 23); break;

@@ -30,6 +30,11 @@ struct DevStore {
   const int64_t* gOff;    // [count*nvars] scalar offset in the permuted vectors, -1 for constants
   const int64_t* hOff;    // [count*npairs] pair (i,j<=i) at i*(i+1)/2+j ; -1 if absent
   const int32_t* hStride; // [count*npairs] row stride | (transposed << 30)
+  // visual stores: processing order grouped by (rig pose, extrinsics, intrinsics) and cut into
+  // chunks of <= 128 observations that share all three camera-side variables
+  const int32_t* order;      // [count] factor index
+  const int32_t* chunkStart; // [nChunks+1] into order
+  int32_t nChunks;
 };
 
 // device view of the variables

@@ -29,7 +29,7 @@ struct vb_problem {
   int* errFlag = nullptr;
   int64_t* blockVar = nullptr;
   int64_t* diagOff = nullptr; int32_t* diagStride = nullptr; int32_t* diagSize = nullptr;
-  int32_t* levelLumps = nullptr; LevelTask* levelTasks = nullptr;
+  int32_t* levelLumps = nullptr; LevelTask* levelTasks = nullptr; LevelTask* schurTasks = nullptr; int nSchurTasks = 0;
   std::vector<int64_t> levelLumpOff, levelTaskOff;
   std::vector<int32_t> levelMaxBelow, levelMaxWidth;
   int64_t varDataLen = 0;
@@ -162,17 +162,17 @@ static void buildDeviceProblem(vb_problem& P) {
   d.lumpRowPtr = P.upload(S.lumpRowPtr); d.lumpRowCam = P.upload(S.lumpRowCam); d.lumpRowOff = P.upload(S.lumpRowOff);
   d.camVec0 = S.vecStart[S.nP];
   {
-    std::vector<int64_t> diagLOff(S.nL), updPtr(S.nL + 1, 0), relPtr(S.nL + 1, 0), colOff;
+    // relative-index tables for every scatter source: supernodes (index L) and landmark groups
+    // (index nL + g).  A source is a sorted list of camera positions (its row blocks).
+    std::vector<int64_t> diagLOff(S.nL), updPtr, relPtr, colOff;
     std::vector<int32_t> stride, tgt, glob, rel;
-    int64_t dl = 0;
-    for (int64_t L = 0; L < S.nL; L++) {
-      diagLOff[L] = dl; dl += (int64_t)S.lumpWidth[L] * S.lumpWidth[L];
-      const int r = S.lumpRows[L] - S.lumpWidth[L];
-      updPtr[L] = (int64_t)colOff.size();
-      relPtr[L] = (int64_t)rel.size();
+    auto appendSource = [&](const int32_t* cams, int64_t n, bool strict) {
+      updPtr.push_back((int64_t)colOff.size());
+      relPtr.push_back((int64_t)rel.size());
       std::vector<int32_t> targets;
-      for (int64_t k = S.lumpRowPtr[L]; k < S.lumpRowPtr[L + 1]; k++) {
-        const int32_t c = S.lumpRowCam[k];
+      int32_t r = 0;
+      for (int64_t k = 0; k < n; k++) {
+        const int32_t c = cams[k];
         const int32_t T = S.camLump[c];
         if (targets.empty() || targets.back() != T) targets.push_back(T);
         const int32_t t = (int32_t)targets.size() - 1;
@@ -181,27 +181,109 @@ static void buildDeviceProblem(vb_problem& P) {
           colOff.push_back(S.lumpOff[T] + (S.camStart[c] + s - S.camStart[S.lumpFirst[T]]));
           stride.push_back(S.lumpWidth[T]); tgt.push_back(t); glob.push_back(S.camStart[c] + s);
         }
+        r += dc;
       }
-      rel.resize(rel.size() + targets.size() * (size_t)r, -1);
+      const size_t base = rel.size();
+      rel.resize(base + targets.size() * (size_t)r, -1);
       for (size_t t = 0; t < targets.size(); t++) {
         const int32_t T = targets[t];
         int32_t q = 0;
-        for (int64_t k = S.lumpRowPtr[L]; k < S.lumpRowPtr[L + 1]; k++) {
-          const int32_t c = S.lumpRowCam[k];
+        for (int64_t k = 0; k < n; k++) {
+          const int32_t c = cams[k];
           const int32_t dc = S.camStart[c + 1] - S.camStart[c];
           if (c >= S.lumpFirst[T]) {
             const int32_t row = S.rowInLump(T, c);
-            if (row < 0) throw std::runtime_error("symbolic: ancestor structure does not contain a descendant row");
-            for (int32_t s = 0; s < dc; s++) rel[relPtr[L] + t * (size_t)r + q + s] = row + s;
+            if (row < 0 && strict) throw std::runtime_error("symbolic: ancestor structure does not contain a descendant row");
+            // (group unions: a block pair no member landmark sees together is absent and receives exact zeros)
+            if (row >= 0) for (int32_t s = 0; s < dc; s++) rel[base + t * (size_t)r + q + s] = row + s;
           }
           q += dc;
         }
       }
+      return r;
+    };
+    int64_t dl = 0;
+    for (int64_t L = 0; L < S.nL; L++) {
+      diagLOff[L] = dl; dl += (int64_t)S.lumpWidth[L] * S.lumpWidth[L];
+      appendSource(S.lumpRowCam.data() + S.lumpRowPtr[L], S.lumpRowPtr[L + 1] - S.lumpRowPtr[L], true);
     }
-    updPtr[S.nL] = (int64_t)colOff.size(); relPtr[S.nL] = (int64_t)rel.size();
+    // ---- landmark groups for the Schur update: landmarks sorted by their first camera block are
+    // packed greedily while the union of their row blocks stays <= kGrpMaxRows scalars and the
+    // group holds <= kGrpMax landmarks; each group is one dense [union rows] x [3 G] operand
+    constexpr int kGrpMax = 32;
+    int kGrpMaxRows = 512;
+    if (const char* e = getenv("VB_GRP_MAX_ROWS")) kGrpMaxRows = std::max(64, atoi(e));
+    if (S.lmDataSize >= (1ll << 31)) throw std::runtime_error("landmark section exceeds 32-bit offsets");
+    std::vector<int32_t> lmOrder;
+    for (int64_t p = 0; p < S.nP; p++) if (S.lmRowPtr[p + 1] > S.lmRowPtr[p]) lmOrder.push_back((int32_t)p);
+    std::sort(lmOrder.begin(), lmOrder.end(), [&](int32_t x, int32_t y) {
+      const int32_t fx = S.lmRowCam[S.lmRowPtr[x]], fy = S.lmRowCam[S.lmRowPtr[y]];
+      const int32_t lx = S.lmRowCam[S.lmRowPtr[x + 1] - 1], ly = S.lmRowCam[S.lmRowPtr[y + 1] - 1];
+      return fx != fy ? fx < fy : (lx != ly ? lx < ly : x < y);
+    });
+    std::vector<int64_t> grpLmPtr(1, 0), grpBlkPtr(1, 0);
+    std::vector<int32_t> grpLm, grpBlkOff, grpRowBlk, grpRowSub, grpRows;
+    std::vector<LevelTask> schurTasks;
+    {
+      std::vector<int32_t> uni, merged, members;
+      auto scal = [&](const std::vector<int32_t>& v) { int64_t s = 0; for (int32_t c : v) s += S.camStart[c + 1] - S.camStart[c]; return s; };
+      auto flush = [&]() {
+        if (members.empty()) return;
+        const int32_t g = (int32_t)grpRows.size();
+        const int32_t r = appendSource(uni.data(), (int64_t)uni.size(), false);
+        grpRows.push_back(r);
+        for (int32_t p : members) grpLm.push_back(p);
+        grpLmPtr.push_back((int64_t)grpLm.size());
+        for (size_t b = 0; b < uni.size(); b++) {
+          const int32_t dc = S.camStart[uni[b] + 1] - S.camStart[uni[b]];
+          for (int32_t s = 0; s < dc; s++) { grpRowBlk.push_back((int32_t)b); grpRowSub.push_back(s); }
+          for (int l = 0; l < kGrpMax; l++) {
+            int32_t off = -1;
+            if (l < (int)members.size()) {
+              const int32_t p = members[l];
+              const int32_t* bb = S.lmRowCam.data() + S.lmRowPtr[p];
+              const int32_t* ee = S.lmRowCam.data() + S.lmRowPtr[p + 1];
+              const int32_t* it = std::lower_bound(bb, ee, uni[b]);
+              if (it != ee && *it == uni[b]) off = (int32_t)(S.lmOff[p] + (int64_t)S.lmRowOff[it - S.lmRowCam.data()] * 3);
+            }
+            grpBlkOff.push_back(off);
+          }
+        }
+        grpBlkPtr.push_back(grpBlkPtr.back() + (int64_t)uni.size());
+        const int nt = (r + 63) / 64;
+        for (int ti = 0; ti < nt; ti++) for (int tj = 0; tj <= ti; tj++) schurTasks.push_back({g, ti, tj});
+        uni.clear(); members.clear();
+      };
+      for (int32_t p : lmOrder) {
+        const int32_t* bb = S.lmRowCam.data() + S.lmRowPtr[p];
+        const int32_t* ee = S.lmRowCam.data() + S.lmRowPtr[p + 1];
+        merged.clear();
+        std::set_union(uni.begin(), uni.end(), bb, ee, std::back_inserter(merged));
+        if (!members.empty() && ((int)members.size() == kGrpMax || scal(merged) > kGrpMaxRows)) {
+          flush();
+          merged.assign(bb, ee);
+        }
+        uni.swap(merged);
+        members.push_back(p);
+      }
+      flush();
+    }
+    updPtr.push_back((int64_t)colOff.size()); relPtr.push_back((int64_t)rel.size());
     d.diagLOff = P.upload(diagLOff); d.diagL = P.alloc<double>(dl);
     d.updPtr = P.upload(updPtr); d.updColOff = P.upload(colOff); d.updStride = P.upload(stride);
     d.updTgt = P.upload(tgt); d.updGlobal = P.upload(glob); d.relPtr = P.upload(relPtr); d.rel = P.upload(rel);
+    d.nG = (int64_t)grpRows.size();
+    d.grpLmPtr = P.upload(grpLmPtr); d.grpLm = P.upload(grpLm); d.grpBlkPtr = P.upload(grpBlkPtr);
+    d.grpBlkOff = P.upload(grpBlkOff); d.grpRowBlk = P.upload(grpRowBlk); d.grpRowSub = P.upload(grpRowSub);
+    d.grpRows = P.upload(grpRows);
+    d.grpRowBase = updPtr[S.nL];
+    P.schurTasks = P.upload(schurTasks); P.nSchurTasks = (int)schurTasks.size();
+    if (getenv("VB_VERBOSE")) {
+      double rs = 0; for (int32_t r : grpRows) rs += r;
+      std::fprintf(stderr, "[viba_b200] landmark groups %zu (avg %.1f landmarks, avg %.0f union rows), schur tasks %zu, lumps %lld, levels %zu\n",
+                   grpRows.size(), grpLm.size() / std::max<double>(1, grpRows.size()), rs / std::max<double>(1, grpRows.size()),
+                   schurTasks.size(), (long long)S.nL, S.levels.size());
+    }
   }
   // level schedules
   {
@@ -437,7 +519,7 @@ int vb_step_from_grad(vb_problem* p) {
 static void factorAsync(vb_problem* p, cudaEvent_t afterSchur) {
   cudaStream_t s = p->ctx->stream;
   VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
-  launchSchur(p->sol, p->hess, p->errFlag, s);
+  launchSchur(p->sol, p->hess, p->schurTasks, p->nSchurTasks, p->errFlag, s);
   if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
   for (size_t lv = 0; lv + 1 < p->levelLumpOff.size(); lv++) {
     const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);

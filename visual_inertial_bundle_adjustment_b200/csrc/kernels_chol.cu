@@ -200,6 +200,81 @@ __global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hes
     }
 }
 
+// ---- K9b: Schur update of the camera system by landmark groups -------------------------------------
+// A group is <= 32 landmarks whose row blocks have a small union (<= 320 scalar rows).  Its dense
+// operand U = [union rows] x [3 G] holds W_p L_p^-T of every member (zeros where a landmark does not
+// see a block), gathered straight from the landmark panels; the update of the reduced system is then
+// -U U^T, tile by tile on DMMA, scattered with the same relative-index tables as the supernodes
+// (source index nL + g).  One reduction per target entry per group instead of one per landmark.
+constexpr int kGrpMax = 32;
+__global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, double* hess, const LevelTask* tasks) {
+  extern __shared__ double sm[];
+  const LevelTask t = tasks[blockIdx.x];
+  const int g = t.lump;
+  const int r = d.grpRows[g];
+  constexpr int K = 3 * kGrpMax;      // 96
+  const int ld = ldFor(K);            // 100
+  double* As = sm;
+  double* Bs = (t.ti == t.tj) ? sm : sm + (size_t)kUpdTile * ld;
+  const int i0 = t.ti * kUpdTile, j0 = t.tj * kUpdTile;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t src = d.nL + g;
+  const int64_t q0 = d.updPtr[src];
+  const int64_t qg = q0 - d.grpRowBase;
+  const int32_t* blkOff = d.grpBlkOff + d.grpBlkPtr[g] * kGrpMax;
+  // gather: element (row a, landmark l) = 3 doubles
+  for (int i = tid; i < kUpdTile * kGrpMax; i += 256) {
+    const int a = i / kGrpMax, l = i % kGrpMax;
+    {
+      const int q = i0 + a;
+      double x0 = 0, x1 = 0, x2 = 0;
+      if (q < r) {
+        const int off = blkOff[d.grpRowBlk[qg + q] * kGrpMax + l];
+        if (off >= 0) { const double* w = hess + off + 3 * d.grpRowSub[qg + q]; x0 = w[0]; x1 = w[1]; x2 = w[2]; }
+      }
+      double* o = As + a * ld + 3 * l;
+      o[0] = x0; o[1] = x1; o[2] = x2;
+    }
+    if (t.ti != t.tj) {
+      const int q = j0 + a;
+      double x0 = 0, x1 = 0, x2 = 0;
+      if (q < r) {
+        const int off = blkOff[d.grpRowBlk[qg + q] * kGrpMax + l];
+        if (off >= 0) { const double* w = hess + off + 3 * d.grpRowSub[qg + q]; x0 = w[0]; x1 = w[1]; x2 = w[2]; }
+      }
+      double* o = Bs + a * ld + 3 * l;
+      o[0] = x0; o[1] = x1; o[2] = x2;
+    }
+  }
+  __syncthreads();
+  const int rowBase = (warp >> 1) * 16, colBase = (warp & 1) * 32;
+  double acc[2][4][2];
+#pragma unroll
+  for (int m = 0; m < 2; m++)
+#pragma unroll
+    for (int n = 0; n < 4; n++) acc[m][n][0] = acc[m][n][1] = 0.0;
+  dmmaABt<2, 4>(As, ld, Bs, ld, K, rowBase, colBase, acc);
+  const int32_t* rel = d.rel + d.relPtr[src];
+#pragma unroll
+  for (int n = 0; n < 4; n++)
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+      const int qj = j0 + colBase + n * 8 + 2 * (lane & 3) + e;
+      if (qj >= r) continue;
+      const int64_t colOff = d.updColOff[q0 + qj];
+      const int stride = d.updStride[q0 + qj];
+      const int32_t* relT = rel + (int64_t)d.updTgt[q0 + qj] * r;
+#pragma unroll
+      for (int m = 0; m < 2; m++) {
+        const int qi = i0 + rowBase + m * 8 + (lane >> 2);
+        if (qi >= r || qi < qj) continue;
+        const double v = acc[m][n][e];
+        const int rr = relT[qi];
+        if (v != 0.0 && rr >= 0) red_add(hess + colOff + (int64_t)rr * stride, -v);
+      }
+    }
+}
+
 // ---- K11 (supernode part) ---------------------------------------------------------------------------
 // warp-level triangular solves with L (w x w, lower, row-major with leading dimension ld) in shared
 // memory and x in shared memory; called by warp 0 only
@@ -293,6 +368,14 @@ __global__ void __launch_bounds__(512) solveLumpBwdKernel(DevSolver d, const dou
 // ---- launchers ----------------------------------------------------------------------------------------
 static void ensureSmem(const void* fn, size_t bytes) {
   if (bytes > 48 * 1024) VB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+}
+void launchSchur(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int* errFlag, cudaStream_t s) {
+  launchSchurPrep(d, hess, errFlag, s);
+  if (nTasks == 0) return;
+  const size_t smem = (size_t)2 * kUpdTile * ldFor(3 * kGrpMax) * sizeof(double);
+  ensureSmem((const void*)schurGroupUpdateKernel, smem);
+  schurGroupUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks);
+  VB_CUDA(cudaGetLastError());
 }
 void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s) {
   const size_t smem = (size_t)(((maxWidth + 7) & ~7) + kPanelRows) * ldFor(maxWidth) * sizeof(double);

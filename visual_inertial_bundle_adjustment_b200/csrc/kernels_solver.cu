@@ -18,8 +18,9 @@ VB_DEV int rowInLump(const DevSolver& d, int T, int c) {
   return d.lumpRowOff[lo];
 }
 
-// ---- K9: landmark elimination, one warp per landmark ------------------------------------------------
-__global__ void __launch_bounds__(256) schurKernel(DevSolver d, double* hess, int* errFlag) {
+// ---- K9a: landmark elimination, first half: one warp per landmark factors H_pp (3x3) in place and
+// turns the row panel into W L^-T.  The Schur update itself is schurGroupUpdateKernel (kernels_chol.cu).
+__global__ void __launch_bounds__(256) schurPrepKernel(DevSolver d, double* hess, int* errFlag) {
   const int64_t p = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (p >= d.nP) return;
@@ -44,30 +45,6 @@ __global__ void __launch_bounds__(256) schurKernel(DevSolver d, double* hess, in
   __syncwarp();
   if (lane == 0) {
     base[0] = l00; base[1] = 0; base[2] = 0; base[3] = l10; base[4] = l11; base[5] = 0; base[6] = l20; base[7] = l21; base[8] = l22;
-  }
-  const int64_t r0 = d.lmRowPtr[p];
-  const int nb = (int)(d.lmRowPtr[p + 1] - r0);
-  const int npairs = nb * (nb + 1) / 2;
-  for (int pr = lane; pr < npairs; pr += 32) {
-    int ia = (int)((sqrt(8.0 * pr + 1.0) - 1.0) * 0.5);
-    while ((ia + 1) * (ia + 2) / 2 <= pr) ia++;
-    while (ia * (ia + 1) / 2 > pr) ia--;
-    const int ib = pr - ia * (ia + 1) / 2;
-    const int ca = d.lmRowCam[r0 + ia], cb = d.lmRowCam[r0 + ib];
-    const int da = d.camStart[ca + 1] - d.camStart[ca], db = d.camStart[cb + 1] - d.camStart[cb];
-    const int T = d.camLump[cb];
-    const int wT = d.lumpWidth[T];
-    const int col = d.camStart[cb] - d.camStart[d.lumpFirst[T]];
-    const int row = rowInLump(d, T, ca);
-    double* tgt = hess + d.lumpOff[T] + (int64_t)row * wT + col;
-    const double* Wa = W + (d.lmRowOff[r0 + ia] - 3) * 3;
-    const double* Wb = W + (d.lmRowOff[r0 + ib] - 3) * 3;
-    for (int s = 0; s < da; s++) {
-      const double x0 = Wa[s * 3], x1 = Wa[s * 3 + 1], x2 = Wa[s * 3 + 2];
-      const int tmax = (ia == ib) ? s + 1 : db;
-      for (int t = 0; t < tmax; t++)
-        red_add(tgt + (int64_t)s * wT + t, -(x0 * Wb[t * 3] + x1 * Wb[t * 3 + 1] + x2 * Wb[t * 3 + 2]));
-    }
   }
 }
 
@@ -154,9 +131,9 @@ double measureDmmaPeak(cudaStream_t s) {
 }
 
 // ---- launchers ----------------------------------------------------------------------------------------
-void launchSchur(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s) {
+void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s) {
   if (d.nP == 0) return;
-  schurKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, errFlag);
+  schurPrepKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, errFlag);
   VB_CUDA(cudaGetLastError());
 }
 void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s) {

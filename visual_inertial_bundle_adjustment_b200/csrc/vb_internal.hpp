@@ -18,6 +18,8 @@ namespace vb {
 constexpr int kPreintStride = 250; // R(4) dV(3) dP(3) dt(1) J(9x23) evalPoint(32)
 constexpr int kMaxVars = 10;
 
+struct LevelTask { int32_t lump, ti, tj; };
+
 // device view of one factor store (SoA tables + scatter map)
 struct DevStore {
   int32_t type, nvars, cpf, npairs;
@@ -67,9 +69,18 @@ struct DevSolver {
   const int64_t* relPtr;    // [nL+1] start of rel table (nT * r ints)
   const int32_t* rel;       // rel[t*r + q] = row of q inside T's panel
   int64_t camVec0;          // scalar offset of the camera section in the permuted vectors (= 3 nP)
+  // landmark groups of the Schur update (scatter source index nL + g in the upd*/rel tables)
+  int64_t nG;
+  const int64_t* grpLmPtr;   // [nG+1] into grpLm
+  const int32_t* grpLm;      // landmark ids
+  const int64_t* grpBlkPtr;  // [nG+1] first union row block of the group
+  const int32_t* grpBlkOff;  // [(grpBlkPtr[g] + b) * 32 + l] offset of landmark l's W block at union block b, or -1
+  const int32_t* grpRowBlk;  // per union scalar row (index updPtr[nL+g] - grpRowBase + q): union block
+  const int32_t* grpRowSub;  //   ... and the row inside that block
+  const int32_t* grpRows;    // [nG] union scalar rows
+  int64_t grpRowBase;        // updPtr[nL]
 };
 
-struct LevelTask { int32_t lump, ti, tj; };
 
 // kernels_factors.cu
 void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
@@ -79,7 +90,8 @@ void launchApplyStep(const DevVars& v, const int64_t* blockVar, int64_t nB, cons
 void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize, int64_t nB,
                    double lambda, cudaStream_t s);
 // kernels_solver.cu
-void launchSchur(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
+void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
+void launchSchur(const DevSolver& d, double* hess, const struct LevelTask* tasks, int nTasks, int* errFlag, cudaStream_t s);
 void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s);
 void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s);
 void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);

@@ -270,6 +270,9 @@ static void buildDeviceProblem(vb_problem& P) {
     }
     updPtr.push_back((int64_t)colOff.size()); relPtr.push_back((int64_t)rel.size());
     d.diagLOff = P.upload(diagLOff); d.diagL = P.alloc<double>(dl);
+    d.solveAcc = P.alloc<double>(S.camStart[S.nC] + 1); d.solveCnt = P.alloc<int>(S.nL + 1);
+    VB_CUDA(cudaMemset(d.solveAcc, 0, (S.camStart[S.nC] + 1) * sizeof(double)));
+    VB_CUDA(cudaMemset(d.solveCnt, 0, (S.nL + 1) * sizeof(int)));
     d.updPtr = P.upload(updPtr); d.updColOff = P.upload(colOff); d.updStride = P.upload(stride);
     d.updTgt = P.upload(tgt); d.updGlobal = P.upload(glob); d.relPtr = P.upload(relPtr); d.rel = P.upload(rel);
     d.nG = (int64_t)grpRows.size();
@@ -541,11 +544,11 @@ static void solveAsync(vb_problem* p, double* vec) {
   launchSolveLandmarksFwd(p->sol, p->hess, vec, s);
   for (int lv = 0; lv < nLv; lv++) {
     const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
-    launchSolveLumpsFwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], nl > 1, s);
+    launchSolveLumpsFwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], p->levelMaxBelow[lv], nl > 1, s);
   }
   for (int lv = nLv - 1; lv >= 0; lv--) {
     const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
-    launchSolveLumpsBwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv] + p->levelMaxBelow[lv], s);
+    launchSolveLumpsBwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], p->levelMaxBelow[lv], s);
   }
   launchSolveLandmarksBwd(p->sol, p->hess, vec, s);
 }

@@ -33,30 +33,22 @@ VB_DEV void dmmaABt(const double* As, int lda, const double* Bs, int ldb, int K4
 constexpr int kPanelRows = 64;  // panel rows per CTA in the factor kernel
 constexpr int kNB = 8;          // column block of the blocked potrf / trsm
 
-// ---- K10a: diagonal potrf + panel trsm -------------------------------------------------------------
-// grid = (row tiles, lumps of the level), 256 threads.  Every CTA factors the w x w diagonal block
-// redundantly in shared memory (no inter-CTA dependency), CTA x==0 publishes L into diagL, each CTA
-// solves X L^T = B for its 64 panel rows.  Both are blocked by 8 columns: the bulk is
-// [rows x 8] -= [rows x k] [8 x k]^T on DMMA, the 8x8 triangles are solved per row in registers.
-__global__ void __launch_bounds__(256) lumpFactorKernel(DevSolver d, double* hess, const int32_t* lumps, int* errFlag) {
+// ---- K10a: diagonal potrf (one CTA per supernode) and panel trsm (one CTA per 64 panel rows) -------
+// Both are blocked by 8 columns: the bulk is [rows x 8] -= [rows x k] [8 x k]^T on DMMA, the 8x8
+// triangles are solved per row in registers.  potrf publishes L into diagL (the panel's diagonal
+// block in hess is left untouched); trsm reads it back into shared memory.
+__global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double* hess, const int32_t* lumps, int* errFlag) {
   extern __shared__ double sm[];
   __shared__ int bad;
-  const int L = lumps[blockIdx.y];
-  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
-  const int tile = blockIdx.x;
-  if (tile > 0 && tile * kPanelRows >= r) return;
+  const int L = lumps[blockIdx.x];
+  const int w = d.lumpWidth[L];
   const int ld = ldFor(w);
   const int wp = (w + 7) & ~7;          // rows padded to the 8-row MMA tiles
   double* A = sm;                        // wp x ld   (diagonal block -> L)
-  double* X = sm + (size_t)wp * ld;      // 64 x ld   (panel rows)
-  double* panel = hess + d.lumpOff[L];
+  const double* panel = hess + d.lumpOff[L];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) bad = 0;
   for (int i = tid; i < wp * ld; i += 256) { const int a = i / ld, b = i % ld; A[i] = (a < w && b <= a) ? panel[(int64_t)a * w + b] : 0.0; }
-  const int row0 = tile * kPanelRows;
-  const int nrows = max(0, min(kPanelRows, r - row0));
-  const double* below = panel + (int64_t)(w + row0) * w;
-  for (int i = tid; i < kPanelRows * ld; i += 256) { const int a = i / ld, b = i % ld; X[i] = (a < nrows && b < w) ? below[(int64_t)a * w + b] : 0.0; }
   __syncthreads();
   // ---- blocked left-looking Cholesky of A (lower), 8 columns at a time
   for (int j0 = 0; j0 < w; j0 += kNB) {
@@ -112,11 +104,29 @@ __global__ void __launch_bounds__(256) lumpFactorKernel(DevSolver d, double* hes
     }
     __syncthreads();
   }
-  if (tile == 0) {
-    double* out = d.diagL + d.diagLOff[L];
-    for (int i = tid; i < w * w; i += 256) { const int a = i / w, b = i % w; out[i] = b <= a ? A[a * ld + b] : 0.0; }
-  }
-  if (nrows == 0) return;
+  double* out = d.diagL + d.diagLOff[L];
+  for (int i = tid; i < w * w; i += 256) { const int a = i / w, b = i % w; out[i] = b <= a ? A[a * ld + b] : 0.0; }
+}
+
+__global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess, const int32_t* lumps) {
+  extern __shared__ double sm[];
+  const int L = lumps[blockIdx.y];
+  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const int tile = blockIdx.x;
+  if (tile * kPanelRows >= r) return;
+  const int ld = ldFor(w);
+  const int wp = (w + 7) & ~7;
+  double* A = sm;                        // wp x ld   (L)
+  double* X = sm + (size_t)wp * ld;      // 64 x ld   (panel rows)
+  double* panel = hess + d.lumpOff[L];
+  const double* Ld = d.diagL + d.diagLOff[L];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < wp * ld; i += 256) { const int a = i / ld, b = i % ld; A[i] = (a < w && b < w) ? Ld[a * w + b] : 0.0; }
+  const int row0 = tile * kPanelRows;
+  const int nrows = min(kPanelRows, r - row0);
+  const double* below = panel + (int64_t)(w + row0) * w;
+  for (int i = tid; i < kPanelRows * ld; i += 256) { const int a = i / ld, b = i % ld; X[i] = (a < nrows && b < w) ? below[(int64_t)a * w + b] : 0.0; }
+  __syncthreads();
   // ---- panel trsm X L^T = B, blocked the same way (8 warps = 8 row tiles of the 64 rows)
   for (int j0 = 0; j0 < w; j0 += kNB) {
     const int nb = min(kNB, w - j0);
@@ -276,93 +286,151 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
 }
 
 // ---- K11 (supernode part) ---------------------------------------------------------------------------
-// warp-level triangular solves with L (w x w, lower, row-major with leading dimension ld) in shared
-// memory and x in shared memory; called by warp 0 only
-VB_DEV void warpSolveL(const double* Ls, int ld, double* x, int w) {  // L y = x
+// Warp-level triangular solves: L (w x w, lower, row-major, odd leading dimension) and the
+// reciprocals of its diagonal in shared memory, x in shared memory.  32 columns at a time live in
+// registers (one per lane) and are eliminated with shuffles; earlier/later blocks enter as GEMVs.
+VB_DEV void warpSolveL(const double* Ls, int ld, const double* dinv, double* x, int w) {  // L y = x
   const int lane = threadIdx.x & 31;
-  for (int c = 0; c < w; c++) {
-    const double xc = x[c] / Ls[c * ld + c];
-    __syncwarp();
-    if (lane == 0) x[c] = xc;
-    for (int k = c + 1 + lane; k < w; k += 32) x[k] = fma(-Ls[k * ld + c], xc, x[k]);
+  for (int b0 = 0; b0 < w; b0 += 32) {
+    const int k = b0 + lane;
+    double xk = k < w ? x[k] : 0.0;
+    if (k < w) for (int c = 0; c < b0; c++) xk = fma(-Ls[k * ld + c], x[c], xk);
+    const int nb = min(32, w - b0);
+    for (int c = 0; c < nb; c++) {
+      const double xc = __shfl_sync(0xffffffffu, xk, c) * dinv[b0 + c];
+      if (lane == c) xk = xc;
+      else if (lane > c && k < w) xk = fma(-Ls[k * ld + b0 + c], xc, xk);
+    }
+    if (k < w) x[k] = xk;
     __syncwarp();
   }
 }
-VB_DEV void warpSolveLt(const double* Ls, int ld, double* x, int w) { // L^T y = x
+VB_DEV void warpSolveLt(const double* Ls, int ld, const double* dinv, double* x, int w) { // L^T y = x
   const int lane = threadIdx.x & 31;
-  for (int c = w - 1; c >= 0; c--) {
-    const double xc = x[c] / Ls[c * ld + c];
-    __syncwarp();
-    if (lane == 0) x[c] = xc;
-    for (int k = lane; k < c; k += 32) x[k] = fma(-Ls[c * ld + k], xc, x[k]);
+  for (int b0 = ((w - 1) / 32) * 32; b0 >= 0; b0 -= 32) {
+    const int k = b0 + lane;
+    double xk = k < w ? x[k] : 0.0;
+    if (k < w) for (int c = b0 + 32; c < w; c++) xk = fma(-Ls[c * ld + k], x[c], xk);
+    const int nb = min(32, w - b0);
+    for (int c = nb - 1; c >= 0; c--) {
+      const double xc = __shfl_sync(0xffffffffu, xk, c) * dinv[b0 + c];
+      if (lane == c) xk = xc;
+      else if (lane < c) xk = fma(-Ls[(b0 + c) * ld + k], xc, xk);
+    }
+    if (k < w) x[k] = xk;
     __syncwarp();
   }
 }
 
-// forward over the lumps of one level: x_L = L^-1 b_L ; b_below -= P x_L.  One CTA per lump.
-__global__ void __launch_bounds__(512) solveLumpFwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps, int useAtomics) {
+constexpr int kSolveSlice = 128; // panel rows per CTA in the solves
+
+// forward over the lumps of one level: x_L = L^-1 b_L ; b_below -= P x_L.
+// grid = (row slices, lumps).  Every slice CTA solves the small triangular system redundantly and
+// applies its 128 panel rows; the CTA that finishes last (per-lump counter) publishes x_L, which
+// guarantees every other slice has already read b_L.
+__global__ void __launch_bounds__(256) solveLumpFwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps, int useAtomics) {
   extern __shared__ double sm[];
-  const int L = lumps[blockIdx.x];
+  __shared__ int isLast;
+  const int L = lumps[blockIdx.y];
   const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const int nSlices = max(1, (r + kSolveSlice - 1) / kSolveSlice);
+  const int slice = blockIdx.x;
+  if (slice >= nSlices) return;
   const int ld = w | 1;
   double* Ls = sm;
   double* x = sm + (size_t)w * ld;
+  double* dinv = x + w;
   double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
   const double* Ld = d.diagL + d.diagLOff[L];
-  const int tid = threadIdx.x;
-  for (int i = tid; i < w * w; i += 512) Ls[(i / w) * ld + (i % w)] = Ld[i];
-  for (int i = tid; i < w; i += 512) x[i] = vL[i];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < w * w; i += 256) Ls[(i / w) * ld + (i % w)] = Ld[i];
+  for (int i = tid; i < w; i += 256) { x[i] = vL[i]; dinv[i] = 1.0 / Ld[i * w + i]; }
   __syncthreads();
-  if (tid < 32) warpSolveL(Ls, ld, x, w);
+  if (warp == 0) warpSolveL(Ls, ld, dinv, x, w);
   __syncthreads();
-  for (int i = tid; i < w; i += 512) vL[i] = x[i];
   const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
   const int64_t q0 = d.updPtr[L];
-  // one warp per panel row: coalesced row read, shuffle reduction
-  const int warp = tid >> 5, lane = tid & 31;
-  for (int row = warp; row < r; row += 16) {
-    const double* P = below + (int64_t)row * w;
-    double s = 0;
-    for (int c = lane; c < w; c += 32) s = fma(P[c], x[c], s);
+  const int rEnd = min(r, (slice + 1) * kSolveSlice);
+  for (int row = slice * kSolveSlice + warp * 2; row < rEnd; row += 16) { // two rows per warp pass
+    const double* P0 = below + (int64_t)row * w;
+    const bool two = row + 1 < rEnd;
+    const double* P1 = two ? P0 + w : P0;
+    double s0 = 0, s1 = 0;
+    for (int c = lane; c < w; c += 32) { const double xc = x[c]; s0 = fma(P0[c], xc, s0); s1 = fma(P1[c], xc, s1); }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int o = 16; o > 0; o >>= 1) { s0 += __shfl_xor_sync(0xffffffffu, s0, o); s1 += __shfl_xor_sync(0xffffffffu, s1, o); }
     if (lane == 0) {
       double* out = vec + d.camVec0 + d.updGlobal[q0 + row];
-      if (useAtomics) red_add(out, -s); else *out -= s;
+      if (useAtomics) red_add(out, -s0); else *out -= s0;
+    } else if (lane == 1 && two) {
+      double* out = vec + d.camVec0 + d.updGlobal[q0 + row + 1];
+      if (useAtomics) red_add(out, -s1); else *out -= s1;
     }
   }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const int done = atomicAdd(d.solveCnt + L, 1);
+    isLast = (done == nSlices - 1);
+    if (isLast) d.solveCnt[L] = 0;
+  }
+  __syncthreads();
+  if (isLast) for (int i = tid; i < w; i += 256) vL[i] = x[i];
 }
-// backward: x_L = L^-T (b_L - P^T x_below)
-__global__ void __launch_bounds__(512) solveLumpBwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps) {
+// backward: x_L = L^-T (b_L - P^T x_below).  Slice CTAs accumulate their part of P^T x_below into a
+// per-lump scratch with fp64 reductions; the last one to arrive finishes the triangular solve.
+__global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps) {
   extern __shared__ double sm[];
-  const int L = lumps[blockIdx.x];
+  __shared__ int isLast;
+  const int L = lumps[blockIdx.y];
   const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const int nSlices = max(1, (r + kSolveSlice - 1) / kSolveSlice);
+  const int slice = blockIdx.x;
+  if (slice >= nSlices) return;
   const int ld = w | 1;
   double* Ls = sm;
-  double* x = sm + (size_t)w * ld;   // w
-  double* part = x + w;              // 4 x w partial sums
-  double* xb = part + 4 * w;         // r
+  double* x = sm + (size_t)w * ld;
+  double* dinv = x + w;
+  double* part = dinv + w;           // 2 x w
+  double* xb = part + 2 * w;         // kSolveSlice
   double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
+  double* accL = d.solveAcc + d.camStart[d.lumpFirst[L]];
   const double* Ld = d.diagL + d.diagLOff[L];
   const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
   const int64_t q0 = d.updPtr[L];
   const int tid = threadIdx.x;
-  for (int i = tid; i < w * w; i += 512) Ls[(i / w) * ld + (i % w)] = Ld[i];
-  for (int row = tid; row < r; row += 512) xb[row] = vec[d.camVec0 + d.updGlobal[q0 + row]];
+  const int rBeg = slice * kSolveSlice, rEnd = min(r, rBeg + kSolveSlice);
+  for (int i = tid; i < rEnd - rBeg; i += 256) xb[i] = vec[d.camVec0 + d.updGlobal[q0 + rBeg + i]];
   __syncthreads();
-  // 4 row slices x 128 column lanes: coalesced along the columns of the row-major panel
-  const int slice = tid >> 7, cl = tid & 127;
-  for (int c = cl; c < w; c += 128) {
+  {
+    const int half = tid >> 7, c = tid & 127;
     double s = 0;
-    for (int row = slice; row < r; row += 4) s = fma(below[(int64_t)row * w + c], xb[row], s);
-    part[slice * w + c] = s;
+    if (c < w) for (int row = rBeg + half; row < rEnd; row += 2) s = fma(below[(int64_t)row * w + c], xb[row - rBeg], s);
+    if (c < w) part[half * w + c] = s;
   }
   __syncthreads();
-  for (int c = tid; c < w; c += 512) x[c] = vL[c] - (part[c] + part[w + c] + part[2 * w + c] + part[3 * w + c]);
+  if (nSlices > 1 && rEnd > rBeg) for (int c = tid; c < w; c += 256) red_add(accL + c, part[c] + part[w + c]);
+  __threadfence();
   __syncthreads();
-  if (tid < 32) warpSolveLt(Ls, ld, x, w);
+  if (tid == 0) {
+    const int done = atomicAdd(d.solveCnt + L, 1);
+    isLast = (done == nSlices - 1);
+    if (isLast) d.solveCnt[L] = 0;
+  }
   __syncthreads();
-  for (int i = tid; i < w; i += 512) vL[i] = x[i];
+  if (!isLast) return;
+  __threadfence();
+  for (int i = tid; i < w * w; i += 256) Ls[(i / w) * ld + (i % w)] = Ld[i];
+  for (int i = tid; i < w; i += 256) {
+    double s;
+    if (nSlices > 1) { s = __ldcg(accL + i); accL[i] = 0.0; } else s = part[i] + part[w + i];
+    x[i] = vL[i] - s;
+    dinv[i] = 1.0 / Ld[i * w + i];
+  }
+  __syncthreads();
+  if (tid < 32) warpSolveLt(Ls, ld, dinv, x, w);
+  __syncthreads();
+  for (int i = tid; i < w; i += 256) vL[i] = x[i];
 }
 
 // ---- launchers ----------------------------------------------------------------------------------------
@@ -378,10 +446,14 @@ void launchSchur(const DevSolver& d, double* hess, const LevelTask* tasks, int n
   VB_CUDA(cudaGetLastError());
 }
 void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s) {
-  const size_t smem = (size_t)(((maxWidth + 7) & ~7) + kPanelRows) * ldFor(maxWidth) * sizeof(double);
-  ensureSmem((const void*)lumpFactorKernel, smem);
-  const int tiles = std::max(1, (maxRows + kPanelRows - 1) / kPanelRows);
-  lumpFactorKernel<<<dim3(tiles, nLumps), 256, smem, s>>>(d, hess, lumps, errFlag);
+  const size_t smemP = (size_t)((maxWidth + 7) & ~7) * ldFor(maxWidth) * sizeof(double);
+  ensureSmem((const void*)lumpPotrfKernel, smemP);
+  lumpPotrfKernel<<<nLumps, 256, smemP, s>>>(d, hess, lumps, errFlag);
+  VB_CUDA(cudaGetLastError());
+  if (maxRows <= 0) return;
+  const size_t smemT = (size_t)(((maxWidth + 7) & ~7) + kPanelRows) * ldFor(maxWidth) * sizeof(double);
+  ensureSmem((const void*)lumpTrsmKernel, smemT);
+  lumpTrsmKernel<<<dim3((maxRows + kPanelRows - 1) / kPanelRows, nLumps), 256, smemT, s>>>(d, hess, lumps);
   VB_CUDA(cudaGetLastError());
 }
 void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s) {
@@ -391,19 +463,18 @@ void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, 
   lumpUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks, useAtomics);
   VB_CUDA(cudaGetLastError());
 }
-void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int useAtomics, cudaStream_t s) {
-  const size_t smem = ((size_t)maxWidth * (maxWidth | 1) + maxWidth) * sizeof(double);
+void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, int useAtomics, cudaStream_t s) {
+  const size_t smem = ((size_t)maxWidth * (maxWidth | 1) + 2 * (size_t)maxWidth) * sizeof(double);
   ensureSmem((const void*)solveLumpFwdKernel, smem);
-  solveLumpFwdKernel<<<nLumps, 512, smem, s>>>(d, hess, vec, lumps, useAtomics);
+  const int slices = std::max(1, (maxBelow + kSolveSlice - 1) / kSolveSlice);
+  solveLumpFwdKernel<<<dim3(slices, nLumps), 256, smem, s>>>(d, hess, vec, lumps, useAtomics);
   VB_CUDA(cudaGetLastError());
 }
-// maxWidthPlusBelow = widest lump of the level + its longest below-row list
-void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidthPlusBelow, cudaStream_t s) {
-  // the width is not passed separately: bound w by 128 (the supernode cap) for the L tile
-  const int wMax = std::min(maxWidthPlusBelow, 128);
-  const size_t smem = ((size_t)wMax * (wMax | 1) + 5 * (size_t)wMax + maxWidthPlusBelow) * sizeof(double);
+void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, cudaStream_t s) {
+  const size_t smem = ((size_t)maxWidth * (maxWidth | 1) + 4 * (size_t)maxWidth + kSolveSlice) * sizeof(double);
   ensureSmem((const void*)solveLumpBwdKernel, smem);
-  solveLumpBwdKernel<<<nLumps, 512, smem, s>>>(d, hess, vec, lumps);
+  const int slices = std::max(1, (maxBelow + kSolveSlice - 1) / kSolveSlice);
+  solveLumpBwdKernel<<<dim3(slices, nLumps), 256, smem, s>>>(d, hess, vec, lumps);
   VB_CUDA(cudaGetLastError());
 }
 

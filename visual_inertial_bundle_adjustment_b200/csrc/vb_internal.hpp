@@ -69,6 +69,8 @@ struct DevSolver {
   const int64_t* relPtr;    // [nL+1] start of rel table (nT * r ints)
   const int32_t* rel;       // rel[t*r + q] = row of q inside T's panel
   int64_t camVec0;          // scalar offset of the camera section in the permuted vectors (= 3 nP)
+  double* solveAcc;         // [reduced order] scratch of the backward solve (kept zero between calls)
+  int* solveCnt;            // [nL] arrival counters of the solve kernels (kept zero between calls)
   // landmark groups of the Schur update (scatter source index nL + g in the upd*/rel tables)
   int64_t nG;
   const int64_t* grpLmPtr;   // [nG+1] into grpLm
@@ -96,8 +98,8 @@ void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, in
 void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s);
 void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);
 void launchSolveLandmarksBwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);
-void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int useAtomics, cudaStream_t s);
-void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, cudaStream_t s);
+void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, int useAtomics, cudaStream_t s);
+void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, cudaStream_t s);
 // op: 0 a=b ; 1 a*=s ; 2 out[0]+=a.b ; 3 a=0
 void launchVecOp(int op, double* a, const double* b, double s, int64_t n, double* out, cudaStream_t st);
 double measureDmmaPeak(cudaStream_t s);

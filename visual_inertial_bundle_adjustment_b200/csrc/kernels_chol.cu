@@ -106,58 +106,81 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
   }
   double* out = d.diagL + d.diagLOff[L];
   for (int i = tid; i < w * w; i += 256) { const int a = i / w, b = i % w; out[i] = b <= a ? A[a * ld + b] : 0.0; }
+  // inverses of the 32x32 diagonal blocks of L (for the DMMA trsm): thread c owns column c
+  double* inv = d.diagInv + (int64_t)d.camStart[d.lumpFirst[L]] * 32;
+  if (tid < w) {
+    const int c = tid, b0 = c & ~31, bEnd = min(b0 + 32, w);
+    double z[32];
+#pragma unroll
+    for (int i = 0; i < 32; i++) z[i] = 0.0;
+#pragma unroll
+    for (int ii = 0; ii < 32; ii++) {
+      const int i = b0 + ii;
+      if (i < c || i >= bEnd) continue;
+      double s = (i == c) ? 1.0 : 0.0;
+#pragma unroll
+      for (int kk = 0; kk < 32; kk++) if (kk < ii && b0 + kk >= c) s = fma(-A[i * ld + b0 + kk], z[kk], s);
+      z[ii] = s / A[i * ld + i];
+    }
+#pragma unroll
+    for (int ii = 0; ii < 32; ii++) if (b0 + ii < bEnd) inv[(int64_t)(b0 + ii) * 32 + (c - b0)] = z[ii];
+  }
 }
 
+// panel trsm X L^T = B by 32-column blocks: X_j <- (X_j - X_{<j} L_{j,<j}^T) Linv_jj^T, both products
+// on DMMA.  Only the 32x32 diagonal blocks are inverted (by lumpPotrfKernel).  64 panel rows per CTA,
+// one 8-row tile per warp (a warp only touches its own rows of X).
+constexpr int kTB = 32;
 __global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess, const int32_t* lumps) {
   extern __shared__ double sm[];
   const int L = lumps[blockIdx.y];
   const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
   const int tile = blockIdx.x;
   if (tile * kPanelRows >= r) return;
-  const int ld = ldFor(w);
-  const int wp = (w + 7) & ~7;
-  double* A = sm;                        // wp x ld   (L)
-  double* X = sm + (size_t)wp * ld;      // 64 x ld   (panel rows)
+  const int nblk = (w + kTB - 1) / kTB;
+  const int ld = ldFor(kTB * nblk);              // X (padded to whole 32-column blocks)
+  const int ldl = ldFor(max(kTB * (nblk - 1), 8)); // L row block [32 x 32 jb]
+  double* X = sm;                                 // 64 x ld
+  double* Lr = X + (size_t)kPanelRows * ld;       // 32 x ldl
+  double* Li = Lr + (size_t)kTB * ldl;            // 32 x 36
   double* panel = hess + d.lumpOff[L];
   const double* Ld = d.diagL + d.diagLOff[L];
+  const double* inv = d.diagInv + (int64_t)d.camStart[d.lumpFirst[L]] * 32;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < wp * ld; i += 256) { const int a = i / ld, b = i % ld; A[i] = (a < w && b < w) ? Ld[a * w + b] : 0.0; }
   const int row0 = tile * kPanelRows;
   const int nrows = min(kPanelRows, r - row0);
-  const double* below = panel + (int64_t)(w + row0) * w;
+  double* below = panel + (int64_t)(w + row0) * w;
   for (int i = tid; i < kPanelRows * ld; i += 256) { const int a = i / ld, b = i % ld; X[i] = (a < nrows && b < w) ? below[(int64_t)a * w + b] : 0.0; }
-  __syncthreads();
-  // ---- panel trsm X L^T = B, blocked the same way (8 warps = 8 row tiles of the 64 rows)
-  for (int j0 = 0; j0 < w; j0 += kNB) {
-    const int nb = min(kNB, w - j0);
-    if (j0 > 0) {
-      double acc[1][1][2] = {{{0.0, 0.0}}};
-      dmmaABt<1, 1>(X, ld, A, ld, j0, warp * 8, j0, acc);
-      const int rr = warp * 8 + (lane >> 2), cc = j0 + 2 * (lane & 3);
-      X[rr * ld + cc] -= acc[0][0][0];
-      X[rr * ld + cc + 1] -= acc[0][0][1];
-    }
+  for (int jb = 0; jb < nblk; jb++) {
+    const int c0 = jb * kTB, nb = min(kTB, w - c0);
     __syncthreads();
-    if (tid < kPanelRows) {
-      double x[kNB];
-#pragma unroll
-      for (int c = 0; c < kNB; c++) x[c] = X[tid * ld + j0 + c];
-#pragma unroll
-      for (int c = 0; c < kNB; c++) {
-        if (c < nb) {
-          double s = x[c];
-#pragma unroll
-          for (int k = 0; k < c; k++) s = fma(-x[k], A[(j0 + c) * ld + j0 + k], s);
-          x[c] = s / A[(j0 + c) * ld + j0 + c];
-        }
-      }
-#pragma unroll
-      for (int c = 0; c < kNB; c++) if (c < nb) X[tid * ld + j0 + c] = x[c];
-    }
+    for (int i = tid; i < kTB * c0; i += 256) { const int a = i / c0, b = i % c0; Lr[a * ldl + b] = a < nb ? Ld[(int64_t)(c0 + a) * w + b] : 0.0; }
+    for (int i = tid; i < kTB * 36; i += 256) { const int a = i / 36, b = i % 36; Li[i] = (a < nb && b < nb) ? inv[(int64_t)(c0 + a) * 32 + b] : 0.0; }
     __syncthreads();
+    double acc[1][4][2];
+#pragma unroll
+    for (int n = 0; n < 4; n++) acc[0][n][0] = acc[0][n][1] = 0.0;
+    if (jb > 0) dmmaABt<1, 4>(X, ld, Lr, ldl, c0, warp * 8, 0, acc);
+    const int rr = warp * 8 + (lane >> 2);
+#pragma unroll
+    for (int n = 0; n < 4; n++) {
+      const int cc = c0 + n * 8 + 2 * (lane & 3);
+      X[rr * ld + cc] -= acc[0][n][0];
+      X[rr * ld + cc + 1] -= acc[0][n][1];
+      acc[0][n][0] = acc[0][n][1] = 0.0;
+    }
+    __syncwarp();
+    dmmaABt<1, 4>(X + c0, ld, Li, 36, kTB, warp * 8, 0, acc);
+    __syncwarp();
+#pragma unroll
+    for (int n = 0; n < 4; n++) {
+      const int cc = c0 + n * 8 + 2 * (lane & 3);
+      X[rr * ld + cc] = acc[0][n][0];
+      X[rr * ld + cc + 1] = acc[0][n][1];
+    }
   }
-  double* belowW = panel + (int64_t)(w + row0) * w;
-  for (int i = tid; i < nrows * w; i += 256) belowW[i] = X[(i / w) * ld + (i % w)];
+  __syncthreads();
+  for (int i = tid; i < nrows * w; i += 256) below[i] = X[(i / w) * ld + (i % w)];
 }
 
 // ---- K10b: supernode update  C = B B^T  (B = factored panel rows), scattered into the ancestors ----
@@ -451,7 +474,8 @@ void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, in
   lumpPotrfKernel<<<nLumps, 256, smemP, s>>>(d, hess, lumps, errFlag);
   VB_CUDA(cudaGetLastError());
   if (maxRows <= 0) return;
-  const size_t smemT = (size_t)(((maxWidth + 7) & ~7) + kPanelRows) * ldFor(maxWidth) * sizeof(double);
+  const int nblk = (maxWidth + kTB - 1) / kTB;
+  const size_t smemT = ((size_t)kPanelRows * ldFor(kTB * nblk) + (size_t)kTB * ldFor(std::max(kTB * (nblk - 1), 8)) + kTB * 36) * sizeof(double);
   ensureSmem((const void*)lumpTrsmKernel, smemT);
   lumpTrsmKernel<<<dim3((maxRows + kPanelRows - 1) / kPanelRows, nLumps), 256, smemT, s>>>(d, hess, lumps);
   VB_CUDA(cudaGetLastError());

@@ -263,6 +263,35 @@ VB_DEV void dmma(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+// ---- asynchronous global -> shared staging (LDGSTS): every copy is issued without waiting for the
+// previous one, so a tile costs about one memory round trip instead of one per element -------------
+VB_DEV void cp_async8(double* smemDst, const double* gsrc, bool valid) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smemDst);
+  const int sz = valid ? 8 : 0; // src-size 0 => zero fill, nothing is read
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(s), "l"(gsrc), "r"(sz) : "memory");
+}
+VB_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+// dst[rowsPad x colsPad] (leading dimension ld) <- src[rows x cols] (row stride srcStride), zero padded.
+// Warps take rows, lanes take columns.  Call cp_async_wait_all() + __syncthreads() before use.
+VB_DEV void loadTileAsync(double* dst, int ld, int rowsPad, int colsPad, const double* src, int64_t srcStride, int rows, int cols) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int r = warp; r < rowsPad; r += nw) {
+    const bool rv = r < rows;
+    const double* srow = src + (rv ? (int64_t)r * srcStride : 0);
+    double* drow = dst + r * ld;
+    for (int c = lane; c < colsPad; c += 32) {
+      const bool v = rv && c < cols;
+      cp_async8(drow + c, v ? srow + c : src, v);
+    }
+  }
+}
+// global[rows x cols] (row stride dstStride) <- smem tile
+VB_DEV void storeTile(double* dst, int64_t dstStride, const double* srcSm, int ld, int rows, int cols) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  for (int r = warp; r < rows; r += nw)
+    for (int c = lane; c < cols; c += 32) dst[(int64_t)r * dstStride + c] = srcSm[r * ld + c];
+}
+
 // fp64 reduction without return value (REDG.E.ADD.F64)
 VB_DEV void red_add(double* addr, double v) { atomicAdd(addr, v); }
 

@@ -48,7 +48,8 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
   const double* panel = hess + d.lumpOff[L];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) bad = 0;
-  for (int i = tid; i < wp * ld; i += 256) { const int a = i / ld, b = i % ld; A[i] = (a < w && b <= a) ? panel[(int64_t)a * w + b] : 0.0; }
+  loadTileAsync(A, ld, wp, ld, panel, w, w, w); // the strict upper part is never read before it is overwritten
+  cp_async_wait_all();
   __syncthreads();
   // ---- blocked left-looking Cholesky of A (lower), 8 columns at a time
   for (int j0 = 0; j0 < w; j0 += kNB) {
@@ -105,7 +106,8 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
     __syncthreads();
   }
   double* out = d.diagL + d.diagLOff[L];
-  for (int i = tid; i < w * w; i += 256) { const int a = i / w, b = i % w; out[i] = b <= a ? A[a * ld + b] : 0.0; }
+  for (int a = warp; a < w; a += 8)
+    for (int b = lane; b < w; b += 32) out[a * w + b] = b <= a ? A[a * ld + b] : 0.0;
   // inverses of the 32x32 diagonal blocks of L (for the DMMA trsm): thread c owns column c
   double* inv = d.diagInv + (int64_t)d.camStart[d.lumpFirst[L]] * 32;
   if (tid < w) {
@@ -150,12 +152,13 @@ __global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess,
   const int row0 = tile * kPanelRows;
   const int nrows = min(kPanelRows, r - row0);
   double* below = panel + (int64_t)(w + row0) * w;
-  for (int i = tid; i < kPanelRows * ld; i += 256) { const int a = i / ld, b = i % ld; X[i] = (a < nrows && b < w) ? below[(int64_t)a * w + b] : 0.0; }
+  loadTileAsync(X, ld, kPanelRows, ld, below, w, nrows, w);
   for (int jb = 0; jb < nblk; jb++) {
     const int c0 = jb * kTB, nb = min(kTB, w - c0);
     __syncthreads();
-    for (int i = tid; i < kTB * c0; i += 256) { const int a = i / c0, b = i % c0; Lr[a * ldl + b] = a < nb ? Ld[(int64_t)(c0 + a) * w + b] : 0.0; }
-    for (int i = tid; i < kTB * 36; i += 256) { const int a = i / 36, b = i % 36; Li[i] = (a < nb && b < nb) ? inv[(int64_t)(c0 + a) * 32 + b] : 0.0; }
+    loadTileAsync(Lr, ldl, kTB, c0, Ld + (int64_t)c0 * w, w, nb, c0);
+    loadTileAsync(Li, 36, kTB, 36, inv + (int64_t)c0 * 32, 32, nb, nb);
+    cp_async_wait_all();
     __syncthreads();
     double acc[1][4][2];
 #pragma unroll
@@ -180,7 +183,7 @@ __global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess,
     }
   }
   __syncthreads();
-  for (int i = tid; i < nrows * w; i += 256) below[i] = X[(i / w) * ld + (i % w)];
+  storeTile(below, w, X, ld, nrows, w);
 }
 
 // ---- K10b: supernode update  C = B B^T  (B = factored panel rows), scattered into the ancestors ----
@@ -199,11 +202,9 @@ __global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hes
   const int i0 = t.ti * kUpdTile, j0 = t.tj * kUpdTile;
   const int ni = min(kUpdTile, r - i0), nj = min(kUpdTile, r - j0);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < kUpdTile * ld; i += 256) {
-    const int a = i / ld, b = i % ld;
-    As[i] = (a < ni && b < w) ? below[(int64_t)(i0 + a) * w + b] : 0.0;
-    if (t.ti != t.tj) Bs[i] = (a < nj && b < w) ? below[(int64_t)(j0 + a) * w + b] : 0.0;
-  }
+  loadTileAsync(As, ld, kUpdTile, ld, below + (int64_t)i0 * w, w, ni, w);
+  if (t.ti != t.tj) loadTileAsync(Bs, ld, kUpdTile, ld, below + (int64_t)j0 * w, w, nj, w);
+  cp_async_wait_all();
   __syncthreads();
   const int rowBase = (warp >> 1) * 16, colBase = (warp & 1) * 32;
   double acc[2][4][2];
@@ -366,8 +367,9 @@ __global__ void __launch_bounds__(256) solveLumpFwdKernel(DevSolver d, const dou
   double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
   const double* Ld = d.diagL + d.diagLOff[L];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  for (int i = tid; i < w * w; i += 256) Ls[(i / w) * ld + (i % w)] = Ld[i];
+  loadTileAsync(Ls, ld, w, w, Ld, w, w, w);
   for (int i = tid; i < w; i += 256) { x[i] = vL[i]; dinv[i] = 1.0 / Ld[i * w + i]; }
+  cp_async_wait_all();
   __syncthreads();
   if (warp == 0) warpSolveL(Ls, ld, dinv, x, w);
   __syncthreads();
@@ -443,13 +445,14 @@ __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const dou
   __syncthreads();
   if (!isLast) return;
   __threadfence();
-  for (int i = tid; i < w * w; i += 256) Ls[(i / w) * ld + (i % w)] = Ld[i];
+  loadTileAsync(Ls, ld, w, w, Ld, w, w, w);
   for (int i = tid; i < w; i += 256) {
     double s;
     if (nSlices > 1) { s = __ldcg(accL + i); accL[i] = 0.0; } else s = part[i] + part[w + i];
     x[i] = vL[i] - s;
     dinv[i] = 1.0 / Ld[i * w + i];
   }
+  cp_async_wait_all();
   __syncthreads();
   if (tid < 32) warpSolveLt(Ls, ld, dinv, x, w);
   __syncthreads();

@@ -40,6 +40,8 @@ constexpr int kNB = 8;          // column block of the blocked potrf / trsm
 __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double* hess, const int32_t* lumps, int* errFlag) {
   extern __shared__ double sm[];
   __shared__ int bad;
+  __shared__ double dinv8[kNB];
+  __shared__ double dinvAll[128];
   const int L = lumps[blockIdx.x];
   const int w = d.lumpWidth[L];
   const int ld = ldFor(w);
@@ -65,24 +67,34 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
       }
     }
     __syncthreads();
-    // (2) 8x8 diagonal block: unblocked Cholesky by warp 0 (lane i owns row j0+i)
+    // (2) 8x8 diagonal block: Cholesky in registers by warp 0 (lane i < 8 owns row j0+i); one
+    // rsqrt per pivot, columns exchanged with shuffles; reciprocals of the pivots go to dinv8
     if (warp == 0) {
-      for (int j = 0; j < nb; j++) {
-        const double djj = A[(j0 + j) * ld + j0 + j];
-        if (!(djj > 0.0)) { if (lane == 0) bad = 1; break; }
-        const double ljj = sqrt(djj);
-        __syncwarp();
-        if (lane == j) A[(j0 + j) * ld + j0 + j] = ljj;
-        else if (lane > j && lane < nb) A[(j0 + lane) * ld + j0 + j] /= ljj;
-        __syncwarp();
-        if (lane > j && lane < nb) {
-          const double lij = A[(j0 + lane) * ld + j0 + j];
-          for (int k = j + 1; k <= lane; k++) A[(j0 + lane) * ld + j0 + k] -= lij * A[(j0 + k) * ld + j0 + j];
+      double a[kNB];
+#pragma unroll
+      for (int k = 0; k < kNB; k++) a[k] = lane < kNB ? A[(j0 + lane) * ld + j0 + k] : 0.0;
+      bool ok = true;
+#pragma unroll
+      for (int j = 0; j < kNB; j++) {
+        if (j < nb) {
+          const double djj = __shfl_sync(0xffffffffu, a[j], j);
+          if (!(djj > 0.0)) ok = false;
+          const double rs = rsqrt(djj);
+          const double lij = (lane == j) ? djj * rs : a[j] * rs;
+          a[j] = lij;
+          if (lane == j) { dinv8[j] = rs; dinvAll[j0 + j] = rs; }
+#pragma unroll
+          for (int k = j + 1; k < kNB; k++) {
+            const double lkj = __shfl_sync(0xffffffffu, lij, k);
+            if (lane >= k) a[k] = fma(-lij, lkj, a[k]);
+          }
         }
-        __syncwarp();
       }
-      // zero the strict upper part of the diagonal block (it received the symmetric DMMA update)
-      if (lane < nb) for (int k = lane + 1; k < kNB; k++) A[(j0 + lane) * ld + j0 + k] = 0.0;
+      if (!ok && lane == 0) bad = 1;
+      if (lane < nb) {
+#pragma unroll
+        for (int k = 0; k < kNB; k++) A[(j0 + lane) * ld + j0 + k] = k <= lane ? a[k] : 0.0;
+      }
     }
     __syncthreads();
     if (bad) { if (tid == 0) atomicExch(errFlag, 2); return; }
@@ -97,7 +109,7 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
           double s = x[c];
 #pragma unroll
           for (int k = 0; k < c; k++) s = fma(-x[k], A[(j0 + c) * ld + j0 + k], s);
-          x[c] = s / A[(j0 + c) * ld + j0 + c];
+          x[c] = s * dinv8[c];
         }
       }
 #pragma unroll
@@ -122,7 +134,7 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
       double s = (i == c) ? 1.0 : 0.0;
 #pragma unroll
       for (int kk = 0; kk < 32; kk++) if (kk < ii && b0 + kk >= c) s = fma(-A[i * ld + b0 + kk], z[kk], s);
-      z[ii] = s / A[i * ld + i];
+      z[ii] = s * dinvAll[i];
     }
 #pragma unroll
     for (int ii = 0; ii < 32; ii++) if (b0 + ii < bEnd) inv[(int64_t)(b0 + ii) * 32 + (c - b0)] = z[ii];

@@ -114,64 +114,74 @@ __device__ void blockReduceAdd(double (&v)[N], double* out) {
   }
 }
 
-// ---- generic (low-count) grad/Hess kernel: one thread per factor ---------------------------------
-// computeSingleGradHess, Factor.h:543-661
+// ---- generic (low-count) grad/Hess kernel: one warp per factor ------------------------------------
+// computeSingleGradHess, Factor.h:543-661.  Lane 0 evaluates residual and Jacobians into shared
+// memory; the J~^T J / J~^T r products are then spread over the lanes, one tangent column each.
 template <int E, int MAXTOT>
-__global__ void __launch_bounds__(64) gradHessSmallKernel(DevStore st, DevVars V, double* grad, double* hess, int updateCache,
-                                                           int dontRetry, double* costAcc) {
-  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(128) gradHessSmallKernel(DevStore st, DevVars V, double* grad, double* hess, int updateCache,
+                                                            int dontRetry, double* costAcc) {
+  __shared__ double Jsh[4][E * MAXTOT];
+  __shared__ double rsh[4][E + 2];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t k = blockIdx.x * 4ll + warp;
   double acc[1] = {0.0};
   if (k < st.count) {
     const int nv = st.nvars;
     const int32_t* v = st.vars + k * nv;
-    double r[E];
-    double Jbuf[E * MAXTOT];
-    double* J[kMaxVars];
-    int dims[kMaxVars];
-    int o = 0;
-    for (int i = 0; i < nv; i++) {
-      dims[i] = V.tdim[v[i]];
-      J[i] = st.gOff[k * nv + i] < 0 ? nullptr : Jbuf + o;
-      o += E * dims[i];
+    double* Jb = Jsh[warp];
+    double* r = rsh[warp];
+    int dims[kMaxVars], joff[kMaxVars];
+    int tot = 0;
+    for (int i = 0; i < nv; i++) { dims[i] = V.tdim[v[i]]; joff[i] = E * tot; tot += dims[i]; }
+    if (lane == 0) {
+      double* J[kMaxVars];
+      double rl[E];
+      for (int i = 0; i < nv; i++) J[i] = st.gOff[k * nv + i] < 0 ? nullptr : Jb + joff[i];
+      evalSmall(st, V, k, rl, J);
+      double soft, dSoft;
+      loss_jet2(st.loss_a, st.loss_k, squaredError(st, k, rl, E), soft, dSoft);
+      for (int e = 0; e < E; e++) r[e] = rl[e];
+      r[E] = dSoft;
+      acc[0] = 0.5 * soft;
     }
-    evalSmall(st, V, k, r, J);
-    double soft, dSoft;
-    loss_jet2(st.loss_a, st.loss_k, squaredError(st, k, r, E), soft, dSoft);
+    __syncwarp();
+    const double dSoft = r[E];
     const double* L = hasPrecision(st.type) ? st.consts + k * (int64_t)st.cpf : nullptr;
-    for (int i = 0; i < nv; i++) {
+    for (int col = lane; col < tot; col += 32) {
+      int i = 0, a = col;
+      while (a >= dims[i]) { a -= dims[i]; i++; }
       const int64_t gi = st.gOff[k * nv + i];
       if (gi < 0) continue;
       const int di = dims[i];
-      for (int a = 0; a < di; a++) {
-        double adj[E];
-        for (int e = 0; e < E; e++) {
-          double s;
-          if (L) { s = 0; for (int f = 0; f < E; f++) s = fma(L[e * E + f], J[i][f * di + a], s); }
-          else s = J[i][e * di + a];
-          adj[e] = s * dSoft;
-        }
-        double gs = 0;
-        for (int e = 0; e < E; e++) gs = fma(r[e], adj[e], gs);
-        if (gs != 0.0) red_add(grad + gi + a, gs);
-        if (!hess) continue;
-        for (int j = 0; j <= i; j++) {
-          if (st.gOff[k * nv + j] < 0) continue;
-          const int64_t pi = k * st.npairs + i * (i + 1) / 2 + j;
-          const int64_t ho = st.hOff[pi];
-          if (ho < 0) continue;
-          const int sw = st.hStride[pi];
-          const int stride = sw & 0x3fffffff;
-          const bool tr = (sw >> 30) & 1;
-          const int dj = dims[j];
-          for (int b = 0; b < dj; b++) {
-            double s = 0;
-            for (int e = 0; e < E; e++) s = fma(adj[e], J[j][e * dj + b], s);
-            if (s != 0.0) red_add(hess + ho + (tr ? (int64_t)b * stride + a : (int64_t)a * stride + b), s);
-          }
+      const double* Ji = Jb + joff[i];
+      double adj[E];
+      for (int e = 0; e < E; e++) {
+        double s;
+        if (L) { s = 0; for (int f = 0; f < E; f++) s = fma(L[e * E + f], Ji[f * di + a], s); }
+        else s = Ji[e * di + a];
+        adj[e] = s * dSoft;
+      }
+      double gs = 0;
+      for (int e = 0; e < E; e++) gs = fma(r[e], adj[e], gs);
+      if (gs != 0.0) red_add(grad + gi + a, gs);
+      if (!hess) continue;
+      for (int j = 0; j <= i; j++) {
+        if (st.gOff[k * nv + j] < 0) continue;
+        const int64_t pi = k * st.npairs + i * (i + 1) / 2 + j;
+        const int64_t ho = st.hOff[pi];
+        if (ho < 0) continue;
+        const int sw = st.hStride[pi];
+        const int stride = sw & 0x3fffffff;
+        const bool tr = (sw >> 30) & 1;
+        const int dj = dims[j];
+        const double* Jj = Jb + joff[j];
+        for (int b = 0; b < dj; b++) {
+          double s = 0;
+          for (int e = 0; e < E; e++) s = fma(adj[e], Jj[e * dj + b], s);
+          if (s != 0.0) red_add(hess + ho + (tr ? (int64_t)b * stride + a : (int64_t)a * stride + b), s);
         }
       }
     }
-    acc[0] = 0.5 * soft;
   }
   blockReduceAdd<1>(acc, costAcc);
 }
@@ -514,7 +524,7 @@ static inline int gridFor(int64_t n, int bs) { return (int)((n + bs - 1) / bs); 
 void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
                     double* costAcc, cudaStream_t s) {
   if (st.count == 0) return;
-#define SMALL(E, TOT) gradHessSmallKernel<E, TOT><<<gridFor(st.count, 64), 64, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc)
+#define SMALL(E, TOT) gradHessSmallKernel<E, TOT><<<gridFor(st.count, 4), 128, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc)
   switch (st.type) {
     case VB_F_VISUAL:
       if (st.order) {

@@ -364,6 +364,7 @@ constexpr int kSolveSlice = 128; // panel rows per CTA in the solves
 // grid = (row slices, lumps).  Every slice CTA solves the small triangular system redundantly and
 // applies its 128 panel rows; the CTA that finishes last (per-lump counter) publishes x_L, which
 // guarantees every other slice has already read b_L.
+template <bool STAGE>
 __global__ void __launch_bounds__(256) solveLumpFwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps, int useAtomics) {
   extern __shared__ double sm[];
   __shared__ int isLast;
@@ -379,17 +380,19 @@ __global__ void __launch_bounds__(256) solveLumpFwdKernel(DevSolver d, const dou
   double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
   const double* Ld = d.diagL + d.diagLOff[L];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
+  const int rBeg = slice * kSolveSlice, rEnd = min(r, rBeg + kSolveSlice);
+  double* Ps = dinv + w; // [kSolveSlice x w] staged panel rows (STAGE only)
   loadTileAsync(Ls, ld, w, w, Ld, w, w, w);
+  if (STAGE && rEnd > rBeg) loadTileAsync(Ps, w, rEnd - rBeg, w, below + (int64_t)rBeg * w, w, rEnd - rBeg, w);
   for (int i = tid; i < w; i += 256) { x[i] = vL[i]; dinv[i] = 1.0 / Ld[i * w + i]; }
   cp_async_wait_all();
   __syncthreads();
   if (warp == 0) warpSolveL(Ls, ld, dinv, x, w);
   __syncthreads();
-  const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
   const int64_t q0 = d.updPtr[L];
-  const int rEnd = min(r, (slice + 1) * kSolveSlice);
-  for (int row = slice * kSolveSlice + warp * 2; row < rEnd; row += 16) { // two rows per warp pass
-    const double* P0 = below + (int64_t)row * w;
+  for (int row = rBeg + warp * 2; row < rEnd; row += 16) { // two rows per warp pass
+    const double* P0 = STAGE ? Ps + (row - rBeg) * w : below + (int64_t)row * w;
     const bool two = row + 1 < rEnd;
     const double* P1 = two ? P0 + w : P0;
     double s0 = 0, s1 = 0;
@@ -425,11 +428,12 @@ __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const dou
   const int slice = blockIdx.x;
   if (slice >= nSlices) return;
   const int ld = w | 1;
-  double* Ls = sm;
-  double* x = sm + (size_t)w * ld;
-  double* dinv = x + w;
+  double* x = sm;                    // w
+  double* dinv = x + w;              // w
   double* part = dinv + w;           // 2 x w
   double* xb = part + 2 * w;         // kSolveSlice
+  double* Ls = xb + kSolveSlice;     // max(w x ld, kSolveSlice x w): staged panel rows first, then L
+  double* Ps = Ls;
   double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
   double* accL = d.solveAcc + d.camStart[d.lumpFirst[L]];
   const double* Ld = d.diagL + d.diagLOff[L];
@@ -437,13 +441,19 @@ __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const dou
   const int64_t q0 = d.updPtr[L];
   const int tid = threadIdx.x;
   const int rBeg = slice * kSolveSlice, rEnd = min(r, rBeg + kSolveSlice);
+  if (rEnd > rBeg) loadTileAsync(Ps, w, rEnd - rBeg, w, below + (int64_t)rBeg * w, w, rEnd - rBeg, w);
   for (int i = tid; i < rEnd - rBeg; i += 256) xb[i] = vec[d.camVec0 + d.updGlobal[q0 + rBeg + i]];
+  cp_async_wait_all();
   __syncthreads();
   {
     const int half = tid >> 7, c = tid & 127;
-    double s = 0;
-    if (c < w) for (int row = rBeg + half; row < rEnd; row += 2) s = fma(below[(int64_t)row * w + c], xb[row - rBeg], s);
-    if (c < w) part[half * w + c] = s;
+    double s0 = 0, s1 = 0;
+    if (c < w) {
+      int row = half;
+      for (; row + 2 < rEnd - rBeg; row += 4) { s0 = fma(Ps[row * w + c], xb[row], s0); s1 = fma(Ps[(row + 2) * w + c], xb[row + 2], s1); }
+      for (; row < rEnd - rBeg; row += 2) s0 = fma(Ps[row * w + c], xb[row], s0);
+      part[half * w + c] = s0 + s1;
+    }
   }
   __syncthreads();
   if (nSlices > 1 && rEnd > rBeg) for (int c = tid; c < w; c += 256) red_add(accL + c, part[c] + part[w + c]);
@@ -503,14 +513,23 @@ void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, 
   VB_CUDA(cudaGetLastError());
 }
 void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, int useAtomics, cudaStream_t s) {
-  const size_t smem = ((size_t)maxWidth * (maxWidth | 1) + 2 * (size_t)maxWidth) * sizeof(double);
-  ensureSmem((const void*)solveLumpFwdKernel, smem);
   const int slices = std::max(1, (maxBelow + kSolveSlice - 1) / kSolveSlice);
-  solveLumpFwdKernel<<<dim3(slices, nLumps), 256, smem, s>>>(d, hess, vec, lumps, useAtomics);
+  const size_t base = ((size_t)maxWidth * (maxWidth | 1) + 2 * (size_t)maxWidth) * sizeof(double);
+  const size_t staged = base + (size_t)kSolveSlice * maxWidth * sizeof(double);
+  // narrow levels are latency bound: stage the panel slice with cp.async behind the triangular solve;
+  // wide levels are throughput bound: keep the small footprint (2 CTAs per SM)
+  if ((int64_t)slices * nLumps <= 2 * 148 && staged <= 200 * 1024) {
+    ensureSmem((const void*)solveLumpFwdKernel<true>, staged);
+    solveLumpFwdKernel<true><<<dim3(slices, nLumps), 256, staged, s>>>(d, hess, vec, lumps, useAtomics);
+  } else {
+    ensureSmem((const void*)solveLumpFwdKernel<false>, base);
+    solveLumpFwdKernel<false><<<dim3(slices, nLumps), 256, base, s>>>(d, hess, vec, lumps, useAtomics);
+  }
   VB_CUDA(cudaGetLastError());
 }
 void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, cudaStream_t s) {
-  const size_t smem = ((size_t)maxWidth * (maxWidth | 1) + 4 * (size_t)maxWidth + kSolveSlice) * sizeof(double);
+  const size_t tile = std::max((size_t)maxWidth * (maxWidth | 1), (size_t)kSolveSlice * maxWidth);
+  const size_t smem = (tile + 4 * (size_t)maxWidth + kSolveSlice) * sizeof(double);
   ensureSmem((const void*)solveLumpBwdKernel, smem);
   const int slices = std::max(1, (maxBelow + kSolveSlice - 1) / kSolveSlice);
   solveLumpBwdKernel<<<dim3(slices, nLumps), 256, smem, s>>>(d, hess, vec, lumps);

@@ -15,6 +15,7 @@
 #include <stdexcept>
 #include "factors.hpp"
 #include "factors_small.hpp"
+#include "factors_ext.hpp"
 
 namespace orc {
 
@@ -39,6 +40,16 @@ struct Engine {
     switch (st.type) {
       case VB_F_VISUAL:
         return visualFactor(D(0), D(1), D(2), D(3), c, P.tdim[v[3]], r, J);
+      case VB_F_VISUAL_RS:
+        return rsVisualFactor(D(0), D(1), D(2), D(3), P.flags[v[3]], P.tdim[v[3]], D(4), c, st.aux.data(), r, J);
+      case VB_F_INERTIAL_SEC:
+        secondaryInertialFactorCommon(D(0), P.flags[v[0]], P.tdim[v[0]], D(1), D(2), D(3), D(4), D(5), D(6), D(7), D(8),
+                                      st.aux.data() + k * kPreintStride, r, J);
+        return true;
+      case VB_F_INERTIAL_SEC_SPLIT:
+        secondaryInertialFactor(D(0), P.flags[v[0]], P.tdim[v[0]], D(1), D(2), D(3), D(4), D(5), D(6), D(7), D(8), D(9),
+                                st.aux.data() + k * kPreintStride, r, J);
+        return true;
       case VB_F_INERTIAL:
         inertialFactor(D(0), P.flags[v[0]], P.tdim[v[0]], D(1), D(2), D(3), D(4), D(5),
                        st.aux.data() + k * kPreintStride, r, J);

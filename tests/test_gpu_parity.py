@@ -50,7 +50,7 @@ def gpu_dense_hessian(p, o):
     return H
 
 
-@pytest.fixture(scope="module", params=["tiny", "small"])
+@pytest.fixture(scope="module", params=["tiny", "small", "tiny_rs", "small_rs"])
 def pair(request, ctx, oracle):
     s = synth.make_session(**synth.CONFIGS[request.param])
     o = Oracle(oracle, s.graph)
@@ -115,8 +115,9 @@ def test_apply_step_backup_restore(pair):
     assert np.array_equal(p.vars, v0) and np.array_equal(o.vars, v0)
 
 
-def test_lm_iteration_parity(ctx, oracle):
-    s = synth.make_session(**synth.CONFIGS["small"])
+@pytest.mark.parametrize("name", ["small", "small_rs"])
+def test_lm_iteration_parity(ctx, oracle, name):
+    s = synth.make_session(**synth.CONFIGS[name])
     o = Oracle(oracle, s.graph); p = capi.Problem(ctx, s.graph)
     st = G.default_settings(8)
     so, tp, tn = o.optimize(st)
@@ -128,8 +129,9 @@ def test_lm_iteration_parity(ctx, oracle):
     p.close()
 
 
-def test_lm_converges_tiny(ctx, oracle):
-    s = synth.make_session(**synth.CONFIGS["tiny"])
+@pytest.mark.parametrize("name", ["tiny", "tiny_rs"])
+def test_lm_converges_tiny(ctx, oracle, name):
+    s = synth.make_session(**synth.CONFIGS[name])
     o = Oracle(oracle, s.graph); p = capi.Problem(ctx, s.graph)
     st = G.default_settings(40)
     so, _, _ = o.optimize(st); sg = p.optimize(st)
@@ -168,4 +170,20 @@ def test_full_size_properties_c1(ctx):
     t2, d0, d1 = p.lm_iteration_timed(1e-5, apply=False)
     assert c1 < c0 and abs(c0 - d0) <= 1e-12 * c0 and abs(c1 - d1) <= 1e-9 * c1
     assert p.dot(0, 2) < 0  # step (negated) . grad < 0: descent direction
+    p.close()
+
+
+def test_rs_time_shift_out_of_range_is_an_error(ctx):
+    """RollingShutterData::getEstimate throws when the time shift leaves the sampled window
+    (RollingShutterData.cpp:83-91); the CUDA path reports VB_ERR_NUMERIC."""
+    s = synth.make_session(**synth.CONFIGS["tiny_rs"])
+    g = s.graph
+    v = s.ext["v_intr_rgb"][0]
+    keep = g.var_data.copy()
+    g.var_data[g.var_off[v] + 16] = 0.5  # 500 ms time offset
+    p = capi.Problem(ctx, g)
+    g.var_data[:] = keep
+    with pytest.raises(capi.VbError) as e:
+        p.compute_grad_hess()
+    assert e.value.code == 3
     p.close()

@@ -9,9 +9,9 @@ from tests.oracle_lib import Oracle, dptr
 from visual_inertial_bundle_adjustment_b200 import synth, graph as G
 
 
-@pytest.fixture(scope="module")
-def tiny(oracle):
-    s = synth.make_session(**synth.CONFIGS["tiny"])
+@pytest.fixture(scope="module", params=["tiny", "tiny_rs"])
+def tiny(request, oracle):
+    s = synth.make_session(**synth.CONFIGS[request.param])
     return s, Oracle(oracle, s.graph)
 
 

@@ -59,6 +59,7 @@ struct vb_problem {
 #define VB_CATCH                                                  \
   }                                                               \
   catch (const std::bad_alloc&) { g_err = "out of host memory"; return VB_ERR_STATE; } \
+  catch (const std::domain_error& ex) { g_err = ex.what(); return VB_ERR_NUMERIC; }     \
   catch (const std::invalid_argument& ex) { g_err = ex.what(); return VB_ERR_ARG; }     \
   catch (const std::exception& ex) {                              \
     g_err = ex.what();                                            \
@@ -126,11 +127,11 @@ static void buildDeviceProblem(vb_problem& P) {
     if (bad) throw std::runtime_error("scatter map: block missing from the structure");
     d.gOff = P.upload(gOff); d.hOff = P.upload(hOff); d.hStride = P.upload(hStride);
     d.order = nullptr; d.chunkStart = nullptr; d.nChunks = 0;
-    if (hs.type == VB_F_VISUAL && hs.count > 0) {
+    if ((hs.type == VB_F_VISUAL || hs.type == VB_F_VISUAL_RS) && hs.count > 0) {
       if (hs.count >= (1ll << 31)) throw std::runtime_error("visual store too large for 32-bit factor indices");
       std::vector<int32_t> order(hs.count);
       for (int64_t k = 0; k < hs.count; k++) order[k] = (int32_t)k;
-      auto key = [&](int32_t k, int a) { return hs.vars[(int64_t)k * 4 + a]; };
+      auto key = [&](int32_t k, int a) { return hs.vars[(int64_t)k * nv + a]; };
       std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
         if (key(x, 1) != key(y, 1)) return key(x, 1) < key(y, 1);
         if (key(x, 2) != key(y, 2)) return key(x, 2) < key(y, 2);
@@ -313,6 +314,7 @@ static void buildDeviceProblem(vb_problem& P) {
   P.grad = P.alloc<double>(S.order); P.step = P.alloc<double>(S.order); P.gradNew = P.alloc<double>(S.order);
   P.acc = P.alloc<double>(64 + 4 * g.stores.size());
   P.errFlag = P.alloc<int>(1);
+  P.dv.errAcc = P.acc + 32;
   VB_CUDA(cudaMallocHost(&P.accHost, (64 + 4 * g.stores.size()) * sizeof(double)));
   VB_CUDA(cudaMemset(P.hess, 0, S.dataSize * sizeof(double)));
   VB_CUDA(cudaMemset(P.grad, 0, S.order * sizeof(double)));
@@ -465,10 +467,12 @@ static double evalGradHess(vb_problem* p, double* gvec, int with_hess, int updat
   VB_CUDA(cudaMemsetAsync(gvec, 0, p->S.order * sizeof(double), s));
   if (with_hess) VB_CUDA(cudaMemsetAsync(p->hess, 0, p->S.dataSize * sizeof(double), s));
   VB_CUDA(cudaMemsetAsync(p->acc, 0, sizeof(double), s));
+  VB_CUDA(cudaMemsetAsync(p->acc + 32, 0, sizeof(double), s));
   for (const DevStore& st : p->ds) launchGradHess(st, p->dv, gvec, with_hess ? p->hess : nullptr, update_cache, dont_retry, p->acc, s);
   if (!sync) return 0.0;
-  VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, sizeof(double), cudaMemcpyDeviceToHost, s));
+  VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, 64 * sizeof(double), cudaMemcpyDeviceToHost, s));
   syncCheck(p);
+  if (p->accHost[32] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
   return p->accHost[0];
 }
 int vb_eval_grad_hess(vb_problem* p, int with_hess, int update_cache, int dont_retry_failed, double* cost) {
@@ -489,9 +493,11 @@ static double evalCost(vb_problem* p, int comparable, vb_cost_stats* stats) {
   const size_t n = p->ds.size();
   double* acc = p->acc + 64;
   VB_CUDA(cudaMemsetAsync(acc, 0, 4 * n * sizeof(double), s));
+  VB_CUDA(cudaMemsetAsync(p->acc + 32, 0, sizeof(double), s));
   for (size_t i = 0; i < n; i++) launchCost(p->ds[i], p->dv, comparable, acc + 4 * i, s);
-  VB_CUDA(cudaMemcpyAsync(p->accHost + 64, acc, 4 * n * sizeof(double), cudaMemcpyDeviceToHost, s));
+  VB_CUDA(cudaMemcpyAsync(p->accHost + 32, p->acc + 32, (32 + 4 * n) * sizeof(double), cudaMemcpyDeviceToHost, s));
   syncCheck(p);
+  if (p->accHost[32] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
   double tot = 0;
   for (size_t i = 0; i < n; i++) tot += p->accHost[64 + 4 * i];
   if (stats && n) { // Q3: CostStats of the last store only (Factor.h:686-688, Optimizer.cpp:93-95)
@@ -763,7 +769,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   cudaEvent_t* e = p->ev;
   const int64_t n = p->S.order;
   VB_CUDA(cudaEventRecord(e[0], s));
-  evalGradHess(p, p->grad, 1, 1, 0, false);
+  evalGradHess(p, p->grad, 1, 1, 0, false); // also clears the evaluation error word
   VB_CUDA(cudaEventRecord(e[1], s));
   launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, s);
   launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
@@ -785,6 +791,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   if (!apply) VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
   VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, (64 + 4 * ns) * sizeof(double), cudaMemcpyDeviceToHost, s));
   checkNumeric(p);
+  if (p->accHost[32] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
   auto ms = [&](int a, int b) { float f = 0; cudaEventElapsedTime(&f, e[a], e[b]); return (double)f; };
   if (t) {
     t->grad_hess = ms(0, 1); t->damping = ms(1, 2); t->factor_schur = ms(2, 3); t->factor_chol = ms(3, 4);

@@ -2,7 +2,7 @@
 // FactorStore::computeGradHess / computeCost (lib/small_thing/Factor.h:390-417,543-734),
 // VariableStore::applyStep (Variable.h:352-370) and Optimizer::addDamping (Optimizer.cpp:136-146).
 #include "vb_internal.hpp"
-#include "dev_factors_small.cuh"
+#include "dev_factors_ext.cuh"
 
 namespace vb {
 
@@ -42,8 +42,39 @@ __device__ bool evalSmall(const DevStore& st, const DevVars& V, int64_t k, doubl
       }
       return true;
     }
+    case VB_F_VISUAL_RS: {
+      double JX[6], JT[12], JE[12], JC[34], JV[6];
+      const uint32_t cf = V.flags[v[3]];
+      const int status = J ? rs_visual_factor<true>(D(0), D(1), D(2), D(3), cf, D(4), c, st.aux, r, JX, JT, JE, JC, JV)
+                           : rs_visual_factor<false>(D(0), D(1), D(2), D(3), cf, D(4), c, st.aux, r, nullptr, nullptr, nullptr, nullptr, nullptr);
+      if (status == 2) V.errAcc[0] = 1.0;
+      if (status != 0) return false;
+      if (!J) return true;
+      const int cd = V.tdim[v[3]];
+      if (J[0]) for (int i = 0; i < 6; i++) J[0][i] = JX[i];
+      if (J[1]) for (int i = 0; i < 12; i++) J[1][i] = JT[i];
+      if (J[2]) for (int i = 0; i < 12; i++) J[2][i] = JE[i];
+      if (J[3]) {
+        for (int e = 0; e < 2; e++) {
+          int n = 15;
+          for (int j = 0; j < 15; j++) J[3][e * cd + j] = JC[e * 17 + j];
+          if (cf & VB_CAM_EST_READOUT) J[3][e * cd + n++] = JC[e * 17 + 15];
+          if (cf & VB_CAM_EST_TIMEOFFSET) J[3][e * cd + n++] = JC[e * 17 + 16];
+        }
+      }
+      if (J[4]) for (int i = 0; i < 6; i++) J[4][i] = JV[i];
+      return true;
+    }
     case VB_F_INERTIAL:
       inertial_factor(D(0), V.flags[v[0]], V.tdim[v[0]], D(1), D(2), D(3), D(4), D(5), st.aux + k * kPreintStride, r, J);
+      return true;
+    case VB_F_INERTIAL_SEC:
+      secondary_inertial_common(D(0), V.flags[v[0]], V.tdim[v[0]], D(1), D(2), D(3), D(4), D(5), D(6), D(7), D(8),
+                                st.aux + k * kPreintStride, r, J);
+      return true;
+    case VB_F_INERTIAL_SEC_SPLIT:
+      secondary_inertial(D(0), V.flags[v[0]], V.tdim[v[0]], D(1), D(2), D(3), D(4), D(5), D(6), D(7), D(8), D(9),
+                         st.aux + k * kPreintStride, r, J);
       return true;
     case VB_F_RW_IMUCALIB: {
       double d[23];
@@ -186,67 +217,6 @@ __global__ void __launch_bounds__(128) gradHessSmallKernel(DevStore st, DevVars 
   blockReduceAdd<1>(acc, costAcc);
 }
 
-// ---- visual factors v0: one thread per observation, fixed dims (3,6,6,15), registers ---------------
-__global__ void __launch_bounds__(128) gradHessVisualKernel(DevStore st, DevVars V, double* grad, double* hess, int updateCache,
-                                                             int dontRetry, double* costAcc) {
-  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  double acc[1] = {0.0};
-  if (k < st.count && !(dontRetry && st.cache[k] < 0.0)) {
-    const int32_t* v = st.vars + k * 4;
-    double r[2], Jall[2][30]; // columns: X 0-2, T 3-8, E 9-14, C 15-29
-    {
-      double JX[6], JT[12], JE[12], JC[30];
-      const bool ok = visual_factor<true>(V.data + V.off[v[0]], V.data + V.off[v[1]], V.data + V.off[v[2]],
-                                          V.data + V.off[v[3]], st.consts + k * 6, r, JX, JT, JE, JC);
-      if (!ok) {
-        if (updateCache || dontRetry) st.cache[k] = -1.0;
-        goto done;
-      }
-#pragma unroll
-      for (int e = 0; e < 2; e++) {
-#pragma unroll
-        for (int j = 0; j < 3; j++) Jall[e][j] = JX[e * 3 + j];
-#pragma unroll
-        for (int j = 0; j < 6; j++) { Jall[e][3 + j] = JT[e * 6 + j]; Jall[e][9 + j] = JE[e * 6 + j]; }
-#pragma unroll
-        for (int j = 0; j < 15; j++) Jall[e][15 + j] = JC[e * 15 + j];
-      }
-    }
-    double soft, dSoft;
-    loss_jet2(st.loss_a, st.loss_k, r[0] * r[0] + r[1] * r[1], soft, dSoft);
-    acc[0] = 0.5 * soft;
-    if (updateCache) st.cache[k] = acc[0];
-    const int c0[4] = {0, 3, 9, 15}, dd[4] = {3, 6, 6, 15};
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      const int64_t gi = st.gOff[k * 4 + i];
-      if (gi < 0) continue;
-#pragma unroll
-      for (int a = 0; a < dd[i]; a++) {
-        const double a0 = Jall[0][c0[i] + a] * dSoft, a1 = Jall[1][c0[i] + a] * dSoft;
-        red_add(grad + gi + a, r[0] * a0 + r[1] * a1);
-        if (hess) {
-#pragma unroll
-          for (int j = 0; j <= i; j++) {
-            const int64_t ho = st.hOff[k * 10 + i * (i + 1) / 2 + j];
-            if (ho < 0) continue;
-            const int sw = st.hStride[k * 10 + i * (i + 1) / 2 + j];
-            const int stride = sw & 0x3fffffff;
-            const bool tr = (sw >> 30) & 1;
-#pragma unroll
-            for (int b = 0; b < dd[j]; b++) {
-              const double s = a0 * Jall[0][c0[j] + b] + a1 * Jall[1][c0[j] + b];
-              red_add(hess + ho + (tr ? (int64_t)b * stride + a : (int64_t)a * stride + b), s);
-            }
-          }
-        }
-      }
-    }
-  }
-done:
-  blockReduceAdd<1>(acc, costAcc);
-}
-
 // ---- visual factors v1 (K1): one CTA per chunk of <= 128 observations sharing rig pose,
 // extrinsics and intrinsics.  Thread t evaluates observation t (residual + Jacobians in registers),
 // scatters the landmark-side blocks (H_pp, g_p, W_r, W_e, W_c: distinct addresses per landmark)
@@ -254,32 +224,44 @@ done:
 // the scaled residual as a 28th column into shared memory:  M = [ sqrt(rho') J_cam | sqrt(rho') r ].
 // The camera-side Hessian blocks and gradients of the whole chunk are then ONE contraction
 // M^T M (27 x 28, K = 256) on the FP64 tensor pipe, written with one reduction per entry per chunk.
-constexpr int kVisChunk = 128, kVisLd = 36;
+constexpr int kVisChunk = 128;
+template <bool RS>
 __global__ void __launch_bounds__(128) gradHessVisualChunkKernel(DevStore st, DevVars V, double* grad, double* hess, int updateCache,
                                                                   int dontRetry, double* costAcc) {
-  extern __shared__ double M[];          // 256 x 36
-  __shared__ double camv[32];            // pose(7) extr(7) intr(15 used of 17)
+  // camera-side columns: pose 0-5, extrinsics 6-11, intrinsics 12-26 (GS) / 12-28 (RS: + readout, time
+  // offset), RS only: velocity 29-31; then the residual column
+  constexpr int NV = RS ? 5 : 4, NP = NV * (NV + 1) / 2;
+  constexpr int CI = RS ? 17 : 15, NC = 12 + CI + (RS ? 3 : 0), LD = RS ? 44 : 36, NCT = RS ? 5 : 4;
+  extern __shared__ double M[];          // 256 x LD
+  __shared__ double camv[40];            // pose(7) extr(7) intr(17) [vel(3)]
   const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int s0 = st.chunkStart[c], n = st.chunkStart[c + 1] - s0;
   const int f0 = st.order[s0];
+  const int32_t* v0 = st.vars + (int64_t)f0 * NV;
   {
-    const int32_t* v0 = st.vars + (int64_t)f0 * 4;
     if (tid < 7) camv[tid] = V.data[V.off[v0[1]] + tid];
     else if (tid < 14) camv[tid] = V.data[V.off[v0[2]] + tid - 7];
-    else if (tid < 29) camv[tid] = V.data[V.off[v0[3]] + tid - 14];
+    else if (tid < 31) camv[tid] = V.data[V.off[v0[3]] + tid - 14];
+    else if (RS && tid < 34) camv[tid] = V.data[V.off[v0[4]] + tid - 31];
   }
+  const uint32_t camFlags = RS ? V.flags[v0[3]] : 0u;
+  const int camDim = V.tdim[v0[3]];
   __syncthreads();
   double acc[1] = {0.0};
-  double* row0 = M + (2 * tid) * kVisLd;
-  double* row1 = row0 + kVisLd;
+  double* row0 = M + (2 * tid) * LD;
+  double* row1 = row0 + LD;
   bool live = false;
   if (tid < n) {
     const int f = st.order[s0 + tid];
     if (!(dontRetry && st.cache[f] < 0.0)) {
-      double r[2], JX[6], JT[12], JE[12], JC[30];
-      const bool ok = visual_factor<true>(V.data + V.off[st.vars[(int64_t)f * 4]], camv, camv + 7, camv + 14,
-                                          st.consts + (int64_t)f * 6, r, JX, JT, JE, JC);
-      if (!ok) {
+      double r[2], JX[6], JT[12], JE[12], JC[2 * CI], JV[6];
+      const double* X = V.data + V.off[st.vars[(int64_t)f * NV]];
+      const double* cst = st.consts + (int64_t)f * st.cpf;
+      int status;
+      if (RS) status = rs_visual_factor<true>(X, camv, camv + 7, camv + 14, camFlags, camv + 31, cst, st.aux, r, JX, JT, JE, JC, JV);
+      else status = visual_factor<true>(X, camv, camv + 7, camv + 14, cst, r, JX, JT, JE, JC) ? 0 : 1;
+      if (status == 2) V.errAcc[0] = 1.0;
+      if (status != 0) {
         if (updateCache || dontRetry) st.cache[f] = -1.0;
       } else {
         live = true;
@@ -291,12 +273,16 @@ __global__ void __launch_bounds__(128) gradHessVisualChunkKernel(DevStore st, De
 #pragma unroll
         for (int j = 0; j < 6; j++) { row0[j] = sw * JT[j]; row1[j] = sw * JT[6 + j]; row0[6 + j] = sw * JE[j]; row1[6 + j] = sw * JE[6 + j]; }
 #pragma unroll
-        for (int j = 0; j < 15; j++) { row0[12 + j] = sw * JC[j]; row1[12 + j] = sw * JC[15 + j]; }
-        row0[27] = sw * r[0]; row1[27] = sw * r[1];
+        for (int j = 0; j < CI; j++) { row0[12 + j] = sw * JC[j]; row1[12 + j] = sw * JC[CI + j]; }
+        if (RS) {
 #pragma unroll
-        for (int j = 28; j < kVisLd; j++) { row0[j] = 0.0; row1[j] = 0.0; }
+          for (int j = 0; j < 3; j++) { row0[12 + CI + j] = sw * JV[j]; row1[12 + CI + j] = sw * JV[3 + j]; }
+        }
+        row0[NC] = sw * r[0]; row1[NC] = sw * r[1];
+#pragma unroll
+        for (int j = NC + 1; j < LD; j++) { row0[j] = 0.0; row1[j] = 0.0; }
         // landmark side: weighted J_X
-        const int64_t gp = st.gOff[(int64_t)f * 4];
+        const int64_t gp = st.gOff[(int64_t)f * NV];
         if (gp >= 0) {
           double X0[3], X1[3];
 #pragma unroll
@@ -304,7 +290,7 @@ __global__ void __launch_bounds__(128) gradHessVisualChunkKernel(DevStore st, De
 #pragma unroll
           for (int a = 0; a < 3; a++) red_add(grad + gp + a, r[0] * X0[a] + r[1] * X1[a]);
           if (hess) {
-            const int64_t* ho = st.hOff + (int64_t)f * 10;
+            const int64_t* ho = st.hOff + (int64_t)f * NP;
             double* Hpp = hess + ho[0];
 #pragma unroll
             for (int a = 0; a < 3; a++)
@@ -326,10 +312,23 @@ __global__ void __launch_bounds__(128) gradHessVisualChunkKernel(DevStore st, De
             }
             if (ho[6] >= 0) {
               double* W = hess + ho[6];
+              // RS: fixed columns 15/16 map to the variable's tangent layout [15, readout?, time offset?]
+              const int cRead = 15, cOff = (camFlags & VB_CAM_EST_READOUT) ? 16 : 15;
 #pragma unroll
-              for (int s_ = 0; s_ < 15; s_++)
+              for (int s_ = 0; s_ < CI; s_++) {
+                int row = s_;
+                if (RS && s_ == 15) { if (!(camFlags & VB_CAM_EST_READOUT)) continue; row = cRead; }
+                if (RS && s_ == 16) { if (!(camFlags & VB_CAM_EST_TIMEOFFSET)) continue; row = cOff; }
 #pragma unroll
-                for (int a = 0; a < 3; a++) red_add(W + s_ * 3 + a, JC[s_] * X0[a] + JC[15 + s_] * X1[a]);
+                for (int a = 0; a < 3; a++) red_add(W + row * 3 + a, JC[s_] * X0[a] + JC[CI + s_] * X1[a]);
+              }
+            }
+            if (RS && ho[10] >= 0) {
+              double* W = hess + ho[10];
+#pragma unroll
+              for (int s_ = 0; s_ < 3; s_++)
+#pragma unroll
+                for (int a = 0; a < 3; a++) red_add(W + s_ * 3 + a, JV[s_] * X0[a] + JV[3 + s_] * X1[a]);
             }
           }
         }
@@ -338,44 +337,56 @@ __global__ void __launch_bounds__(128) gradHessVisualChunkKernel(DevStore st, De
   }
   if (!live) {
 #pragma unroll
-    for (int j = 0; j < kVisLd; j++) { row0[j] = 0.0; row1[j] = 0.0; }
+    for (int j = 0; j < LD; j++) { row0[j] = 0.0; row1[j] = 0.0; }
   }
   __syncthreads();
-  // M^T M on DMMA: warp = 8-row tile of the output, 4 column tiles
-  double C[4][2];
+  // M^T M on DMMA: warp = 8-row tile of the output, NCT column tiles
+  double C[NCT][2];
 #pragma unroll
-  for (int t = 0; t < 4; t++) C[t][0] = C[t][1] = 0.0;
+  for (int t = 0; t < NCT; t++) C[t][0] = C[t][1] = 0.0;
   {
-    const double* ap = M + (lane & 3) * kVisLd + warp * 8 + (lane >> 2);
-    const double* bp = M + (lane & 3) * kVisLd + (lane >> 2);
+    const double* ap = M + (lane & 3) * LD + warp * 8 + (lane >> 2);
+    const double* bp = M + (lane & 3) * LD + (lane >> 2);
     for (int k = 0; k < 2 * kVisChunk; k += 4) {
-      const double a = ap[k * kVisLd];
+      const double a = ap[k * LD];
 #pragma unroll
-      for (int t = 0; t < 4; t++) dmma(C[t][0], C[t][1], a, bp[k * kVisLd + 8 * t]);
+      for (int t = 0; t < NCT; t++) dmma(C[t][0], C[t][1], a, bp[k * LD + 8 * t]);
     }
   }
-  // epilogue: entry (i, j) of [H_cam | g_cam]; rows/cols 0-5 pose, 6-11 extrinsics, 12-26 intrinsics
+  // epilogue: entry (i, j) of [H_cam | g_cam]
   {
     const int i = warp * 8 + (lane >> 2);
-    if (i < 27) {
-      const int bi = i < 6 ? 0 : (i < 12 ? 1 : 2);
-      const int ai = i - (bi == 0 ? 0 : (bi == 1 ? 6 : 12));
-      const int64_t gi = st.gOff[(int64_t)f0 * 4 + 1 + bi];
-      if (gi >= 0) {
+    // block of a column index and its offset inside the variable's tangent vector (-1: not estimated)
+    auto locate = [&](int col, int& blk, int& a) {
+      if (col < 6) { blk = 0; a = col; }
+      else if (col < 12) { blk = 1; a = col - 6; }
+      else if (col < 12 + CI) {
+        blk = 2; a = col - 12;
+        if (RS && a == 15) a = (camFlags & VB_CAM_EST_READOUT) ? 15 : -1;
+        else if (RS && a == 16) a = (camFlags & VB_CAM_EST_TIMEOFFSET) ? ((camFlags & VB_CAM_EST_READOUT) ? 16 : 15) : -1;
+        if (a >= camDim) a = -1;
+      } else { blk = 3; a = col - 12 - CI; }
+    };
+    if (i < NC) {
+      int bi, ai;
+      locate(i, bi, ai);
+      const int64_t gi = st.gOff[(int64_t)f0 * NV + 1 + bi];
+      if (gi >= 0 && ai >= 0) {
 #pragma unroll
-        for (int t = 0; t < 4; t++)
+        for (int t = 0; t < NCT; t++)
 #pragma unroll
           for (int e = 0; e < 2; e++) {
             const int j = 8 * t + 2 * (lane & 3) + e;
             const double val = C[t][e];
-            if (j == 27) { if (val != 0.0) red_add(grad + gi + ai, val); continue; }
-            if (!hess || j > i || j >= 27) continue;
-            const int bj = j < 6 ? 0 : (j < 12 ? 1 : 2);
-            const int aj = j - (bj == 0 ? 0 : (bj == 1 ? 6 : 12));
+            if (j == NC) { if (val != 0.0) red_add(grad + gi + ai, val); continue; }
+            if (!hess || j > i || j > NC) continue;
+            int bj, aj;
+            locate(j, bj, aj);
+            if (aj < 0) continue;
             const int pi = (bi + 1) * (bi + 2) / 2 + (bj + 1);
-            const int64_t ho = st.hOff[(int64_t)f0 * 10 + pi];
+            const int64_t ho = st.hOff[(int64_t)f0 * NP + pi];
             if (ho < 0) continue;
-            const int sw_ = st.hStride[(int64_t)f0 * 10 + pi];
+            const int sw_ = st.hStride[(int64_t)f0 * NP + pi];
             const int stride = sw_ & 0x3fffffff;
             const bool tr = (sw_ >> 30) & 1;
             red_add(hess + ho + (tr ? (int64_t)aj * stride + ai : (int64_t)ai * stride + aj), val);
@@ -527,16 +538,22 @@ void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* 
 #define SMALL(E, TOT) gradHessSmallKernel<E, TOT><<<gridFor(st.count, 4), 128, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc)
   switch (st.type) {
     case VB_F_VISUAL:
-      if (st.order) {
-        const size_t smem = (size_t)2 * kVisChunk * kVisLd * sizeof(double);
-        static bool attr = false;
-        if (!attr) { VB_CUDA(cudaFuncSetAttribute(gradHessVisualChunkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-        gradHessVisualChunkKernel<<<st.nChunks, 128, smem, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc);
+    case VB_F_VISUAL_RS: {
+      if (!st.order) throw std::runtime_error("visual store without a chunk schedule");
+      const bool rs = st.type == VB_F_VISUAL_RS;
+      const size_t smem = (size_t)2 * kVisChunk * (rs ? 44 : 36) * sizeof(double);
+      if (rs) {
+        VB_CUDA(cudaFuncSetAttribute(gradHessVisualChunkKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gradHessVisualChunkKernel<true><<<st.nChunks, 128, smem, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc);
       } else {
-        gradHessVisualKernel<<<gridFor(st.count, 128), 128, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc);
+        VB_CUDA(cudaFuncSetAttribute(gradHessVisualChunkKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gradHessVisualChunkKernel<false><<<st.nChunks, 128, smem, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc);
       }
       break;
+    }
     case VB_F_INERTIAL: SMALL(9, 43); break;
+    case VB_F_INERTIAL_SEC: SMALL(9, 55); break;
+    case VB_F_INERTIAL_SEC_SPLIT: SMALL(9, 61); break;
     case VB_F_RW_IMUCALIB: SMALL(23, 46); break;
     case VB_F_PRIOR_IMUCALIB: SMALL(23, 23); break;
     case VB_F_RW_CAM: SMALL(17, 34); break;

@@ -49,6 +49,7 @@ struct DevVars {
   const int64_t* vecOff; // permuted scalar offset or -1
   const double* aux;
   double* data;
+  double* errAcc;        // set to 1.0 by a factor kernel on a hard evaluation error (RS time shift out of range)
 };
 
 // device view of the solver structure

@@ -178,7 +178,8 @@ class Session:
 
 
 def make_session(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, seed=42, frame_hz=10.0,
-                 window_s=5.0, outlier_frac=0.02, pixel_sigma=1.0 / 0.7, init_noise=1.0):
+                 window_s=5.0, outlier_frac=0.02, pixel_sigma=1.0 / 0.7, init_noise=1.0, rgb=False, n_imus=1,
+                 rgb_obs_frac=0.35):
     """Aria-Gen1-like session: 2 global-shutter SLAM cameras + IMU 0, every calibration state
     variable in 5 s windows with random-walk and factory-prior factors."""
     rng = np.random.default_rng(seed)
@@ -333,8 +334,15 @@ def make_session(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, seed=42, f
     c_pe = np.concatenate([wgt / sd_ext, se3_inv(T_cb0.reshape(-1, 7))], -1)
     g.add_store(G.FactorStore(G.F_PRIOR_SE3, np.concatenate(v_extr)[:, None], c_pe))
 
+    ext = {}
+    if rgb or n_imus > 1:
+        ext = _extend_session(g, rng, dict(times=times, win=win, n_win=n_win, window_s=window_s, T_bw_gt=T_bw_gt, v_w=v_w,
+                                           X_gt=X_gt, lm=lm, rig=rig, v_pt=v_pt, v_pose=v_pose, v_vel=v_vel, v_g=v_g,
+                                           grav=grav, imu_gt=imu_gt, s=s, pixel_sigma=pixel_sigma, outlier_frac=outlier_frac,
+                                           inflate=inflate, rigs_in_win=rigs_in_win), rgb, n_imus, rgb_obs_frac)
     g.finalize(v_pt)
     s_ = Session()
+    s_.ext = ext
     s_.graph, s_.n_rigs, s_.n_win, s_.n_points, s_.n_obs = g, n_rigs, n_win, P, n_ob
     s_.ids = dict(point=v_pt, pose=v_pose, vel=v_vel, extr=v_extr, intr=v_intr, imu=v_imu, gravity=v_g)
     s_.gt = dict(X=X_gt, T_bw=T_bw_gt, vel=v_w, T_cb=T_cb_gt, cam=cam_gt, imu=imu_gt)
@@ -346,7 +354,227 @@ def make_session(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, seed=42, f
 CONFIGS = {
     "tiny": dict(duration_s=4.0, n_landmarks=60, n_obs=1200, window_s=2.0),
     "small": dict(duration_s=12.0, n_landmarks=800, n_obs=24000),
+    "tiny_rs": dict(duration_s=4.0, n_landmarks=60, n_obs=1200, window_s=2.0, rgb=True, n_imus=2),
+    "small_rs": dict(duration_s=12.0, n_landmarks=800, n_obs=24000, rgb=True, n_imus=2),
     "c1_60s": dict(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000),
+    "c2_5min_rs": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000, rgb=True, n_imus=2),
     "c2_5min": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000),
     "c3_20min": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000),
 }
+
+
+# ---- motion integrals (lib/motion/preintegration/MotionIntegral.cpp:28-160), vectorised, used to
+# build the per-rig rolling-shutter tables that RollingShutterData::compute produces on the host ----
+def so3_log(q):
+    n2 = np.sum(q[..., :3] ** 2, -1)
+    n = np.sqrt(n2)
+    w = q[..., 3]
+    at = np.where(w < 0, np.arctan2(-n, -w), np.arctan2(n, w))
+    f = np.where(n2 < 1e-20, 2.0 / w - (2.0 / 3.0) * n2 / (w ** 3), 2.0 * at / np.where(n == 0, 1.0, n))
+    return f[..., None] * q[..., :3]
+
+
+def rvp_integrate(gyro, accel, dt):
+    om, up = gyro * dt[..., None], accel * dt[..., None]
+    q = quat_from_rotvec(om)
+    th2 = np.sum(om * om, -1); th = np.sqrt(th2); th4 = th2 * th2
+    small = th < 1e-3
+    ths = np.where(small, 1.0, th); th2s = np.where(small, 1.0, th2)
+    m = (1.0 - np.cos(ths)) / th2s
+    c1 = np.where(small, 0.5 - th2 / 24.0 + th4 / 729.0, m)  # F6 = 729 as in MotionIntegral.cpp:82
+    c2 = np.where(small, 1.0 / 6.0 - th2 / 120.0 + th4 / 5040.0, (1.0 - np.sin(ths) / ths) / th2s)
+    c3 = np.where(small, 1.0 / 24.0 - th2 / 729.0 + th4 / 40320.0, (0.5 - m) / th2s)
+    wx = lambda v: np.cross(om, v)
+    dV = up + c1[..., None] * wx(up) + c2[..., None] * wx(wx(up))
+    upd = up * dt[..., None]
+    dP = 0.5 * upd + c2[..., None] * wx(upd) + c3[..., None] * wx(wx(upd))
+    return q, dV, dP
+
+
+def rvp_differentiate(q, dV, dP, dt):
+    om = so3_log(q)
+    th2 = np.sum(om * om, -1); th = np.sqrt(th2)
+    h = 0.5 * np.where(th < 1e-3, 1.0, th)
+    q2 = np.where(th < 1e-3, 1.0 / 12.0 - th2 / (4.0 * 180.0) + th2 * th2 / (16.0 * 1890.0),
+                  (1.0 - h * np.cos(h) / np.sin(h)) / np.where(th < 1e-3, 1.0, th2))
+    ov = np.cross(om, dV)
+    ups = dV - 0.5 * ov + q2[..., None] * np.cross(om, ov)
+    gyro, accel = om / dt[..., None], ups / dt[..., None]
+    _, _, rP = rvp_integrate(gyro, accel, dt)
+    return np.concatenate([gyro, accel, (dP - rP) / dt[..., None]], -1)
+
+
+RS_MAX_SAMPLES = 32
+RS_STRIDE = 1 + RS_MAX_SAMPLES * 11 + (RS_MAX_SAMPLES - 1) * 9
+
+
+def rs_tables(times, grav, half_ms=14):
+    """Per-rig table of RollingShutterData (RollingShutterData.cpp:16-65): mid->t motion integrals at
+    1 ms steps over +-half_ms and their interpolation data, from the closed-form trajectory."""
+    tau = np.arange(-half_ms, half_ms + 1) * 1e-3
+    n = tau.size
+    assert n <= RS_MAX_SAMPLES
+    p0, v0, q0 = _traj(times)
+    t = times[:, None] + tau[None, :]
+    p, v, q = _traj(t.ravel())
+    p, v, q = p.reshape(-1, n, 3), v.reshape(-1, n, 3), q.reshape(-1, n, 4)
+    qbw = quat_conj(q0)[:, None, :]
+    qs = quat_mul(np.broadcast_to(qbw, q.shape), q)
+    dV = quat_rotate(np.broadcast_to(qbw, q.shape), v - v0[:, None] - grav * tau[None, :, None])
+    dP = quat_rotate(np.broadcast_to(qbw, q.shape), p - p0[:, None] - v0[:, None] * tau[None, :, None] - 0.5 * grav * (tau ** 2)[None, :, None])
+    # interp[i] = differentiate(uncombineLeft(s[i+1], s[i]))
+    qa, qc = qs[:, :-1], qs[:, 1:]
+    bq = quat_mul(quat_conj(qa), qc)
+    bdt = np.broadcast_to((tau[1:] - tau[:-1])[None, :], bq.shape[:2])
+    bdV = quat_rotate(quat_conj(qa), dV[:, 1:] - dV[:, :-1])
+    bdP = quat_rotate(quat_conj(qa), dP[:, 1:] - dP[:, :-1] - dV[:, :-1] * bdt[..., None])
+    interp = rvp_differentiate(bq, bdV, bdP, bdt)
+    tab = np.zeros((times.size, RS_STRIDE))
+    tab[:, 0] = n
+    smp = np.concatenate([qs, dV, dP, np.broadcast_to(tau[None, :, None], (times.size, n, 1))], -1)
+    tab[:, 1:1 + n * 11] = smp.reshape(times.size, -1)
+    off = 1 + RS_MAX_SAMPLES * 11
+    tab[:, off:off + (n - 1) * 9] = interp.reshape(times.size, -1)
+    return tab
+
+
+def _synth_preint(T_iw, vel_iw, prev, nxt, dt, grav, eval_point, rng):
+    """Preintegration records (PREINT_STRIDE doubles) consistent with InertialFactor.cpp:23-123 at the
+    given IMU trajectory, plus a fixed information matrix; J(9x23) is a structured stand-in."""
+    nI = prev.size
+    qp, qn = T_iw[prev, :4], T_iw[nxt, :4]
+    preR = quat_mul(qp, quat_conj(qn))
+    dV = quat_rotate(qp, vel_iw[nxt] - vel_iw[prev] - grav * dt[:, None])
+    dP = T_iw[prev, 4:] - quat_rotate(preR, T_iw[nxt, 4:]) - quat_rotate(qp, vel_iw[prev] * dt[:, None] + grav * (0.5 * dt * dt)[:, None])
+    sig = np.array([2e-4] * 3 + [3e-3] * 3 + [2e-4] * 3)
+    noise = rng.normal(0, 1, (nI, 9)) * sig
+    preR = quat_mul(quat_from_rotvec(noise[:, :3]), preR)
+    dV, dP = dV + noise[:, 3:6], dP + noise[:, 6:9]
+    PJ = np.zeros((nI, 9, 23))
+    eye = np.eye(3)
+    PJ[:, 0:3, 0:3] = -dt[:, None, None] * eye
+    PJ[:, 3:6, 3:6] = -dt[:, None, None] * eye
+    PJ[:, 6:9, 3:6] = -(0.5 * dt * dt)[:, None, None] * eye
+    PJ[:, 0:3, 6:9] = 0.3 * dt[:, None, None] * eye
+    PJ[:, 3:6, 9:12] = 9.0 * dt[:, None, None] * eye
+    PJ[:, 6:9, 9:12] = 4.5 * (dt * dt)[:, None, None] * eye
+    PJ[:, :, 12:23] = rng.normal(0, 1, (nI, 9, 11)) * 0.2 * dt[:, None, None]
+    pre = np.zeros((nI, G.PREINT_STRIDE))
+    pre[:, 0:4], pre[:, 4:7], pre[:, 7:10], pre[:, 10] = preR, dV, dP, dt
+    pre[:, 11:218] = PJ.reshape(nI, -1)
+    pre[:, 218:250] = eval_point
+    A = np.eye(9) + 0.05 * rng.normal(0, 1, (9, 9))
+    Lam = np.linalg.inv((A * sig) @ (A * sig).T)
+    return pre, 0.5 * (Lam + Lam.T)
+
+
+def _extend_session(g, rng, L, rgb, n_imus, rgb_obs_frac):
+    """RGB rolling-shutter camera (B2 factors, 17-dim intrinsics with readout time and time offset)
+    and a secondary IMU (B5/B6 inertial factors, body angular velocity variables, omega priors B15/B16,
+    IMU extrinsics with RW + factory prior) — the BASELINE C2/C4 ingredients."""
+    times, win, n_win, grav, s = L["times"], L["win"], L["n_win"], L["grav"], L["s"]
+    T_bw_gt, v_w = L["T_bw_gt"], L["v_w"]
+    n_rigs = times.size
+    inflate, rigs_in_win, window_s = L["inflate"], L["rigs_in_win"], L["window_s"]
+    w0, w1 = np.arange(n_win - 1), np.arange(1, n_win)
+    ext = {}
+    if rgb:
+        H_IMG = 1408.0
+        prm = np.concatenate([[610.0, 704.0, 704.0], 0.5 * SLAM_CAM[3:]])
+        cam_gt = np.zeros((n_win, 17))
+        cam_gt[:, :15] = prm + np.cumsum(rng.normal(0, 1.0, (n_win, 15)) * np.array([0.02] * 3 + [1e-5] * 12), 0)
+        cam_gt[:, 15], cam_gt[:, 16] = 0.016, 0.003
+        T_bc = np.concatenate([quat_from_rotvec(np.array([0.1, 0.0, 0.0])), [0.0, 0.02, 0.01]])
+        T_cb_gt = se3_perturb(np.broadcast_to(se3_inv(T_bc), (n_win, 7)),
+                              np.cumsum(rng.normal(0, 1.0, (n_win, 6)) * np.array([2e-5] * 3 + [5e-5] * 3), 0))
+        pairs = np.unique(np.stack([L["lm"], L["rig"]], -1), axis=0)
+        pairs = pairs[(pairs[:, 1] > 0) & (rng.random(pairs.shape[0]) < 2.0 * rgb_obs_frac)]  # XR_CHECK(rigIndex)
+        lm, rig = pairs[:, 0], pairs[:, 1]
+        dt = np.zeros(lm.size)
+        for _ in range(4):  # rolling shutter: the row fixes the capture time, iterate to the fixed point
+            p, _, q = _traj(times[rig] + dt)
+            Tbw_t = se3_inv(np.concatenate([q, p], -1))
+            pc = se3_act(T_cb_gt[win[rig]], se3_act(Tbw_t, L["X_gt"][lm]))
+            uv, ok = fisheye624_project(pc, cam_gt[win[rig], :15])
+            dt = cam_gt[win[rig], 15] * (uv[:, 1] / H_IMG - 0.5) - cam_gt[win[rig], 16]
+        ok &= (pc[:, 2] > 0.3) & (uv[:, 0] > 0) & (uv[:, 0] < H_IMG) & (uv[:, 1] > 0) & (uv[:, 1] < H_IMG)
+        lm, rig, uv = lm[ok], rig[ok], uv[ok]
+        uv = uv + rng.normal(0, L["pixel_sigma"], uv.shape)
+        outl = rng.random(lm.size) < L["outlier_frac"]
+        uv[outl] += rng.uniform(-30, 30, (int(outl.sum()), 2))
+        uv = uv.astype(np.float32).astype(np.float64)
+        cam0 = cam_gt.copy()
+        cam0[:, :15] += s * rng.normal(0, 1, (n_win, 15)) * np.array([0.3] * 3 + [2e-4] * 6 + [5e-5] * 6)
+        cam0[:, 15] += s * rng.normal(0, 1e-4, n_win)
+        cam0[:, 16] += s * rng.normal(0, 1e-4, n_win)
+        T_cb0 = se3_perturb(T_cb_gt, s * rng.normal(0, 1, (n_win, 6)) * np.array([3e-4] * 3 + [5e-4] * 3))
+        fl = G.CAM_EST_READOUT | G.CAM_EST_TIMEOFFSET | G.CAM_HAS_READOUT
+        v_extr = g.add_vars(G.VAR_SE3, T_cb0, 6)
+        v_intr = g.add_vars(G.VAR_CAM, cam0, 17, flags=fl)
+        o = np.lexsort((rig, lm))
+        lm, rig, uv = lm[o], rig[o], uv[o]
+        n = lm.size
+        vars_ = np.stack([L["v_pt"][lm], L["v_pose"][rig], v_extr[win[rig]], v_intr[win[rig]], L["v_vel"][rig]], -1)
+        c = np.concatenate([uv, np.broadcast_to(np.array([0.7, 0.0, 0.0, 0.7]), (n, 4)), rig[:, None].astype(np.float64),
+                            np.full((n, 1), H_IMG)], -1)
+        aux = np.concatenate([grav, [float(n_rigs)], rs_tables(times, grav).ravel()])
+        g.add_store(G.FactorStore(G.F_VISUAL_RS, vars_, c, loss=(1.0, 3.0), aux=aux))
+        if n_win > 1:
+            d_cam = 1.0 / np.sqrt(np.array([1e-4] * 3 + [1e-10] * 12 + [1e-12, 1e-12]) * window_s * inflate)
+            g.add_store(G.FactorStore(G.F_RW_CAM, np.stack([v_intr[w0], v_intr[w1]], -1), np.broadcast_to(d_cam, (n_win - 1, 17))))
+            d_ext = 1.0 / np.sqrt(np.array([1e-9] * 3 + [1e-8] * 3) * window_s * inflate)
+            g.add_store(G.FactorStore(G.F_RW_SE3, np.stack([v_extr[w0], v_extr[w1]], -1), np.broadcast_to(d_ext, (n_win - 1, 6))))
+        wgt = np.sqrt(rigs_in_win)[:, None]
+        sd_cam = inflate * np.array([1.0] * 3 + [1e-3] * 12 + [1e-4, 1e-4])
+        g.add_store(G.FactorStore(G.F_PRIOR_CAM, v_intr[:, None], np.concatenate([wgt / sd_cam, cam0], -1)))
+        sd_ext = inflate * np.array([1e-3] * 3 + [3e-3] * 3)
+        g.add_store(G.FactorStore(G.F_PRIOR_SE3, v_extr[:, None], np.concatenate([wgt / sd_ext, se3_inv(T_cb0)], -1)))
+        ext.update(rs_obs=n, v_extr_rgb=v_extr, v_intr_rgb=v_intr, rgb_cam_gt=cam_gt)
+    if n_imus > 1:
+        h = 1e-4
+        w_gt = so3_log(quat_mul(quat_conj(_traj(times - h)[2]), _traj(times + h)[2])) / (2 * h)  # body frame
+        v_om = g.add_vars(G.VAR_VEC3, w_gt + s * rng.normal(0, 0.01, w_gt.shape), 3)
+        T_bi = np.concatenate([quat_from_rotvec(np.array([0.0, 0.0, 0.02])), [-0.10, 0.0, 0.01]])
+        T_ib_gt = se3_perturb(np.broadcast_to(se3_inv(T_bi), (n_win, 7)),
+                              np.cumsum(rng.normal(0, 1.0, (n_win, 6)) * np.array([2e-5] * 3 + [5e-5] * 3), 0))
+        T_ib0 = se3_perturb(T_ib_gt, s * rng.normal(0, 1, (n_win, 6)) * np.array([3e-4] * 3 + [5e-4] * 3))
+        imu1_gt = imu_boxplus(np.broadcast_to(factory_imu_calib(), (n_win, 32)), np.cumsum(rng.normal(0, 1.0, (n_win, 23)) * 2e-5, 0))
+        imu1_0 = imu_boxplus(imu1_gt, s * rng.normal(0, 1, (n_win, 23)) * np.array([1e-4] * 3 + [2e-3] * 3 + [2e-4] * 6 + [1e-4] * 9 + [1e-4] * 2))
+        v_iext = g.add_vars(G.VAR_SE3, T_ib0, 6)
+        v_imu1 = g.add_vars(G.VAR_IMUCALIB, imu1_0, 23, flags=IMU_ALL)
+        # GT secondary-IMU trajectory: T_imu_world = T_ib * T_bw ; v = v_b + R_wb (w x t_b_i)
+        T_iw = se3_mul(T_ib_gt[win], T_bw_gt)
+        t_b_i = se3_inv(T_ib_gt[win])[:, 4:]
+        vel_iw = v_w + quat_rotate(quat_conj(T_bw_gt[:, :4]), np.cross(w_gt, t_b_i))
+        prev, nxt = np.arange(n_rigs - 1), np.arange(1, n_rigs)
+        dt = times[nxt] - times[prev]
+        pre, Lam = _synth_preint(T_iw, vel_iw, prev, nxt, dt, grav, imu1_0[win[prev]], rng)
+        same = win[prev] == win[nxt]
+        vp, vv, vg = L["v_pose"], L["v_vel"], L["v_g"]
+        a, b = prev[same], nxt[same]
+        g.add_store(G.FactorStore(G.F_INERTIAL_SEC,
+                                  np.stack([v_imu1[win[a]], vp[a], vv[a], v_om[a], vp[b], vv[b], v_om[b], v_iext[win[a]],
+                                            np.broadcast_to(vg, a.shape)], -1),
+                                  np.broadcast_to(Lam.ravel(), (a.size, 81)), loss=(np.inf, np.inf), aux=pre[same]))
+        a, b = prev[~same], nxt[~same]
+        if a.size:
+            g.add_store(G.FactorStore(G.F_INERTIAL_SEC_SPLIT,
+                                      np.stack([v_imu1[win[a]], vp[a], vv[a], v_om[a], v_iext[win[a]], vp[b], vv[b], v_om[b],
+                                                v_iext[win[b]], np.broadcast_to(vg, a.shape)], -1),
+                                      np.broadcast_to(Lam.ravel(), (a.size, 81)), loss=(np.inf, np.inf), aux=pre[~same]))
+        if n_win > 1:
+            d_imu = 1.0 / np.sqrt(np.array([1e-10] * 3 + [1e-7] * 3 + [1e-10] * 6 + [1e-11] * 9 + [1e-10] * 2) * window_s * inflate)
+            g.add_store(G.FactorStore(G.F_RW_IMUCALIB, np.stack([v_imu1[w0], v_imu1[w1]], -1), np.broadcast_to(d_imu, (n_win - 1, 23))))
+            d_ext = 1.0 / np.sqrt(np.array([1e-9] * 3 + [1e-8] * 3) * window_s * inflate)
+            g.add_store(G.FactorStore(G.F_RW_SE3, np.stack([v_iext[w0], v_iext[w1]], -1), np.broadcast_to(d_ext, (n_win - 1, 6))))
+        wgt = np.sqrt(rigs_in_win)[:, None]
+        sd_imu = inflate * np.array([1e-3] * 3 + [5e-2] * 3 + [2e-3] * 6 + [1e-3] * 9 + [1e-3] * 2)
+        g.add_store(G.FactorStore(G.F_PRIOR_IMUCALIB, v_imu1[:, None], np.concatenate([wgt / sd_imu, imu1_0], -1)))
+        sd_ext = inflate * np.array([1e-3] * 3 + [3e-3] * 3)
+        g.add_store(G.FactorStore(G.F_PRIOR_SE3, v_iext[:, None], np.concatenate([wgt / sd_ext, se3_inv(T_ib0)], -1)))
+        # omega priors (OmegaPriors.cpp:19-31): gyro measurements of IMU 0 and of IMU 1 in its own frame
+        g.add_store(G.FactorStore(G.F_OMEGA_PRIOR, v_om[:, None], w_gt + rng.normal(0, 0.01, w_gt.shape)))
+        meas1 = quat_rotate(T_ib_gt[win, :4], w_gt) + rng.normal(0, 0.01, w_gt.shape)
+        g.add_store(G.FactorStore(G.F_OMEGA_PRIOR_SEC, np.stack([v_om, v_iext[win]], -1), meas1))
+        ext.update(v_omega=v_om, v_imu_extr=v_iext, v_imu1=v_imu1)
+    return ext

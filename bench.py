@@ -21,8 +21,8 @@ sys.path.insert(0, ROOT)
 
 import numpy as np  # noqa: E402
 
-DEFAULT_WORKLOAD = "c2_5min"
-SAMPLE_WORKLOAD = "c1_60s"  # bounded CPU sample: the first 60 s of the same kind of session
+DEFAULT_WORKLOAD = "c2_5min_rs"
+SAMPLE_WORKLOAD = "c1_60s_rs"  # bounded CPU sample: 60 s of the same kind of session
 
 
 def read_peaks():
@@ -75,9 +75,10 @@ def cpu_leg(workload, steps, warmup):
     F1,F3), so the CPU arm is the oracle port (single thread), timed on a bounded sample."""
     from tests.oracle_lib import load_oracle, Oracle
     from visual_inertial_bundle_adjustment_b200 import synth
-    s, _ = make_workload(SAMPLE_WORKLOAD)
+    sample = SAMPLE_WORKLOAD if synth.CONFIGS[workload].get("rgb") else "c1_60s"
+    s, _ = make_workload(sample)
     o = Oracle(load_oracle(), s.graph)
-    scale = synth.CONFIGS[workload]["duration_s"] / synth.CONFIGS[SAMPLE_WORKLOAD]["duration_s"]
+    scale = synth.CONFIGS[workload]["duration_s"] / synth.CONFIGS[sample]["duration_s"]
     ts = []
     for i in range(warmup + steps):
         ms, c0, c1 = o.lm_iteration_timed(1e-5)
@@ -85,7 +86,7 @@ def cpu_leg(workload, steps, warmup):
             ts.append(ms)
     ms = np.mean(np.array(ts), 0)
     return {"value": float(ms[6] * scale), "unit": "ms/iteration", "cores": 1, "kind": "port",
-            "sample": f"oracle port on the {SAMPLE_WORKLOAD} session ({s.n_obs} observations, {s.n_rigs} rigs), "
+            "sample": f"oracle port on the {sample} session ({s.n_obs + s.ext.get("rs_obs", 0)} observations, {s.n_rigs} rigs), "
                       f"x{scale:g} by session duration to {workload}; split g/H {ms[0]:.0f} ms, factor {ms[2]:.0f} ms, "
                       f"solve {ms[3]:.0f} ms, cost {ms[5]:.0f} ms on the sample",
             "sample_ms": float(ms[6]), "scale": scale}
@@ -105,8 +106,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     metric = "ms per LM iteration (Jacobian+Hessian build, Schur+Cholesky solve)"
-    config = {"workload": f"synthetic {a.workload} Aria Gen1-like session per GPU (2 global-shutter SLAM cameras + IMU 0, "
-                          "5 s calibration windows, RW + factory priors)",
+    config = {"workload": f"synthetic {a.workload} Aria Gen1-like session per GPU (2 global-shutter SLAM cameras + RGB rolling-shutter "
+                          "camera with readout/time-offset states, 2 IMUs, 5 s calibration windows, RW + factory priors)",
               "l2": "inputs larger than L2 (Hessian + factor tables exceed 126 MB); no flush needed"}
 
     if a.impl == "reference":
@@ -187,7 +188,7 @@ def main():
     gh_ms = phases["grad_hess"]
     dmma = ctx.dmma_peak_tflops()
     roof_gh = {"bound": "hbm", "achieved": work["visual_bytes"] / (gh_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
-               "traffic": None, "kernel": "gradHessVisualKernel", "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
+               "traffic": None, "kernel": "gradHessVisualChunkKernel<GS>+<RS>", "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
                "algorithmic_bytes": work["visual_bytes"], "ms": gh_ms}
     roof_gh["frac"] = roof_gh["achieved"] / hbm
     fac_ms = phases["factor_schur"] + phases["factor_chol"]
@@ -199,7 +200,7 @@ def main():
     dominant = roof_gh if gh_ms >= fac_ms else roof_fac
     line = {"metric": metric, "value": ms_dev, "unit": "ms/iteration", "n_gpus": a.gpus, "steps": a.steps, "warmup": warmup,
             "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": dict(config, observations=int(s.n_obs), landmarks=int(s.n_points), rigs=int(s.n_rigs),
+            "data": "synthetic", "config": dict(config, observations=int(s.n_obs + s.ext.get("rs_obs", 0)), rs_observations=int(s.ext.get("rs_obs", 0)), landmarks=int(s.n_points), rigs=int(s.n_rigs),
                                                 order=int(p.order), hess_doubles=int(p.data_size), lumps=int(p.num_lumps),
                                                 levels=int(p.num_levels), setup_s=round(setup_s, 2)),
             "phases_ms": {k_: round(v, 4) for k_, v in phases.items()}, "wall_ms_per_step": wall_ms,

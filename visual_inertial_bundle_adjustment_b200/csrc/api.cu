@@ -29,7 +29,7 @@ struct vb_problem {
   int* errFlag = nullptr;
   int64_t* blockVar = nullptr;
   int64_t* diagOff = nullptr; int32_t* diagStride = nullptr; int32_t* diagSize = nullptr;
-  int32_t* levelLumps = nullptr; LevelTask* levelTasks = nullptr; LevelTask* schurTasks = nullptr; int nSchurTasks = 0;
+  int32_t* levelLumps = nullptr; LevelTask* levelTasks = nullptr; SchurTask* schurTasks = nullptr; int nSchurTasks = 0;
   std::vector<int64_t> levelLumpOff, levelTaskOff;
   std::vector<int32_t> levelMaxBelow, levelMaxWidth;
   int64_t varDataLen = 0;
@@ -212,7 +212,7 @@ static void buildDeviceProblem(vb_problem& P) {
     // packed greedily while the union of their row blocks stays <= kGrpMaxRows scalars and the
     // group holds <= kGrpMax landmarks; each group is one dense [union rows] x [3 G] operand
     constexpr int kGrpMax = 32;
-    int kGrpMaxRows = 512;
+    int kGrpMaxRows = 1024;
     if (const char* e = getenv("VB_GRP_MAX_ROWS")) kGrpMaxRows = std::max(64, atoi(e));
     if (S.lmDataSize >= (1ll << 31)) throw std::runtime_error("landmark section exceeds 32-bit offsets");
     std::vector<int32_t> lmOrder;
@@ -224,7 +224,7 @@ static void buildDeviceProblem(vb_problem& P) {
     });
     std::vector<int64_t> grpLmPtr(1, 0), grpBlkPtr(1, 0);
     std::vector<int32_t> grpLm, grpBlkOff, grpRowBlk, grpRowSub, grpRows;
-    std::vector<LevelTask> schurTasks;
+    std::vector<SchurTask> schurTasks;
     {
       std::vector<int32_t> uni, merged, members;
       auto scal = [&](const std::vector<int32_t>& v) { int64_t s = 0; for (int32_t c : v) s += S.camStart[c + 1] - S.camStart[c]; return s; };
@@ -251,8 +251,26 @@ static void buildDeviceProblem(vb_problem& P) {
           }
         }
         grpBlkPtr.push_back(grpBlkPtr.back() + (int64_t)uni.size());
+        // per 64-row tile: which member landmarks have rows in it; a tile pair only needs the landmarks
+        // present in both tiles (the others contribute exact zeros), pairs with none are dropped
         const int nt = (r + 63) / 64;
-        for (int ti = 0; ti < nt; ti++) for (int tj = 0; tj <= ti; tj++) schurTasks.push_back({g, ti, tj});
+        std::vector<uint32_t> tileMask(nt, 0u);
+        {
+          int32_t q = 0;
+          const size_t base = grpBlkOff.size() - uni.size() * kGrpMax;
+          for (size_t b = 0; b < uni.size(); b++) {
+            const int32_t dc = S.camStart[uni[b] + 1] - S.camStart[uni[b]];
+            uint32_t m = 0;
+            for (int l = 0; l < kGrpMax; l++) if (grpBlkOff[base + b * kGrpMax + l] >= 0) m |= 1u << l;
+            for (int32_t s = 0; s < dc; s++) tileMask[(q + s) / 64] |= m;
+            q += dc;
+          }
+        }
+        for (int ti = 0; ti < nt; ti++)
+          for (int tj = 0; tj <= ti; tj++) {
+            const uint32_t m = tileMask[ti] & tileMask[tj];
+            if (m) schurTasks.push_back({g, ti, tj, m});
+          }
         uni.clear(); members.clear();
       };
       for (int32_t p : lmOrder) {

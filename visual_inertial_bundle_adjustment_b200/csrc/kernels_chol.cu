@@ -253,13 +253,15 @@ __global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hes
 // -U U^T, tile by tile on DMMA, scattered with the same relative-index tables as the supernodes
 // (source index nL + g).  One reduction per target entry per group instead of one per landmark.
 constexpr int kGrpMax = 32;
-__global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, double* hess, const LevelTask* tasks) {
+__global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, double* hess, const SchurTask* tasks) {
   extern __shared__ double sm[];
-  const LevelTask t = tasks[blockIdx.x];
-  const int g = t.lump;
+  __shared__ int lmList[kGrpMax];
+  const SchurTask t = tasks[blockIdx.x];
+  const int g = t.group;
   const int r = d.grpRows[g];
-  constexpr int K = 3 * kGrpMax;      // 96
-  const int ld = ldFor(K);            // 100
+  const int cnt = __popc(t.mask);           // landmarks present in both row tiles
+  const int K4 = (3 * cnt + 3) & ~3;
+  constexpr int ld = 3 * kGrpMax + 4;       // 100
   double* As = sm;
   double* Bs = (t.ti == t.tj) ? sm : sm + (size_t)kUpdTile * ld;
   const int i0 = t.ti * kUpdTile, j0 = t.tj * kUpdTile;
@@ -268,30 +270,27 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
   const int64_t q0 = d.updPtr[src];
   const int64_t qg = q0 - d.grpRowBase;
   const int32_t* blkOff = d.grpBlkOff + d.grpBlkPtr[g] * kGrpMax;
-  // gather: element (row a, landmark l) = 3 doubles
-  for (int i = tid; i < kUpdTile * kGrpMax; i += 256) {
-    const int a = i / kGrpMax, l = i % kGrpMax;
-    {
-      const int q = i0 + a;
-      double x0 = 0, x1 = 0, x2 = 0;
+  if (tid < kGrpMax && ((t.mask >> tid) & 1u)) lmList[__popc(t.mask & ((1u << tid) - 1u))] = tid;
+  __syncthreads();
+  // gather: element (row a, k-th present landmark) = 3 doubles, straight from the landmark panels
+  const int per = cnt + 1;                  // one extra slot zero-fills the K padding
+  for (int i = tid; i < kUpdTile * per; i += 256) {
+    const int a = i / per, k = i % per;
+    for (int side = 0; side < 2; side++) {
+      if (side == 1 && t.ti == t.tj) break;
+      const int q = (side == 0 ? i0 : j0) + a;
+      double* o = (side == 0 ? As : Bs) + a * ld + 3 * k;
+      if (k == cnt) { for (int z = 3 * cnt; z < K4; z++) (side == 0 ? As : Bs)[a * ld + z] = 0.0; continue; }
+      const double* w = hess;
+      bool v = false;
       if (q < r) {
-        const int off = blkOff[d.grpRowBlk[qg + q] * kGrpMax + l];
-        if (off >= 0) { const double* w = hess + off + 3 * d.grpRowSub[qg + q]; x0 = w[0]; x1 = w[1]; x2 = w[2]; }
+        const int off = blkOff[d.grpRowBlk[qg + q] * kGrpMax + lmList[k]];
+        if (off >= 0) { w = hess + off + 3 * d.grpRowSub[qg + q]; v = true; }
       }
-      double* o = As + a * ld + 3 * l;
-      o[0] = x0; o[1] = x1; o[2] = x2;
-    }
-    if (t.ti != t.tj) {
-      const int q = j0 + a;
-      double x0 = 0, x1 = 0, x2 = 0;
-      if (q < r) {
-        const int off = blkOff[d.grpRowBlk[qg + q] * kGrpMax + l];
-        if (off >= 0) { const double* w = hess + off + 3 * d.grpRowSub[qg + q]; x0 = w[0]; x1 = w[1]; x2 = w[2]; }
-      }
-      double* o = Bs + a * ld + 3 * l;
-      o[0] = x0; o[1] = x1; o[2] = x2;
+      cp_async8(o, w, v); cp_async8(o + 1, w + 1, v); cp_async8(o + 2, w + 2, v);
     }
   }
+  cp_async_wait_all();
   __syncthreads();
   const int rowBase = (warp >> 1) * 16, colBase = (warp & 1) * 32;
   double acc[2][4][2];
@@ -299,7 +298,7 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
   for (int m = 0; m < 2; m++)
 #pragma unroll
     for (int n = 0; n < 4; n++) acc[m][n][0] = acc[m][n][1] = 0.0;
-  dmmaABt<2, 4>(As, ld, Bs, ld, K, rowBase, colBase, acc);
+  dmmaABt<2, 4>(As, ld, Bs, ld, K4, rowBase, colBase, acc);
   const int32_t* rel = d.rel + d.relPtr[src];
 #pragma unroll
   for (int n = 0; n < 4; n++)
@@ -485,10 +484,10 @@ __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const dou
 static void ensureSmem(const void* fn, size_t bytes) {
   if (bytes > 48 * 1024) VB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
 }
-void launchSchur(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int* errFlag, cudaStream_t s) {
+void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s) {
   launchSchurPrep(d, hess, errFlag, s);
   if (nTasks == 0) return;
-  const size_t smem = (size_t)2 * kUpdTile * ldFor(3 * kGrpMax) * sizeof(double);
+  const size_t smem = (size_t)2 * kUpdTile * (3 * kGrpMax + 4) * sizeof(double);
   ensureSmem((const void*)schurGroupUpdateKernel, smem);
   schurGroupUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks);
   VB_CUDA(cudaGetLastError());

@@ -19,6 +19,7 @@ constexpr int kPreintStride = 250; // R(4) dV(3) dP(3) dt(1) J(9x23) evalPoint(3
 constexpr int kMaxVars = 10;
 
 struct LevelTask { int32_t lump, ti, tj; };
+struct SchurTask { int32_t group, ti, tj; uint32_t mask; }; // mask: member landmarks present in both row tiles
 
 // device view of one factor store (SoA tables + scatter map)
 struct DevStore {
@@ -95,7 +96,7 @@ void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStri
                    double lambda, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
-void launchSchur(const DevSolver& d, double* hess, const struct LevelTask* tasks, int nTasks, int* errFlag, cudaStream_t s);
+void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s);
 void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s);
 void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s);
 void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);

@@ -357,6 +357,7 @@ CONFIGS = {
     "tiny_rs": dict(duration_s=4.0, n_landmarks=60, n_obs=1200, window_s=2.0, rgb=True, n_imus=2),
     "small_rs": dict(duration_s=12.0, n_landmarks=800, n_obs=24000, rgb=True, n_imus=2),
     "c1_60s": dict(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000),
+    "c1_60s_rs": dict(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, rgb=True, n_imus=2),
     "c2_5min_rs": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000, rgb=True, n_imus=2),
     "c2_5min": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000),
     "c3_20min": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000),

@@ -272,22 +272,28 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
   const int32_t* blkOff = d.grpBlkOff + d.grpBlkPtr[g] * kGrpMax;
   if (tid < kGrpMax && ((t.mask >> tid) & 1u)) lmList[__popc(t.mask & ((1u << tid) - 1u))] = tid;
   __syncthreads();
-  // gather: element (row a, k-th present landmark) = 3 doubles, straight from the landmark panels
-  const int per = cnt + 1;                  // one extra slot zero-fills the K padding
-  for (int i = tid; i < kUpdTile * per; i += 256) {
-    const int a = i / per, k = i % per;
+  // gather: 4 threads per tile row; each loads the row's block/sub-row once and walks the present
+  // landmarks, copying their 3-double W rows straight from the landmark panels with cp.async
+  {
+    const int a = tid >> 2, kq = tid & 3;
     for (int side = 0; side < 2; side++) {
       if (side == 1 && t.ti == t.tj) break;
+      double* T = side == 0 ? As : Bs;
       const int q = (side == 0 ? i0 : j0) + a;
-      double* o = (side == 0 ? As : Bs) + a * ld + 3 * k;
-      if (k == cnt) { for (int z = 3 * cnt; z < K4; z++) (side == 0 ? As : Bs)[a * ld + z] = 0.0; continue; }
-      const double* w = hess;
-      bool v = false;
+      double* o = T + a * ld;
+      if (kq == 0) for (int z = 3 * cnt; z < K4; z++) o[z] = 0.0;
       if (q < r) {
-        const int off = blkOff[d.grpRowBlk[qg + q] * kGrpMax + lmList[k]];
-        if (off >= 0) { w = hess + off + 3 * d.grpRowSub[qg + q]; v = true; }
+        const int32_t* bo = blkOff + d.grpRowBlk[qg + q] * kGrpMax;
+        const int sub3 = 3 * d.grpRowSub[qg + q];
+        for (int k = kq; k < cnt; k += 4) {
+          const int off = bo[lmList[k]];
+          const bool v = off >= 0;
+          const double* w = v ? hess + off + sub3 : hess;
+          cp_async8(o + 3 * k, w, v); cp_async8(o + 3 * k + 1, w + 1, v); cp_async8(o + 3 * k + 2, w + 2, v);
+        }
+      } else {
+        for (int k = kq; k < cnt; k += 4) { o[3 * k] = 0.0; o[3 * k + 1] = 0.0; o[3 * k + 2] = 0.0; }
       }
-      cp_async8(o, w, v); cp_async8(o + 1, w + 1, v); cp_async8(o + 2, w + 2, v);
     }
   }
   cp_async_wait_all();

@@ -1,0 +1,19 @@
+"""Export the key raw metrics of every kernel in an .ncu-rep (ncu -i X --page raw --csv) to text."""
+import csv, subprocess, sys
+KEYS = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'launch__registers_per_thread',
+        'launch__shared_mem_per_block_dynamic', 'sm__warps_active.avg.pct_of_peak_sustained_active',
+        'dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
+        'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'smsp__inst_executed.sum',
+        'sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active',
+        'sm__inst_executed_pipe_tensor_subpipe_dmma.avg.pct_of_peak_sustained_active',
+        'SM_C.TriageCompute.smsp__pipe_tensor_subpipe_dmma_cycles_active.avg', 'lts__t_sectors_op_red.sum', 'lts__t_bytes.sum']
+def main(path):
+    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    for r in rows[2:]:
+        print(r[hdr.index('Kernel Name')])
+        for k in KEYS:
+            if k in hdr: print(f"    {k:90s} {r[hdr.index(k)]:>18s} {units[hdr.index(k)]}")
+if __name__ == '__main__':
+    main(sys.argv[1])

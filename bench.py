@@ -5,8 +5,10 @@ Aria-like sessions, the metric of BASELINE.json.  One "step" = one accepted-path
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
 
-N>1 is launched by torchrun (one rank per GPU); the path shards by time window, here as one
-independent session shard per rank (weak scaling, no data-path collective yet: DESIGN.md §multi-GPU).
+N>1 is launched by torchrun (one rank per GPU): every rank holds the SAME session, landmarks (with
+all of their observations) are split over the ranks, and the reduced camera system / camera
+right-hand side / landmark steps are summed over NCCL at the exchange points of the C ABI's
+collective hook.  Total work is fixed as N grows: "scaling": "strong".
 """
 import argparse
 import json
@@ -66,7 +68,7 @@ class ClockSampler(threading.Thread):
 def make_workload(name, rank=0):
     from visual_inertial_bundle_adjustment_b200 import synth
     cfg = dict(synth.CONFIGS[name])
-    cfg["seed"] = 42 + rank
+    cfg["seed"] = 42  # every rank builds the same session (rank is kept for callers that want replicas)
     return synth.make_session(**cfg), cfg
 
 
@@ -106,7 +108,7 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     metric = "ms per LM iteration (Jacobian+Hessian build, Schur+Cholesky solve)"
-    config = {"workload": f"synthetic {a.workload} Aria Gen1-like session per GPU (2 global-shutter SLAM cameras + RGB rolling-shutter "
+    config = {"workload": f"synthetic {a.workload} Aria Gen1-like session, the same session at every N (2 global-shutter SLAM cameras + RGB rolling-shutter "
                           "camera with readout/time-offset states, 2 IMUs, 5 s calibration windows, RW + factory priors)",
               "l2": "inputs larger than L2 (Hessian + factor tables exceed 126 MB); no flush needed"}
 
@@ -116,7 +118,7 @@ def main():
         k, w = min(a.steps, 3), min(a.warmup, 1)
         cb = cpu_leg(a.workload, k, w)
         line = {"impl": "reference", "metric": metric, "value": cb["value"], "unit": "ms/iteration", "n_gpus": a.gpus,
-                "steps": k, "warmup": w, "ms_per_step": cb["value"], "higher_is_better": False, "scaling": "weak",
+                "steps": k, "warmup": w, "ms_per_step": cb["value"], "higher_is_better": False, "scaling": "strong",
                 "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config, "cpu_baseline": cb,
                 "e2e": {"value": cb["value"], "unit": "ms/iteration", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
@@ -131,10 +133,15 @@ def main():
         torch.cuda.set_device(local_rank)
         dist_.init_process_group("nccl")
         dist = dist_
-    ctx = capi.Context(local_rank)
     s, cfg = make_workload(a.workload, rank)
     t0 = time.time()
-    p = capi.Problem(ctx, s.graph)
+    coll = None
+    if world > 1:
+        from visual_inertial_bundle_adjustment_b200 import sharding
+        ctx, p, coll = sharding.make_sharded_problem(s.graph, rank, world, local_rank)
+    else:
+        ctx = capi.Context(local_rank)
+        p = capi.Problem(ctx, s.graph)
     setup_s = time.time() - t0
     lam = 1e-5
 
@@ -174,12 +181,24 @@ def main():
     e2e_ms = (time.perf_counter() - e0) * 1e3 / a.steps
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    shard = p.shard_info()
     if dist is not None:
         import torch
-        tt = torch.tensor([ms_dev, e2e_ms, wall_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        ms_dev, e2e_ms, wall_ms = [float(x) for x in tt.tolist()]
+        names = sorted(phases)
+        tt = torch.tensor([ms_dev, e2e_ms, wall_ms] + [phases[k_] for k_ in names], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)  # every timing is the max over ranks
+        vals = [float(x) for x in tt.tolist()]
+        ms_dev, e2e_ms, wall_ms = vals[:3]
+        phases = dict(zip(names, vals[3:]))
+        own = torch.tensor([shard["owned_landmarks"], shard["owned_visual"]], device="cuda", dtype=torch.float64)
+        gathered = [torch.zeros_like(own) for _ in range(world)]
+        dist.all_gather(gathered, own)
+        shard["per_rank_landmarks"] = [int(x[0]) for x in gathered]
+        shard["per_rank_observations"] = [int(x[1]) for x in gathered]
     if rank != 0:
+        p.close(); ctx.close()
+        if dist is not None:
+            dist.destroy_process_group()
         return 0
 
     peaks, which = read_peaks()
@@ -199,7 +218,7 @@ def main():
     roof_fac["frac"] = roof_fac["achieved"] / dmma if dmma > 0 else None
     dominant = roof_gh if gh_ms >= fac_ms else roof_fac
     line = {"metric": metric, "value": ms_dev, "unit": "ms/iteration", "n_gpus": a.gpus, "steps": a.steps, "warmup": warmup,
-            "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": dict(config, observations=int(s.n_obs + s.ext.get("rs_obs", 0)), rs_observations=int(s.ext.get("rs_obs", 0)), landmarks=int(s.n_points), rigs=int(s.n_rigs),
                                                 order=int(p.order), hess_doubles=int(p.data_size), lumps=int(p.num_lumps),
                                                 levels=int(p.num_levels), setup_s=round(setup_s, 2)),
@@ -207,7 +226,15 @@ def main():
             "roofline": dominant, "roofline_other": roof_fac if dominant is roof_gh else roof_gh,
             "e2e": {"value": e2e_ms, "unit": "ms/iteration", "h2d_bytes_per_step": int(host_vars.nbytes),
                     "d2h_bytes_per_step": int(out_vars.nbytes + 8 * (64 + 4 * len(s.graph.stores)))},
-            "gpu_launches": int(p.launches_per_iteration * a.steps), "clocks": sampler.summary()}
+            "gpu_launches": int(p.launches_per_iteration * a.steps * world), "clocks": sampler.summary()}
+    if world > 1:
+        per_it = coll.calls / max(1, (warmup + 2 * a.steps + 2))
+        line["sharding"] = {"plan": "landmark owners (all observations of a landmark on its owner), small factor stores sliced; "
+                                    "reduced camera system + camera rhs + landmark steps all-reduced over NCCL; Cholesky of the "
+                                    "reduced system replicated", "per_rank_landmarks": shard["per_rank_landmarks"],
+                            "per_rank_observations": shard["per_rank_observations"],
+                            "allreduce_bytes_per_iteration": int(coll.bytes / max(1, (warmup + 2 * a.steps + 2))),
+                            "collectives_per_iteration": round(per_it, 2)}
     if world == 1 and not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_leg(a.workload, 1, 0)
     print(json.dumps(line))

@@ -125,6 +125,9 @@ void vb_settings_default(vb_settings* s);
 
 /* device context (one host thread drives one context; Optimizer is not thread-safe either) */
 int vb_ctx_create(int device, vb_ctx** out);
+/* same, but every kernel and copy is ordered on a caller-owned cudaStream_t (the stream the caller's
+ * NCCL communicator is ordered against), so collectives interleave without host synchronisation */
+int vb_ctx_create_on_stream(int device, void* cuda_stream, vb_ctx** out);
 int vb_ctx_destroy(vb_ctx* ctx);
 
 /* Optimizer::initSolver (Optimizer.cpp:166-207) + FactorStore::registerBlocks (Factor.h:761-785)
@@ -132,6 +135,29 @@ int vb_ctx_destroy(vb_ctx* ctx);
  * (block structure, ordering, supernodes, scatter maps).  Host arrays in `g` may be freed after. */
 int vb_problem_create(vb_ctx* ctx, const vb_graph_desc* g, vb_problem** out);
 int vb_problem_destroy(vb_problem* p);
+
+/* ---- multi-GPU (one process per GPU) ------------------------------------------------
+ * Every rank creates the SAME graph with its own (rank, nranks).  The symbolic phase is identical on
+ * all ranks; each landmark has one owner rank (vb_shard_plan) that evaluates all of its observations,
+ * eliminates it (Schur) and solves for it; the small factor stores are split into equal slices.  The
+ * exchange steps call the hook, which must perform the collective IN PLACE on device memory, ordered
+ * on `cuda_stream` (ncclAllReduce(sum, double) / ncclBroadcast(root 0) in a C++ host, torch.distributed
+ * in the Python mirror), and return 0:
+ *   - factor : sum of the reduced camera system (hess past the landmark section) after the local Schur
+ *   - solve  : sum of the camera right-hand side, broadcast of the camera step, sum of the landmark steps
+ *   - scalars: cost, CostStats, step.grad (one small sum per host decision)
+ * The reference parallelises this path with threads only (Optimizer.cpp:797); there is no
+ * reference interface to cite for the exchange. */
+#define VB_COLL_SUM 0
+#define VB_COLL_BCAST0 1
+typedef int (*vb_collective_fn)(void* user, int op, double* dev_ptr, int64_t count, void* cuda_stream);
+int vb_problem_create_sharded(vb_ctx* ctx, const vb_graph_desc* g, int rank, int nranks,
+                              vb_collective_fn fn, void* user, vb_problem** out);
+/* host-only: owner rank of every landmark (indexed by registration index, n = num_points) */
+int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, int64_t n);
+/* out8 = {rank, nranks, owned landmarks, owned visual factors, reduced-camera-system doubles summed per
+ * factorisation, collective calls so far, collective bytes so far, landmark-section doubles} */
+int vb_shard_info(const vb_problem* p, double* out8);
 
 /* Solver::order(), dataSize() (Optimizer.cpp:339-340,777,783-784) and symbolic-phase outputs */
 /* host-only symbolic statistics for a given supernode width cap / nested-dissection leaf size:

@@ -1,0 +1,84 @@
+"""GPU tests of the N>1 path on ONE GPU: N shards of the same session run as N host threads, each
+with its own context/stream, exchanging through the C ABI's collective hook
+(sharding.ThreadCollective).  Same kernels and exchange points as the torchrun/NCCL path; the gates
+are the single-GPU ones (the only difference between N=1 and N>1 is floating-point summation order)."""
+import numpy as np
+import pytest
+from tests.oracle_lib import Oracle
+from visual_inertial_bundle_adjustment_b200 import synth, capi, sharding, graph as G
+
+pytestmark = pytest.mark.gpu
+
+
+def one_iteration(p, rank):
+    c0 = p.compute_grad_hess()
+    p.add_damping(1e-5)
+    p.step_from_grad()
+    p.factor()
+    p.solve(0)
+    md = 0.5 * p.dot(0, 2)
+    step = p.step
+    p.scale(0, -1.0)
+    p.backup_variables()
+    ratios = p.apply_step(0)
+    c1, stats = p.compute_cost(True)
+    v = p.vars
+    return dict(c0=c0, md=md, step=step, ratios=ratios, c1=c1, stats=stats, vars=v, info=p.shard_info())
+
+
+@pytest.mark.parametrize("name,nranks", [("small", 2), ("small_rs", 2), ("small_rs", 3), ("tiny_rs", 4)])
+def test_sharded_iteration_matches_single(name, nranks):
+    s = synth.make_session(**synth.CONFIGS[name])
+    ctx = capi.Context(0)
+    p = capi.Problem(ctx, s.graph)
+    ref = one_iteration(p, 0)
+    p.close(); ctx.close()
+    outs = sharding.run_threaded(s.graph, nranks, one_iteration)
+    owner = capi.shard_plan(s.graph, nranks)
+    n_vis = sum(st.count for st in s.graph.stores if st.type in (G.F_VISUAL, G.F_VISUAL_RS))
+    assert sum(o["info"]["owned_landmarks"] for o in outs) == s.n_points
+    assert sum(o["info"]["owned_visual"] for o in outs) == n_vis
+    for r, o in enumerate(outs):
+        assert o["info"]["owned_landmarks"] == np.count_nonzero(owner == r)
+        assert abs(o["c0"] - ref["c0"]) <= 1e-12 * abs(ref["c0"])
+        assert abs(o["md"] - ref["md"]) <= 1e-8 * abs(ref["md"])
+        assert np.abs(o["step"] - ref["step"]).max() <= 1e-7 * np.abs(ref["step"]).max()
+        assert abs(o["c1"] - ref["c1"]) <= 1e-9 * abs(ref["c1"])
+        assert o["stats"] == ref["stats"]
+        assert np.abs(o["vars"] - ref["vars"]).max() <= 1e-7
+        assert np.allclose(o["ratios"], ref["ratios"], rtol=1e-6)
+        # every rank holds the same bits after the exchange
+        assert np.array_equal(o["step"], outs[0]["step"]) and np.array_equal(o["vars"], outs[0]["vars"])
+
+
+def test_sharded_optimize_matches_oracle(oracle):
+    """whole LM run on 2 shards: same iteration count, final cost rel 1e-9, final state 1e-6"""
+    s = synth.make_session(**synth.CONFIGS["small_rs"])
+    st = G.default_settings(8)
+    o = Oracle(oracle, s.graph)
+    so, _, _ = o.optimize(st)
+
+    def run(p, rank):
+        summ = p.optimize(st)
+        return summ.num_iterations, summ.final_cost, p.vars
+    outs = sharding.run_threaded(s.graph, 2, run)
+    for it, fc, v in outs:
+        assert it == so.num_iterations
+        assert abs(fc - so.final_cost) <= 1e-9 * abs(so.final_cost)
+        assert np.abs(v - o.vars).max() <= 1e-6
+    assert np.array_equal(outs[0][2], outs[1][2])
+
+
+def test_sharded_timed_iteration():
+    s = synth.make_session(**synth.CONFIGS["small"])
+    ctx = capi.Context(0)
+    p = capi.Problem(ctx, s.graph)
+    _, c0, c1 = p.lm_iteration_timed(1e-5)
+    p.close(); ctx.close()
+
+    def run(p, rank):
+        t, a, b = p.lm_iteration_timed(1e-5)
+        return a, b, p.shard_info()["coll_calls"]
+    for a, b, calls in sharding.run_threaded(s.graph, 2, run):
+        assert abs(a - c0) <= 1e-12 * abs(c0) and abs(b - c1) <= 1e-9 * abs(c1)
+        assert calls == 5  # reduced system, camera rhs, camera step broadcast, landmark steps, scalars

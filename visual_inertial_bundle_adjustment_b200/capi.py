@@ -23,7 +23,11 @@ EXPORTS = [
     "vb_optimize", "vb_lm_iteration_timed", "vb_download_vars", "vb_upload_vars", "vb_download_grad",
     "vb_download_step", "vb_download_hess", "vb_upload_hess", "vb_upload_grad", "vb_download_factor_cache",
     "vb_upload_store_aux", "vb_upload_store_consts", "vb_measure_dmma_peak",
+    "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info",
 ]
+# int fn(void* user, int op, double* dev_ptr, int64_t count, void* cuda_stream)  (include/viba_b200.h)
+COLLECTIVE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p)
+COLL_SUM, COLL_BCAST0 = 0, 1
 
 _lib = None
 
@@ -42,6 +46,11 @@ def load():
         getattr(lib, f).argtypes = [C.c_void_p]
     lib.vb_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
     lib.vb_ctx_destroy.argtypes = [C.c_void_p]
+    lib.vb_ctx_create_on_stream.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.vb_problem_create_sharded.argtypes = [C.c_void_p, C.POINTER(G.vb_graph_desc), C.c_int, C.c_int, COLLECTIVE_FN,
+                                              C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.vb_shard_plan.argtypes = [C.POINTER(G.vb_graph_desc), C.c_int, C.POINTER(C.c_int32), C.c_int64]
+    lib.vb_shard_info.argtypes = [C.c_void_p, _dp]
     lib.vb_problem_create.argtypes = [C.c_void_p, C.POINTER(G.vb_graph_desc), C.POINTER(C.c_void_p)]
     lib.vb_problem_destroy.argtypes = [C.c_void_p]
     lib.vb_get_param_start.argtypes = [C.c_void_p, _ip, C.c_int64]
@@ -109,11 +118,26 @@ def symbolic_stats(graph, max_lump_width=0, nd_leaf_blocks=600):
     return dict(zip(["order", "data_size", "lumps", "levels", "max_lump_rows", "chol_flops", "schur_flops", "widest_level"], out))
 
 
+def shard_plan(graph, nranks):
+    """Host-only: owner rank of every landmark (registration index) for an nranks-way split."""
+    lib = load()
+    desc = graph.desc()
+    out = np.zeros(graph.num_points, np.int32)
+    _ck(lib, lib.vb_shard_plan(C.byref(desc), nranks, out.ctypes.data_as(C.POINTER(C.c_int32)), out.size))
+    return out
+
+
 class Context:
-    def __init__(self, device=0):
+    def __init__(self, device=0, stream=None):
+        """`stream`: a raw cudaStream_t handle (int) every kernel is ordered on (sharded runs pass
+        the stream their collectives are ordered against); default is a private stream."""
         self.lib = load()
         self.h = C.c_void_p()
-        _ck(self.lib, self.lib.vb_ctx_create(device, C.byref(self.h)))
+        self.device = device
+        if stream is None:
+            _ck(self.lib, self.lib.vb_ctx_create(device, C.byref(self.h)))
+        else:
+            _ck(self.lib, self.lib.vb_ctx_create_on_stream(device, C.c_void_p(stream), C.byref(self.h)))
 
     def dmma_peak_tflops(self):
         t = C.c_double()
@@ -130,11 +154,27 @@ class Problem:
     """Thin object wrapper over vb_problem; method names follow small_thing::Optimizer
     (lib/small_thing/Optimizer.h:115-335) where one exists."""
 
-    def __init__(self, ctx, graph):
+    def __init__(self, ctx, graph, rank=0, nranks=1, collective=None):
+        """`collective(op, dev_ptr, count, stream) -> None` performs the in-place exchange of a sharded
+        problem (sharding.TorchCollective for torch.distributed/NCCL)."""
         self.ctx, self.lib, self.g = ctx, ctx.lib, graph
         self.h = C.c_void_p()
         desc = graph.desc()
-        _ck(self.lib, self.lib.vb_problem_create(ctx.h, C.byref(desc), C.byref(self.h)))
+        self.rank, self.nranks = rank, nranks
+        if nranks == 1:
+            _ck(self.lib, self.lib.vb_problem_create(ctx.h, C.byref(desc), C.byref(self.h)))
+        else:
+            self._coll_error = None
+
+            def hook(user, op, ptr, count, stream):
+                try:
+                    collective(op, ptr, count, stream)
+                    return 0
+                except BaseException as ex:  # never let an exception cross the C ABI
+                    self._coll_error = ex
+                    return 1
+            self._hook = COLLECTIVE_FN(hook)  # keep alive as long as the problem
+            _ck(self.lib, self.lib.vb_problem_create_sharded(ctx.h, C.byref(desc), rank, nranks, self._hook, None, C.byref(self.h)))
         self.order = self.lib.vb_order(self.h)
         self.data_size = self.lib.vb_data_size(self.h)
         self.num_blocks = self.lib.vb_num_blocks(self.h)
@@ -172,6 +212,12 @@ class Problem:
         o, s, t = C.c_int64(), C.c_int64(), C.c_int32()
         _ck(self.lib, self.lib.vb_block_offset(self.h, i, j, C.byref(o), C.byref(s), C.byref(t)))
         return o.value, s.value, t.value
+
+    def shard_info(self):
+        out = np.zeros(8)
+        _ck(self.lib, self.lib.vb_shard_info(self.h, _d(out)))
+        return dict(zip(["rank", "nranks", "owned_landmarks", "owned_visual", "reduced_doubles", "coll_calls",
+                         "coll_bytes", "landmark_doubles"], out))
 
     def work(self):
         a, b, c = C.c_double(), C.c_double(), C.c_double()

@@ -14,6 +14,7 @@ static thread_local std::string g_err;
 struct vb_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
+  bool ownsStream = true;
 };
 
 struct vb_problem {
@@ -34,6 +35,12 @@ struct vb_problem {
   std::vector<int32_t> levelMaxBelow, levelMaxWidth;
   int64_t varDataLen = 0;
   double visualBytes = 0;
+  // shard state (vb_problem_create_sharded): this rank evaluates `owned` factors / landmarks and the
+  // collective hook sums the reduced camera system over ranks
+  int rank = 0, nranks = 1;
+  vb_collective_fn coll = nullptr; void* collUser = nullptr;
+  bool partial[3] = {false, false, true}; // step, gradNew, grad: holds only this rank's contributions
+  int64_t ownedLandmarks = 0, ownedVisual = 0, collCalls = 0; double collBytes = 0;
   cudaEvent_t ev[10];
 
   template <typename T>
@@ -67,6 +74,39 @@ struct vb_problem {
   }                                                               \
   return VB_OK;
 
+constexpr int kAccErrSlot = 63;
+// landmarks that have camera-side rows, sorted by (first, last) camera position: the packing order of
+// the Schur groups and the axis the shard plan cuts
+static std::vector<int32_t> landmarkOrder(const Symbolic& S) {
+  std::vector<int32_t> lmOrder;
+  for (int64_t p = 0; p < S.nP; p++) if (S.lmRowPtr[p + 1] > S.lmRowPtr[p]) lmOrder.push_back((int32_t)p);
+  std::sort(lmOrder.begin(), lmOrder.end(), [&](int32_t x, int32_t y) {
+    const int32_t fx = S.lmRowCam[S.lmRowPtr[x]], fy = S.lmRowCam[S.lmRowPtr[y]];
+    const int32_t lx = S.lmRowCam[S.lmRowPtr[x + 1] - 1], ly = S.lmRowCam[S.lmRowPtr[y + 1] - 1];
+    return fx != fy ? fx < fy : (lx != ly ? lx < ly : x < y);
+  });
+  return lmOrder;
+}
+// Shard plan: every landmark has one owning rank, which evaluates ALL of its
+// observations and eliminates it; the owner ranges are contiguous pieces of landmarkOrder() balanced
+// by a per-landmark cost m^2 + 300 m (m = camera-side rows: Schur flops + evaluation work).
+static std::vector<int32_t> planOwners(const Symbolic& S, int nranks) {
+  std::vector<int32_t> owner(S.nP, 0);
+  if (nranks <= 1) return owner;
+  const std::vector<int32_t> lmOrder = landmarkOrder(S);
+  auto weight = [&](int32_t p) { const double m = (double)((S.lmOff[p + 1] - S.lmOff[p]) / 3 - 3); return m * m + 300.0 * m; };
+  double total = 0;
+  for (int32_t p : lmOrder) total += weight(p);
+  double run = 0;
+  for (int32_t p : lmOrder) {
+    const double w = weight(p);
+    owner[p] = (int32_t)std::min<double>(nranks - 1, std::floor((run + 0.5 * w) / std::max(total, 1.0) * nranks));
+    run += w;
+  }
+  for (int64_t p = 0; p < S.nP; p++) if (S.lmRowPtr[p + 1] == S.lmRowPtr[p]) owner[p] = (int32_t)(p % nranks);
+  return owner;
+}
+
 static void buildDeviceProblem(vb_problem& P) {
   const HostGraph& g = P.g;
   const Symbolic& S = P.S;
@@ -92,6 +132,9 @@ static void buildDeviceProblem(vb_problem& P) {
     }
     P.diagOff = P.upload(off); P.diagStride = P.upload(st); P.diagSize = P.upload(sz);
   }
+  const std::vector<int32_t> owner = planOwners(S, P.nranks);
+  const bool sharded = P.nranks > 1;
+  auto ownerOfVar = [&](int32_t v) { const int64_t ii = g.index[v]; return ii < 0 ? 0 : (ii < S.nP ? owner[S.pos[ii]] : 0); };
   // factor stores + scatter maps
   P.ds.resize(g.stores.size());
   for (size_t s = 0; s < g.stores.size(); s++) {
@@ -127,10 +170,17 @@ static void buildDeviceProblem(vb_problem& P) {
     if (bad) throw std::runtime_error("scatter map: block missing from the structure");
     d.gOff = P.upload(gOff); d.hOff = P.upload(hOff); d.hStride = P.upload(hStride);
     d.order = nullptr; d.chunkStart = nullptr; d.nChunks = 0;
+    // shard view of a small store: an equal contiguous slice per rank
+    d.kBegin = hs.count * P.rank / P.nranks; d.nActive = hs.count * (P.rank + 1) / P.nranks - d.kBegin; d.active = nullptr;
     if ((hs.type == VB_F_VISUAL || hs.type == VB_F_VISUAL_RS) && hs.count > 0) {
       if (hs.count >= (1ll << 31)) throw std::runtime_error("visual store too large for 32-bit factor indices");
-      std::vector<int32_t> order(hs.count);
-      for (int64_t k = 0; k < hs.count; k++) order[k] = (int32_t)k;
+      std::vector<int32_t> order;
+      order.reserve(hs.count / P.nranks + 16);
+      for (int64_t k = 0; k < hs.count; k++) if (!sharded || ownerOfVar(hs.vars[k * nv]) == P.rank) order.push_back((int32_t)k);
+      const int64_t nOwn = (int64_t)order.size();
+      d.kBegin = 0; d.nActive = nOwn;
+      if (sharded) d.active = P.upload(order); // ascending factor index: the cost kernel's order
+      P.ownedVisual += nOwn;
       auto key = [&](int32_t k, int a) { return hs.vars[(int64_t)k * nv + a]; };
       std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
         if (key(x, 1) != key(y, 1)) return key(x, 1) < key(y, 1);
@@ -139,15 +189,15 @@ static void buildDeviceProblem(vb_problem& P) {
       });
       std::vector<int32_t> chunkStart;
       int64_t groupStart = 0;
-      for (int64_t i = 0; i <= hs.count; i++) {
-        const bool boundary = i == hs.count || (i > 0 && (key(order[i], 1) != key(order[i - 1], 1) ||
+      for (int64_t i = 0; i <= nOwn; i++) {
+        const bool boundary = i == nOwn || (i > 0 && (key(order[i], 1) != key(order[i - 1], 1) ||
                               key(order[i], 2) != key(order[i - 1], 2) || key(order[i], 3) != key(order[i - 1], 3)));
         if (boundary || i - groupStart == 128) {
           if (i > groupStart) chunkStart.push_back((int32_t)groupStart);
           groupStart = i;
         }
       }
-      chunkStart.push_back((int32_t)hs.count);
+      chunkStart.push_back((int32_t)nOwn);
       d.nChunks = (int32_t)chunkStart.size() - 1;
       d.order = P.upload(order); d.chunkStart = P.upload(chunkStart);
     }
@@ -215,13 +265,16 @@ static void buildDeviceProblem(vb_problem& P) {
     int kGrpMaxRows = 1024;
     if (const char* e = getenv("VB_GRP_MAX_ROWS")) kGrpMaxRows = std::max(64, atoi(e));
     if (S.lmDataSize >= (1ll << 31)) throw std::runtime_error("landmark section exceeds 32-bit offsets");
-    std::vector<int32_t> lmOrder;
-    for (int64_t p = 0; p < S.nP; p++) if (S.lmRowPtr[p + 1] > S.lmRowPtr[p]) lmOrder.push_back((int32_t)p);
-    std::sort(lmOrder.begin(), lmOrder.end(), [&](int32_t x, int32_t y) {
-      const int32_t fx = S.lmRowCam[S.lmRowPtr[x]], fy = S.lmRowCam[S.lmRowPtr[y]];
-      const int32_t lx = S.lmRowCam[S.lmRowPtr[x + 1] - 1], ly = S.lmRowCam[S.lmRowPtr[y + 1] - 1];
-      return fx != fy ? fx < fy : (lx != ly ? lx < ly : x < y);
-    });
+    std::vector<int32_t> lmOrder = landmarkOrder(S);
+    d.lmActive = nullptr; d.nLmActive = S.nP;
+    if (sharded) { // keep this rank's landmarks only
+      lmOrder.erase(std::remove_if(lmOrder.begin(), lmOrder.end(), [&](int32_t p) { return owner[p] != P.rank; }), lmOrder.end());
+      std::vector<int32_t> mine;
+      for (int64_t p = 0; p < S.nP; p++) if (owner[p] == P.rank) mine.push_back((int32_t)p);
+      d.nLmActive = (int64_t)mine.size();
+      d.lmActive = P.upload(mine);
+    }
+    P.ownedLandmarks = d.nLmActive;
     std::vector<int64_t> grpLmPtr(1, 0), grpBlkPtr(1, 0);
     std::vector<int32_t> grpLm, grpBlkOff, grpRowBlk, grpRowSub, grpRows;
     std::vector<SchurTask> schurTasks;
@@ -332,7 +385,7 @@ static void buildDeviceProblem(vb_problem& P) {
   P.grad = P.alloc<double>(S.order); P.step = P.alloc<double>(S.order); P.gradNew = P.alloc<double>(S.order);
   P.acc = P.alloc<double>(64 + 4 * g.stores.size());
   P.errFlag = P.alloc<int>(1);
-  P.dv.errAcc = P.acc + 32;
+  P.dv.errAcc = P.acc + kAccErrSlot;
   VB_CUDA(cudaMallocHost(&P.accHost, (64 + 4 * g.stores.size()) * sizeof(double)));
   VB_CUDA(cudaMemset(P.hess, 0, S.dataSize * sizeof(double)));
   VB_CUDA(cudaMemset(P.grad, 0, S.order * sizeof(double)));
@@ -342,6 +395,16 @@ static void buildDeviceProblem(vb_problem& P) {
   for (auto& e : P.ev) VB_CUDA(cudaEventCreate(&e));
 }
 
+// scalar accumulator slots in p->acc: the reducible ones are contiguous so that a sharded run sums
+// them over ranks with one collective.  [16,20) applyStep ratio stats (identical on every rank).
+constexpr int kAccDot = 61, kAccCost = 62, kAccErr = 63, kAccStores = 64;
+// collective hook: in-place sum over ranks / broadcast from rank 0, ordered on the problem's stream
+static void collective(vb_problem* p, int op, double* ptr, int64_t n) {
+  if (p->nranks <= 1 || n <= 0) return;
+  if (!p->coll) throw std::runtime_error("sharded problem without a collective hook");
+  if (p->coll(p->collUser, op, ptr, n, (void*)p->ctx->stream) != 0) throw std::runtime_error("collective hook failed");
+  p->collCalls++; p->collBytes += 8.0 * n;
+}
 static double* vecOf(vb_problem* p, int which) { return which == 0 ? p->step : which == 1 ? p->gradNew : p->grad; }
 static void requireProblem(const vb_problem* p) { if (!p) throw std::invalid_argument("null problem"); }
 static void syncCheck(vb_problem* p) { VB_CUDA(cudaStreamSynchronize(p->ctx->stream)); }
@@ -378,19 +441,34 @@ int vb_ctx_create(int device, vb_ctx** out) {
   *out = c;
   VB_CATCH
 }
+int vb_ctx_create_on_stream(int device, void* cuda_stream, vb_ctx** out) {
+  const int rc = vb_ctx_create(device, out);
+  if (rc != VB_OK) return rc;
+  cudaStreamDestroy((*out)->stream);
+  (*out)->stream = (cudaStream_t)cuda_stream; // caller-owned (e.g. the stream its NCCL communicator orders against)
+  (*out)->ownsStream = false;
+  return VB_OK;
+}
 int vb_ctx_destroy(vb_ctx* ctx) {
   if (!ctx) return VB_OK;
-  cudaStreamDestroy(ctx->stream);
+  if (ctx->ownsStream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return VB_OK;
 }
 
 int vb_problem_create(vb_ctx* ctx, const vb_graph_desc* g, vb_problem** out) {
+  return vb_problem_create_sharded(ctx, g, 0, 1, nullptr, nullptr, out);
+}
+int vb_problem_create_sharded(vb_ctx* ctx, const vb_graph_desc* g, int rank, int nranks, vb_collective_fn fn, void* user, vb_problem** out) {
   VB_TRY
   if (!ctx || !g || !out) throw std::invalid_argument("null argument");
+  if (nranks < 1 || rank < 0 || rank >= nranks) throw std::invalid_argument("rank / nranks out of range");
+  if (nranks > 1 && !fn) throw std::invalid_argument("a sharded problem needs a collective hook");
   VB_CUDA(cudaSetDevice(ctx->device));
   std::unique_ptr<vb_problem> P(new vb_problem());
   P->ctx = ctx;
+  P->rank = rank; P->nranks = nranks; P->coll = fn; P->collUser = user;
+  P->partial[2] = nranks > 1;
   P->g.load(g);
   SymbolicOptions opt;
   if (const char* e = getenv("VB_MAX_LUMP_WIDTH")) opt.maxLumpWidth = std::max(8, std::min(128, atoi(e)));
@@ -401,6 +479,31 @@ int vb_problem_create(vb_ctx* ctx, const vb_graph_desc* g, vb_problem** out) {
   VB_CATCH
 }
 int vb_problem_destroy(vb_problem* p) { delete p; return VB_OK; }
+
+// host-only shard plan: owner rank of every landmark (registration index) for an nranks-way split
+int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, int64_t n) {
+  VB_TRY
+  if (!g || !landmark_owner || nranks < 1) throw std::invalid_argument("bad argument");
+  HostGraph hg; hg.load(g);
+  SymbolicOptions opt;
+  if (const char* e = getenv("VB_MAX_LUMP_WIDTH")) opt.maxLumpWidth = std::max(8, std::min(128, atoi(e)));
+  if (const char* e = getenv("VB_ND_LEAF_BLOCKS")) opt.ndLeafBlocks = atoi(e);
+  Symbolic S; buildSymbolic(hg, opt, &S);
+  if (n != S.nP) throw std::invalid_argument("length must be num_points");
+  const std::vector<int32_t> owner = planOwners(S, nranks);
+  for (int64_t i = 0; i < S.nP; i++) landmark_owner[i] = owner[S.pos[i]];
+  VB_CATCH
+}
+// {rank, nranks, owned landmarks, owned visual factors, doubles of the reduced camera system summed
+//  over ranks per factorisation, collective calls so far, collective bytes so far, landmark-section doubles}
+int vb_shard_info(const vb_problem* p, double* out8) {
+  VB_TRY
+  requireProblem(p);
+  out8[0] = p->rank; out8[1] = p->nranks; out8[2] = (double)p->ownedLandmarks; out8[3] = (double)p->ownedVisual;
+  out8[4] = (double)(p->S.dataSize - p->S.lmDataSize); out8[5] = (double)p->collCalls; out8[6] = p->collBytes;
+  out8[7] = (double)p->S.lmDataSize;
+  VB_CATCH
+}
 
 // symbolic-only entry (host): lets CPU-side tests check the structure without a GPU
 int vb_symbolic_only(const vb_graph_desc* g, int64_t* order, int64_t* dataSize, int64_t* nLumps, int64_t* perm, int64_t permLen) {
@@ -484,14 +587,15 @@ static double evalGradHess(vb_problem* p, double* gvec, int with_hess, int updat
   cudaStream_t s = p->ctx->stream;
   VB_CUDA(cudaMemsetAsync(gvec, 0, p->S.order * sizeof(double), s));
   if (with_hess) VB_CUDA(cudaMemsetAsync(p->hess, 0, p->S.dataSize * sizeof(double), s));
-  VB_CUDA(cudaMemsetAsync(p->acc, 0, sizeof(double), s));
-  VB_CUDA(cudaMemsetAsync(p->acc + 32, 0, sizeof(double), s));
-  for (const DevStore& st : p->ds) launchGradHess(st, p->dv, gvec, with_hess ? p->hess : nullptr, update_cache, dont_retry, p->acc, s);
+  VB_CUDA(cudaMemsetAsync(p->acc + kAccCost, 0, 2 * sizeof(double), s)); // cost + evaluation error word
+  for (const DevStore& st : p->ds) launchGradHess(st, p->dv, gvec, with_hess ? p->hess : nullptr, update_cache, dont_retry, p->acc + kAccCost, s);
+  p->partial[gvec == p->step ? 0 : gvec == p->gradNew ? 1 : 2] = p->nranks > 1;
   if (!sync) return 0.0;
-  VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, 64 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  collective(p, VB_COLL_SUM, p->acc + kAccCost, 2);
+  VB_CUDA(cudaMemcpyAsync(p->accHost + kAccCost, p->acc + kAccCost, 2 * sizeof(double), cudaMemcpyDeviceToHost, s));
   syncCheck(p);
-  if (p->accHost[32] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
-  return p->accHost[0];
+  if (p->accHost[kAccErr] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
+  return p->accHost[kAccCost];
 }
 int vb_eval_grad_hess(vb_problem* p, int with_hess, int update_cache, int dont_retry_failed, double* cost) {
   VB_TRY
@@ -509,17 +613,17 @@ int vb_eval_grad_new(vb_problem* p, int dont_retry_failed) {
 static double evalCost(vb_problem* p, int comparable, vb_cost_stats* stats) {
   cudaStream_t s = p->ctx->stream;
   const size_t n = p->ds.size();
-  double* acc = p->acc + 64;
-  VB_CUDA(cudaMemsetAsync(acc, 0, 4 * n * sizeof(double), s));
-  VB_CUDA(cudaMemsetAsync(p->acc + 32, 0, sizeof(double), s));
+  double* acc = p->acc + kAccStores;
+  VB_CUDA(cudaMemsetAsync(p->acc + kAccErr, 0, (1 + 4 * n) * sizeof(double), s));
   for (size_t i = 0; i < n; i++) launchCost(p->ds[i], p->dv, comparable, acc + 4 * i, s);
-  VB_CUDA(cudaMemcpyAsync(p->accHost + 32, p->acc + 32, (32 + 4 * n) * sizeof(double), cudaMemcpyDeviceToHost, s));
+  collective(p, VB_COLL_SUM, p->acc + kAccErr, 1 + 4 * (int64_t)n);
+  VB_CUDA(cudaMemcpyAsync(p->accHost + kAccErr, p->acc + kAccErr, (1 + 4 * n) * sizeof(double), cudaMemcpyDeviceToHost, s));
   syncCheck(p);
-  if (p->accHost[32] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
+  if (p->accHost[kAccErr] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
   double tot = 0;
-  for (size_t i = 0; i < n; i++) tot += p->accHost[64 + 4 * i];
+  for (size_t i = 0; i < n; i++) tot += p->accHost[kAccStores + 4 * i];
   if (stats && n) { // Q3: CostStats of the last store only (Factor.h:686-688, Optimizer.cpp:93-95)
-    const double* a = p->accHost + 64 + 4 * (n - 1);
+    const double* a = p->accHost + kAccStores + 4 * (n - 1);
     stats->num_total = (int64_t)a[1]; stats->num_invalid = (int64_t)a[2]; stats->num_prev_invalid = (int64_t)a[3];
   }
   return tot;
@@ -534,13 +638,14 @@ int vb_eval_cost(vb_problem* p, int comparable, double* cost, vb_cost_stats* sta
 int vb_damp(vb_problem* p, double lambda) {
   VB_TRY
   requireProblem(p);
-  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->ctx->stream);
+  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->S.nP, p->rank == 0 ? lambda : 0.0, p->ctx->stream);
   VB_CATCH
 }
 int vb_step_from_grad(vb_problem* p) {
   VB_TRY
   requireProblem(p);
   launchVecOp(0, p->step, p->grad, 0, p->S.order, nullptr, p->ctx->stream);
+  p->partial[0] = p->partial[2];
   VB_CATCH
 }
 
@@ -548,6 +653,9 @@ static void factorAsync(vb_problem* p, cudaEvent_t afterSchur) {
   cudaStream_t s = p->ctx->stream;
   VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
   launchSchur(p->sol, p->hess, p->schurTasks, p->nSchurTasks, p->errFlag, s);
+  // sharded: every rank eliminated its own landmarks from its own partial camera system; the sum over
+  // ranks is the reduced camera system (the exchange step of SURVEY.md §8e), factored by all ranks
+  collective(p, VB_COLL_SUM, p->hess + p->S.lmDataSize, p->S.dataSize - p->S.lmDataSize);
   if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
   for (size_t lv = 0; lv + 1 < p->levelLumpOff.size(); lv++) {
     const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
@@ -566,7 +674,9 @@ static void checkNumeric(vb_problem* p) {
 static void solveAsync(vb_problem* p, double* vec) {
   cudaStream_t s = p->ctx->stream;
   const int nLv = (int)p->levelLumpOff.size() - 1;
+  const int64_t nCam = p->S.order - p->sol.camVec0;
   launchSolveLandmarksFwd(p->sol, p->hess, vec, s);
+  collective(p, VB_COLL_SUM, vec + p->sol.camVec0, nCam); // partial camera gradients - owned landmark eliminations
   for (int lv = 0; lv < nLv; lv++) {
     const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
     launchSolveLumpsFwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], p->levelMaxBelow[lv], nl > 1, s);
@@ -575,7 +685,10 @@ static void solveAsync(vb_problem* p, double* vec) {
     const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
     launchSolveLumpsBwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], p->levelMaxBelow[lv], s);
   }
+  collective(p, VB_COLL_BCAST0, vec + p->sol.camVec0, nCam); // one bit pattern of the camera step on all ranks
   launchSolveLandmarksBwd(p->sol, p->hess, vec, s);
+  collective(p, VB_COLL_SUM, vec, p->sol.camVec0);           // owned landmark steps -> full step everywhere
+  p->partial[vec == p->step ? 0 : vec == p->gradNew ? 1 : 2] = false;
 }
 #define VB_CATCH_NUMERIC                                                             \
   }                                                                                  \
@@ -598,19 +711,27 @@ int vb_solve(vb_problem* p, int which) {
   syncCheck(p);
   VB_CATCH_NUMERIC
 }
+static bool isPartial(const vb_problem* p, const double* v) { return p->partial[v == p->step ? 0 : v == p->gradNew ? 1 : 2]; }
+// a.b; sharded: a full (replicated) vector against a partial one is the sum of the local dots
 static double dotVec(vb_problem* p, const double* a, const double* b) {
   cudaStream_t s = p->ctx->stream;
-  VB_CUDA(cudaMemsetAsync(p->acc + 8, 0, sizeof(double), s));
-  launchVecOp(2, const_cast<double*>(a), b, 0, p->S.order, p->acc + 8, s);
-  VB_CUDA(cudaMemcpyAsync(p->accHost + 8, p->acc + 8, sizeof(double), cudaMemcpyDeviceToHost, s));
+  const bool pa = isPartial(p, a), pb = isPartial(p, b);
+  if (pa && pb) throw std::logic_error("dot of two rank-partial vectors is not defined on a sharded problem");
+  VB_CUDA(cudaMemsetAsync(p->acc + kAccDot, 0, sizeof(double), s));
+  launchVecOp(2, const_cast<double*>(a), b, 0, p->S.order, p->acc + kAccDot, s);
+  if (pa != pb) collective(p, VB_COLL_SUM, p->acc + kAccDot, 1);
+  VB_CUDA(cudaMemcpyAsync(p->accHost + kAccDot, p->acc + kAccDot, sizeof(double), cudaMemcpyDeviceToHost, s));
   syncCheck(p);
-  return p->accHost[8];
+  return p->accHost[kAccDot];
 }
 int vb_step_stats(vb_problem* p, double* step_dot_grad, double* grad_norm, double* step_norm) {
   VB_TRY
   requireProblem(p);
   if (step_dot_grad) *step_dot_grad = dotVec(p, p->step, p->grad);
-  if (grad_norm) *grad_norm = std::sqrt(dotVec(p, p->grad, p->grad));
+  if (grad_norm) { // needs the full gradient: sum the rank-partial vectors first (idempotent afterwards)
+    if (p->partial[2]) { collective(p, VB_COLL_SUM, p->grad, p->S.order); p->partial[2] = false; }
+    *grad_norm = std::sqrt(dotVec(p, p->grad, p->grad));
+  }
   if (step_norm) *step_norm = std::sqrt(dotVec(p, p->step, p->step));
   VB_CATCH
 }
@@ -679,7 +800,7 @@ int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) {
     const double prevCost = evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
     finalCost = prevCost;
     if (iterationNum == 0) initialCost = prevCost;
-    launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, damping, s);
+    launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, damping, p->S.nP, p->rank == 0 ? damping : 0.0, s);
     launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
     factorAsync(p, nullptr);
     checkNumeric(p);
@@ -789,34 +910,35 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   VB_CUDA(cudaEventRecord(e[0], s));
   evalGradHess(p, p->grad, 1, 1, 0, false); // also clears the evaluation error word
   VB_CUDA(cudaEventRecord(e[1], s));
-  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, s);
+  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->S.nP, p->rank == 0 ? lambda : 0.0, s);
   launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
   VB_CUDA(cudaEventRecord(e[2], s));
   factorAsync(p, e[3]);
   VB_CUDA(cudaEventRecord(e[4], s));
   solveAsync(p, p->step);
-  VB_CUDA(cudaMemsetAsync(p->acc + 8, 0, sizeof(double), s));
-  launchVecOp(2, p->step, p->grad, 0, n, p->acc + 8, s);
+  VB_CUDA(cudaMemsetAsync(p->acc + kAccDot, 0, sizeof(double), s));
+  launchVecOp(2, p->step, p->grad, 0, n, p->acc + kAccDot, s);
   launchVecOp(1, p->step, nullptr, -1.0, n, nullptr, s);
   VB_CUDA(cudaEventRecord(e[5], s));
   VB_CUDA(cudaMemcpyAsync(p->backup, p->dv.data, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
   applyStep(p, p->step, nullptr);
   VB_CUDA(cudaEventRecord(e[6], s));
   const size_t ns = p->ds.size();
-  VB_CUDA(cudaMemsetAsync(p->acc + 64, 0, 4 * ns * sizeof(double), s));
-  for (size_t i = 0; i < ns; i++) launchCost(p->ds[i], p->dv, 1, p->acc + 64 + 4 * i, s);
+  VB_CUDA(cudaMemsetAsync(p->acc + kAccStores, 0, 4 * ns * sizeof(double), s));
+  for (size_t i = 0; i < ns; i++) launchCost(p->ds[i], p->dv, 1, p->acc + kAccStores + 4 * i, s);
+  collective(p, VB_COLL_SUM, p->acc + kAccDot, 3 + 4 * (int64_t)ns); // step.grad, cost before, error word, cost stats
   VB_CUDA(cudaEventRecord(e[7], s));
   if (!apply) VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
   VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, (64 + 4 * ns) * sizeof(double), cudaMemcpyDeviceToHost, s));
   checkNumeric(p);
-  if (p->accHost[32] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
+  if (p->accHost[kAccErr] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
   auto ms = [&](int a, int b) { float f = 0; cudaEventElapsedTime(&f, e[a], e[b]); return (double)f; };
   if (t) {
     t->grad_hess = ms(0, 1); t->damping = ms(1, 2); t->factor_schur = ms(2, 3); t->factor_chol = ms(3, 4);
     t->solve = ms(4, 5); t->apply = ms(5, 6); t->cost = ms(6, 7); t->total = ms(0, 7);
   }
-  if (cost_before) *cost_before = p->accHost[0];
-  if (cost_after) { double c = 0; for (size_t i = 0; i < ns; i++) c += p->accHost[64 + 4 * i]; *cost_after = c; }
+  if (cost_before) *cost_before = p->accHost[kAccCost];
+  if (cost_after) { double c = 0; for (size_t i = 0; i < ns; i++) c += p->accHost[kAccStores + 4 * i]; *cost_after = c; }
   VB_CATCH_NUMERIC
 }
 

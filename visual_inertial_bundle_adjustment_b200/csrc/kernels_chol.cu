@@ -2,6 +2,8 @@
 // solves (K11), level-scheduled over the elimination tree.  The dense contractions — panel trsm
 // updates and the supernode outer product B B^T — run on the FP64 tensor pipe through
 // mma.sync.aligned.m8n8k4.f64 (DMMA; tcgen05 has no f64 kind), operands staged in shared memory.
+#include <map>
+#include <mutex>
 #include "vb_internal.hpp"
 #include "dev_math.cuh"
 
@@ -487,8 +489,20 @@ __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const dou
 }
 
 // ---- launchers ----------------------------------------------------------------------------------------
+// The opt-in limit is a per-function, per-context attribute: raise it monotonically under a lock so
+// that several host threads driving their own problems on one device never lower each other's limit.
 static void ensureSmem(const void* fn, size_t bytes) {
-  if (bytes > 48 * 1024) VB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  if (bytes <= 48 * 1024) return;
+  static std::mutex mu;
+  static std::map<std::pair<int, const void*>, size_t> cur;
+  int dev = 0;
+  VB_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
+  size_t& c = cur[{dev, fn}];
+  if (bytes > c) {
+    VB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    c = bytes;
+  }
 }
 void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s) {
   launchSchurPrep(d, hess, errFlag, s);

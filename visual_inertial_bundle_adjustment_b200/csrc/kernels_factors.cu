@@ -154,9 +154,10 @@ __global__ void __launch_bounds__(128) gradHessSmallKernel(DevStore st, DevVars 
   __shared__ double Jsh[4][E * MAXTOT];
   __shared__ double rsh[4][E + 2];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t k = blockIdx.x * 4ll + warp;
+  const int64_t idx = blockIdx.x * 4ll + warp;
+  const int64_t k = st.active ? (idx < st.nActive ? st.active[idx] : 0) : st.kBegin + idx; // shard: this rank's factors only
   double acc[1] = {0.0};
-  if (k < st.count) {
+  if (idx < st.nActive) {
     const int nv = st.nvars;
     const int32_t* v = st.vars + k * nv;
     double* Jb = Jsh[warp];
@@ -401,9 +402,10 @@ __global__ void __launch_bounds__(128) gradHessVisualChunkKernel(DevStore st, De
 // acc = {cost, numTotal, numInvalid, numPrevInvalid}
 template <int E>
 __global__ void __launch_bounds__(128) costKernel(DevStore st, DevVars V, int comparable, double* accOut) {
-  const int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t k = st.active ? (idx < st.nActive ? st.active[idx] : 0) : st.kBegin + idx; // shard: this rank's factors only
   double acc[4] = {0, 0, 0, 0};
-  if (k < st.count) {
+  if (idx < st.nActive) {
     double r[E];
     const bool valid = evalSmall(st, V, k, r, nullptr);
     acc[1] = 1.0;
@@ -508,12 +510,15 @@ __global__ void __launch_bounds__(128) applyStepKernel(DevVars V, const int64_t*
 
 // Optimizer::addDamping (Optimizer.cpp:136-146): d <- d (1 + lambda) + lambda on every diagonal scalar
 __global__ void dampingKernel(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize,
-                              int64_t nB, double lambda) {
+                              int64_t nB, double lambda, int64_t nP, double lambdaAddCam) {
+  // sharded runs: camera-side diagonals are partial sums over ranks, so only rank 0 adds the "+ lambda"
+  // term there (the update is affine in d); landmark diagonals are complete on their owner
   const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (b >= nB) return;
   double* D = hess + diagOff[b];
   const int st = diagStride[b], n = diagSize[b];
-  for (int a = 0; a < n; a++) { double* p = D + (int64_t)a * st + a; *p = *p * (1.0 + lambda) + lambda; }
+  const double add = b < nP ? lambda : lambdaAddCam;
+  for (int a = 0; a < n; a++) { double* p = D + (int64_t)a * st + a; *p = *p * (1.0 + lambda) + add; }
 }
 
 // op: 0 a=b ; 1 a*=s ; 2 out[0]+=a.b ; 3 a=0
@@ -534,12 +539,13 @@ static inline int gridFor(int64_t n, int bs) { return (int)((n + bs - 1) / bs); 
 
 void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
                     double* costAcc, cudaStream_t s) {
-  if (st.count == 0) return;
-#define SMALL(E, TOT) gradHessSmallKernel<E, TOT><<<gridFor(st.count, 4), 128, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc)
+  if (st.nActive == 0) return;
+#define SMALL(E, TOT) gradHessSmallKernel<E, TOT><<<gridFor(st.nActive, 4), 128, 0, s>>>(st, v, grad, hess, updateCache, dontRetry, costAcc)
   switch (st.type) {
     case VB_F_VISUAL:
     case VB_F_VISUAL_RS: {
       if (!st.order) throw std::runtime_error("visual store without a chunk schedule");
+      if (st.nChunks == 0) break; // a shard that owns none of this store's landmarks
       const bool rs = st.type == VB_F_VISUAL_RS;
       const size_t smem = (size_t)2 * kVisChunk * (rs ? 44 : 36) * sizeof(double);
       if (rs) {
@@ -569,8 +575,8 @@ void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* 
 }
 
 void launchCost(const DevStore& st, const DevVars& v, int comparable, double* acc, cudaStream_t s) {
-  if (st.count == 0) return;
-#define COST(E) costKernel<E><<<gridFor(st.count, 128), 128, 0, s>>>(st, v, comparable, acc)
+  if (st.nActive == 0) return;
+#define COST(E) costKernel<E><<<gridFor(st.nActive, 128), 128, 0, s>>>(st, v, comparable, acc)
   switch (errSize(st.type)) {
     case 2: COST(2); break;
     case 3: COST(3); break;
@@ -589,8 +595,8 @@ void launchApplyStep(const DevVars& v, const int64_t* blockVar, int64_t nB, cons
   VB_CUDA(cudaGetLastError());
 }
 void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize, int64_t nB,
-                   double lambda, cudaStream_t s) {
-  dampingKernel<<<gridFor(nB, 256), 256, 0, s>>>(hess, diagOff, diagStride, diagSize, nB, lambda);
+                   double lambda, int64_t nP, double lambdaAddCam, cudaStream_t s) {
+  dampingKernel<<<gridFor(nB, 256), 256, 0, s>>>(hess, diagOff, diagStride, diagSize, nB, lambda, nP, lambdaAddCam);
   VB_CUDA(cudaGetLastError());
 }
 void launchVecOp(int op, double* a, const double* b, double sc, int64_t n, double* out, cudaStream_t st) {

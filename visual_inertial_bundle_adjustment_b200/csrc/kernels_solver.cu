@@ -21,9 +21,10 @@ VB_DEV int rowInLump(const DevSolver& d, int T, int c) {
 // ---- K9a: landmark elimination, first half: one warp per landmark factors H_pp (3x3) in place and
 // turns the row panel into W L^-T.  The Schur update itself is schurGroupUpdateKernel (kernels_chol.cu).
 __global__ void __launch_bounds__(256) schurPrepKernel(DevSolver d, double* hess, int* errFlag) {
-  const int64_t p = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t ip = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (p >= d.nP) return;
+  if (ip >= d.nLmActive) return;
+  const int64_t p = d.lmActive ? d.lmActive[ip] : ip; // shard: the landmarks this rank owns
   double* base = hess + d.lmOff[p];
   const int m = (int)((d.lmOff[p + 1] - d.lmOff[p]) / 3) - 3;
   const double a00 = base[0], a10 = base[3], a11 = base[4], a20 = base[6], a21 = base[7], a22 = base[8];
@@ -51,9 +52,10 @@ __global__ void __launch_bounds__(256) schurPrepKernel(DevSolver d, double* hess
 // ---- K11: solves -------------------------------------------------------------------------------------
 // forward over landmarks: y_p = L_pp^-1 g_p ; g_cam -= W'_p y_p
 __global__ void __launch_bounds__(256) solveLmFwdKernel(DevSolver d, const double* hess, double* vec) {
-  const int64_t p = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t ip = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (p >= d.nP) return;
+  if (ip >= d.nLmActive) return;
+  const int64_t p = d.lmActive ? d.lmActive[ip] : ip; // shard: the landmarks this rank owns
   const double* base = hess + d.lmOff[p];
   double* g = vec + 3 * p;
   const double y0 = g[0] / base[0];
@@ -73,9 +75,10 @@ __global__ void __launch_bounds__(256) solveLmFwdKernel(DevSolver d, const doubl
 }
 // backward over landmarks: x_p = L_pp^-T (y_p - sum W'^T x_cam)
 __global__ void __launch_bounds__(256) solveLmBwdKernel(DevSolver d, const double* hess, double* vec) {
-  const int64_t p = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t ip = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (p >= d.nP) return;
+  if (ip >= d.nLmActive) return;
+  const int64_t p = d.lmActive ? d.lmActive[ip] : ip; // shard: the landmarks this rank owns
   const double* base = hess + d.lmOff[p];
   const int64_t r0 = d.lmRowPtr[p];
   const int nb = (int)(d.lmRowPtr[p + 1] - r0);
@@ -132,18 +135,18 @@ double measureDmmaPeak(cudaStream_t s) {
 
 // ---- launchers ----------------------------------------------------------------------------------------
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s) {
-  if (d.nP == 0) return;
-  schurPrepKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, errFlag);
+  if (d.nLmActive == 0) return;
+  schurPrepKernel<<<(int)((d.nLmActive * 32 + 255) / 256), 256, 0, s>>>(d, hess, errFlag);
   VB_CUDA(cudaGetLastError());
 }
 void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s) {
-  if (d.nP == 0) return;
-  solveLmFwdKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, vec);
+  if (d.nLmActive == 0) return;
+  solveLmFwdKernel<<<(int)((d.nLmActive * 32 + 255) / 256), 256, 0, s>>>(d, hess, vec);
   VB_CUDA(cudaGetLastError());
 }
 void launchSolveLandmarksBwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s) {
-  if (d.nP == 0) return;
-  solveLmBwdKernel<<<(int)((d.nP * 32 + 255) / 256), 256, 0, s>>>(d, hess, vec);
+  if (d.nLmActive == 0) return;
+  solveLmBwdKernel<<<(int)((d.nLmActive * 32 + 255) / 256), 256, 0, s>>>(d, hess, vec);
   VB_CUDA(cudaGetLastError());
 }
 } // namespace vb

@@ -38,6 +38,11 @@ struct DevStore {
   const int32_t* order;      // [count] factor index
   const int32_t* chunkStart; // [nChunks+1] into order
   int32_t nChunks;
+  // shard view (vb_problem_create_sharded): the factors this rank evaluates.  Small stores: the
+  // contiguous range [kBegin, kBegin + nActive); visual stores: the sorted list `active` (factors
+  // whose landmark this rank owns).  Unsharded: kBegin = 0, nActive = count, active = null.
+  int64_t kBegin, nActive;
+  const int32_t* active;
 };
 
 // device view of the variables
@@ -84,6 +89,8 @@ struct DevSolver {
   const int32_t* grpRowSub;  //   ... and the row inside that block
   const int32_t* grpRows;    // [nG] union scalar rows
   int64_t grpRowBase;        // updPtr[nL]
+  // shard view: landmarks this rank owns (null = all nP)
+  const int32_t* lmActive; int64_t nLmActive;
 };
 
 
@@ -93,7 +100,7 @@ void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* 
 void launchCost(const DevStore& st, const DevVars& v, int comparable, double* acc /* cost,total,invalid,prevInvalid */, cudaStream_t s);
 void launchApplyStep(const DevVars& v, const int64_t* blockVar, int64_t nB, const double* step, double* ratioAcc, cudaStream_t s);
 void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize, int64_t nB,
-                   double lambda, cudaStream_t s);
+                   double lambda, int64_t nP, double lambdaAddCam, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
 void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s);

@@ -229,23 +229,34 @@ __global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hes
   dmmaABt<2, 4>(As, ld, Bs, ld, (w + 3) & ~3, rowBase, colBase, acc);
   const int64_t q0 = d.updPtr[L];
   const int32_t* rel = d.rel + d.relPtr[L];
+  // scatter in two phases so that the index loads of all 16 entries are in flight together (atomics
+  // order memory operations, which would otherwise serialise every lookup behind the previous update)
+  double* dst[4][2][2];
 #pragma unroll
   for (int n = 0; n < 4; n++)
 #pragma unroll
     for (int e = 0; e < 2; e++) {
       const int qj = j0 + colBase + n * 8 + 2 * (lane & 3) + e;
-      if (qj >= r) continue;
-      const int64_t colOff = d.updColOff[q0 + qj];
-      const int stride = d.updStride[q0 + qj];
-      const int32_t* relT = rel + (int64_t)d.updTgt[q0 + qj] * r;
+      const bool cv = qj < r;
+      const int64_t colOff = cv ? d.updColOff[q0 + qj] : 0;
+      const int stride = cv ? d.updStride[q0 + qj] : 0;
+      const int32_t* relT = rel + (int64_t)(cv ? d.updTgt[q0 + qj] : 0) * r;
 #pragma unroll
       for (int m = 0; m < 2; m++) {
         const int qi = i0 + rowBase + m * 8 + (lane >> 2);
-        if (qi >= r || qi < qj) continue;
-        double* p = hess + colOff + (int64_t)relT[qi] * stride;
-        if (useAtomics) red_add(p, -acc[m][n][e]); else *p -= acc[m][n][e];
+        dst[n][e][m] = (cv && qi < r && qi >= qj) ? hess + colOff + (int64_t)relT[qi] * stride : nullptr;
       }
     }
+#pragma unroll
+  for (int n = 0; n < 4; n++)
+#pragma unroll
+    for (int e = 0; e < 2; e++)
+#pragma unroll
+      for (int m = 0; m < 2; m++) {
+        double* p = dst[n][e][m];
+        if (!p) continue;
+        if (useAtomics) red_add(p, -acc[m][n][e]); else *p -= acc[m][n][e];
+      }
 }
 
 // ---- K9b: Schur update of the camera system by landmark groups -------------------------------------
@@ -285,13 +296,22 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
       double* o = T + a * ld;
       if (kq == 0) for (int z = 3 * cnt; z < K4; z++) o[z] = 0.0;
       if (q < r) {
-        const int32_t* bo = blkOff + d.grpRowBlk[qg + q] * kGrpMax;
+        // thread kq of the row's quad owns member slots 8 kq .. 8 kq + 7: their 8 panel offsets come in
+        // with two 16-byte loads (one round trip), then every present member's 3-double W row is copied
+        // with cp.async into its compacted column (rank among the present members)
+        const int4* bo = reinterpret_cast<const int4*>(blkOff + d.grpRowBlk[qg + q] * kGrpMax + 8 * kq);
         const int sub3 = 3 * d.grpRowSub[qg + q];
-        for (int k = kq; k < cnt; k += 4) {
-          const int off = bo[lmList[k]];
+        const int4 o0 = bo[0], o1 = bo[1];
+        const int offs[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+        int k = __popc(t.mask & ((1u << (8 * kq)) - 1u));
+#pragma unroll
+        for (int z = 0; z < 8; z++) {
+          if (!((t.mask >> (8 * kq + z)) & 1u)) continue;
+          const int off = offs[z];
           const bool v = off >= 0;
           const double* w = v ? hess + off + sub3 : hess;
           cp_async8(o + 3 * k, w, v); cp_async8(o + 3 * k + 1, w + 1, v); cp_async8(o + 3 * k + 2, w + 2, v);
+          k++;
         }
       } else {
         for (int k = kq; k < cnt; k += 4) { o[3 * k] = 0.0; o[3 * k + 1] = 0.0; o[3 * k + 2] = 0.0; }
@@ -308,24 +328,33 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
     for (int n = 0; n < 4; n++) acc[m][n][0] = acc[m][n][1] = 0.0;
   dmmaABt<2, 4>(As, ld, Bs, ld, K4, rowBase, colBase, acc);
   const int32_t* rel = d.rel + d.relPtr[src];
+  // two-phase scatter: every index lookup first (independent loads in flight together), then the reductions
+  double* dst[4][2][2];
 #pragma unroll
   for (int n = 0; n < 4; n++)
 #pragma unroll
     for (int e = 0; e < 2; e++) {
       const int qj = j0 + colBase + n * 8 + 2 * (lane & 3) + e;
-      if (qj >= r) continue;
-      const int64_t colOff = d.updColOff[q0 + qj];
-      const int stride = d.updStride[q0 + qj];
-      const int32_t* relT = rel + (int64_t)d.updTgt[q0 + qj] * r;
+      const bool cv = qj < r;
+      const int64_t colOff = cv ? d.updColOff[q0 + qj] : 0;
+      const int stride = cv ? d.updStride[q0 + qj] : 0;
+      const int32_t* relT = rel + (int64_t)(cv ? d.updTgt[q0 + qj] : 0) * r;
 #pragma unroll
       for (int m = 0; m < 2; m++) {
         const int qi = i0 + rowBase + m * 8 + (lane >> 2);
-        if (qi >= r || qi < qj) continue;
-        const double v = acc[m][n][e];
-        const int rr = relT[qi];
-        if (v != 0.0 && rr >= 0) red_add(hess + colOff + (int64_t)rr * stride, -v);
+        const int rr = (cv && qi < r && qi >= qj) ? relT[qi] : -1;
+        dst[n][e][m] = rr >= 0 ? hess + colOff + (int64_t)rr * stride : nullptr;
       }
     }
+#pragma unroll
+  for (int n = 0; n < 4; n++)
+#pragma unroll
+    for (int e = 0; e < 2; e++)
+#pragma unroll
+      for (int m = 0; m < 2; m++) {
+        const double v = acc[m][n][e];
+        if (dst[n][e][m] && v != 0.0) red_add(dst[n][e][m], -v);
+      }
 }
 
 // ---- K11 (supernode part) ---------------------------------------------------------------------------

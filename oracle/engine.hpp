@@ -131,6 +131,16 @@ struct Engine {
     return blkOff[p - colInd.data()];
   }
 
+  // CPU-baseline mode (bench.py only): factor loop over `threads` OpenMP threads with atomic block
+  // adds, the way the reference runs it on its thread pool with locked adds (Factor.h:704-734,
+  // AtomicOps.h:80-112).  threads == 1 is the serial checker path the tests use (bit-stable).
+  int threads = 1;
+  inline void acc(double& dst, double v) const {
+    if (threads > 1) {
+#pragma omp atomic
+      dst += v;
+    } else dst += v;
+  }
   // ---- computeSingleGradHess (Factor.h:543-661) ------------------------------------------------
   double singleGradHess(const Store& st, int64_t k, double* g, double* H, bool updateCache, bool dontRetryFailed) {
     const bool opt = optionalErrors(st.type);
@@ -156,7 +166,7 @@ struct Engine {
       if (L) matmul(L, J[i], adj, E, E, di); else std::memcpy(adj, J[i], sizeof(double) * E * di);
       for (int t = 0; t < E * di; t++) adj[t] *= dSoft;
       double* gs = g + paramStart[ii];
-      for (int a = 0; a < di; a++) { double s = 0; for (int e = 0; e < E; e++) s += r[e] * adj[e * di + a]; gs[a] += s; }
+      for (int a = 0; a < di; a++) { double s = 0; for (int e = 0; e < E; e++) s += r[e] * adj[e * di + a]; acc(gs[a], s); }
       if (!H) continue;
       for (int j = 0; j < i; j++) {
         const int64_t jj = P.index[v[j]];
@@ -165,18 +175,18 @@ struct Engine {
         matmulTN(adj, J[j], blk, E, di, dj); // iAdjJac^T * jJac  (di x dj)
         if (ii > jj) {
           double* B = H + findBlock(ii, jj);
-          for (int t = 0; t < di * dj; t++) B[t] += blk[t];
+          for (int t = 0; t < di * dj; t++) acc(B[t], blk[t]);
         } else if (ii < jj) { // stored transposed as block (jj, ii): dj x di
           double* B = H + findBlock(jj, ii);
-          for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) B[b * di + a] += blk[a * dj + b];
+          for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) acc(B[b * di + a], blk[a * dj + b]);
         } else { // same variable twice: diagonal block gets the off-diagonal product too
           double* B = H + findBlock(ii, ii);
-          for (int t = 0; t < di * dj; t++) B[t] += blk[t];
+          for (int t = 0; t < di * dj; t++) acc(B[t], blk[t]);
         }
       }
       matmulTN(adj, J[i], blk, E, di, di);
       double* B = H + findBlock(ii, ii);
-      for (int t = 0; t < di * di; t++) B[t] += blk[t];
+      for (int t = 0; t < di * di; t++) acc(B[t], blk[t]);
     }
     const double ret = soft * 0.5;
     if (opt && updateCache) st.cache[k] = ret;
@@ -188,7 +198,12 @@ struct Engine {
     double tot = 0;
     for (const Store& st : P.stores) {
       double c = 0;
-      for (int64_t k = 0; k < st.count; k++) c += singleGradHess(st, k, g, H, updateCache, dontRetryFailed);
+      if (threads > 1) {
+#pragma omp parallel for schedule(dynamic, 512) reduction(+ : c) num_threads(threads)
+        for (int64_t k = 0; k < st.count; k++) c += singleGradHess(st, k, g, H, updateCache, dontRetryFailed);
+      } else {
+        for (int64_t k = 0; k < st.count; k++) c += singleGradHess(st, k, g, H, updateCache, dontRetryFailed);
+      }
       tot += c;
     }
     return tot;
@@ -221,6 +236,16 @@ struct Engine {
     for (const Store& st : P.stores) {
       CostStats cs;
       double c = 0;
+      if (threads > 1) {
+        int64_t nt = 0, ni = 0, np = 0;
+#pragma omp parallel for schedule(static) reduction(+ : c, nt, ni, np) num_threads(threads)
+        for (int64_t k = 0; k < st.count; k++) {
+          bool has; CostStats one;
+          c += singleCost(st, k, comparable, &one, has);
+          nt += one.numTotal; ni += one.numInvalid; np += one.numPrevInvalid;
+        }
+        cs.numTotal = nt; cs.numInvalid = ni; cs.numPrevInvalid = np;
+      } else
       for (int64_t k = 0; k < st.count; k++) { bool has; c += singleCost(st, k, comparable, &cs, has); }
       if (stats) *stats = cs;
       tot += c;

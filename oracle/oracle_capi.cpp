@@ -1,6 +1,7 @@
 // ORACLE (test infrastructure, CPU only) — see vmath.hpp header note.
 // C entry points over the oracle so that tests/ (ctypes) and bench.py's cpu_baseline /
 // --impl reference legs can drive it.  Never linked into the product library.
+#include <dlfcn.h>
 #include <cstring>
 #include <string>
 #include <chrono>
@@ -159,6 +160,26 @@ int orc_optimize(OrcHandle* h, const vb_settings* s, vb_summary* out, double* tr
 }
 
 // one accepted-path LM iteration, wall-clock split in ms: {gradhess, damp, factor, solve, apply, cost, total}
+// CPU-baseline mode (bench.py): `threads` OpenMP threads for the factor loops and landmark elimination;
+// `blas_path` (may be null) = a shared library exporting LAPACK dpbtrf/dpbtrs under `prefix` (scipy's
+// OpenBLAS uses "scipy_"), used for the reduced-system Cholesky.  threads <= 1 restores the checker path.
+int orc_set_parallel(OrcHandle* h, int threads, const char* blas_path, const char* prefix) {
+  ORC_TRY
+  h->eng.threads = threads < 1 ? 1 : threads;
+  h->sol.pbtrf = nullptr; h->sol.pbtrs = nullptr;
+  if (threads > 1 && blas_path) {
+    void* lib = dlopen(blas_path, RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) throw std::runtime_error(std::string("dlopen failed: ") + dlerror());
+    const std::string pre = prefix ? prefix : "";
+    h->sol.pbtrf = (SchurSkylineSolver::pbtrf_fn)dlsym(lib, (pre + "dpbtrf_").c_str());
+    h->sol.pbtrs = (SchurSkylineSolver::pbtrs_fn)dlsym(lib, (pre + "dpbtrs_").c_str());
+    if (!h->sol.pbtrf || !h->sol.pbtrs) throw std::runtime_error("dpbtrf_/dpbtrs_ not found in " + std::string(blas_path));
+    typedef void (*setn_fn)(int);
+    if (auto setn = (setn_fn)dlsym(lib, (pre + "openblas_set_num_threads").c_str())) setn(threads);
+  }
+  ORC_CATCH
+}
+
 int orc_lm_iteration_timed(OrcHandle* h, double lambda, double* ms, double* costBefore, double* costAfter) {
   ORC_TRY
   using clk = std::chrono::steady_clock;

@@ -97,14 +97,29 @@ struct SchurSkylineSolver {
   void addBlock(int64_t bi, int64_t bj, const double* B, double sign) {
     const int di = E->P.blockSize[bi], dj = E->P.blockSize[bj];
     const int64_t si = cstart[bi - nP], sj = cstart[bj - nP];
+    const bool par = E->threads > 1; // CPU-baseline mode: landmarks are eliminated by several threads
+    auto add = [par](double& dst, double v) {
+      if (par) {
+#pragma omp atomic
+        dst += v;
+      } else dst += v;
+    };
     if (bi == bj) {
-      for (int a = 0; a < di; a++) for (int b = 0; b <= a; b++) at(si + a, sj + b) += sign * B[a * dj + b];
+      for (int a = 0; a < di; a++) for (int b = 0; b <= a; b++) add(at(si + a, sj + b), sign * B[a * dj + b]);
     } else if (si > sj) {
-      for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) at(si + a, sj + b) += sign * B[a * dj + b];
+      for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) add(at(si + a, sj + b), sign * B[a * dj + b]);
     } else {
-      for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) at(sj + b, si + a) += sign * B[a * dj + b];
+      for (int a = 0; a < di; a++) for (int b = 0; b < dj; b++) add(at(sj + b, si + a), sign * B[a * dj + b]);
     }
   }
+  // ---- CPU-baseline mode only: LAPACK band Cholesky (dpbtrf/dpbtrs) of the reduced system on a
+  // multi-threaded OpenBLAS loaded at run time (the reference factors with BaSpaCho's BLAS backend on
+  // OpenBLAS, README.md:109-118).  Under the RCM ordering the envelope is a band, so the blocked
+  // BLAS-3 band routine is the closest stock stand-in for a supernodal factorisation.
+  typedef void (*pbtrf_fn)(const char*, const int*, const int*, double*, const int*, int*);
+  typedef void (*pbtrs_fn)(const char*, const int*, const int*, const int*, const double*, const int*, double*, const int*, int*);
+  pbtrf_fn pbtrf = nullptr; pbtrs_fn pbtrs = nullptr;
+  std::vector<double> AB; int kd = 0; bool bandFactored = false;
 
   static void inv3sym(const double* A, double* I) { // symmetric 3x3 (lower used), via Cholesky
     const double l00 = std::sqrt(A[0]), l10 = A[3] / l00, l20 = A[6] / l00;
@@ -136,15 +151,17 @@ struct SchurSkylineSolver {
       }
     // landmark elimination
     flopsSchur = 0;
-    std::vector<double> Y;
+    double fl = 0;
+#pragma omp parallel for schedule(dynamic, 64) reduction(+ : fl) num_threads(e.threads) if (e.threads > 1)
     for (int64_t p = 0; p < nP; p++) {
+      std::vector<double> Y;
       const double* Hpp = H + e.blkOff[e.rowPtr[p + 1] - 1];
       double* Hi = &HppInv[9 * p];
       inv3sym(Hpp, Hi);
       const auto& cb = colBlocks[p];
       int64_t m = 0;
       for (int64_t k : cb) m += e.P.blockSize[rowOfEntry[k]];
-      flopsSchur += 3.0 * m * m + 9.0 * m + 9.0;
+      fl += 3.0 * m * m + 9.0 * m + 9.0;
       // Y_a = W_a Hpp^-1 (d_a x 3), W_a = block (a,p) (d_a x 3)
       Y.assign(3 * m, 0.0);
       int64_t o = 0;
@@ -172,6 +189,23 @@ struct SchurSkylineSolver {
         }
         oa += da;
       }
+    }
+    flopsSchur = fl;
+    bandFactored = false;
+    if (pbtrf && e.threads > 1) { // CPU-baseline mode: band storage (lower), AB[(i-j) + j*ldab] = A(i,j)
+      kd = 0;
+      for (int64_t i = 0; i < nr; i++) kd = std::max<int>(kd, (int)(i - first[i]));
+      const int64_t ldab = kd + 1;
+      AB.assign((size_t)ldab * nr, 0.0);
+#pragma omp parallel for schedule(static) num_threads(e.threads)
+      for (int64_t i = 0; i < nr; i++)
+        for (int64_t j = first[i]; j <= i; j++) AB[(size_t)(i - j) + (size_t)j * ldab] = S[rowStart[i] + (j - first[i])];
+      const int n = (int)nr, ld = (int)ldab;
+      int info = 0;
+      pbtrf("L", &n, &kd, AB.data(), &ld, &info);
+      if (info != 0) throw std::runtime_error("oracle: dpbtrf failed (reduced system not positive definite)");
+      bandFactored = true;
+      return;
     }
     // envelope Cholesky (row by row)
     for (int64_t i = 0; i < nr; i++) {
@@ -212,6 +246,12 @@ struct SchurSkylineSolver {
     }
     // solve L y = gr ; L^T z = y
     std::vector<double> y(gr);
+    if (bandFactored) {
+      const int n = (int)nr, ld = kd + 1, one = 1;
+      int info = 0;
+      pbtrs("L", &n, &kd, &one, AB.data(), &ld, y.data(), &n, &info);
+      if (info != 0) throw std::runtime_error("oracle: dpbtrs failed");
+    } else {
     for (int64_t i = 0; i < nr; i++) {
       const double* Li = &S[rowStart[i]];
       double s = y[i];
@@ -223,6 +263,7 @@ struct SchurSkylineSolver {
       y[i] /= Li[i - first[i]];
       const double yi = y[i];
       for (int64_t k = first[i]; k < i; k++) y[k] -= Li[k - first[i]] * yi;
+    }
     }
     for (int64_t c = 0; c < nC; c++)
       for (int a = 0; a < e.P.blockSize[nP + c]; a++) x[e.paramStart[nP + c] + a] = y[cstart[c] + a];

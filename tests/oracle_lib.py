@@ -23,7 +23,19 @@ def load_oracle():
     lib.orc_boxplus.argtypes = [C.c_int, C.c_uint32, C.c_double, _dp, _dp, C.c_int, _dp]
     lib.orc_lm_iteration_timed.argtypes = [C.c_void_p, C.c_double, _dp, _dp, _dp]
     lib.orc_eval_factor.argtypes = [C.c_void_p, C.c_int, C.c_int64, _dp, _dp, C.POINTER(C.c_int)]
+    lib.orc_set_parallel.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_char_p]
     return lib
+
+
+def find_openblas():
+    """scipy's bundled OpenBLAS (LAPACK symbols prefixed `scipy_`), or None."""
+    import glob
+    try:
+        import scipy
+        hits = glob.glob(os.path.join(os.path.dirname(os.path.dirname(scipy.__file__)), "scipy.libs", "libscipy_openblas*.so"))
+        return (hits[0], "scipy_") if hits else None
+    except Exception:
+        return None
 
 
 def dptr(a):
@@ -50,6 +62,14 @@ class Oracle:
             self.lib.orc_destroy(self.h)
         except Exception:
             pass
+
+    def set_parallel(self, threads):
+        """CPU-baseline mode: OpenMP factor loops + landmark elimination on `threads` threads and, when
+        scipy's OpenBLAS is present, LAPACK dpbtrf/dpbtrs for the reduced system.  Returns the solver kind."""
+        blas = find_openblas() if threads > 1 else None
+        self._ck(self.lib.orc_set_parallel(self.h, int(threads), blas[0].encode() if blas else None,
+                                           blas[1].encode() if blas else None))
+        return "openblas-dpbtrf" if blas else "envelope"
 
     def structure(self):
         rp = np.zeros(self.nblocks + 1, np.int64); ci = np.zeros(self.nnz, np.int64)

@@ -98,3 +98,20 @@ def test_lm_converges_and_is_deterministic(oracle, tiny):
     assert sa.final_cost < 0.1 * sa.initial_cost and sa.stop_reason == 0
     assert sa.final_cost == sb.final_cost and np.array_equal(a.vars, b.vars)
     assert np.all(np.diff(tpa) <= 1e-9)
+
+
+def test_parallel_baseline_mode_matches_serial(oracle):
+    """bench.py's CPU-baseline mode (OpenMP factor loops, atomic adds, OpenBLAS band Cholesky) computes
+    the same iteration as the serial checker path up to summation order."""
+    from visual_inertial_bundle_adjustment_b200 import synth
+    s = synth.make_session(**synth.CONFIGS["small_rs"])
+    a, b = Oracle(oracle, s.graph), Oracle(oracle, s.graph)
+    kind = b.set_parallel(4)
+    _, a0, a1 = a.lm_iteration_timed(1e-5)
+    _, b0, b1 = b.lm_iteration_timed(1e-5)
+    assert abs(a0 - b0) <= 1e-12 * abs(a0) and abs(a1 - b1) <= 1e-9 * abs(a1)
+    assert np.abs(a.step - b.step).max() <= 1e-7 * np.abs(a.step).max()
+    assert kind in ("openblas-dpbtrf", "envelope")
+    b.set_parallel(1)
+    _, c0, c1 = b.lm_iteration_timed(1e-5)
+    assert c0 == a0

@@ -268,7 +268,6 @@ __global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hes
 constexpr int kGrpMax = 32;
 __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, double* hess, const SchurTask* tasks) {
   extern __shared__ double sm[];
-  __shared__ int lmList[kGrpMax];
   const SchurTask t = tasks[blockIdx.x];
   const int g = t.group;
   const int r = d.grpRows[g];
@@ -283,8 +282,6 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
   const int64_t q0 = d.updPtr[src];
   const int64_t qg = q0 - d.grpRowBase;
   const int32_t* blkOff = d.grpBlkOff + d.grpBlkPtr[g] * kGrpMax;
-  if (tid < kGrpMax && ((t.mask >> tid) & 1u)) lmList[__popc(t.mask & ((1u << tid) - 1u))] = tid;
-  __syncthreads();
   // gather: 4 threads per tile row; each loads the row's block/sub-row once and walks the present
   // landmarks, copying their 3-double W rows straight from the landmark panels with cp.async
   {

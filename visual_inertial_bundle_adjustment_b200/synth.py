@@ -361,6 +361,7 @@ CONFIGS = {
     "c2_5min_rs": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000, rgb=True, n_imus=2),
     "c2_5min": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000),
     "c3_20min": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000),
+    "c3_20min_rs": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000, rgb=True, n_imus=2),
 }
 
 

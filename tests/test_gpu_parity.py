@@ -187,3 +187,33 @@ def test_rs_time_shift_out_of_range_is_an_error(ctx):
         p.compute_grad_hess()
     assert e.value.code == 3
     p.close()
+
+
+@pytest.mark.parametrize("name", ["small", "small_rs"])
+def test_two_pass_visual_schedule(name, ctx, oracle, monkeypatch):
+    """The two-pass visual schedule (camera side per chunk, landmark side in landmark-major order with
+    in-warp segmented sums) is selected automatically only for sessions whose landmark panels exceed
+    L2; force it here and hold it to the same gates, including the dont-retry / cache semantics."""
+    monkeypatch.setenv("VB_VISUAL_TWO_PASS", "1")
+    s = synth.make_session(**synth.CONFIGS[name])
+    o = Oracle(oracle, s.graph)
+    p = capi.Problem(ctx, s.graph)
+    try:
+        co, cg = o.eval_grad_hess(), p.compute_grad_hess()
+        assert abs(cg - co) <= 1e-12 * abs(co)
+        go = o.grad; gg = to_reg(p, o, p.grad)
+        assert np.abs(gg - go).max() <= 1e-10 * np.abs(go).max()
+        Ho = o.dense_hessian() if o.order <= 1000 else None
+        if Ho is not None:
+            assert np.abs(gpu_dense_hessian(p, o) - Ho).max() <= 1e-10 * np.abs(Ho).max()
+        p.add_damping(1e-5); o.damp(1e-5)
+        p.step_from_grad(); p.factor(); p.solve(0)
+        o.factor(); o.solve()
+        so = o.step; sg = to_reg(p, o, p.step)
+        assert np.abs(sg - so).max() <= 1e-7 * np.abs(so).max()
+        # second evaluation with dont_retry_failed (reads the caches the first pass wrote)
+        co2, cg2 = o.eval_grad_hess(True, True, True), p.compute_grad_hess(True, True, True)
+        assert abs(cg2 - co2) <= 1e-12 * abs(co2)
+        assert np.abs(to_reg(p, o, p.grad) - o.grad).max() <= 1e-10 * np.abs(o.grad).max()
+    finally:
+        p.close()

@@ -38,6 +38,8 @@ struct DevStore {
   const int32_t* order;      // [count] factor index
   const int32_t* chunkStart; // [nChunks+1] into order
   int32_t nChunks;
+  int32_t twoPass;           // 1: camera side per chunk + landmark side in landmark-major order (two kernels)
+  const int32_t* orderLm;    // [nActive] visual stores: owned factors sorted by (landmark, extrinsics, intrinsics)
   // shard view (vb_problem_create_sharded): the factors this rank evaluates.  Small stores: the
   // contiguous range [kBegin, kBegin + nActive); visual stores: the sorted list `active` (factors
   // whose landmark this rank owns).  Unsharded: kBegin = 0, nActive = count, active = null.

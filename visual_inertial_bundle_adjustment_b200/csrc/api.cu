@@ -275,9 +275,13 @@ static void buildDeviceProblem(vb_problem& P) {
     // ---- landmark groups for the Schur update: landmarks sorted by their first camera block are
     // packed greedily while the union of their row blocks stays <= kGrpMaxRows scalars and the
     // group holds <= kGrpMax landmarks; each group is one dense [union rows] x [3 G] operand
+    // A group is the scatter unit: up to kGrpChunks chunks of <= 32 landmarks that share one union of
+    // row blocks.  The kernel accumulates the chunks of a tile pair in registers (K loop) and scatters
+    // once, so the reductions per target entry drop with the number of chunks.
     constexpr int kGrpMax = 32;
-    int kGrpMaxRows = 1024;
+    int kGrpMaxRows = 1024, kGrpChunks = 4; // measured on B200 at C2: 1 chunk 5.8 ms, 4: 4.9, 8: 5.0, 16: 5.3
     if (const char* e = getenv("VB_GRP_MAX_ROWS")) kGrpMaxRows = std::max(64, atoi(e));
+    if (const char* e = getenv("VB_GRP_CHUNKS")) kGrpChunks = std::max(1, std::min(32, atoi(e)));
     if (S.lmDataSize >= (1ll << 31)) throw std::runtime_error("landmark section exceeds 32-bit offsets");
     std::vector<int32_t> lmOrder = landmarkOrder(S);
     d.lmActive = nullptr; d.nLmActive = S.nP;
@@ -289,9 +293,11 @@ static void buildDeviceProblem(vb_problem& P) {
       d.lmActive = P.upload(mine);
     }
     P.ownedLandmarks = d.nLmActive;
-    std::vector<int64_t> grpLmPtr(1, 0), grpBlkPtr(1, 0);
-    std::vector<int32_t> grpLm, grpBlkOff, grpRowBlk, grpRowSub, grpRows;
+    std::vector<int64_t> grpBlkPtr(1, 0), grpMaskPtr(1, 0);
+    std::vector<int32_t> grpBlkOff, grpRowBlk, grpRowSub, grpRows, grpChunks, grpBlks;
+    std::vector<uint32_t> grpTileMask;
     std::vector<SchurTask> schurTasks;
+    int64_t nGrpLm = 0;
     {
       std::vector<int32_t> uni, merged, members;
       auto scal = [&](const std::vector<int32_t>& v) { int64_t s = 0; for (int32_t c : v) s += S.camStart[c + 1] - S.camStart[c]; return s; };
@@ -300,43 +306,51 @@ static void buildDeviceProblem(vb_problem& P) {
         const int32_t g = (int32_t)grpRows.size();
         const int32_t r = appendSource(uni.data(), (int64_t)uni.size(), false);
         grpRows.push_back(r);
-        for (int32_t p : members) grpLm.push_back(p);
-        grpLmPtr.push_back((int64_t)grpLm.size());
-        for (size_t b = 0; b < uni.size(); b++) {
+        nGrpLm += (int64_t)members.size();
+        const int nch = ((int)members.size() + kGrpMax - 1) / kGrpMax;
+        grpChunks.push_back(nch);
+        const size_t nblk = uni.size();
+        grpBlks.push_back((int32_t)nblk);
+        for (size_t b = 0; b < nblk; b++) {
           const int32_t dc = S.camStart[uni[b] + 1] - S.camStart[uni[b]];
           for (int32_t s = 0; s < dc; s++) { grpRowBlk.push_back((int32_t)b); grpRowSub.push_back(s); }
-          for (int l = 0; l < kGrpMax; l++) {
-            int32_t off = -1;
-            if (l < (int)members.size()) {
-              const int32_t p = members[l];
-              const int32_t* bb = S.lmRowCam.data() + S.lmRowPtr[p];
-              const int32_t* ee = S.lmRowCam.data() + S.lmRowPtr[p + 1];
-              const int32_t* it = std::lower_bound(bb, ee, uni[b]);
-              if (it != ee && *it == uni[b]) off = (int32_t)(S.lmOff[p] + (int64_t)S.lmRowOff[it - S.lmRowCam.data()] * 3);
-            }
-            grpBlkOff.push_back(off);
+        }
+        // offsets table: row (c * nblk + b), 32 member slots each
+        const size_t base = grpBlkOff.size();
+        grpBlkOff.resize(base + (size_t)nch * nblk * kGrpMax, -1);
+        for (size_t mi = 0; mi < members.size(); mi++) {
+          const int32_t p = members[mi];
+          const int c = (int)(mi / kGrpMax), l = (int)(mi % kGrpMax);
+          size_t b = 0;
+          for (int64_t k = S.lmRowPtr[p]; k < S.lmRowPtr[p + 1]; k++) { // both lists ascend
+            while (uni[b] != S.lmRowCam[k]) b++;
+            grpBlkOff[base + ((size_t)c * nblk + b) * kGrpMax + l] = (int32_t)(S.lmOff[p] + (int64_t)S.lmRowOff[k] * 3);
           }
         }
-        grpBlkPtr.push_back(grpBlkPtr.back() + (int64_t)uni.size());
-        // per 64-row tile: which member landmarks have rows in it; a tile pair only needs the landmarks
-        // present in both tiles (the others contribute exact zeros), pairs with none are dropped
+        grpBlkPtr.push_back(grpBlkPtr.back() + (int64_t)nch * (int64_t)nblk);
+        // per chunk and 64-row tile: which member slots have rows in it; a tile pair only needs, chunk by
+        // chunk, the landmarks present in both tiles (the others contribute exact zeros)
         const int nt = (r + 63) / 64;
-        std::vector<uint32_t> tileMask(nt, 0u);
+        const size_t mbase = grpTileMask.size();
+        grpTileMask.resize(mbase + (size_t)nch * nt, 0u);
         {
           int32_t q = 0;
-          const size_t base = grpBlkOff.size() - uni.size() * kGrpMax;
-          for (size_t b = 0; b < uni.size(); b++) {
+          for (size_t b = 0; b < nblk; b++) {
             const int32_t dc = S.camStart[uni[b] + 1] - S.camStart[uni[b]];
-            uint32_t m = 0;
-            for (int l = 0; l < kGrpMax; l++) if (grpBlkOff[base + b * kGrpMax + l] >= 0) m |= 1u << l;
-            for (int32_t s = 0; s < dc; s++) tileMask[(q + s) / 64] |= m;
+            for (int c = 0; c < nch; c++) {
+              uint32_t m = 0;
+              for (int l = 0; l < kGrpMax; l++) if (grpBlkOff[base + ((size_t)c * nblk + b) * kGrpMax + l] >= 0) m |= 1u << l;
+              for (int32_t s = 0; s < dc; s++) grpTileMask[mbase + (size_t)c * nt + (q + s) / 64] |= m;
+            }
             q += dc;
           }
         }
+        grpMaskPtr.push_back((int64_t)grpTileMask.size());
         for (int ti = 0; ti < nt; ti++)
           for (int tj = 0; tj <= ti; tj++) {
-            const uint32_t m = tileMask[ti] & tileMask[tj];
-            if (m) schurTasks.push_back({g, ti, tj, m});
+            uint32_t any = 0;
+            for (int c = 0; c < nch; c++) any |= grpTileMask[mbase + (size_t)c * nt + ti] & grpTileMask[mbase + (size_t)c * nt + tj];
+            if (any) schurTasks.push_back({g, ti, tj, any});
           }
         uni.clear(); members.clear();
       };
@@ -345,7 +359,7 @@ static void buildDeviceProblem(vb_problem& P) {
         const int32_t* ee = S.lmRowCam.data() + S.lmRowPtr[p + 1];
         merged.clear();
         std::set_union(uni.begin(), uni.end(), bb, ee, std::back_inserter(merged));
-        if (!members.empty() && ((int)members.size() == kGrpMax || scal(merged) > kGrpMaxRows)) {
+        if (!members.empty() && ((int)members.size() == kGrpMax * kGrpChunks || scal(merged) > kGrpMaxRows)) {
           flush();
           merged.assign(bb, ee);
         }
@@ -363,15 +377,16 @@ static void buildDeviceProblem(vb_problem& P) {
     d.updPtr = P.upload(updPtr); d.updColOff = P.upload(colOff); d.updStride = P.upload(stride);
     d.updTgt = P.upload(tgt); d.updGlobal = P.upload(glob); d.relPtr = P.upload(relPtr); d.rel = P.upload(rel);
     d.nG = (int64_t)grpRows.size();
-    d.grpLmPtr = P.upload(grpLmPtr); d.grpLm = P.upload(grpLm); d.grpBlkPtr = P.upload(grpBlkPtr);
+    d.grpBlkPtr = P.upload(grpBlkPtr); d.grpChunks = P.upload(grpChunks);
+    d.grpMaskPtr = P.upload(grpMaskPtr); d.grpTileMask = P.upload(grpTileMask);
     d.grpBlkOff = P.upload(grpBlkOff); d.grpRowBlk = P.upload(grpRowBlk); d.grpRowSub = P.upload(grpRowSub);
-    d.grpRows = P.upload(grpRows);
+    d.grpRows = P.upload(grpRows); d.grpBlks = P.upload(grpBlks);
     d.grpRowBase = updPtr[S.nL];
     P.schurTasks = P.upload(schurTasks); P.nSchurTasks = (int)schurTasks.size();
     if (getenv("VB_VERBOSE")) {
       double rs = 0; for (int32_t r : grpRows) rs += r;
       std::fprintf(stderr, "[viba_b200] landmark groups %zu (avg %.1f landmarks, avg %.0f union rows), schur tasks %zu, lumps %lld, levels %zu\n",
-                   grpRows.size(), grpLm.size() / std::max<double>(1, grpRows.size()), rs / std::max<double>(1, grpRows.size()),
+                   grpRows.size(), nGrpLm / std::max<double>(1, grpRows.size()), rs / std::max<double>(1, grpRows.size()),
                    schurTasks.size(), (long long)S.nL, S.levels.size());
     }
   }

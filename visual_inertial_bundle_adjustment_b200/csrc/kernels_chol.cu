@@ -260,19 +260,19 @@ __global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hes
 }
 
 // ---- K9b: Schur update of the camera system by landmark groups -------------------------------------
-// A group is <= 32 landmarks whose row blocks have a small union (<= 320 scalar rows).  Its dense
-// operand U = [union rows] x [3 G] holds W_p L_p^-T of every member (zeros where a landmark does not
-// see a block), gathered straight from the landmark panels; the update of the reduced system is then
-// -U U^T, tile by tile on DMMA, scattered with the same relative-index tables as the supernodes
-// (source index nL + g).  One reduction per target entry per group instead of one per landmark.
+// A group is a few chunks of <= 32 landmarks whose row blocks have a small union (<= 1024 scalar
+// rows).  Per chunk the dense operand U = [union rows] x [3 G] holds W_p L_p^-T of every member (zeros
+// where a landmark does not see a block), gathered straight from the landmark panels; the update of
+// the reduced system is -sum_chunks U U^T, accumulated tile by tile on DMMA (K loop over the chunks)
+// and scattered ONCE with the same relative-index tables as the supernodes (source index nL + g):
+// one reduction per target entry per group instead of one per landmark.
 constexpr int kGrpMax = 32;
 __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, double* hess, const SchurTask* tasks) {
   extern __shared__ double sm[];
   const SchurTask t = tasks[blockIdx.x];
   const int g = t.group;
   const int r = d.grpRows[g];
-  const int cnt = __popc(t.mask);           // landmarks present in both row tiles
-  const int K4 = (3 * cnt + 3) & ~3;
+  const int nch = d.grpChunks[g], nblk = d.grpBlks[g], nt = (r + kUpdTile - 1) / kUpdTile;
   constexpr int ld = 3 * kGrpMax + 4;       // 100
   double* As = sm;
   double* Bs = (t.ti == t.tj) ? sm : sm + (size_t)kUpdTile * ld;
@@ -281,32 +281,48 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
   const int64_t src = d.nL + g;
   const int64_t q0 = d.updPtr[src];
   const int64_t qg = q0 - d.grpRowBase;
-  const int32_t* blkOff = d.grpBlkOff + d.grpBlkPtr[g] * kGrpMax;
-  // gather: 4 threads per tile row; each loads the row's block/sub-row once and walks the present
-  // landmarks, copying their 3-double W rows straight from the landmark panels with cp.async
-  {
-    const int a = tid >> 2, kq = tid & 3;
+  const uint32_t* tmask = d.grpTileMask + d.grpMaskPtr[g];
+  const int rowBase = (warp >> 1) * 16, colBase = (warp & 1) * 32;
+  double acc[2][4][2];
+#pragma unroll
+  for (int m = 0; m < 2; m++)
+#pragma unroll
+    for (int n = 0; n < 4; n++) acc[m][n][0] = acc[m][n][1] = 0.0;
+  // this thread's gather row (4 threads per tile row) and its union block / sub-row, per side
+  const int a = tid >> 2, kq = tid & 3;
+  int rowBlk[2], rowSub3[2];
+#pragma unroll
+  for (int side = 0; side < 2; side++) {
+    const int q = (side == 0 ? i0 : j0) + a;
+    rowBlk[side] = q < r ? d.grpRowBlk[qg + q] : -1;
+    rowSub3[side] = q < r ? 3 * d.grpRowSub[qg + q] : 0;
+  }
+  // K loop over the chunks of the group: gather [tile rows x 3 present members], accumulate on DMMA
+  for (int c = 0; c < nch; c++) {
+    const uint32_t mask = tmask[c * nt + t.ti] & tmask[c * nt + t.tj];
+    if (!mask) continue;                     // uniform over the CTA
+    const int cnt = __popc(mask);            // members of this chunk present in both row tiles
+    const int K4 = (3 * cnt + 3) & ~3;
+    const int32_t* blkOff = d.grpBlkOff + (d.grpBlkPtr[g] + (int64_t)c * nblk) * kGrpMax;
+    __syncthreads();                         // the previous chunk's fragments have been read
     for (int side = 0; side < 2; side++) {
       if (side == 1 && t.ti == t.tj) break;
-      double* T = side == 0 ? As : Bs;
-      const int q = (side == 0 ? i0 : j0) + a;
-      double* o = T + a * ld;
+      double* o = (side == 0 ? As : Bs) + a * ld;
       if (kq == 0) for (int z = 3 * cnt; z < K4; z++) o[z] = 0.0;
-      if (q < r) {
+      if (rowBlk[side] >= 0) {
         // thread kq of the row's quad owns member slots 8 kq .. 8 kq + 7: their 8 panel offsets come in
         // with two 16-byte loads (one round trip), then every present member's 3-double W row is copied
         // with cp.async into its compacted column (rank among the present members)
-        const int4* bo = reinterpret_cast<const int4*>(blkOff + d.grpRowBlk[qg + q] * kGrpMax + 8 * kq);
-        const int sub3 = 3 * d.grpRowSub[qg + q];
+        const int4* bo = reinterpret_cast<const int4*>(blkOff + rowBlk[side] * kGrpMax + 8 * kq);
         const int4 o0 = bo[0], o1 = bo[1];
         const int offs[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
-        int k = __popc(t.mask & ((1u << (8 * kq)) - 1u));
+        int k = __popc(mask & ((1u << (8 * kq)) - 1u));
 #pragma unroll
         for (int z = 0; z < 8; z++) {
-          if (!((t.mask >> (8 * kq + z)) & 1u)) continue;
+          if (!((mask >> (8 * kq + z)) & 1u)) continue;
           const int off = offs[z];
           const bool v = off >= 0;
-          const double* w = v ? hess + off + sub3 : hess;
+          const double* w = v ? hess + off + rowSub3[side] : hess;
           cp_async8(o + 3 * k, w, v); cp_async8(o + 3 * k + 1, w + 1, v); cp_async8(o + 3 * k + 2, w + 2, v);
           k++;
         }
@@ -314,16 +330,10 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
         for (int k = kq; k < cnt; k += 4) { o[3 * k] = 0.0; o[3 * k + 1] = 0.0; o[3 * k + 2] = 0.0; }
       }
     }
+    cp_async_wait_all();
+    __syncthreads();
+    dmmaABt<2, 4>(As, ld, Bs, ld, K4, rowBase, colBase, acc);
   }
-  cp_async_wait_all();
-  __syncthreads();
-  const int rowBase = (warp >> 1) * 16, colBase = (warp & 1) * 32;
-  double acc[2][4][2];
-#pragma unroll
-  for (int m = 0; m < 2; m++)
-#pragma unroll
-    for (int n = 0; n < 4; n++) acc[m][n][0] = acc[m][n][1] = 0.0;
-  dmmaABt<2, 4>(As, ld, Bs, ld, K4, rowBase, colBase, acc);
   const int32_t* rel = d.rel + d.relPtr[src];
   // two-phase scatter: every index lookup first (independent loads in flight together), then the reductions
   double* dst[4][2][2];

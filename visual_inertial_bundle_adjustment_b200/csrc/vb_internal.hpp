@@ -83,13 +83,15 @@ struct DevSolver {
   int* solveCnt;            // [nL] arrival counters of the solve kernels (kept zero between calls)
   // landmark groups of the Schur update (scatter source index nL + g in the upd*/rel tables)
   int64_t nG;
-  const int64_t* grpLmPtr;   // [nG+1] into grpLm
-  const int32_t* grpLm;      // landmark ids
-  const int64_t* grpBlkPtr;  // [nG+1] first union row block of the group
-  const int32_t* grpBlkOff;  // [(grpBlkPtr[g] + b) * 32 + l] offset of landmark l's W block at union block b, or -1
+  const int32_t* grpChunks;  // [nG] chunks of <= 32 member landmarks
+  const int64_t* grpBlkPtr;  // [nG+1] first row of the group's offset table (rows of 32 ints)
+  const int32_t* grpBlkOff;  // [(grpBlkPtr[g] + c * nblk + b) * 32 + l] offset of member l of chunk c at union block b, or -1
+  const int64_t* grpMaskPtr; // [nG+1] into grpTileMask
+  const uint32_t* grpTileMask; // [grpMaskPtr[g] + c * ntiles + t] members of chunk c with rows in 64-row tile t
   const int32_t* grpRowBlk;  // per union scalar row (index updPtr[nL+g] - grpRowBase + q): union block
   const int32_t* grpRowSub;  //   ... and the row inside that block
   const int32_t* grpRows;    // [nG] union scalar rows
+  const int32_t* grpBlks;    // [nG] union row blocks
   int64_t grpRowBase;        // updPtr[nL]
   // shard view: landmarks this rank owns (null = all nP)
   const int32_t* lmActive; int64_t nLmActive;

@@ -156,7 +156,7 @@ int vb_problem_create_sharded(vb_ctx* ctx, const vb_graph_desc* g, int rank, int
 /* host-only: owner rank of every landmark (indexed by registration index, n = num_points) */
 int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, int64_t n);
 /* out8 = {rank, nranks, owned landmarks, owned visual factors, reduced-camera-system doubles summed per
- * factorisation, collective calls so far, collective bytes so far, landmark-section doubles} */
+ * factorisation, collective calls so far, collective bytes so far, lumps of this rank's own subtrees} */
 int vb_shard_info(const vb_problem* p, double* out8);
 
 /* Solver::order(), dataSize() (Optimizer.cpp:339-340,777,783-784) and symbolic-phase outputs */

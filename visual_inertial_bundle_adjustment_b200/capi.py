@@ -217,7 +217,7 @@ class Problem:
         out = np.zeros(8)
         _ck(self.lib, self.lib.vb_shard_info(self.h, _d(out)))
         return dict(zip(["rank", "nranks", "owned_landmarks", "owned_visual", "reduced_doubles", "coll_calls",
-                         "coll_bytes", "landmark_doubles"], out))
+                         "coll_bytes", "own_lumps"], out))
 
     def work(self):
         a, b, c = C.c_double(), C.c_double(), C.c_double()

@@ -30,9 +30,15 @@ struct vb_problem {
   int* errFlag = nullptr;
   int64_t* blockVar = nullptr;
   int64_t* diagOff = nullptr; int32_t* diagStride = nullptr; int32_t* diagSize = nullptr;
-  int32_t* levelLumps = nullptr; LevelTask* levelTasks = nullptr; SchurTask* schurTasks = nullptr; int nSchurTasks = 0;
-  std::vector<int64_t> levelLumpOff, levelTaskOff;
-  std::vector<int32_t> levelMaxBelow, levelMaxWidth;
+  SchurTask* schurTasks = nullptr; int nSchurTasks = 0;
+  // level schedules of the supernodal kernels: [0] the lumps of this rank's own subtrees (multi-GPU only),
+  // [1] the shared top of the elimination tree (one GPU: every lump)
+  struct Sched {
+    int32_t* lumps = nullptr; LevelTask* tasks = nullptr;
+    std::vector<int64_t> lumpOff, taskOff;
+    std::vector<int32_t> maxBelow, maxWidth;
+  } sched[2];
+  double* camKeep = nullptr; // multi-GPU: 1 on the camera scalars whose value this rank contributes to a sum
   int64_t varDataLen = 0;
   double visualBytes = 0;
   // shard state (vb_problem_create_sharded): this rank evaluates `owned` factors / landmarks and the
@@ -105,6 +111,72 @@ static std::vector<int32_t> planOwners(const Symbolic& S, int nranks) {
   }
   for (int64_t p = 0; p < S.nP; p++) if (S.lmRowPtr[p + 1] == S.lmRowPtr[p]) owner[p] = (int32_t)(p % nranks);
   return owner;
+}
+
+// Subtree-to-rank plan of the supernodal Cholesky ("the elimination tree is split into
+// independent subtrees with the top separator factored on one GPU" — here on every GPU, replicated).
+// Starting from the roots, the heaviest subtree is opened (its root becomes shared, its children become
+// subtrees) until no subtree carries more than 1/(3 nranks) of the flops; the subtrees are then dealt to
+// the ranks largest first.  The panels are re-laid out so that the shared lumps form one contiguous tail.
+static void planLumpOwners(Symbolic& S, int nranks) {
+  const int64_t nL = S.nL;
+  S.lumpOwner.assign(nL, -1);
+  S.sharedOff = S.dataSize;
+  if (nranks <= 1 || nL == 0) return;
+  std::vector<double> work(nL), sub(nL);
+  std::vector<std::vector<int32_t>> kids(nL);
+  double total = 0;
+  for (int64_t L = 0; L < nL; L++) {
+    const double w = S.lumpWidth[L], r = S.lumpRows[L] - S.lumpWidth[L];
+    work[L] = sub[L] = w * w * w / 3.0 + w * w * r + w * r * r + 1.0;
+    total += work[L];
+  }
+  for (int64_t L = 0; L < nL; L++) { // parents come after their children in elimination order
+    const int32_t p = S.lumpParent[L];
+    if (p >= 0) { if (p <= L) throw std::runtime_error("elimination tree is not topologically ordered"); sub[p] += sub[L]; kids[p].push_back((int32_t)L); }
+  }
+  std::vector<int32_t> roots;
+  std::vector<char> shared(nL, 0), closed(nL, 0);
+  for (int64_t L = 0; L < nL; L++) if (S.lumpParent[L] < 0) roots.push_back((int32_t)L);
+  const double cap = total / (3.0 * nranks);
+  while (true) {
+    int best = -1;
+    for (size_t i = 0; i < roots.size(); i++)
+      if (!closed[roots[i]] && sub[roots[i]] > cap && (best < 0 || sub[roots[i]] > sub[roots[best]])) best = (int)i;
+    if (best < 0) break;
+    const int32_t q = roots[best];
+    if (kids[q].empty()) { closed[q] = 1; continue; }
+    shared[q] = 1;
+    roots[best] = roots.back(); roots.pop_back();
+    for (int32_t k : kids[q]) roots.push_back(k);
+  }
+  std::sort(roots.begin(), roots.end(), [&](int32_t a, int32_t b) { return sub[a] != sub[b] ? sub[a] > sub[b] : a < b; });
+  std::vector<double> load(nranks, 0.0);
+  std::vector<int32_t> rootOwner(nL, -1);
+  for (int32_t q : roots) {
+    const int r = (int)(std::min_element(load.begin(), load.end()) - load.begin());
+    load[r] += sub[q];
+    rootOwner[q] = r;
+  }
+  for (int64_t L = nL - 1; L >= 0; L--) { // owners flow down from the subtree roots
+    if (shared[L]) continue;
+    if (rootOwner[L] >= 0) S.lumpOwner[L] = rootOwner[L];
+    else S.lumpOwner[L] = S.lumpOwner[S.lumpParent[L]];
+  }
+  int64_t off = S.lmDataSize;
+  for (int pass = 0; pass < 2; pass++) {
+    if (pass == 1) S.sharedOff = off;
+    for (int64_t L = 0; L < nL; L++)
+      if ((S.lumpOwner[L] < 0) == (pass == 1)) { S.lumpOff[L] = off; off += (int64_t)S.lumpRows[L] * S.lumpWidth[L]; }
+  }
+  if (off != S.dataSize) throw std::runtime_error("panel re-layout changed the data size");
+  if (getenv("VB_VERBOSE")) {
+    double sw = 0; int64_t ns = 0;
+    for (int64_t L = 0; L < nL; L++) if (S.lumpOwner[L] < 0) { sw += work[L]; ns++; }
+    std::fprintf(stderr, "[viba_b200] cholesky plan: %zu subtrees over %d ranks, %lld shared lumps (%.1f%% of the flops, %.1f%% of the panels), max rank load %.1f%%\n",
+                 roots.size(), nranks, (long long)ns, 100.0 * sw / total, 100.0 * (S.dataSize - S.sharedOff) / std::max<int64_t>(1, S.dataSize - S.lmDataSize),
+                 100.0 * *std::max_element(load.begin(), load.end()) / total);
+  }
 }
 
 static void buildDeviceProblem(vb_problem& P) {
@@ -391,24 +463,36 @@ static void buildDeviceProblem(vb_problem& P) {
     }
   }
   // level schedules
-  {
+  for (int which = 0; which < 2; which++) {
+    vb_problem::Sched& sc = P.sched[which];
     std::vector<int32_t> lumps; std::vector<LevelTask> tasks;
     for (const auto& lv : S.levels) {
-      P.levelLumpOff.push_back((int64_t)lumps.size());
-      P.levelTaskOff.push_back((int64_t)tasks.size());
+      sc.lumpOff.push_back((int64_t)lumps.size());
+      sc.taskOff.push_back((int64_t)tasks.size());
       int32_t mb = 0, mw = 0;
       for (int32_t L : lv) {
+        const int32_t own = S.lumpOwner.empty() ? -1 : S.lumpOwner[L];
+        if (which == 0 ? own != P.rank : own >= 0) continue;
         lumps.push_back(L);
         const int r = S.lumpRows[L] - S.lumpWidth[L];
         mb = std::max(mb, r); mw = std::max(mw, S.lumpWidth[L]);
         const int nt = (r + 63) / 64;
         for (int ti = 0; ti < nt; ti++) for (int tj = 0; tj <= ti; tj++) tasks.push_back({L, ti, tj});
       }
-      P.levelMaxBelow.push_back(mb); P.levelMaxWidth.push_back(mw);
+      sc.maxBelow.push_back(mb); sc.maxWidth.push_back(mw);
     }
-    P.levelLumpOff.push_back((int64_t)lumps.size());
-    P.levelTaskOff.push_back((int64_t)tasks.size());
-    P.levelLumps = P.upload(lumps); P.levelTasks = P.upload(tasks);
+    sc.lumpOff.push_back((int64_t)lumps.size());
+    sc.taskOff.push_back((int64_t)tasks.size());
+    sc.lumps = P.upload(lumps); sc.tasks = P.upload(tasks);
+  }
+  if (sharded) { // camera scalars this rank contributes to the sums of the distributed solves
+    std::vector<double> keep(S.camStart[S.nC], 0.0);
+    for (int64_t L = 0; L < S.nL; L++) {
+      const int32_t own = S.lumpOwner[L];
+      const double k = own == P.rank || (own < 0 && P.rank == 0) ? 1.0 : 0.0;
+      for (int32_t q = S.camStart[S.lumpFirst[L]]; q < S.camStart[S.lumpFirst[L + 1]]; q++) keep[q] = k;
+    }
+    P.camKeep = P.upload(keep);
   }
   P.hess = P.alloc<double>(S.dataSize);
   P.grad = P.alloc<double>(S.order); P.step = P.alloc<double>(S.order); P.gradNew = P.alloc<double>(S.order);
@@ -503,6 +587,7 @@ int vb_problem_create_sharded(vb_ctx* ctx, const vb_graph_desc* g, int rank, int
   if (const char* e = getenv("VB_MAX_LUMP_WIDTH")) opt.maxLumpWidth = std::max(8, std::min(128, atoi(e)));
   if (const char* e = getenv("VB_ND_LEAF_BLOCKS")) opt.ndLeafBlocks = atoi(e);
   buildSymbolic(P->g, opt, &P->S);
+  planLumpOwners(P->S, getenv("VB_REPLICATED_CHOLESKY") ? 1 : nranks);
   buildDeviceProblem(*P);
   *out = P.release();
   VB_CATCH
@@ -524,13 +609,13 @@ int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, i
   VB_CATCH
 }
 // {rank, nranks, owned landmarks, owned visual factors, doubles of the reduced camera system summed
-//  over ranks per factorisation, collective calls so far, collective bytes so far, landmark-section doubles}
+//  over ranks per factorisation, collective calls so far, collective bytes so far, lumps in this rank's own subtrees}
 int vb_shard_info(const vb_problem* p, double* out8) {
   VB_TRY
   requireProblem(p);
   out8[0] = p->rank; out8[1] = p->nranks; out8[2] = (double)p->ownedLandmarks; out8[3] = (double)p->ownedVisual;
   out8[4] = (double)(p->S.dataSize - p->S.lmDataSize); out8[5] = (double)p->collCalls; out8[6] = p->collBytes;
-  out8[7] = (double)p->S.lmDataSize;
+  out8[7] = (double)p->sched[0].lumpOff.back(); // lumps of this rank's own subtrees (0 on one GPU)
   VB_CATCH
 }
 
@@ -570,7 +655,8 @@ int64_t vb_num_launches_per_iteration(const vb_problem* p) { // kernels one vb_l
   if (!p) return -1;
   int64_t n = 0;
   for (const auto& st : p->ds) n += st.count > 0 ? (st.orderLm && st.twoPass ? 3 : 2) : 0; // grad/Hess (visual: two passes) + cost
-  const int64_t lv = (int64_t)p->S.levels.size();
+  int64_t lv = 0;
+  for (const auto& sc : p->sched) for (size_t i = 0; i + 1 < sc.lumpOff.size(); i++) lv += sc.lumpOff[i + 1] > sc.lumpOff[i];
   return n + 2 /*damp, step=grad*/ + 1 + 2 * lv /*factor*/ + 2 + 2 * lv /*solve*/ + 2 /*dot, negate*/ + 1 /*apply*/;
 }
 int vb_get_param_start(const vb_problem* p, int64_t* out, int64_t n) {
@@ -678,45 +764,85 @@ int vb_step_from_grad(vb_problem* p) {
   VB_CATCH
 }
 
+static void factorLevels(vb_problem* p, int which) {
+  cudaStream_t s = p->ctx->stream;
+  const vb_problem::Sched& sc = p->sched[which];
+  for (size_t lv = 0; lv + 1 < sc.lumpOff.size(); lv++) {
+    const int nl = (int)(sc.lumpOff[lv + 1] - sc.lumpOff[lv]);
+    const int nt = (int)(sc.taskOff[lv + 1] - sc.taskOff[lv]);
+    if (nl == 0) continue;
+    launchLumpFactor(p->sol, p->hess, sc.lumps + sc.lumpOff[lv], nl, sc.maxBelow[lv], sc.maxWidth[lv], p->errFlag, s);
+    launchLumpUpdate(p->sol, p->hess, sc.tasks + sc.taskOff[lv], nt, sc.maxWidth[lv], nl > 1, s);
+  }
+}
 static void factorAsync(vb_problem* p, cudaEvent_t afterSchur) {
   cudaStream_t s = p->ctx->stream;
+  const Symbolic& S = p->S;
   VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
   launchSchur(p->sol, p->hess, p->schurTasks, p->nSchurTasks, p->errFlag, s);
   // sharded: every rank eliminated its own landmarks from its own partial camera system; the sum over
-  // ranks is the reduced camera system (the exchange step of SURVEY.md §8e), factored by all ranks
-  collective(p, VB_COLL_SUM, p->hess + p->S.lmDataSize, p->S.dataSize - p->S.lmDataSize);
+  // ranks is the reduced camera system (the exchange step of SURVEY.md §8e).  The panels of the
+  // rank-owned subtrees are summed now; the shared top keeps accumulating partial sums (local Schur
+  // part + the updates of this rank's subtrees) and is summed once, after the subtrees are factored.
+  collective(p, VB_COLL_SUM, p->hess + S.lmDataSize, S.sharedOff - S.lmDataSize);
   if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
-  for (size_t lv = 0; lv + 1 < p->levelLumpOff.size(); lv++) {
-    const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
-    const int nt = (int)(p->levelTaskOff[lv + 1] - p->levelTaskOff[lv]);
-    launchLumpFactor(p->sol, p->hess, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxBelow[lv], p->levelMaxWidth[lv], p->errFlag, s);
-    launchLumpUpdate(p->sol, p->hess, p->levelTasks + p->levelTaskOff[lv], nt, p->levelMaxWidth[lv], nl > 1, s);
+  if (p->nranks > 1) {
+    factorLevels(p, 0);
+    collective(p, VB_COLL_SUM, p->hess + S.sharedOff, S.dataSize - S.sharedOff);
   }
+  factorLevels(p, 1);
 }
 static void checkNumeric(vb_problem* p) {
   int flag = 0;
   VB_CUDA(cudaMemcpyAsync(&flag, p->errFlag, sizeof(int), cudaMemcpyDeviceToHost, p->ctx->stream));
   syncCheck(p);
+  if (p->nranks > 1) { // every rank must leave the iteration together: share the verdict
+    p->accHost[60] = (double)flag;
+    VB_CUDA(cudaMemcpyAsync(p->acc + 60, p->accHost + 60, sizeof(double), cudaMemcpyHostToDevice, p->ctx->stream));
+    collective(p, VB_COLL_SUM, p->acc + 60, 1);
+    VB_CUDA(cudaMemcpyAsync(p->accHost + 60, p->acc + 60, sizeof(double), cudaMemcpyDeviceToHost, p->ctx->stream));
+    syncCheck(p);
+    if (flag == 0 && p->accHost[60] != 0.0) throw std::domain_error("factor: not positive definite on another rank");
+  }
   if (flag == 1) throw std::domain_error("factor: landmark block not positive definite");
   if (flag == 2) throw std::domain_error("factor: reduced camera system not positive definite");
 }
+static void solveLevels(vb_problem* p, double* vec, int which, bool forward) {
+  cudaStream_t s = p->ctx->stream;
+  const vb_problem::Sched& sc = p->sched[which];
+  const int nLv = (int)sc.lumpOff.size() - 1;
+  for (int i = 0; i < nLv; i++) {
+    const int lv = forward ? i : nLv - 1 - i;
+    const int nl = (int)(sc.lumpOff[lv + 1] - sc.lumpOff[lv]);
+    if (nl == 0) continue;
+    if (forward) launchSolveLumpsFwd(p->sol, p->hess, vec, sc.lumps + sc.lumpOff[lv], nl, sc.maxWidth[lv], sc.maxBelow[lv], nl > 1, s);
+    else launchSolveLumpsBwd(p->sol, p->hess, vec, sc.lumps + sc.lumpOff[lv], nl, sc.maxWidth[lv], sc.maxBelow[lv], s);
+  }
+}
 static void solveAsync(vb_problem* p, double* vec) {
   cudaStream_t s = p->ctx->stream;
-  const int nLv = (int)p->levelLumpOff.size() - 1;
   const int64_t nCam = p->S.order - p->sol.camVec0;
+  double* cam = vec + p->sol.camVec0;
   launchSolveLandmarksFwd(p->sol, p->hess, vec, s);
-  collective(p, VB_COLL_SUM, vec + p->sol.camVec0, nCam); // partial camera gradients - owned landmark eliminations
-  for (int lv = 0; lv < nLv; lv++) {
-    const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
-    launchSolveLumpsFwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], p->levelMaxBelow[lv], nl > 1, s);
+  if (p->nranks > 1) {
+    collective(p, VB_COLL_SUM, cam, nCam);           // partial camera gradients - owned landmark eliminations
+    // forward over this rank's subtrees: keep only the scalars this rank contributes (its subtrees; the
+    // shared top on rank 0), so that one sum yields the solved subtrees of every rank and the complete
+    // right-hand side of the shared top
+    launchVecOp(4, cam, p->camKeep, 0, nCam, nullptr, s);
+    solveLevels(p, vec, 0, true);
+    collective(p, VB_COLL_SUM, cam, nCam);
   }
-  for (int lv = nLv - 1; lv >= 0; lv--) {
-    const int nl = (int)(p->levelLumpOff[lv + 1] - p->levelLumpOff[lv]);
-    launchSolveLumpsBwd(p->sol, p->hess, vec, p->levelLumps + p->levelLumpOff[lv], nl, p->levelMaxWidth[lv], p->levelMaxBelow[lv], s);
+  solveLevels(p, vec, 1, true);
+  solveLevels(p, vec, 1, false);
+  if (p->nranks > 1) {
+    solveLevels(p, vec, 0, false);
+    // every camera scalar from exactly one rank: one bit pattern of the camera step everywhere
+    launchVecOp(4, cam, p->camKeep, 0, nCam, nullptr, s);
+    collective(p, VB_COLL_SUM, cam, nCam);
   }
-  collective(p, VB_COLL_BCAST0, vec + p->sol.camVec0, nCam); // one bit pattern of the camera step on all ranks
   launchSolveLandmarksBwd(p->sol, p->hess, vec, s);
-  collective(p, VB_COLL_SUM, vec, p->sol.camVec0);           // owned landmark steps -> full step everywhere
+  collective(p, VB_COLL_SUM, vec, p->sol.camVec0);   // owned landmark steps -> full step everywhere
   p->partial[vec == p->step ? 0 : vec == p->gradNew ? 1 : 2] = false;
 }
 #define VB_CATCH_NUMERIC                                                             \

@@ -677,7 +677,7 @@ __global__ void dampingKernel(double* hess, const int64_t* diagOff, const int32_
   for (int a = 0; a < n; a++) { double* p = D + (int64_t)a * st + a; *p = *p * (1.0 + lambda) + add; }
 }
 
-// op: 0 a=b ; 1 a*=s ; 2 out[0]+=a.b ; 3 a=0
+// op: 0 a=b ; 1 a*=s ; 2 out[0]+=a.b ; 3 a=0 ; 4 a*=b (elementwise)
 __global__ void vecOpKernel(int op, double* a, const double* b, double s, int64_t n, double* out) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   double acc[1] = {0.0};
@@ -685,6 +685,7 @@ __global__ void vecOpKernel(int op, double* a, const double* b, double s, int64_
     if (op == 0) a[i] = b[i];
     else if (op == 1) a[i] *= s;
     else if (op == 2) acc[0] = fma(a[i], b[i], acc[0]);
+    else if (op == 4) a[i] *= b[i];
     else a[i] = 0.0;
   }
   if (op == 2) blockReduceAdd<1>(acc, out);

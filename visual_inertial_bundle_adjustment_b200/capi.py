@@ -23,7 +23,7 @@ EXPORTS = [
     "vb_optimize", "vb_lm_iteration_timed", "vb_download_vars", "vb_upload_vars", "vb_download_grad",
     "vb_download_step", "vb_download_hess", "vb_upload_hess", "vb_upload_grad", "vb_download_factor_cache",
     "vb_upload_store_aux", "vb_upload_store_consts", "vb_measure_dmma_peak",
-    "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info",
+    "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info", "vb_shard_factor_owners",
 ]
 # int fn(void* user, int op, double* dev_ptr, int64_t count, void* cuda_stream)  (include/viba_b200.h)
 COLLECTIVE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p)
@@ -51,6 +51,8 @@ def load():
                                               C.c_void_p, C.POINTER(C.c_void_p)]
     lib.vb_shard_plan.argtypes = [C.POINTER(G.vb_graph_desc), C.c_int, C.POINTER(C.c_int32), C.c_int64]
     lib.vb_shard_info.argtypes = [C.c_void_p, _dp]
+    lib.vb_shard_factor_owners.argtypes = [C.POINTER(G.vb_graph_desc), C.c_int, C.c_int32, C.POINTER(C.c_int32), C.c_int64,
+                                           C.POINTER(C.c_int32)]
     lib.vb_problem_create.argtypes = [C.c_void_p, C.POINTER(G.vb_graph_desc), C.POINTER(C.c_void_p)]
     lib.vb_problem_destroy.argtypes = [C.c_void_p]
     lib.vb_get_param_start.argtypes = [C.c_void_p, _ip, C.c_int64]
@@ -125,6 +127,16 @@ def shard_plan(graph, nranks):
     out = np.zeros(graph.num_points, np.int32)
     _ck(lib, lib.vb_shard_plan(C.byref(desc), nranks, out.ctypes.data_as(C.POINTER(C.c_int32)), out.size))
     return out
+
+
+def shard_factor_owners(graph, nranks, store):
+    """Host-only: (owner rank of every factor of `store`, plan aligned with the elimination tree?)."""
+    lib = load()
+    desc = graph.desc()
+    out = np.zeros(graph.stores[store].count, np.int32)
+    al = C.c_int32()
+    _ck(lib, lib.vb_shard_factor_owners(C.byref(desc), nranks, store, out.ctypes.data_as(C.POINTER(C.c_int32)), out.size, C.byref(al)))
+    return out, bool(al.value)
 
 
 class Context:

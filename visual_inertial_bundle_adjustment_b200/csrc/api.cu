@@ -38,6 +38,7 @@ struct vb_problem {
     std::vector<int64_t> lumpOff, taskOff;
     std::vector<int32_t> maxBelow, maxWidth;
   } sched[2];
+  double* dampMask = nullptr; // multi-GPU: 1 on the blocks whose diagonal gets this rank's "+ lambda"
   double* camKeep = nullptr; // multi-GPU: 1 on the camera scalars whose value this rank contributes to a sum
   int64_t varDataLen = 0;
   double visualBytes = 0;
@@ -47,6 +48,7 @@ struct vb_problem {
   vb_collective_fn coll = nullptr; void* collUser = nullptr;
   bool partial[3] = {false, false, true}; // step, gradNew, grad: holds only this rank's contributions
   int64_t ownedLandmarks = 0, ownedVisual = 0, collCalls = 0; double collBytes = 0;
+  bool alignedPlan = true; // every contribution to a non-shared panel is local to its owner (planOwners)
   cudaEvent_t ev[10];
 
   template <typename T>
@@ -93,26 +95,6 @@ static std::vector<int32_t> landmarkOrder(const Symbolic& S) {
   });
   return lmOrder;
 }
-// Shard plan: every landmark has one owning rank, which evaluates ALL of its
-// observations and eliminates it; the owner ranges are contiguous pieces of landmarkOrder() balanced
-// by a per-landmark cost m^2 + 300 m (m = camera-side rows: Schur flops + evaluation work).
-static std::vector<int32_t> planOwners(const Symbolic& S, int nranks) {
-  std::vector<int32_t> owner(S.nP, 0);
-  if (nranks <= 1) return owner;
-  const std::vector<int32_t> lmOrder = landmarkOrder(S);
-  auto weight = [&](int32_t p) { const double m = (double)((S.lmOff[p + 1] - S.lmOff[p]) / 3 - 3); return m * m + 300.0 * m; };
-  double total = 0;
-  for (int32_t p : lmOrder) total += weight(p);
-  double run = 0;
-  for (int32_t p : lmOrder) {
-    const double w = weight(p);
-    owner[p] = (int32_t)std::min<double>(nranks - 1, std::floor((run + 0.5 * w) / std::max(total, 1.0) * nranks));
-    run += w;
-  }
-  for (int64_t p = 0; p < S.nP; p++) if (S.lmRowPtr[p + 1] == S.lmRowPtr[p]) owner[p] = (int32_t)(p % nranks);
-  return owner;
-}
-
 // Subtree-to-rank plan of the supernodal Cholesky ("the elimination tree is split into
 // independent subtrees with the top separator factored on one GPU" — here on every GPU, replicated).
 // Starting from the roots, the heaviest subtree is opened (its root becomes shared, its children become
@@ -121,7 +103,7 @@ static std::vector<int32_t> planOwners(const Symbolic& S, int nranks) {
 static void planLumpOwners(Symbolic& S, int nranks) {
   const int64_t nL = S.nL;
   S.lumpOwner.assign(nL, -1);
-  S.sharedOff = S.dataSize;
+  S.sharedOff = S.lmDataSize; // everything shared: the whole reduced system is one summed region
   if (nranks <= 1 || nL == 0) return;
   std::vector<double> work(nL), sub(nL);
   std::vector<std::vector<int32_t>> kids(nL);
@@ -150,6 +132,7 @@ static void planLumpOwners(Symbolic& S, int nranks) {
     roots[best] = roots.back(); roots.pop_back();
     for (int32_t k : kids[q]) roots.push_back(k);
   }
+  if ((int)roots.size() < nranks) return; // too small a tree to give every rank a subtree: replicated factorisation
   std::sort(roots.begin(), roots.end(), [&](int32_t a, int32_t b) { return sub[a] != sub[b] ? sub[a] > sub[b] : a < b; });
   std::vector<double> load(nranks, 0.0);
   std::vector<int32_t> rootOwner(nL, -1);
@@ -179,6 +162,78 @@ static void planLumpOwners(Symbolic& S, int nranks) {
   }
 }
 
+// Shard plan, aligned with the subtree plan of the Cholesky (planLumpOwners, called
+// first).  Nested dissection separates the Schur-filled camera graph, so the cameras any landmark (or
+// any factor) touches lie on ONE root-to-leaf path of the elimination tree: all of its non-shared
+// cameras belong to the same rank.  That rank owns the landmark: it evaluates ALL of its observations
+// and eliminates it, and every contribution to a non-shared panel is local — only the shared top of
+// the reduced system is summed over ranks.  Landmarks (factors) that touch shared cameras only are
+// dealt in contiguous, weight-balanced pieces (round robin for factors).  `aligned` comes back false if
+// some landmark or factor straddles two ranks (not expected; the subtree panels are then summed too).
+static std::vector<int32_t> planOwners(const Symbolic& S, int nranks, bool* aligned) {
+  std::vector<int32_t> owner(S.nP, 0);
+  if (aligned) *aligned = true;
+  if (nranks <= 1) return owner;
+  const std::vector<int32_t> lmOrder = landmarkOrder(S);
+  auto weight = [&](int32_t p) { const double m = (double)((S.lmOff[p + 1] - S.lmOff[p]) / 3 - 3); return m * m + 300.0 * m; };
+  std::vector<int32_t> loose; // landmarks that see shared cameras only
+  std::vector<double> load(nranks, 0.0);
+  double looseW = 0, total = 0;
+  for (int32_t p : lmOrder) {
+    int32_t o = -1;
+    for (int64_t k = S.lmRowPtr[p]; k < S.lmRowPtr[p + 1]; k++) {
+      const int32_t lo = S.lumpOwner.empty() ? -1 : S.lumpOwner[S.camLump[S.lmRowCam[k]]];
+      if (lo < 0) continue;
+      if (o < 0) o = lo; else if (o != lo && aligned) *aligned = false;
+    }
+    const double w = weight(p);
+    total += w;
+    if (o >= 0) { owner[p] = o; load[o] += w; } else { loose.push_back(p); looseW += w; }
+  }
+  // the loose landmarks fill the ranks up to the mean load, in contiguous pieces
+  std::vector<double> room(nranks);
+  double roomSum = 0;
+  for (int r = 0; r < nranks; r++) { room[r] = std::max(0.0, total / nranks - load[r]); roomSum += room[r]; }
+  if (roomSum <= 0) { for (int r = 0; r < nranks; r++) room[r] = 1.0; roomSum = nranks; }
+  int cur = 0;
+  double used = 0, run = 0;
+  for (int32_t p : loose) {
+    const double w = weight(p);
+    while (cur + 1 < nranks && run + 0.5 * w > (used + room[cur]) / roomSum * looseW) { used += room[cur]; cur++; }
+    owner[p] = cur;
+    run += w;
+  }
+  for (int64_t p = 0; p < S.nP; p++) if (S.lmRowPtr[p + 1] == S.lmRowPtr[p]) owner[p] = (int32_t)(p % nranks);
+  return owner;
+}
+// owner rank of every factor of one store: visual stores follow their landmark; the others follow the
+// rank of the non-shared cameras they touch (shared only: round robin)
+static std::vector<int32_t> planFactorOwners(const HostGraph& g, const Symbolic& S, const HostGraph::Store& hs,
+                                             const std::vector<int32_t>& lmOwner, int nranks, bool* aligned) {
+  std::vector<int32_t> out(hs.count, 0);
+  if (nranks <= 1) return out;
+  const bool visual = hs.type == VB_F_VISUAL || hs.type == VB_F_VISUAL_RS;
+  bool ok = true;
+#pragma omp parallel for schedule(static) reduction(&& : ok)
+  for (int64_t k = 0; k < hs.count; k++) {
+    const int32_t* v = &hs.vars[k * hs.nvars];
+    if (visual) { const int64_t ii = g.index[v[0]]; out[k] = ii < 0 ? (int32_t)(k % nranks) : lmOwner[S.pos[ii]]; continue; }
+    int32_t o = -1;
+    for (int i = 0; i < hs.nvars; i++) {
+      const int64_t ii = g.index[v[i]];
+      if (ii < 0) continue;
+      const int64_t pos = S.pos[ii];
+      if (pos < S.nP) { const int32_t lo = lmOwner[pos]; if (o < 0) o = lo; else if (o != lo) ok = false; continue; }
+      const int32_t lo = S.lumpOwner.empty() ? -1 : S.lumpOwner[S.camLump[pos - S.nP]];
+      if (lo < 0) continue;
+      if (o < 0) o = lo; else if (o != lo) ok = false;
+    }
+    out[k] = o >= 0 ? o : (int32_t)(k % nranks);
+  }
+  if (!ok && aligned) *aligned = false;
+  return out;
+}
+
 static void buildDeviceProblem(vb_problem& P) {
   const HostGraph& g = P.g;
   const Symbolic& S = P.S;
@@ -204,9 +259,9 @@ static void buildDeviceProblem(vb_problem& P) {
     }
     P.diagOff = P.upload(off); P.diagStride = P.upload(st); P.diagSize = P.upload(sz);
   }
-  const std::vector<int32_t> owner = planOwners(S, P.nranks);
+  bool aligned = true;
+  const std::vector<int32_t> owner = planOwners(S, P.nranks, &aligned);
   const bool sharded = P.nranks > 1;
-  auto ownerOfVar = [&](int32_t v) { const int64_t ii = g.index[v]; return ii < 0 ? 0 : (ii < S.nP ? owner[S.pos[ii]] : 0); };
   // factor stores + scatter maps
   P.ds.resize(g.stores.size());
   for (size_t s = 0; s < g.stores.size(); s++) {
@@ -247,13 +302,20 @@ static void buildDeviceProblem(vb_problem& P) {
     // VB_VISUAL_TWO_PASS=0/1 overrides.
     d.twoPass = (double)S.lmDataSize * 8.0 > 1.5e9 ? 1 : 0;
     if (const char* e = getenv("VB_VISUAL_TWO_PASS")) d.twoPass = atoi(e) != 0;
-    // shard view of a small store: an equal contiguous slice per rank
-    d.kBegin = hs.count * P.rank / P.nranks; d.nActive = hs.count * (P.rank + 1) / P.nranks - d.kBegin; d.active = nullptr;
+    // shard view: the factors this rank owns (planFactorOwners)
+    d.kBegin = 0; d.nActive = hs.count; d.active = nullptr;
+    const std::vector<int32_t> fOwner = planFactorOwners(g, S, hs, owner, P.nranks, &aligned);
+    if (sharded && hs.type != VB_F_VISUAL && hs.type != VB_F_VISUAL_RS) {
+      std::vector<int32_t> mine;
+      for (int64_t k = 0; k < hs.count; k++) if (fOwner[k] == P.rank) mine.push_back((int32_t)k);
+      d.nActive = (int64_t)mine.size();
+      d.active = P.upload(mine);
+    }
     if ((hs.type == VB_F_VISUAL || hs.type == VB_F_VISUAL_RS) && hs.count > 0) {
       if (hs.count >= (1ll << 31)) throw std::runtime_error("visual store too large for 32-bit factor indices");
       std::vector<int32_t> order;
       order.reserve(hs.count / P.nranks + 16);
-      for (int64_t k = 0; k < hs.count; k++) if (!sharded || ownerOfVar(hs.vars[k * nv]) == P.rank) order.push_back((int32_t)k);
+      for (int64_t k = 0; k < hs.count; k++) if (!sharded || fOwner[k] == P.rank) order.push_back((int32_t)k);
       const int64_t nOwn = (int64_t)order.size();
       d.kBegin = 0; d.nActive = nOwn;
       if (sharded) d.active = P.upload(order); // ascending factor index: the cost kernel's order
@@ -290,6 +352,8 @@ static void buildDeviceProblem(vb_problem& P) {
     if (hs.type == VB_F_VISUAL) P.visualBytes += 224.0 * hs.count; // SURVEY.md §8d algorithmic bytes/obs
     if (hs.type == VB_F_VISUAL_RS) P.visualBytes += 296.0 * hs.count;
   }
+  P.alignedPlan = aligned;
+  if (sharded && !aligned && getenv("VB_VERBOSE")) std::fprintf(stderr, "[viba_b200] shard plan not aligned with the elimination tree: subtree panels are summed too\n");
   // solver structure
   DevSolver& d = P.sol;
   d.nP = S.nP; d.nC = S.nC; d.nL = S.nL;
@@ -493,6 +557,14 @@ static void buildDeviceProblem(vb_problem& P) {
       for (int32_t q = S.camStart[S.lumpFirst[L]]; q < S.camStart[S.lumpFirst[L + 1]]; q++) keep[q] = k;
     }
     P.camKeep = P.upload(keep);
+    std::vector<double> dm(S.nB, 1.0);
+    for (int64_t b = 0; b < S.nB; b++) {
+      const int64_t pos = S.pos[b];
+      if (pos < S.nP) continue;
+      const int32_t own = S.lumpOwner[S.camLump[pos - S.nP]];
+      dm[b] = own == P.rank || (own < 0 && P.rank == 0) ? 1.0 : 0.0;
+    }
+    P.dampMask = P.upload(dm);
   }
   P.hess = P.alloc<double>(S.dataSize);
   P.grad = P.alloc<double>(S.order); P.step = P.alloc<double>(S.order); P.gradNew = P.alloc<double>(S.order);
@@ -595,17 +667,35 @@ int vb_problem_create_sharded(vb_ctx* ctx, const vb_graph_desc* g, int rank, int
 int vb_problem_destroy(vb_problem* p) { delete p; return VB_OK; }
 
 // host-only shard plan: owner rank of every landmark (registration index) for an nranks-way split
-int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, int64_t n) {
-  VB_TRY
-  if (!g || !landmark_owner || nranks < 1) throw std::invalid_argument("bad argument");
-  HostGraph hg; hg.load(g);
+static void hostPlan(const vb_graph_desc* g, int nranks, HostGraph& hg, Symbolic& S) {
+  hg.load(g);
   SymbolicOptions opt;
   if (const char* e = getenv("VB_MAX_LUMP_WIDTH")) opt.maxLumpWidth = std::max(8, std::min(128, atoi(e)));
   if (const char* e = getenv("VB_ND_LEAF_BLOCKS")) opt.ndLeafBlocks = atoi(e);
-  Symbolic S; buildSymbolic(hg, opt, &S);
+  buildSymbolic(hg, opt, &S);
+  planLumpOwners(S, getenv("VB_REPLICATED_CHOLESKY") ? 1 : nranks);
+}
+int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, int64_t n) {
+  VB_TRY
+  if (!g || !landmark_owner || nranks < 1) throw std::invalid_argument("bad argument");
+  HostGraph hg; Symbolic S;
+  hostPlan(g, nranks, hg, S);
   if (n != S.nP) throw std::invalid_argument("length must be num_points");
-  const std::vector<int32_t> owner = planOwners(S, nranks);
+  const std::vector<int32_t> owner = planOwners(S, nranks, nullptr);
   for (int64_t i = 0; i < S.nP; i++) landmark_owner[i] = owner[S.pos[i]];
+  VB_CATCH
+}
+int vb_shard_factor_owners(const vb_graph_desc* g, int nranks, int32_t store, int32_t* factor_owner, int64_t n, int32_t* aligned) {
+  VB_TRY
+  if (!g || !factor_owner || nranks < 1 || store < 0 || store >= g->num_stores) throw std::invalid_argument("bad argument");
+  HostGraph hg; Symbolic S;
+  hostPlan(g, nranks, hg, S);
+  if (n != hg.stores[store].count) throw std::invalid_argument("length must be the store's factor count");
+  bool al = true;
+  const std::vector<int32_t> owner = planOwners(S, nranks, &al);
+  const std::vector<int32_t> fo = planFactorOwners(hg, S, hg.stores[store], owner, nranks, &al);
+  std::copy(fo.begin(), fo.end(), factor_owner);
+  if (aligned) *aligned = al ? 1 : 0;
   VB_CATCH
 }
 // {rank, nranks, owned landmarks, owned visual factors, doubles of the reduced camera system summed
@@ -753,7 +843,7 @@ int vb_eval_cost(vb_problem* p, int comparable, double* cost, vb_cost_stats* sta
 int vb_damp(vb_problem* p, double lambda) {
   VB_TRY
   requireProblem(p);
-  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->S.nP, p->rank == 0 ? lambda : 0.0, p->ctx->stream);
+  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->dampMask, p->ctx->stream);
   VB_CATCH
 }
 int vb_step_from_grad(vb_problem* p) {
@@ -781,10 +871,11 @@ static void factorAsync(vb_problem* p, cudaEvent_t afterSchur) {
   VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
   launchSchur(p->sol, p->hess, p->schurTasks, p->nSchurTasks, p->errFlag, s);
   // sharded: every rank eliminated its own landmarks from its own partial camera system; the sum over
-  // ranks is the reduced camera system (the exchange step of SURVEY.md §8e).  The panels of the
-  // rank-owned subtrees are summed now; the shared top keeps accumulating partial sums (local Schur
-  // part + the updates of this rank's subtrees) and is summed once, after the subtrees are factored.
-  collective(p, VB_COLL_SUM, p->hess + S.lmDataSize, S.sharedOff - S.lmDataSize);
+  // ranks is the reduced camera system (the exchange step of SURVEY.md §8e).  With the tree-aligned
+  // shard plan every contribution to the panels of a rank-owned subtree is already local to that rank;
+  // the shared top keeps accumulating partial sums (local Schur part + the updates of this rank's
+  // subtrees) and is summed once, after the subtrees are factored.
+  if (!p->alignedPlan) collective(p, VB_COLL_SUM, p->hess + S.lmDataSize, S.sharedOff - S.lmDataSize);
   if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
   if (p->nranks > 1) {
     factorLevels(p, 0);
@@ -955,7 +1046,7 @@ int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) {
     const double prevCost = evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
     finalCost = prevCost;
     if (iterationNum == 0) initialCost = prevCost;
-    launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, damping, p->S.nP, p->rank == 0 ? damping : 0.0, s);
+    launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, damping, p->dampMask, s);
     launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
     factorAsync(p, nullptr);
     checkNumeric(p);
@@ -1065,7 +1156,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   VB_CUDA(cudaEventRecord(e[0], s));
   evalGradHess(p, p->grad, 1, 1, 0, false); // also clears the evaluation error word
   VB_CUDA(cudaEventRecord(e[1], s));
-  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->S.nP, p->rank == 0 ? lambda : 0.0, s);
+  launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->dampMask, s);
   launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
   VB_CUDA(cudaEventRecord(e[2], s));
   factorAsync(p, e[3]);

@@ -666,14 +666,15 @@ __global__ void __launch_bounds__(128) applyStepKernel(DevVars V, const int64_t*
 
 // Optimizer::addDamping (Optimizer.cpp:136-146): d <- d (1 + lambda) + lambda on every diagonal scalar
 __global__ void dampingKernel(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize,
-                              int64_t nB, double lambda, int64_t nP, double lambdaAddCam) {
-  // sharded runs: camera-side diagonals are partial sums over ranks, so only rank 0 adds the "+ lambda"
-  // term there (the update is affine in d); landmark diagonals are complete on their owner
+                              int64_t nB, double lambda, const double* addMask) {
+  // sharded runs: the diagonals of the shared top are partial sums over ranks, so only rank 0 adds the
+  // "+ lambda" term there (the update is affine in d); a subtree's diagonals are complete on its owner,
+  // landmark diagonals on theirs (addMask: 1 where this rank adds, null = everywhere)
   const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (b >= nB) return;
   double* D = hess + diagOff[b];
   const int st = diagStride[b], n = diagSize[b];
-  const double add = b < nP ? lambda : lambdaAddCam;
+  const double add = addMask ? lambda * addMask[b] : lambda;
   for (int a = 0; a < n; a++) { double* p = D + (int64_t)a * st + a; *p = *p * (1.0 + lambda) + add; }
 }
 
@@ -762,8 +763,8 @@ void launchApplyStep(const DevVars& v, const int64_t* blockVar, int64_t nB, cons
   VB_CUDA(cudaGetLastError());
 }
 void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize, int64_t nB,
-                   double lambda, int64_t nP, double lambdaAddCam, cudaStream_t s) {
-  dampingKernel<<<gridFor(nB, 256), 256, 0, s>>>(hess, diagOff, diagStride, diagSize, nB, lambda, nP, lambdaAddCam);
+                   double lambda, const double* addMask, cudaStream_t s) {
+  dampingKernel<<<gridFor(nB, 256), 256, 0, s>>>(hess, diagOff, diagStride, diagSize, nB, lambda, addMask);
   VB_CUDA(cudaGetLastError());
 }
 void launchVecOp(int op, double* a, const double* b, double sc, int64_t n, double* out, cudaStream_t st) {

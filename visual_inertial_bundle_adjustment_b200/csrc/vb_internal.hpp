@@ -104,7 +104,7 @@ void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* 
 void launchCost(const DevStore& st, const DevVars& v, int comparable, double* acc /* cost,total,invalid,prevInvalid */, cudaStream_t s);
 void launchApplyStep(const DevVars& v, const int64_t* blockVar, int64_t nB, const double* step, double* ratioAcc, cudaStream_t s);
 void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize, int64_t nB,
-                   double lambda, int64_t nP, double lambdaAddCam, cudaStream_t s);
+                   double lambda, const double* addMask, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
 void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s);

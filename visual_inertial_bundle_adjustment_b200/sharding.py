@@ -143,17 +143,15 @@ def run_threaded(graph, nranks, fn, device=0):
 
 # ---- the shard rule on the host graph -----------------------------------------------------------
 def owned_factors(graph, owner, rank, nranks):
-    """Per store: indices of the factors rank `rank` evaluates.  Visual stores follow the owner of
-    their landmark (argument 0); every other store is cut into equal contiguous slices."""
+    """Per store: indices of the factors rank `rank` evaluates (the library's own plan, host-only):
+    visual factors follow the owner of their landmark, the others the rank whose subtree they touch."""
     out = []
-    for st in graph.stores:
-        n = st.count
+    for i, st in enumerate(graph.stores):
+        fo, _ = capi.shard_factor_owners(graph, nranks, i)
         if st.type in (G.F_VISUAL, G.F_VISUAL_RS):
             idx = graph.var_index[st.vars[:, 0]]
-            own = np.where(idx >= 0, owner[np.clip(idx, 0, len(owner) - 1)], 0)
-            out.append(np.nonzero(own == rank)[0])
-        else:
-            out.append(np.arange(n * rank // nranks, n * (rank + 1) // nranks))
+            assert np.array_equal(fo[idx >= 0], owner[idx[idx >= 0]])  # all observations of a landmark on its owner
+        out.append(np.nonzero(fo == rank)[0])
     return out
 
 

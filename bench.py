@@ -6,9 +6,9 @@ Aria-like sessions, the metric of BASELINE.json.  One "step" = one accepted-path
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
 
 N>1 is launched by torchrun (one rank per GPU): every rank holds the SAME session, landmarks (with
-all of their observations) are split over the ranks, and the reduced camera system / camera
-right-hand side / landmark steps are summed over NCCL at the exchange points of the C ABI's
-collective hook.  Total work is fixed as N grows: "scaling": "strong".
+all of their observations), factors and the subtrees of the reduced system's elimination tree are
+split over the ranks; the shared top of the reduced system, the camera right-hand side / step and the
+landmark steps are summed over NCCL at the exchange points of the C ABI's collective hook.  Total work is fixed as N grows: "scaling": "strong".
 """
 import argparse
 import json
@@ -236,9 +236,9 @@ def main():
             "gpu_launches": int(p.launches_per_iteration * a.steps * world), "clocks": sampler.summary()}
     if world > 1:
         per_it = coll.calls / max(1, (warmup + 2 * a.steps + 2))
-        line["sharding"] = {"plan": "landmark owners (all observations of a landmark on its owner), small factor stores sliced; "
-                                    "reduced camera system + camera rhs + landmark steps all-reduced over NCCL; Cholesky of the "
-                                    "reduced system replicated", "per_rank_landmarks": shard["per_rank_landmarks"],
+        line["sharding"] = {"plan": "elimination-tree subtrees of the reduced camera system dealt to the ranks under a replicated "
+                                    "shared top; landmarks (with all their observations) and factors follow the rank whose subtree "
+                                    "they touch; only the shared top, the camera rhs/step and the landmark steps are summed over NCCL", "per_rank_landmarks": shard["per_rank_landmarks"],
                             "per_rank_observations": shard["per_rank_observations"],
                             "allreduce_bytes_per_iteration": int(coll.bytes / max(1, (warmup + 2 * a.steps + 2))),
                             "collectives_per_iteration": round(per_it, 2)}

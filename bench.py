@@ -223,6 +223,17 @@ def main():
                 "peak_source": "FP64 mma.sync m8n8k4 probe measured in this run (no FP64 entry in MEASURED_PEAKS.json)",
                 "algorithmic_flops": work["schur_flops"] + work["chol_flops"], "ms": fac_ms}
     roof_fac["frac"] = roof_fac["achieved"] / dmma if dmma > 0 else None
+    # DRAM traffic of the same kernels from the committed ncu --set full capture of this workload (N=1)
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
+            tr = json.load(f).get(a.workload)
+        if tr and world == 1:
+            roof_gh["traffic"] = tr["gradHessVisualChunkKernel<GS>+<RS>"]
+            roof_gh["traffic_note"] = "bytes per iteration (one launch of each visual kernel); " + tr["source"]
+            roof_fac["traffic"] = tr["schurGroupUpdateKernel"]
+            roof_fac["traffic_note"] = "schurGroupUpdateKernel only, bytes per launch; " + tr["source"]
+    except Exception:
+        pass
     dominant = roof_gh if gh_ms >= fac_ms else roof_fac
     line = {"metric": metric, "value": ms_dev, "unit": "ms/iteration", "n_gpus": a.gpus, "steps": a.steps, "warmup": warmup,
             "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",

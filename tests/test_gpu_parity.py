@@ -50,7 +50,7 @@ def gpu_dense_hessian(p, o):
     return H
 
 
-@pytest.fixture(scope="module", params=["tiny", "small", "tiny_rs", "small_rs"])
+@pytest.fixture(scope="module", params=["tiny", "small", "tiny_rs", "small_rs", "tiny_lc", "small_lc_rs"])
 def pair(request, ctx, oracle):
     s = synth.make_session(**synth.CONFIGS[request.param])
     o = Oracle(oracle, s.graph)

@@ -29,7 +29,7 @@ def one_iteration(p, rank):
     return dict(c0=c0, md=md, step=step, ratios=ratios, c1=c1, stats=stats, vars=v, info=p.shard_info())
 
 
-@pytest.mark.parametrize("name,nranks", [("small", 2), ("small_rs", 2), ("small_rs", 3), ("tiny_rs", 4)])
+@pytest.mark.parametrize("name,nranks", [("small", 2), ("small_rs", 2), ("small_rs", 3), ("tiny_rs", 4), ("small_lc_rs", 2)])
 def test_sharded_iteration_matches_single(name, nranks):
     s = synth.make_session(**synth.CONFIGS[name])
     ctx = capi.Context(0)
@@ -54,7 +54,7 @@ def test_sharded_iteration_matches_single(name, nranks):
         assert np.array_equal(o["step"], outs[0]["step"]) and np.array_equal(o["vars"], outs[0]["vars"])
 
 
-@pytest.mark.parametrize("name,nranks,leaf", [("small_rs", 2, 12), ("small_rs", 4, 8), ("small", 3, 10)])
+@pytest.mark.parametrize("name,nranks,leaf", [("small_rs", 2, 12), ("small_rs", 4, 8), ("small", 3, 10), ("small_lc_rs", 2, 10)])
 def test_distributed_cholesky_subtrees(name, nranks, leaf, monkeypatch):
     """Small nested-dissection leaves give the small sessions a branching elimination tree, so every rank
     owns real subtrees (factored and solved only there) under a shared top."""

@@ -21,7 +21,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-@pytest.mark.parametrize("name,nranks", [("small", 2), ("small_rs", 3), ("tiny_rs", 4), ("small", 8)])
+@pytest.mark.parametrize("name,nranks", [("small", 2), ("small_rs", 3), ("tiny_rs", 4), ("small", 8), ("small_lc_rs", 2)])
 def test_shard_plan_partitions_everything_once(name, nranks):
     g = synth.make_session(**synth.CONFIGS[name]).graph
     owner = capi.shard_plan(g, nranks)
@@ -94,7 +94,7 @@ def _worker(rank, world, port, name, out_dir):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,world", [("tiny_rs", 2), ("tiny", 2)])
+@pytest.mark.parametrize("name,world", [("tiny_rs", 2), ("tiny", 2), ("tiny_lc", 2)])
 def test_exchange_algebra_gloo(tmp_path, oracle, name, world):
     import torch.multiprocessing as mp
     mp.spawn(_worker, args=(world, _free_port(), name, str(tmp_path)), nprocs=world, join=True)

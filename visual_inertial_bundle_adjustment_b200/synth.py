@@ -148,12 +148,23 @@ def fisheye624_project(p, prm):
 
 
 # ---- ground-truth trajectory (closed form, ~1 m/s walk) -------------------------------------------
+_LOOP_PERIOD = None  # set by make_session(loop_period_s=...): closed circular walk that revisits places
+
+
 def _traj(t):
     """body(IMU0) pose in world: position, velocity, quaternion q_wb."""
-    p = np.stack([0.9 * t + 0.5 * np.sin(0.3 * t), 2.0 * np.sin(0.15 * t), 0.1 * np.sin(0.9 * t)], -1)
-    v = np.stack([0.9 + 0.15 * np.cos(0.3 * t), 0.3 * np.cos(0.15 * t), 0.09 * np.cos(0.9 * t)], -1)
     z = np.zeros_like(t)
-    q_yaw = quat_from_rotvec(np.stack([z, z, 0.3 * np.sin(0.1 * t)], -1))
+    if _LOOP_PERIOD is None:
+        p = np.stack([0.9 * t + 0.5 * np.sin(0.3 * t), 2.0 * np.sin(0.15 * t), 0.1 * np.sin(0.9 * t)], -1)
+        v = np.stack([0.9 + 0.15 * np.cos(0.3 * t), 0.3 * np.cos(0.15 * t), 0.09 * np.cos(0.9 * t)], -1)
+        q_yaw = quat_from_rotvec(np.stack([z, z, 0.3 * np.sin(0.1 * t)], -1))
+    else:  # circle walked at 0.9 m/s, heading along the tangent: the same places come back every period
+        om = 2 * np.pi / _LOOP_PERIOD
+        R = 0.9 / om
+        th = om * t
+        p = np.stack([R * np.cos(th), R * np.sin(th), 0.1 * np.sin(0.9 * t)], -1)
+        v = np.stack([-R * om * np.sin(th), R * om * np.cos(th), 0.09 * np.cos(0.9 * t)], -1)
+        q_yaw = quat_from_rotvec(np.stack([z, z, th + np.pi / 2], -1))
     q0 = quat_from_rotvec(np.array([-np.pi / 2, 0.0, 0.0]))  # body z (optical axis) -> world +y
     q_wob = quat_from_rotvec(np.stack([0.05 * np.sin(1.1 * t), 0.05 * np.sin(0.7 * t + 1.0),
                                        0.08 * np.sin(0.9 * t + 2.0)], -1))
@@ -179,9 +190,22 @@ class Session:
 
 def make_session(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, seed=42, frame_hz=10.0,
                  window_s=5.0, outlier_frac=0.02, pixel_sigma=1.0 / 0.7, init_noise=1.0, rgb=False, n_imus=1,
-                 rgb_obs_frac=0.35):
+                 rgb_obs_frac=0.35, loop_period_s=None, lc_frac=0.0):
     """Aria-Gen1-like session: 2 global-shutter SLAM cameras + IMU 0, every calibration state
-    variable in 5 s windows with random-walk and factory-prior factors."""
+    variable in 5 s windows with random-walk and factory-prior factors.
+    `loop_period_s` + `lc_frac`: closed walk where that fraction of the landmarks is observed again
+    on later laps (loop-closure tracks, BASELINE C4)."""
+    global _LOOP_PERIOD
+    _LOOP_PERIOD = loop_period_s
+    try:
+        return _make_session(duration_s, n_landmarks, n_obs, seed, frame_hz, window_s, outlier_frac, pixel_sigma,
+                             init_noise, rgb, n_imus, rgb_obs_frac, loop_period_s, lc_frac)
+    finally:
+        _LOOP_PERIOD = None
+
+
+def _make_session(duration_s, n_landmarks, n_obs, seed, frame_hz, window_s, outlier_frac, pixel_sigma, init_noise, rgb,
+                  n_imus, rgb_obs_frac, loop_period_s, lc_frac):
     rng = np.random.default_rng(seed)
     n_rigs = int(round(duration_s * frame_hz))
     times = np.arange(n_rigs) / frame_hz
@@ -214,6 +238,15 @@ def make_session(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, seed=42, f
         X = pl + quat_rotate(ql, dirb * d[:, None])
         tau = tau_mean * rg.uniform(0.5, 1.5, nl)
         lm, rig = _pairs_in_window(t_l, tau, times)
+        if loop_period_s and lc_frac > 0:  # loop closures: the same landmark seen again on later laps
+            again = np.nonzero(rg.random(nl) < lc_frac)[0]
+            k = 1
+            while k * loop_period_s < duration_s:
+                lm2, rig2 = _pairs_in_window(t_l[again] + k * loop_period_s, tau[again], times)
+                lm, rig = np.concatenate([lm, again[lm2]]), np.concatenate([rig, rig2])
+                k += 1
+            o = np.lexsort((rig, lm))
+            lm, rig = lm[o], rig[o]
         lm = np.repeat(lm, n_cams)
         rig = np.repeat(rig, n_cams)
         cam = np.tile(np.arange(n_cams), lm.size // n_cams)
@@ -356,6 +389,9 @@ CONFIGS = {
     "small": dict(duration_s=12.0, n_landmarks=800, n_obs=24000),
     "tiny_rs": dict(duration_s=4.0, n_landmarks=60, n_obs=1200, window_s=2.0, rgb=True, n_imus=2),
     "small_rs": dict(duration_s=12.0, n_landmarks=800, n_obs=24000, rgb=True, n_imus=2),
+    # loop closures (BASELINE C4 ingredient): a closed walk, 30 % of the landmarks re-observed on later laps
+    "tiny_lc": dict(duration_s=6.0, n_landmarks=80, n_obs=1500, window_s=2.0, loop_period_s=3.0, lc_frac=0.3),
+    "small_lc_rs": dict(duration_s=16.0, n_landmarks=800, n_obs=24000, rgb=True, n_imus=2, loop_period_s=8.0, lc_frac=0.3),
     "c1_60s": dict(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000),
     "c1_60s_rs": dict(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, rgb=True, n_imus=2),
     "c2_5min_rs": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000, rgb=True, n_imus=2),

@@ -132,6 +132,10 @@ def main():
         print(json.dumps(line))
         return 0
 
+    # stdout carries exactly ONE JSON line: library chatter on fd 1 (e.g. NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     from visual_inertial_bundle_adjustment_b200 import capi
     dist = None
     if world > 1:
@@ -255,7 +259,9 @@ def main():
                             "collectives_per_iteration": round(per_it, 2)}
     if world == 1 and not a.no_cpu_baseline:
         line["cpu_baseline"] = cpu_leg(a.workload, 2, 1)
-    print(json.dumps(line))
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
+    print(json.dumps(line), flush=True)
     p.close()
     ctx.close()
     if dist is not None:

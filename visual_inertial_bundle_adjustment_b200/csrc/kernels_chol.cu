@@ -125,21 +125,24 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
   // inverses of the 32x32 diagonal blocks of L (for the DMMA trsm): thread c owns column c
   double* inv = d.diagInv + (int64_t)d.camStart[d.lumpFirst[L]] * 32;
   if (tid < w) {
-    const int c = tid, b0 = c & ~31, bEnd = min(b0 + 32, w);
+    // column-oriented forward substitution on e_c with the column in registers (compile-time indices
+    // only: no local memory); the updates of one step are independent FMAs, L is read by broadcast
+    const int c = tid, b0 = c & ~31, nbk = min(32, w - b0), cc = c - b0;
+    const double* Lb = A + b0 * ld + b0;
     double z[32];
 #pragma unroll
-    for (int i = 0; i < 32; i++) z[i] = 0.0;
+    for (int i = 0; i < 32; i++) z[i] = (i == cc) ? 1.0 : 0.0;
 #pragma unroll
-    for (int ii = 0; ii < 32; ii++) {
-      const int i = b0 + ii;
-      if (i < c || i >= bEnd) continue;
-      double s = (i == c) ? 1.0 : 0.0;
+    for (int i = 0; i < 32; i++) {
+      if (i < nbk) {
+        const double zi = (i >= cc) ? z[i] * dinvAll[b0 + i] : 0.0;
+        z[i] = zi;
 #pragma unroll
-      for (int kk = 0; kk < 32; kk++) if (kk < ii && b0 + kk >= c) s = fma(-A[i * ld + b0 + kk], z[kk], s);
-      z[ii] = s * dinvAll[i];
+        for (int k = i + 1; k < 32; k++) if (k < nbk) z[k] = fma(-zi, Lb[k * ld + i], z[k]);
+      }
     }
 #pragma unroll
-    for (int ii = 0; ii < 32; ii++) if (b0 + ii < bEnd) inv[(int64_t)(b0 + ii) * 32 + (c - b0)] = z[ii];
+    for (int i = 0; i < 32; i++) if (i < nbk) inv[(int64_t)(b0 + i) * 32 + cc] = z[i];
   }
 }
 

@@ -396,6 +396,9 @@ CONFIGS = {
     "c1_60s_rs": dict(duration_s=60.0, n_landmarks=20000, n_obs=1_000_000, rgb=True, n_imus=2),
     "c2_5min_rs": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000, rgb=True, n_imus=2),
     "c2_5min": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000),
+    # C4 ingredients at the C2 scale: RS camera, two IMUs and loop closures (three 100 s laps, 2 % of the
+    # landmarks seen again on every later lap): 9x the Cholesky flops of c2_5min_rs through loop-closure fill
+    "c4_5min_lc": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000, rgb=True, n_imus=2, loop_period_s=100.0, lc_frac=0.02),
     "c3_20min": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000),
     "c3_20min_rs": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000, rgb=True, n_imus=2),
 }

@@ -560,7 +560,7 @@ static void buildDeviceProblem(vb_problem& P) {
     std::vector<double> dm(S.nB, 1.0);
     for (int64_t b = 0; b < S.nB; b++) {
       const int64_t pos = S.pos[b];
-      if (pos < S.nP) continue;
+      if (pos < S.nP) { if (owner[pos] != P.rank) dm[b] = -1.0; continue; } // not this rank's landmark: untouched
       const int32_t own = S.lumpOwner[S.camLump[pos - S.nP]];
       dm[b] = own == P.rank || (own < 0 && P.rank == 0) ? 1.0 : 0.0;
     }
@@ -791,7 +791,14 @@ int vb_get_work(const vb_problem* p, double* schur_flops, double* chol_flops, do
 static double evalGradHess(vb_problem* p, double* gvec, int with_hess, int update_cache, int dont_retry, bool sync) {
   cudaStream_t s = p->ctx->stream;
   VB_CUDA(cudaMemsetAsync(gvec, 0, p->S.order * sizeof(double), s));
-  if (with_hess) VB_CUDA(cudaMemsetAsync(p->hess, 0, p->S.dataSize * sizeof(double), s));
+  if (with_hess) {
+    if (p->nranks > 1) { // only what this rank writes: its landmarks' panels and the camera part
+      launchZeroOwnedPanels(p->sol, p->hess, s);
+      VB_CUDA(cudaMemsetAsync(p->hess + p->S.lmDataSize, 0, (p->S.dataSize - p->S.lmDataSize) * sizeof(double), s));
+    } else {
+      VB_CUDA(cudaMemsetAsync(p->hess, 0, p->S.dataSize * sizeof(double), s));
+    }
+  }
   VB_CUDA(cudaMemsetAsync(p->acc + kAccCost, 0, 2 * sizeof(double), s)); // cost + evaluation error word
   for (const DevStore& st : p->ds) launchGradHess(st, p->dv, gvec, with_hess ? p->hess : nullptr, update_cache, dont_retry, p->acc + kAccCost, s);
   p->partial[gvec == p->step ? 0 : gvec == p->gradNew ? 1 : 2] = p->nranks > 1;

@@ -674,6 +674,7 @@ __global__ void dampingKernel(double* hess, const int64_t* diagOff, const int32_
   if (b >= nB) return;
   double* D = hess + diagOff[b];
   const int st = diagStride[b], n = diagSize[b];
+  if (addMask && addMask[b] < 0.0) return; // a landmark of another rank
   const double add = addMask ? lambda * addMask[b] : lambda;
   for (int a = 0; a < n; a++) { double* p = D + (int64_t)a * st + a; *p = *p * (1.0 + lambda) + add; }
 }

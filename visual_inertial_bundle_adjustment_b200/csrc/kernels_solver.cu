@@ -49,6 +49,23 @@ __global__ void __launch_bounds__(256) schurPrepKernel(DevSolver d, double* hess
   }
 }
 
+// sharded runs: zero only the landmark panels this rank owns (the others are never touched), one warp
+// per landmark
+__global__ void __launch_bounds__(256) zeroOwnedPanelsKernel(DevSolver d, double* hess) {
+  const int64_t ip = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (ip >= d.nLmActive) return;
+  const int64_t p = d.lmActive ? d.lmActive[ip] : ip;
+  double* base = hess + d.lmOff[p];
+  const int n = (int)(d.lmOff[p + 1] - d.lmOff[p]);
+  for (int i = lane; i < n; i += 32) base[i] = 0.0;
+}
+void launchZeroOwnedPanels(const DevSolver& d, double* hess, cudaStream_t s) {
+  if (d.nLmActive == 0) return;
+  zeroOwnedPanelsKernel<<<(int)((d.nLmActive * 32 + 255) / 256), 256, 0, s>>>(d, hess);
+  VB_CUDA(cudaGetLastError());
+}
+
 // ---- K11: solves -------------------------------------------------------------------------------------
 // forward over landmarks: y_p = L_pp^-1 g_p ; g_cam -= W'_p y_p
 __global__ void __launch_bounds__(256) solveLmFwdKernel(DevSolver d, const double* hess, double* vec) {

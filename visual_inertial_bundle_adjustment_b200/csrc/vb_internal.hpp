@@ -107,6 +107,7 @@ void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStri
                    double lambda, const double* addMask, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
+void launchZeroOwnedPanels(const DevSolver& d, double* hess, cudaStream_t s);
 void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s);
 void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s);
 void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s);

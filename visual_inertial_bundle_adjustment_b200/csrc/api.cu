@@ -146,11 +146,11 @@ static void planLumpOwners(Symbolic& S, int nranks) {
     if (rootOwner[L] >= 0) S.lumpOwner[L] = rootOwner[L];
     else S.lumpOwner[L] = S.lumpOwner[S.lumpParent[L]];
   }
-  int64_t off = S.lmDataSize;
+  int64_t off = (S.lmDataSize + 1) & ~int64_t(1); // same even-sized slots as buildSymbolic
   for (int pass = 0; pass < 2; pass++) {
     if (pass == 1) S.sharedOff = off;
     for (int64_t L = 0; L < nL; L++)
-      if ((S.lumpOwner[L] < 0) == (pass == 1)) { S.lumpOff[L] = off; off += (int64_t)S.lumpRows[L] * S.lumpWidth[L]; }
+      if ((S.lumpOwner[L] < 0) == (pass == 1)) { S.lumpOff[L] = off; off += ((int64_t)S.lumpRows[L] * S.lumpWidth[L] + 1) & ~int64_t(1); }
   }
   if (off != S.dataSize) throw std::runtime_error("panel re-layout changed the data size");
   if (getenv("VB_VERBOSE")) {
@@ -405,7 +405,7 @@ static void buildDeviceProblem(vb_problem& P) {
     };
     int64_t dl = 0;
     for (int64_t L = 0; L < S.nL; L++) {
-      diagLOff[L] = dl; dl += (int64_t)S.lumpWidth[L] * S.lumpWidth[L];
+      diagLOff[L] = dl; dl += ((int64_t)S.lumpWidth[L] * S.lumpWidth[L] + 1) & ~int64_t(1);
       appendSource(S.lumpRowCam.data() + S.lumpRowPtr[L], S.lumpRowPtr[L + 1] - S.lumpRowPtr[L], true);
     }
     // ---- landmark groups for the Schur update: landmarks sorted by their first camera block are

@@ -270,11 +270,29 @@ VB_DEV void cp_async8(double* smemDst, const double* gsrc, bool valid) {
   const int sz = valid ? 8 : 0; // src-size 0 => zero fill, nothing is read
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(s), "l"(gsrc), "r"(sz) : "memory");
 }
+// 16-byte variant (L2 only): srcBytes in {0, 8, 16}, the rest of the 16 bytes is zero filled
+VB_DEV void cp_async16(double* smemDst, const double* gsrc, int srcBytes) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smemDst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(s), "l"(gsrc), "r"(srcBytes) : "memory");
+}
 VB_DEV void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 // dst[rowsPad x colsPad] (leading dimension ld) <- src[rows x cols] (row stride srcStride), zero padded.
 // Warps take rows, lanes take columns.  Call cp_async_wait_all() + __syncthreads() before use.
 VB_DEV void loadTileAsync(double* dst, int ld, int rowsPad, int colsPad, const double* src, int64_t srcStride, int rows, int cols) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  // 16-byte copies when every row of source and destination is 16-byte aligned (half the LDGSTS count)
+  if ((((uintptr_t)src | (uintptr_t)dst) & 15) == 0 && ((srcStride | ld | colsPad) & 1) == 0) {
+    for (int r = warp; r < rowsPad; r += nw) {
+      const bool rv = r < rows;
+      const double* srow = src + (rv ? (int64_t)r * srcStride : 0);
+      double* drow = dst + r * ld;
+      for (int c = 2 * lane; c < colsPad; c += 64) {
+        const int nv = rv ? min(2, max(0, cols - c)) : 0;
+        cp_async16(drow + c, nv ? srow + c : src, 8 * nv);
+      }
+    }
+    return;
+  }
   for (int r = warp; r < rowsPad; r += nw) {
     const bool rv = r < rows;
     const double* srow = src + (rv ? (int64_t)r * srcStride : 0);

@@ -366,10 +366,10 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
   S.lumpParent.assign(S.nL, -1);
   S.lumpLevel.assign(S.nL, 0);
   S.cholFlops = 0; S.maxLumpWidth = 0; S.maxLumpRows = 0;
-  int64_t off = S.lmDataSize;
+  int64_t off = (S.lmDataSize + 1) & ~int64_t(1); // panels start 16-byte aligned (16-byte async copies)
   for (int64_t L = 0; L < S.nL; L++) {
     S.lumpOff[L] = off;
-    off += (int64_t)S.lumpRows[L] * S.lumpWidth[L];
+    off += ((int64_t)S.lumpRows[L] * S.lumpWidth[L] + 1) & ~int64_t(1);
     const double w = S.lumpWidth[L], r = S.lumpRows[L] - S.lumpWidth[L];
     S.cholFlops += w * w * w / 3.0 + w * w * r + w * r * r;
     S.maxLumpWidth = std::max(S.maxLumpWidth, S.lumpWidth[L]);

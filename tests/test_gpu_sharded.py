@@ -113,3 +113,23 @@ def test_sharded_timed_iteration():
         # shared panels, camera rhs, rhs after the subtree forward pass, camera step,
         # landmark steps, scalars, factorisation verdict
         assert calls == 7
+
+
+def test_sharded_c1_scale_matches_single():
+    """BASELINE C1 scale (600 rigs, ~1 M observations): the default nested-dissection plan gives every
+    rank real subtrees; 3 shards must reproduce the single-GPU iteration."""
+    s = synth.make_session(**synth.CONFIGS["c1_60s"])
+    ctx = capi.Context(0)
+    p = capi.Problem(ctx, s.graph)
+    ref = one_iteration(p, 0)
+    p.close(); ctx.close()
+    outs = sharding.run_threaded(s.graph, 3, one_iteration)
+    assert min(o["info"]["own_lumps"] for o in outs) >= 1
+    assert sum(o["info"]["owned_visual"] for o in outs) == s.n_obs
+    for o in outs:
+        assert abs(o["c0"] - ref["c0"]) <= 1e-12 * abs(ref["c0"])
+        assert abs(o["md"] - ref["md"]) <= 1e-8 * abs(ref["md"])
+        assert np.abs(o["step"] - ref["step"]).max() <= STEP_TOL * np.abs(ref["step"]).max()
+        assert abs(o["c1"] - ref["c1"]) <= 1e-9 * abs(ref["c1"])
+        assert o["stats"] == ref["stats"]
+        assert np.array_equal(o["vars"], outs[0]["vars"])

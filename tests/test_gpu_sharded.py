@@ -133,3 +133,31 @@ def test_sharded_c1_scale_matches_single():
         assert abs(o["c1"] - ref["c1"]) <= 1e-9 * abs(ref["c1"])
         assert o["stats"] == ref["stats"]
         assert np.array_equal(o["vars"], outs[0]["vars"])
+
+
+def test_nccl_optimize_two_processes(tmp_path):
+    """A whole LM run as a real 2-process torchrun/NCCL job (needs 2 GPUs; skipped otherwise): same
+    iteration count and final cost as one GPU, final state within 1e-6, identical bits on both ranks."""
+    import json, os, subprocess, sys, socket
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    name, iters = "c1_60s_rs", 4
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0)); port = so.getsockname()[1]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                          "127.0.0.1", "--master-port", str(port), os.path.join(root, "tests", "_nccl_optimize_worker.py"),
+                          name, str(iters), str(tmp_path / "vars.npy")], capture_output=True, text=True, timeout=900, cwd=root)
+    assert out.returncode == 0, out.stderr[-3000:]
+    d = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
+    s = synth.make_session(**synth.CONFIGS[name])
+    ctx = capi.Context(0)
+    p = capi.Problem(ctx, s.graph)
+    summ = p.optimize(G.default_settings(iters))
+    v1 = p.vars
+    p.close(); ctx.close()
+    assert d["identical_state_on_all_ranks"] and d["own_lumps"] >= 1
+    assert d["iterations"] == summ.num_iterations
+    assert abs(d["final_cost"] - summ.final_cost) <= 1e-9 * abs(summ.final_cost)
+    assert np.abs(np.load(tmp_path / "vars.npy") - v1).max() <= 1e-6

@@ -220,7 +220,9 @@ int vb_optimize(vb_problem* p, const vb_settings* s, vb_summary* out);
 /* one accepted-path LM iteration with per-phase CUDA-event timing (bench / profiling) */
 int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times* t, double* cost_before, double* cost_after);
 
-/* data movement */
+/* data movement.  On a sharded problem the variables and the step are complete and bit-identical on every
+ * rank; grad holds this rank's contributions (vb_step_stats sums it on demand) and hess this rank's
+ * panels: its own landmarks and subtrees, plus the summed shared top after vb_factor. */
 int vb_download_vars(vb_problem* p, double* var_data, int64_t n);       /* all variable data */
 int vb_upload_vars(vb_problem* p, const double* var_data, int64_t n);
 int vb_download_grad(vb_problem* p, double* out, int64_t n);             /* permuted order */

@@ -1,0 +1,324 @@
+// Test driver for the C++17 host mirror (include/small_thing/*.h): reads a session written by
+// tests/test_host_mirror.py, rebuilds it through small_thing::Optimizer exactly as a user of the
+// reference would (Variables owned here, one addFactor call per factor), and writes back either
+//   * the graph the mirror hands to the C ABI (host only; compared array by array with the Python
+//     builder's graph), or
+//   * with --optimize N: the Summary and the optimised values (needs a B200; throws otherwise).
+//
+// File format, little endian, arrays back to back:
+//   int64 nv | int32 kind[nv] | int32 tdim[nv] | uint32 flags[nv] | double aux[nv] | uint8 const[nv]
+//   int64 dataLen | double data[dataLen] | int64 np | int32 pointIds[np] | int32 nstores
+//   per store: int32 type, nvars | int64 count | int32 cpf | double lossA, lossK | int64 auxLen
+//              | int32 vars[count*nvars] | double consts[count*cpf] | double aux[auxLen]
+#include <small_thing/Optimizer.h>
+
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <fstream>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+using namespace small_thing;
+
+namespace {
+
+struct Reader {
+  std::ifstream f;
+  explicit Reader(const char* p) : f(p, std::ios::binary) {
+    if (!f) throw std::runtime_error(std::string("cannot open ") + p);
+  }
+  template <typename T>
+  T one() {
+    T v;
+    f.read(reinterpret_cast<char*>(&v), sizeof(T));
+    return v;
+  }
+  template <typename T>
+  std::vector<T> many(int64_t n) {
+    std::vector<T> v((size_t)n);
+    f.read(reinterpret_cast<char*>(v.data()), (std::streamsize)(sizeof(T) * (size_t)n));
+    if (!f) throw std::runtime_error("short read");
+    return v;
+  }
+};
+
+struct Writer {
+  std::ofstream f;
+  explicit Writer(const char* p) : f(p, std::ios::binary) {}
+  template <typename T>
+  void one(T v) { f.write(reinterpret_cast<const char*>(&v), sizeof(T)); }
+  template <typename T>
+  void many(const T* p, size_t n) { f.write(reinterpret_cast<const char*>(p), (std::streamsize)(sizeof(T) * n)); }
+  template <typename T>
+  void many(const std::vector<T>& v) { many(v.data(), v.size()); }
+};
+
+template <typename T>
+Variable<T>& as(std::vector<std::unique_ptr<VarBase>>& vars, int32_t id) {
+  auto* p = dynamic_cast<Variable<T>*>(vars.at((size_t)id).get());
+  if (!p) throw std::runtime_error("variable " + std::to_string(id) + " has an unexpected type");
+  return *p;
+}
+
+template <int N>
+std::array<double, N> arr(const double* p) {
+  std::array<double, N> a;
+  for (int i = 0; i < N; i++) a[i] = p[i];
+  return a;
+}
+
+}  // namespace
+
+int run(int argc, char** argv) {
+  if (argc < 3) {
+    std::fprintf(stderr, "usage: %s in.bin out.bin [--optimize N]\n", argv[0]);
+    return 2;
+  }
+  int optimizeIters = -1;
+  if (argc >= 5 && std::string(argv[3]) == "--optimize") optimizeIters = std::atoi(argv[4]);
+
+  Reader in(argv[1]);
+  const int64_t nv = in.one<int64_t>();
+  auto kind = in.many<int32_t>(nv);
+  auto tdim = in.many<int32_t>(nv);
+  auto flags = in.many<uint32_t>(nv);
+  auto aux = in.many<double>(nv);
+  auto isConst = in.many<uint8_t>(nv);
+  const int64_t dataLen = in.one<int64_t>();
+  auto data = in.many<double>(dataLen);
+
+  // user-owned variables, created in the session's own order
+  std::vector<std::unique_ptr<VarBase>> vars;
+  const double* d = data.data();
+  for (int64_t i = 0; i < nv; i++) {
+    std::unique_ptr<VarBase> v;
+    switch (kind[i]) {
+      case VB_VAR_VEC3: v = std::make_unique<Variable<Vec3>>(); break;
+      case VB_VAR_VEC2: v = std::make_unique<Variable<Vec2>>(); break;
+      case VB_VAR_SE3: v = std::make_unique<Variable<SE3>>(); break;
+      case VB_VAR_S2: {
+        auto s = std::make_unique<Variable<S2>>();
+        s->value.radius = aux[i];
+        v = std::move(s);
+        break;
+      }
+      case VB_VAR_CAM: {
+        auto c = std::make_unique<Variable<CameraModelParam>>();
+        c->value.estimateReadoutTime = flags[i] & VB_CAM_EST_READOUT;
+        c->value.estimateTimeOffset = flags[i] & VB_CAM_EST_TIMEOFFSET;
+        c->value.hasReadoutTime = flags[i] & VB_CAM_HAS_READOUT;
+        v = std::move(c);
+        break;
+      }
+      case VB_VAR_IMUCALIB: {
+        auto c = std::make_unique<Variable<ImuCalibParam>>();
+        c->value.options = flags[i];
+        c->value.tangentDim = tdim[i];
+        v = std::move(c);
+        break;
+      }
+      default: throw std::runtime_error("unknown variable kind");
+    }
+    v->setData(d);
+    d += v->getDataDim();
+    if (isConst[i]) v->setConstant();
+    if (v->getTangentDim() != tdim[i]) throw std::runtime_error("tangent dim mismatch for variable " + std::to_string(i));
+    vars.push_back(std::move(v));
+  }
+
+  Optimizer opt;
+  // registerPointVariables + registeredVariablesToEliminationRange (SingleSessionProblem.cpp:41-45,
+  // main_AriaKit_ViBa.cpp:76-77)
+  const int64_t np = in.one<int64_t>();
+  auto pointIds = in.many<int32_t>(np);
+  for (int32_t id : pointIds) opt.registerVariable(as<Vec3>(vars, id));
+  opt.registeredVariablesToEliminationRange();
+
+  std::deque<HuberLossWithCutoff> losses;          // addresses must stay valid (Factor.h:141)
+  std::deque<std::vector<PreIntegrationData>> preints;
+  std::deque<std::vector<RollingShutterData>> rsTables;
+  auto lossFor = [&](double a, double k) -> const HuberLossWithCutoff& {
+    for (auto& l : losses)
+      if (l.a == a && l.k == k) return l;
+    losses.emplace_back(a, k);
+    return losses.back();
+  };
+
+  const int32_t ns = in.one<int32_t>();
+  for (int32_t s = 0; s < ns; s++) {
+    const int32_t type = in.one<int32_t>(), nvars = in.one<int32_t>();
+    const int64_t count = in.one<int64_t>();
+    const int32_t cpf = in.one<int32_t>();
+    const double lossA = in.one<double>(), lossK = in.one<double>();
+    const int64_t auxLen = in.one<int64_t>();
+    auto sv = in.many<int32_t>(count * nvars);
+    auto sc = in.many<double>(count * cpf);
+    auto sa = in.many<double>(auxLen);
+    const bool soft = lossA > 0.0;
+    if (type == VB_F_INERTIAL || type == VB_F_INERTIAL_SEC || type == VB_F_INERTIAL_SEC_SPLIT) {
+      preints.emplace_back((size_t)count);
+      std::memcpy(static_cast<void*>(preints.back().data()), sa.data(), sizeof(double) * 250 * (size_t)count);
+    }
+    if (type == VB_F_VISUAL_RS) {
+      const int64_t nRigs = (int64_t)sa[3];
+      rsTables.emplace_back((size_t)nRigs);
+      for (int64_t r = 0; r < nRigs; r++) {
+        auto& t = rsTables.back()[(size_t)r];
+        t.gravityWorld = {{sa[0], sa[1], sa[2]}};
+        std::memcpy(t.table.data(), sa.data() + 4 + r * RollingShutterData::kStride, sizeof(double) * RollingShutterData::kStride);
+      }
+    }
+    for (int64_t k = 0; k < count; k++) {
+      const int32_t* v = sv.data() + k * nvars;
+      const double* c = sc.data() + k * cpf;
+      switch (type) {
+        case VB_F_VISUAL: {
+          VisualFactor f{{{c[0], c[1]}}, arr<4>(c + 2)};
+          if (soft) opt.addFactor(f, lossFor(lossA, lossK), as<Vec3>(vars, v[0]), as<SE3>(vars, v[1]), as<SE3>(vars, v[2]), as<CameraModelParam>(vars, v[3]));
+          else opt.addFactor(f, as<Vec3>(vars, v[0]), as<SE3>(vars, v[1]), as<SE3>(vars, v[2]), as<CameraModelParam>(vars, v[3]));
+          break;
+        }
+        case VB_F_VISUAL_RS: {
+          RollingShutterVisualFactor f;
+          f.projBaseRes = {{c[0], c[1]}};
+          f.sqrtH_BaseRes = arr<4>(c + 2);
+          f.rigIndex = (int64_t)c[6];
+          f.imageHeight = c[7];
+          f.rsData = &rsTables.back()[(size_t)f.rigIndex];
+          if (!soft) throw std::runtime_error("RS store without a loss is not part of this test");
+          opt.addFactor(f, lossFor(lossA, lossK), as<Vec3>(vars, v[0]), as<SE3>(vars, v[1]), as<SE3>(vars, v[2]),
+                        as<CameraModelParam>(vars, v[3]), as<Vec3>(vars, v[4]));
+          break;
+        }
+        case VB_F_INERTIAL: {
+          InertialFactor f{&preints.back()[(size_t)k]};
+          opt.addFactor(f, c, lossFor(lossA, lossK), as<ImuCalibParam>(vars, v[0]), as<SE3>(vars, v[1]), as<Vec3>(vars, v[2]),
+                        as<SE3>(vars, v[3]), as<Vec3>(vars, v[4]), as<S2>(vars, v[5]));
+          break;
+        }
+        case VB_F_INERTIAL_SEC: {
+          SecondaryImuInertialFactor f{&preints.back()[(size_t)k]};
+          opt.addFactor(f, c, lossFor(lossA, lossK), as<ImuCalibParam>(vars, v[0]), as<SE3>(vars, v[1]), as<Vec3>(vars, v[2]),
+                        as<Vec3>(vars, v[3]), as<SE3>(vars, v[4]), as<Vec3>(vars, v[5]), as<Vec3>(vars, v[6]), as<SE3>(vars, v[7]),
+                        as<S2>(vars, v[8]));
+          break;
+        }
+        case VB_F_INERTIAL_SEC_SPLIT: {
+          SecondaryImuInertialFactor f{&preints.back()[(size_t)k]};
+          opt.addFactor(f, c, lossFor(lossA, lossK), as<ImuCalibParam>(vars, v[0]), as<SE3>(vars, v[1]), as<Vec3>(vars, v[2]),
+                        as<Vec3>(vars, v[3]), as<SE3>(vars, v[4]), as<SE3>(vars, v[5]), as<Vec3>(vars, v[6]), as<Vec3>(vars, v[7]),
+                        as<SE3>(vars, v[8]), as<S2>(vars, v[9]));
+          break;
+        }
+        case VB_F_RW_IMUCALIB:
+          opt.addFactor(ImuCalibRandomWalkFactor{arr<23>(c)}, as<ImuCalibParam>(vars, v[0]), as<ImuCalibParam>(vars, v[1]));
+          break;
+        case VB_F_RW_CAM:
+          opt.addFactor(CamIntrRandomWalkFactor{arr<17>(c)}, as<CameraModelParam>(vars, v[0]), as<CameraModelParam>(vars, v[1]));
+          break;
+        case VB_F_RW_SE3:
+          opt.addFactor(SE3RandomWalkFactor{arr<6>(c)}, as<SE3>(vars, v[0]), as<SE3>(vars, v[1]));
+          break;
+        case VB_F_PRIOR_IMUCALIB:
+          opt.addFactor(ImuCalibPriorFactor{arr<23>(c), arr<32>(c + 23)}, as<ImuCalibParam>(vars, v[0]));
+          break;
+        case VB_F_PRIOR_CAM:
+          opt.addFactor(CamIntrPriorFactor{arr<17>(c), arr<17>(c + 17)}, as<CameraModelParam>(vars, v[0]));
+          break;
+        case VB_F_PRIOR_SE3: {
+          SE3PriorFactor f;
+          f.diagSqrtH = arr<6>(c);
+          f.priorInverse.q = arr<4>(c + 6);
+          f.priorInverse.t = arr<3>(c + 10);
+          opt.addFactor(f, as<SE3>(vars, v[0]));
+          break;
+        }
+        case VB_F_OMEGA_PRIOR:
+          opt.addFactor(OmegaPriorFactor{arr<3>(c)}, as<Vec3>(vars, v[0]));
+          break;
+        case VB_F_OMEGA_PRIOR_SEC:
+          opt.addFactor(OmegaPriorFactor{arr<3>(c)}, as<Vec3>(vars, v[0]), as<SE3>(vars, v[1]));
+          break;
+        default: throw std::runtime_error("unknown factor type " + std::to_string(type));
+      }
+    }
+  }
+
+  Writer out(argv[2]);
+  if (optimizeIters >= 0) {
+    Optimizer::Settings st;
+    st.maxNumIterations = optimizeIters;
+    st.log = nullptr;
+    const double cost0 = opt.computeCost();
+    Optimizer::Summary sm = opt.optimize(st);
+    const double cost1 = opt.computeCost();
+    out.one<double>(sm.initialCost);
+    out.one<double>(sm.finalCost);
+    out.one<double>((double)sm.numIterations);
+    out.one<double>(cost0);
+    out.one<double>(cost1);
+    std::vector<double> buf(32);
+    for (auto& v : vars) {   // the user's own Variables now hold the optimised values
+      v->getData(buf.data());
+      out.many(buf.data(), (size_t)v->getDataDim());
+    }
+    return 0;
+  }
+
+  // host only: the graph as the mirror hands it to vb_problem_create, plus the symbolic phase on it
+  auto g = opt.exportGraph();
+  std::unordered_map<const VarBase*, int32_t> poolId;
+  for (size_t i = 0; i < g->pool.size(); i++) poolId[g->pool[i]] = (int32_t)i;
+  std::vector<int32_t> py2cpp((size_t)nv, -1);
+  for (int64_t i = 0; i < nv; i++) {
+    auto it = poolId.find(vars[(size_t)i].get());
+    if (it != poolId.end()) py2cpp[(size_t)i] = it->second;
+  }
+  const int64_t n = g->desc.num_vars;
+  out.one<int64_t>(n);
+  out.many(g->kind);
+  out.many(g->tdim);
+  out.many(g->flags);
+  out.many(g->index);
+  out.many(g->off);
+  out.many(g->aux);
+  out.one<int64_t>(g->desc.var_data_len);
+  out.many(g->data);
+  out.one<int64_t>(g->desc.num_points);
+  out.one<int64_t>(nv);
+  out.many(py2cpp);
+  out.one<int32_t>(g->desc.num_stores);
+  for (const auto& s : g->stores) {
+    out.one<int32_t>(s.type);
+    out.one<int32_t>(s.nvars);
+    out.one<int64_t>(s.count);
+    out.one<int32_t>(s.consts_per_factor);
+    out.one<double>(s.loss_a);
+    out.one<double>(s.loss_k);
+    out.one<int64_t>(s.aux_len);
+    out.many(s.vars, (size_t)(s.count * s.nvars));
+    out.many(s.consts, (size_t)(s.count * s.consts_per_factor));
+    out.many(s.aux, (size_t)s.aux_len);
+  }
+  int64_t order = 0, dataSize = 0, numLumps = 0;
+  if (vb_symbolic_only(&g->desc, &order, &dataSize, &numLumps, nullptr, 0) != VB_OK)
+    throw std::runtime_error(std::string("vb_symbolic_only: ") + vb_last_error());
+  out.one<int64_t>(order);
+  out.one<int64_t>(dataSize);
+  out.one<int64_t>(numLumps);
+  out.one<int64_t>(opt.totalVarDimensionality());
+  out.one<int64_t>(opt.totalErrorDimensionality());
+  return 0;
+}
+
+int main(int argc, char** argv) {
+  try {
+    return run(argc, argv);
+  } catch (const std::runtime_error& e) {   // what a caller of the reference would catch
+    std::fprintf(stderr, "runtime_error: %s\n", e.what());
+    return 3;
+  }
+}

@@ -233,6 +233,23 @@ int vb_upload_grad(vb_problem* p, const double* in, int64_t n);
 int vb_download_factor_cache(vb_problem* p, int32_t store, double* out, int64_t n); /* ResultCache, Factor.h:92-94 */
 int vb_upload_store_aux(vb_problem* p, int32_t store, const double* aux, int64_t n); /* refreshed preint / RS tables */
 int vb_upload_store_consts(vb_problem* p, int32_t store, const double* consts, int64_t n);
+int vb_download_store_aux(vb_problem* p, int32_t store, double* out, int64_t n);
+
+/* Per-iteration refresher of the rolling-shutter tables on the device:
+ * RollingShutterData::compute (lib/motion/preintegration/RollingShutterData.cpp:16-65), which the reference
+ * runs on the host for every RS rig at the top of every LM iteration
+ * (SingleSessionAdapter::updateRollingShutterData, viba/single_session/InitCalibration.cpp:316-325, from the
+ * preStepCallback at Optimizer.cpp:801-805).
+ * vb_rs_set_imu hands the raw IMU-0 samples (time in ns, float rad/s and m/s^2 as in ImuMeasurement) and,
+ * per table row of a VB_F_VISUAL_RS store, the rig's timestamp in us and the pool id of the IMU calibration
+ * variable of its window (-1: leave that row alone); half_length_us is intervalHalfLengthUs_ (readout / 2 +
+ * 2 ms in the reference).  From then on vb_optimize recomputes the tables from the current calibration at the
+ * top of every iteration; vb_rs_refresh does it on request.  VB_ERR_NUMERIC when a window runs off the
+ * samples, holds more than 32 gyro boundaries, or sample times do not increase (the reference throws). */
+int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* rig_mid_time_us, const int32_t* rig_calib_var,
+                  int64_t half_length_us, int64_t n_samples, const int64_t* sample_time_ns, const float* gyro_rad_s,
+                  const float* accel_m_s2);
+int vb_rs_refresh(vb_problem* p, int32_t store); /* store < 0: every store that has IMU samples */
 
 /* FP64 DMMA peak probe (mma.sync m8n8k4 f64) used as the tensor roofline denominator */
 int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops);

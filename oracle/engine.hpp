@@ -13,6 +13,7 @@
 #include <utility>
 #include <string>
 #include <stdexcept>
+#include <functional>
 #include "factors.hpp"
 #include "factors_small.hpp"
 #include "factors_ext.hpp"
@@ -135,6 +136,7 @@ struct Engine {
   // adds, the way the reference runs it on its thread pool with locked adds (Factor.h:704-734,
   // AtomicOps.h:80-112).  threads == 1 is the serial checker path the tests use (bit-stable).
   int threads = 1;
+  std::function<void()> preStep; // Settings::preStepCallback (Optimizer.cpp:801-805): data refresh before every iteration
   inline void acc(double& dst, double v) const {
     if (threads > 1) {
 #pragma omp atomic

@@ -31,6 +31,7 @@ inline int optimize(Engine& e, SchurSkylineSolver& sol, const vb_settings& st, v
     return rate < 0.03 && (s.numInvalid < s.numPrevInvalid * 2.0 + 50);
   };
   while (true) {
+    if (e.preStep) e.preStep();
     std::fill(e.grad.begin(), e.grad.end(), 0.0);
     std::fill(e.hess.begin(), e.hess.end(), 0.0);
     const double prevCost = e.computeGradHess(e.grad.data(), e.hess.data(), true, dontRetryFailed);

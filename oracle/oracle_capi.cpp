@@ -6,10 +6,20 @@
 #include <string>
 #include <chrono>
 #include "lm.hpp"
+#include "rs_refresh.hpp"
 
 using namespace orc;
 
+struct RsSource {   // raw IMU-0 samples + per-rig windows of one rolling-shutter store
+  int store = -1;
+  ImuSamples meas;
+  std::vector<int64_t> midUs;
+  std::vector<int32_t> calibVar;
+  int64_t halfUs = 0;
+};
+
 struct OrcHandle {
+  std::vector<RsSource> rs;
   Engine eng;
   SchurSkylineSolver sol;
   bool analyzed = false;
@@ -157,6 +167,45 @@ int orc_optimize(OrcHandle* h, const vb_settings* s, vb_summary* out, double* tr
     if (traceNew) traceNew[i] = tr.newCost[i];
   }
   ORC_CATCH
+}
+
+static void rsRefresh(OrcHandle* h, int store) {
+  for (const RsSource& src : h->rs) {
+    if (store >= 0 && src.store != store) continue;
+    Problem& P = h->eng.P;
+    double* tables = P.stores[src.store].aux.data() + 4;
+    for (size_t r = 0; r < src.midUs.size(); r++)
+      if (src.calibVar[r] >= 0) rsCompute(src.meas, P.data.data() + P.off[src.calibVar[r]], src.midUs[r], src.halfUs, tables + r * kRsStride);
+  }
+}
+
+// SingleSessionAdapter::updateRollingShutterData (InitCalibration.cpp:316-325): same arguments as vb_rs_set_imu
+int orc_rs_set_imu(OrcHandle* h, int store, int64_t n_rigs, const int64_t* rig_mid_time_us, const int32_t* rig_calib_var,
+                   int64_t half_length_us, int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel) {
+  ORC_TRY
+  RsSource src;
+  src.store = store;
+  src.halfUs = half_length_us;
+  src.midUs.assign(rig_mid_time_us, rig_mid_time_us + n_rigs);
+  src.calibVar.assign(rig_calib_var, rig_calib_var + n_rigs);
+  src.meas.timeNs.assign(sample_time_ns, sample_time_ns + n_samples);
+  src.meas.gyro.assign(gyro, gyro + 3 * n_samples);
+  src.meas.accel.assign(accel, accel + 3 * n_samples);
+  if ((int64_t)h->eng.P.stores.at(store).aux.size() != 4 + n_rigs * kRsStride) throw std::runtime_error("rig count does not match the store's tables");
+  h->rs.push_back(std::move(src));
+  h->eng.preStep = [h]() { rsRefresh(h, -1); };
+  ORC_CATCH
+}
+int orc_rs_refresh(OrcHandle* h, int store) {
+  ORC_TRY
+  rsRefresh(h, store);
+  ORC_CATCH
+}
+int orc_get_store_aux(OrcHandle* h, int store, double* out, int64_t n) {
+  const auto& a = h->eng.P.stores[store].aux;
+  if ((int64_t)a.size() != n) return 1;
+  std::memcpy(out, a.data(), n * 8);
+  return 0;
 }
 
 // one accepted-path LM iteration, wall-clock split in ms: {gradhess, damp, factor, solve, apply, cost, total}

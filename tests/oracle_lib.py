@@ -112,6 +112,24 @@ class Oracle:
     grad = property(lambda s: s.get(0)); step = property(lambda s: s.get(1))
     hess = property(lambda s: s.get(3)); vars = property(lambda s: s.get(4))
 
+    def rs_set_imu(self, store, time_ns, gyro, accel, rig_mid_time_us, rig_calib_var, half_length_us):
+        t = np.ascontiguousarray(time_ns, np.int64); gy = np.ascontiguousarray(gyro, np.float32); ac = np.ascontiguousarray(accel, np.float32)
+        mid = np.ascontiguousarray(rig_mid_time_us, np.int64); cv = np.ascontiguousarray(rig_calib_var, np.int32)
+        fp = C.POINTER(C.c_float)
+        self.lib.orc_rs_set_imu.argtypes = [C.c_void_p, C.c_int, C.c_int64, _ip, C.POINTER(C.c_int32), C.c_int64, C.c_int64, _ip, fp, fp]
+        self._ck(self.lib.orc_rs_set_imu(self.h, int(store), mid.size, mid.ctypes.data_as(_ip), cv.ctypes.data_as(C.POINTER(C.c_int32)),
+                                         int(half_length_us), t.size, t.ctypes.data_as(_ip), gy.ctypes.data_as(fp), ac.ctypes.data_as(fp)))
+
+    def rs_refresh(self, store=-1):
+        self.lib.orc_rs_refresh.argtypes = [C.c_void_p, C.c_int]
+        self._ck(self.lib.orc_rs_refresh(self.h, int(store)))
+
+    def store_aux(self, store):
+        out = np.zeros(self.g.stores[store].aux.size)
+        self.lib.orc_get_store_aux.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_int64]
+        assert self.lib.orc_get_store_aux(self.h, int(store), dptr(out), out.size) == 0
+        return out
+
     def cache(self, store):
         out = np.zeros(self.g.stores[store].count)
         self.lib.orc_get_cache(self.h, store, dptr(out), out.size)

@@ -23,6 +23,7 @@ EXPORTS = [
     "vb_optimize", "vb_lm_iteration_timed", "vb_download_vars", "vb_upload_vars", "vb_download_grad",
     "vb_download_step", "vb_download_hess", "vb_upload_hess", "vb_upload_grad", "vb_download_factor_cache",
     "vb_upload_store_aux", "vb_upload_store_consts", "vb_measure_dmma_peak",
+    "vb_download_store_aux", "vb_rs_set_imu", "vb_rs_refresh",
     "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info", "vb_shard_factor_owners",
 ]
 # int fn(void* user, int op, double* dev_ptr, int64_t count, void* cuda_stream)  (include/viba_b200.h)
@@ -78,9 +79,12 @@ def load():
     for f in ("vb_download_vars", "vb_upload_vars", "vb_download_grad", "vb_download_step", "vb_download_hess",
               "vb_upload_hess", "vb_upload_grad"):
         getattr(lib, f).argtypes = [C.c_void_p, _dp, C.c_int64]
-    for f in ("vb_download_factor_cache", "vb_upload_store_aux", "vb_upload_store_consts"):
+    for f in ("vb_download_factor_cache", "vb_upload_store_aux", "vb_upload_store_consts", "vb_download_store_aux"):
         getattr(lib, f).argtypes = [C.c_void_p, C.c_int32, _dp, C.c_int64]
     lib.vb_measure_dmma_peak.argtypes = [C.c_void_p, _dp]
+    lib.vb_rs_set_imu.argtypes = [C.c_void_p, C.c_int32, C.c_int64, _ip, C.POINTER(C.c_int32), C.c_int64, C.c_int64, _ip,
+                                  C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    lib.vb_rs_refresh.argtypes = [C.c_void_p, C.c_int32]
     lib.vb_symbolic_only.argtypes = [C.POINTER(G.vb_graph_desc), _ip, _ip, _ip, _ip, C.c_int64]
     lib.vb_symbolic_stats.argtypes = [C.POINTER(G.vb_graph_desc), C.c_int, C.c_int, _dp]
     _lib = lib
@@ -298,6 +302,24 @@ class Problem:
         out = np.zeros(self.g.stores[store].count)
         _ck(self.lib, self.lib.vb_download_factor_cache(self.h, store, _d(out), out.size))
         return out
+
+    def store_aux(self, store):
+        out = np.zeros(self.g.stores[store].aux.size)
+        _ck(self.lib, self.lib.vb_download_store_aux(self.h, store, _d(out), out.size))
+        return out
+
+    def rs_set_imu(self, store, time_ns, gyro, accel, rig_mid_time_us, rig_calib_var, half_length_us):
+        """raw IMU-0 samples + per-rig windows of a rolling-shutter store (vb_rs_set_imu): from now on optimize()
+        recomputes the store's tables from the current calibration at the top of every iteration"""
+        t = np.ascontiguousarray(time_ns, np.int64); gy = np.ascontiguousarray(gyro, np.float32); ac = np.ascontiguousarray(accel, np.float32)
+        mid = np.ascontiguousarray(rig_mid_time_us, np.int64); cv = np.ascontiguousarray(rig_calib_var, np.int32)
+        assert gy.shape == (t.size, 3) and ac.shape == (t.size, 3) and mid.size == cv.size
+        _ck(self.lib, self.lib.vb_rs_set_imu(self.h, int(store), mid.size, mid.ctypes.data_as(_ip), cv.ctypes.data_as(C.POINTER(C.c_int32)),
+                                             int(half_length_us), t.size, t.ctypes.data_as(_ip), gy.ctypes.data_as(C.POINTER(C.c_float)),
+                                             ac.ctypes.data_as(C.POINTER(C.c_float))))
+
+    def rs_refresh(self, store=-1):
+        _ck(self.lib, self.lib.vb_rs_refresh(self.h, int(store)))
 
     def upload_store_aux(self, store, aux):
         aux = np.ascontiguousarray(aux, np.float64)

@@ -49,6 +49,16 @@ struct vb_problem {
   bool partial[3] = {false, false, true}; // step, gradNew, grad: holds only this rank's contributions
   int64_t ownedLandmarks = 0, ownedVisual = 0, collCalls = 0; double collBytes = 0;
   bool alignedPlan = true; // every contribution to a non-shared panel is local to its owner (planOwners)
+  // raw IMU-0 samples and per-rig windows of the rolling-shutter stores (vb_rs_set_imu): when present the
+  // tables are recomputed on the device at the top of every LM iteration
+  struct RsSource {
+    int store = -1;
+    int64_t nRigs = 0, nSamples = 0, halfUs = 0;
+    int64_t *timeNs = nullptr, *midUs = nullptr, *calibOff = nullptr;
+    float *gyro = nullptr, *accel = nullptr;
+    int* status = nullptr;
+  };
+  std::vector<RsSource> rsSources;
   cudaEvent_t ev[10];
 
   template <typename T>
@@ -594,6 +604,31 @@ static double* vecOf(vb_problem* p, int which) { return which == 0 ? p->step : w
 static void requireProblem(const vb_problem* p) { if (!p) throw std::invalid_argument("null problem"); }
 static void syncCheck(vb_problem* p) { VB_CUDA(cudaStreamSynchronize(p->ctx->stream)); }
 
+constexpr int64_t kRsTableStride = 1 + 32 * 11 + 31 * 9; // per-rig table (dev_factors_ext.cuh)
+
+// RollingShutterData::compute for every rig of the stores that were given IMU samples
+// (InitCalibration.cpp:316-325, called from the preStepCallback: Optimizer.cpp:801-805)
+static void refreshRsTables(vb_problem* p, int store) {
+  cudaStream_t s = p->ctx->stream;
+  bool any = false;
+  for (auto& src : p->rsSources) {
+    if (store >= 0 && src.store != store) continue;
+    any = true;
+    VB_CUDA(cudaMemsetAsync(src.status, 0, sizeof(int), s));
+    double* tables = const_cast<double*>(p->ds[src.store].aux) + 4;
+    launchRsRefresh(src.timeNs, src.gyro, src.accel, src.nSamples, p->dv.data, src.calibOff, src.midUs, src.halfUs, src.nRigs,
+                    tables, src.status, s);
+    VB_CUDA(cudaGetLastError());
+    int st = 0;
+    VB_CUDA(cudaMemcpyAsync(&st, src.status, sizeof(int), cudaMemcpyDeviceToHost, s));
+    VB_CUDA(cudaStreamSynchronize(s));
+    if (st == 1) throw std::domain_error("enumIntegrationSteps: not enough IMU samples around a rolling-shutter window");
+    if (st == 2) throw std::domain_error("RollingShutterData::compute: more than 32 samples in a window");
+    if (st != 0) throw std::domain_error("RollingShutterData::compute: sample times not increasing");
+  }
+  if (store >= 0 && !any) throw std::invalid_argument("store has no IMU samples (vb_rs_set_imu)");
+}
+
 extern "C" {
 
 int vb_version(void) { return 100; }
@@ -1050,6 +1085,7 @@ int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) {
     return rate < 0.03 && (c.num_invalid < c.num_prev_invalid * 2.0 + 50);
   };
   while (true) {
+    if (!p->rsSources.empty()) refreshRsTables(p, -1); // preStepCallback (Optimizer.cpp:801-805)
     const double prevCost = evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
     finalCost = prevCost;
     if (iterationNum == 0) initialCost = prevCost;
@@ -1229,6 +1265,50 @@ int vb_upload_store_aux(vb_problem* p, int32_t store, const double* aux, int64_t
 int vb_upload_store_consts(vb_problem* p, int32_t store, const double* c, int64_t n) {
   if (!p || store < 0 || store >= (int)p->ds.size()) { g_err = "store index out of range"; return VB_ERR_ARG; }
   return copyIn(p, const_cast<double*>(p->ds[store].consts), (int64_t)p->g.stores[store].consts.size(), c, n);
+}
+int vb_download_store_aux(vb_problem* p, int32_t store, double* out, int64_t n) {
+  if (!p || store < 0 || store >= (int)p->ds.size()) { g_err = "store index out of range"; return VB_ERR_ARG; }
+  return copyOut(p, p->ds[store].aux, (int64_t)p->g.stores[store].aux.size(), out, n);
+}
+int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* rig_mid_time_us, const int32_t* rig_calib_var,
+                  int64_t half_length_us, int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel) {
+  VB_TRY
+  requireProblem(p);
+  if (store < 0 || store >= (int)p->ds.size() || p->g.stores[store].type != VB_F_VISUAL_RS) throw std::invalid_argument("not a rolling-shutter store");
+  const auto& hs = p->g.stores[store];
+  if (!rig_mid_time_us || !rig_calib_var || !sample_time_ns || !gyro || !accel || n_samples < 2 || half_length_us <= 0)
+    throw std::invalid_argument("null or empty IMU data");
+  if (hs.aux.size() < 4 || n_rigs != (int64_t)hs.aux[3] || (int64_t)hs.aux.size() != 4 + n_rigs * kRsTableStride)
+    throw std::invalid_argument("rig count does not match the store's tables");
+  for (int64_t i = 1; i < n_samples; i++)
+    if (sample_time_ns[i] <= sample_time_ns[i - 1]) throw std::invalid_argument("IMU sample times must increase");
+  std::vector<int64_t> calibOff((size_t)n_rigs, -1);
+  for (int64_t r = 0; r < n_rigs; r++) {
+    const int32_t v = rig_calib_var[r];
+    if (v < 0) continue;
+    if (v >= p->g.nv || p->g.kind[v] != VB_VAR_IMUCALIB) throw std::invalid_argument("rig_calib_var must name IMU calibration variables");
+    calibOff[(size_t)r] = p->g.off[v];
+  }
+  VB_CUDA(cudaSetDevice(p->ctx->device));
+  vb_problem::RsSource src;
+  src.store = store; src.nRigs = n_rigs; src.nSamples = n_samples; src.halfUs = half_length_us;
+  src.timeNs = p->upload(std::vector<int64_t>(sample_time_ns, sample_time_ns + n_samples));
+  src.gyro = p->upload(std::vector<float>(gyro, gyro + 3 * n_samples));
+  src.accel = p->upload(std::vector<float>(accel, accel + 3 * n_samples));
+  src.midUs = p->upload(std::vector<int64_t>(rig_mid_time_us, rig_mid_time_us + n_rigs));
+  src.calibOff = p->upload(calibOff);
+  src.status = p->alloc<int>(1);
+  for (auto it = p->rsSources.begin(); it != p->rsSources.end();)
+    it = it->store == store ? p->rsSources.erase(it) : it + 1;
+  p->rsSources.push_back(src);
+  VB_CATCH
+}
+int vb_rs_refresh(vb_problem* p, int32_t store) {
+  VB_TRY
+  requireProblem(p);
+  VB_CUDA(cudaSetDevice(p->ctx->device));
+  refreshRsTables(p, store);
+  VB_CATCH
 }
 int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops) {
   VB_TRY

@@ -117,6 +117,10 @@ void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, co
 void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, cudaStream_t s);
 // op: 0 a=b ; 1 a*=s ; 2 out[0]+=a.b ; 3 a=0
 void launchVecOp(int op, double* a, const double* b, double s, int64_t n, double* out, cudaStream_t st);
+// RollingShutterData::compute per rig (kernels_refresh.cu); status receives the largest rf::k* code
+void launchRsRefresh(const int64_t* timeNs, const float* gyro, const float* accel, int64_t nSamples, const double* varData,
+                     const int64_t* calibOff, const int64_t* midUs, int64_t halfUs, int64_t nRigs, double* tables, int* status,
+                     cudaStream_t st);
 double measureDmmaPeak(cudaStream_t s);
 
 } // namespace vb

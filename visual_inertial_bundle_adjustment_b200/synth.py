@@ -380,6 +380,7 @@ def _make_session(duration_s, n_landmarks, n_obs, seed, frame_hz, window_s, outl
     s_.ids = dict(point=v_pt, pose=v_pose, vel=v_vel, extr=v_extr, intr=v_intr, imu=v_imu, gravity=v_g)
     s_.gt = dict(X=X_gt, T_bw=T_bw_gt, vel=v_w, T_cb=T_cb_gt, cam=cam_gt, imu=imu_gt)
     s_.obs = dict(lm=lm, rig=rig, cam=cam, uv=uv)
+    s_.times, s_.win, s_.loop_period_s = times, win, loop_period_s
     return s_
 
 
@@ -477,6 +478,50 @@ def rs_tables(times, grav, half_ms=14):
     off = 1 + RS_MAX_SAMPLES * 11
     tab[:, off:off + (n - 1) * 9] = interp.reshape(times.size, -1)
     return tab
+
+
+def imu0_samples(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
+    """Raw IMU-0 samples for the per-iteration refreshers (the reference reads them from
+    the session's IMU CSV, lib/motion/imu_types/ImuDataFormat.h:14-23): time stamps in ns, float32 gyro
+    (rad/s) and accelerometer (m/s^2) readings at `rate_hz`, each the mean of the true body rate / specific
+    force over the sample's interval, distorted by the ground-truth calibration of its window
+    (measured = scale_matrix * (true + bias), the inverse of getCompensatedImuMeasurement) plus white noise
+    (ImuNoiseModelParameters defaults).  Returns dict(time_ns, gyro, accel, rig_mid_time_us, rig_calib_var,
+    half_length_us) ready for vb_rs_set_imu; rigs without rolling-shutter observations get calib var -1."""
+    global _LOOP_PERIOD
+    g = session.graph
+    times, win = session.times, session.win
+    dt = 1.0 / rate_hz
+    n = int(round((times[-1] - times[0] + 2 * margin_s) * rate_hz)) + 1
+    t_end = times[0] - margin_s + dt * np.arange(n)          # a sample closes the interval (t - dt, t]
+    t_mid = t_end - 0.5 * dt
+    h = 1e-4
+    _LOOP_PERIOD = session.loop_period_s
+    try:
+        qm = _traj(t_mid)[2]
+        w_body = so3_log(quat_mul(quat_conj(_traj(t_mid - h)[2]), _traj(t_mid + h)[2])) / (2 * h)
+        a_world = (_traj(t_mid + h)[1] - _traj(t_mid - h)[1]) / (2 * h)
+    finally:
+        _LOOP_PERIOD = None
+    grav = np.array([0.0, 0.0, -9.81])
+    f_body = quat_rotate(quat_conj(qm), a_world - grav)
+    w_idx = np.clip(np.searchsorted(times, t_mid, side="right") - 1, 0, times.size - 1)
+    calib = session.gt["imu"][win[w_idx]]                   # (n, 32): gs, as, gb, ab, Gn(col-major), An, dta, dtg
+    Gn = calib[:, 12:21].reshape(n, 3, 3).transpose(0, 2, 1)
+    An = calib[:, 21:30].reshape(n, 3, 3).transpose(0, 2, 1)
+    gyro = calib[:, 0:3] * np.einsum("nij,nj->ni", Gn, w_body + calib[:, 6:9])
+    accel = calib[:, 3:6] * np.einsum("nij,nj->ni", An, f_body + calib[:, 9:12])
+    if noise:
+        rng = np.random.default_rng(seed)
+        gyro = gyro + rng.normal(0, np.sqrt(2.74e-5 * rate_hz) * 1e-2, gyro.shape)
+        accel = accel + rng.normal(0, np.sqrt(6.63e-3 * rate_hz) * 1e-2, accel.shape)
+    rs_store = next(i for i, st in enumerate(g.stores) if st.type == G.F_VISUAL_RS)
+    rigs = np.unique(g.stores[rs_store].consts[:, 6].astype(np.int64))
+    calib_var = np.full(times.size, -1, np.int32)
+    calib_var[rigs] = session.ids["imu"][win[rigs]]
+    return dict(store=rs_store, time_ns=np.round(t_end * 1e9).astype(np.int64), gyro=gyro.astype(np.float32),
+                accel=accel.astype(np.float32), rig_mid_time_us=np.round(times * 1e6).astype(np.int64),
+                rig_calib_var=calib_var, half_length_us=13000)
 
 
 def _synth_preint(T_iw, vel_iw, prev, nxt, dt, grav, eval_point, rng):

@@ -72,6 +72,23 @@ def make_workload(name, rank=0):
     return synth.make_session(**cfg), cfg
 
 
+def attach_rs_imu(target, session):
+    """raw IMU-0 samples for the rolling-shutter store, if the session has one; `target` is a capi.Problem or
+    the oracle.  Returns a note for the JSON line; a failure leaves the tables of the session as they are."""
+    from visual_inertial_bundle_adjustment_b200 import synth, graph as G
+    if not any(st.type == G.F_VISUAL_RS for st in session.graph.stores):
+        return "no rolling-shutter camera"
+    d = synth.imu0_samples(session)
+    try:
+        target.rs_set_imu(d["store"], d["time_ns"], d["gyro"], d["accel"], d["rig_mid_time_us"], d["rig_calib_var"], d["half_length_us"])
+        target.rs_refresh(d["store"])
+        return "RollingShutterData::compute for %d rigs inside every iteration (grad_hess phase)" % int((d["rig_calib_var"] >= 0).sum())
+    except Exception as ex:  # keep the bench alive: measured without the refresh, and say so
+        if hasattr(target, "rs_clear_imu"):
+            target.rs_clear_imu(d["store"])
+        return "off (%s)" % str(ex)[:120]
+
+
 def cpu_leg(workload, steps, warmup):
     """The reference's CPU path cannot be built offline (BaSpaCho/Eigen/Sophus absent: SURVEY.md
     F1,F3), so the CPU arm is the oracle port in its baseline mode — factor loops and landmark
@@ -86,6 +103,7 @@ def cpu_leg(workload, steps, warmup):
     o = Oracle(load_oracle(), s.graph)
     cores = os.cpu_count() or 1
     solver_kind = o.set_parallel(cores)
+    attach_rs_imu(o, s)
     scale = synth.CONFIGS[workload]["duration_s"] / synth.CONFIGS[sample]["duration_s"]
     ts = []
     for i in range(warmup + steps):
@@ -155,6 +173,9 @@ def main():
         p = capi.Problem(ctx, s.graph)
     setup_s = time.time() - t0
     lam = 1e-5
+    # the reference refreshes the rolling-shutter tables from the raw IMU samples at the top of every iteration
+    # (preStepCallback, Optimizer.cpp:801-805 -> InitCalibration.cpp:316-325): same here, on the device
+    rs_note = attach_rs_imu(p, s)
 
     def barrier():
         if dist is not None:
@@ -241,7 +262,7 @@ def main():
     dominant = roof_gh if gh_ms >= fac_ms else roof_fac
     line = {"metric": metric, "value": ms_dev, "unit": "ms/iteration", "n_gpus": a.gpus, "steps": a.steps, "warmup": warmup,
             "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": dict(config, observations=int(s.n_obs + s.ext.get("rs_obs", 0)), rs_observations=int(s.ext.get("rs_obs", 0)), landmarks=int(s.n_points), rigs=int(s.n_rigs),
+            "data": "synthetic", "config": dict(config, observations=int(s.n_obs + s.ext.get("rs_obs", 0)), rs_observations=int(s.ext.get("rs_obs", 0)), landmarks=int(s.n_points), rigs=int(s.n_rigs), rs_refresh=rs_note,
                                                 order=int(p.order), hess_doubles=int(p.data_size), lumps=int(p.num_lumps),
                                                 levels=int(p.num_levels), setup_s=round(setup_s, 2)),
             "phases_ms": {k_: round(v, 4) for k_, v in phases.items()}, "wall_ms_per_step": wall_ms,

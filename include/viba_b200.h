@@ -244,7 +244,8 @@ int vb_download_store_aux(vb_problem* p, int32_t store, double* out, int64_t n);
  * per table row of a VB_F_VISUAL_RS store, the rig's timestamp in us and the pool id of the IMU calibration
  * variable of its window (-1: leave that row alone); half_length_us is intervalHalfLengthUs_ (readout / 2 +
  * 2 ms in the reference).  From then on vb_optimize recomputes the tables from the current calibration at the
- * top of every iteration; vb_rs_refresh does it on request.  VB_ERR_NUMERIC when a window runs off the
+ * top of every iteration (vb_lm_iteration_timed too, inside its grad_hess phase); vb_rs_refresh does it on request;
+ * n_samples = 0 forgets the samples of that store.  VB_ERR_NUMERIC when a window runs off the
  * samples, holds more than 32 gyro boundaries, or sample times do not increase (the reference throws). */
 int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* rig_mid_time_us, const int32_t* rig_calib_var,
                   int64_t half_length_us, int64_t n_samples, const int64_t* sample_time_ns, const float* gyro_rad_s,

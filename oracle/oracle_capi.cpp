@@ -174,8 +174,19 @@ static void rsRefresh(OrcHandle* h, int store) {
     if (store >= 0 && src.store != store) continue;
     Problem& P = h->eng.P;
     double* tables = P.stores[src.store].aux.data() + 4;
-    for (size_t r = 0; r < src.midUs.size(); r++)
-      if (src.calibVar[r] >= 0) rsCompute(src.meas, P.data.data() + P.off[src.calibVar[r]], src.midUs[r], src.halfUs, tables + r * kRsStride);
+    const int threads = h->eng.threads;
+    std::string failure;   // exceptions must not leave the OpenMP region
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads) if (threads > 1)
+    for (int64_t r = 0; r < (int64_t)src.midUs.size(); r++) {
+      if (src.calibVar[r] < 0) continue;
+      try {
+        rsCompute(src.meas, P.data.data() + P.off[src.calibVar[r]], src.midUs[r], src.halfUs, tables + r * kRsStride);
+      } catch (const std::exception& ex) {
+#pragma omp critical
+        failure = ex.what();
+      }
+    }
+    if (!failure.empty()) throw std::runtime_error(failure);
   }
 }
 
@@ -236,6 +247,7 @@ int orc_lm_iteration_timed(OrcHandle* h, double lambda, double* ms, double* cost
   Engine& e = h->eng;
   if (!h->analyzed) { h->sol.analyze(h->eng); h->analyzed = true; }
   const auto t0 = clk::now();
+  if (e.preStep) e.preStep(); // the reference's preStepCallback is inside the iteration (Optimizer.cpp:801-805)
   std::fill(e.grad.begin(), e.grad.end(), 0.0);
   std::fill(e.hess.begin(), e.hess.end(), 0.0);
   const double c0 = e.computeGradHess(e.grad.data(), e.hess.data(), true, false);

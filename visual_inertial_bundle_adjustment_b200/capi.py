@@ -318,6 +318,9 @@ class Problem:
                                              int(half_length_us), t.size, t.ctypes.data_as(_ip), gy.ctypes.data_as(C.POINTER(C.c_float)),
                                              ac.ctypes.data_as(C.POINTER(C.c_float))))
 
+    def rs_clear_imu(self, store):
+        _ck(self.lib, self.lib.vb_rs_set_imu(self.h, int(store), 0, None, None, 0, 0, None, None, None))
+
     def rs_refresh(self, store=-1):
         _ck(self.lib, self.lib.vb_rs_refresh(self.h, int(store)))
 

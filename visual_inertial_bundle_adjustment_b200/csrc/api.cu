@@ -608,7 +608,7 @@ constexpr int64_t kRsTableStride = 1 + 32 * 11 + 31 * 9; // per-rig table (dev_f
 
 // RollingShutterData::compute for every rig of the stores that were given IMU samples
 // (InitCalibration.cpp:316-325, called from the preStepCallback: Optimizer.cpp:801-805)
-static void refreshRsTables(vb_problem* p, int store) {
+static bool launchRsTables(vb_problem* p, int store) {
   cudaStream_t s = p->ctx->stream;
   bool any = false;
   for (auto& src : p->rsSources) {
@@ -619,6 +619,14 @@ static void refreshRsTables(vb_problem* p, int store) {
     launchRsRefresh(src.timeNs, src.gyro, src.accel, src.nSamples, p->dv.data, src.calibOff, src.midUs, src.halfUs, src.nRigs,
                     tables, src.status, s);
     VB_CUDA(cudaGetLastError());
+  }
+  return any;
+}
+// the reference throws from inside compute(); here the status word is read back when the host next waits
+static void checkRsTables(vb_problem* p, int store) {
+  cudaStream_t s = p->ctx->stream;
+  for (auto& src : p->rsSources) {
+    if (store >= 0 && src.store != store) continue;
     int st = 0;
     VB_CUDA(cudaMemcpyAsync(&st, src.status, sizeof(int), cudaMemcpyDeviceToHost, s));
     VB_CUDA(cudaStreamSynchronize(s));
@@ -626,7 +634,10 @@ static void refreshRsTables(vb_problem* p, int store) {
     if (st == 2) throw std::domain_error("RollingShutterData::compute: more than 32 samples in a window");
     if (st != 0) throw std::domain_error("RollingShutterData::compute: sample times not increasing");
   }
-  if (store >= 0 && !any) throw std::invalid_argument("store has no IMU samples (vb_rs_set_imu)");
+}
+static void refreshRsTables(vb_problem* p, int store) {
+  if (!launchRsTables(p, store) && store >= 0) throw std::invalid_argument("store has no IMU samples (vb_rs_set_imu)");
+  checkRsTables(p, store);
 }
 
 extern "C" {
@@ -782,6 +793,7 @@ int64_t vb_num_launches_per_iteration(const vb_problem* p) { // kernels one vb_l
   for (const auto& st : p->ds) n += st.count > 0 ? (st.orderLm && st.twoPass ? 3 : 2) : 0; // grad/Hess (visual: two passes) + cost
   int64_t lv = 0;
   for (const auto& sc : p->sched) for (size_t i = 0; i + 1 < sc.lumpOff.size(); i++) lv += sc.lumpOff[i + 1] > sc.lumpOff[i];
+  n += (int64_t)p->rsSources.size(); // rolling-shutter table refresh
   return n + 2 /*damp, step=grad*/ + 1 + 2 * lv /*factor*/ + 2 + 2 * lv /*solve*/ + 2 /*dot, negate*/ + 1 /*apply*/;
 }
 int vb_get_param_start(const vb_problem* p, int64_t* out, int64_t n) {
@@ -1197,6 +1209,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   cudaEvent_t* e = p->ev;
   const int64_t n = p->S.order;
   VB_CUDA(cudaEventRecord(e[0], s));
+  launchRsTables(p, -1); // preStepCallback (Optimizer.cpp:801-805): part of the iteration, timed with grad/Hess
   evalGradHess(p, p->grad, 1, 1, 0, false); // also clears the evaluation error word
   VB_CUDA(cudaEventRecord(e[1], s));
   launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->dampMask, s);
@@ -1220,6 +1233,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   if (!apply) VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
   VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, (64 + 4 * ns) * sizeof(double), cudaMemcpyDeviceToHost, s));
   checkNumeric(p);
+  checkRsTables(p, -1);
   if (p->accHost[kAccErr] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
   auto ms = [&](int a, int b) { float f = 0; cudaEventElapsedTime(&f, e[a], e[b]); return (double)f; };
   if (t) {
@@ -1275,6 +1289,10 @@ int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* r
   VB_TRY
   requireProblem(p);
   if (store < 0 || store >= (int)p->ds.size() || p->g.stores[store].type != VB_F_VISUAL_RS) throw std::invalid_argument("not a rolling-shutter store");
+  if (n_samples == 0) { // forget the samples of this store: its tables stay as they are
+    for (auto it = p->rsSources.begin(); it != p->rsSources.end();) it = it->store == store ? p->rsSources.erase(it) : it + 1;
+    return VB_OK;
+  }
   const auto& hs = p->g.stores[store];
   if (!rig_mid_time_us || !rig_calib_var || !sample_time_ns || !gyro || !accel || n_samples < 2 || half_length_us <= 0)
     throw std::invalid_argument("null or empty IMU data");

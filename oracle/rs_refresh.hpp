@@ -13,6 +13,7 @@
 // trajectory, combine/uncombine round trips); the reference's own tests for this code
 // (lib/motion/preintegration/tests) need Eigen/Sophus and cannot be built here.
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <functional>
 #include <stdexcept>
@@ -100,11 +101,9 @@ inline void differentiate(const Rvp& rvp, double* interp) {
 
 // PreIntegration.cpp:16-26
 inline int64_t measIndexGT(const ImuSamples& meas, int64_t timeNs) {
-  const int64_t n = (int64_t)meas.timeNs.size();
-  int64_t i = 0;
-  while (i < n && !(timeNs < meas.timeNs[i])) i++;
-  if (i == n) throw std::runtime_error("measIndex_GT: unexpected, it == meas.end()");
-  return i;
+  const auto it = std::upper_bound(meas.timeNs.begin(), meas.timeNs.end(), timeNs);   // first sample strictly later
+  if (it == meas.timeNs.end()) throw std::runtime_error("measIndex_GT: unexpected, it == meas.end()");
+  return (int64_t)(it - meas.timeNs.begin());
 }
 
 // PreIntegration.cpp:28-111: fn(gyro sample, accel sample, dtSec, newAccelMeas, newGyroMeas)

@@ -5,6 +5,9 @@
 #include <stdexcept>
 #include <queue>
 #include <cstring>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 namespace vb {
 
@@ -78,6 +81,13 @@ bool Symbolic::block(int64_t ri, int64_t rj, BlockRef* out) const {
 
 void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp) {
   Symbolic& S = *Sp;
+  const bool verbose = std::getenv("VB_VERBOSE") != nullptr;
+  auto tPrev = std::chrono::steady_clock::now();
+  auto stage = [&](const char* what) {
+    const auto now = std::chrono::steady_clock::now();
+    if (verbose) std::fprintf(stderr, "[viba_b200] symbolic: %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - tPrev).count());
+    tPrev = now;
+  };
   const int64_t nP = g.nP;
   int64_t nB = 0;
   for (int64_t v = 0; v < g.nv; v++) if (g.index[v] >= 0) nB = std::max(nB, g.index[v] + 1);
@@ -96,9 +106,17 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
   for (int64_t p = 0; p < nP; p++) if (S.bsize[p] != 3) throw std::runtime_error("elimination range must hold 3-dim landmarks");
 
   // ---- adjacency: landmark -> camera blocks, camera <-> camera (direct) --------------------
-  std::vector<int64_t> lmKeys, ccKeys;
+  // Both key lists are sorted and made unique below, so the two filters here only have to be safe (never
+  // drop a key that was not pushed before): `camLast[c] == lm` means (lm, c) was pushed while this landmark
+  // was being walked, `recent` is a direct-mapped cache of camera-pair keys.  On landmark-major factor lists
+  // they remove most of the duplicates (one (landmark, calibration) pair per observation, one
+  // (pose, calibration) pair per observation of a rig) before they reach the sort.
+  std::vector<int32_t> pairLm, pairCam;   // (landmark, camera block) incidences, duplicates possible
+  std::vector<int64_t> ccKeys;
+  std::vector<int64_t> camLast(nC, -1);
+  constexpr int kRecentBits = 16;
+  std::vector<int64_t> recent(size_t(1) << kRecentBits, -1);
   for (const auto& st : g.stores) {
-    int64_t last = -1;
     for (int64_t k = 0; k < st.count; k++) {
       const int32_t* v = &st.vars[k * st.nvars];
       int64_t lm = -1;
@@ -111,24 +129,51 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
       }
       if (lm >= 0)
         for (int a = 0; a < nc; a++) {
-          const int64_t key = lm * nC + cams[a];
-          if (key != last) lmKeys.push_back(key);
-          last = key;
+          if (camLast[cams[a]] == lm) continue;
+          camLast[cams[a]] = lm;
+          pairLm.push_back((int32_t)lm);
+          pairCam.push_back((int32_t)cams[a]);
         }
       for (int a = 0; a < nc; a++)
-        for (int b = 0; b < a; b++)
-          if (cams[a] != cams[b]) ccKeys.push_back(std::max(cams[a], cams[b]) * nC + std::min(cams[a], cams[b]));
+        for (int b = 0; b < a; b++) {
+          if (cams[a] == cams[b]) continue;
+          const int64_t key = std::max(cams[a], cams[b]) * nC + std::min(cams[a], cams[b]);
+          int64_t& slot = recent[(size_t)((uint64_t)key * 0x9E3779B97F4A7C15ull >> (64 - kRecentBits))];
+          if (slot == key) continue;
+          slot = key;
+          ccKeys.push_back(key);
+        }
       if (ccKeys.size() > (size_t)(1 << 24)) sortUnique(ccKeys);
     }
   }
-  sortUnique(lmKeys);
+  stage("collect adjacency keys");
   sortUnique(ccKeys);
-  // landmark -> cams CSR (camera registration order c = reg - nP)
+  // landmark -> cams CSR (camera registration order c = reg - nP), cameras ascending and unique per landmark:
+  // bucket the incidences by landmark, then sort each (short) bucket
   std::vector<int64_t> lmPtr(nP + 1, 0);
-  std::vector<int32_t> lmCam(lmKeys.size());
-  for (size_t i = 0; i < lmKeys.size(); i++) { lmPtr[lmKeys[i] / nC + 1]++; lmCam[i] = (int32_t)(lmKeys[i] % nC); }
-  for (int64_t p = 0; p < nP; p++) lmPtr[p + 1] += lmPtr[p];
-  std::vector<int64_t>().swap(lmKeys);
+  std::vector<int32_t> lmCam;
+  {
+    std::vector<int64_t> bucket(nP + 1, 0);
+    for (int32_t p : pairLm) bucket[p + 1]++;
+    for (int64_t p = 0; p < nP; p++) bucket[p + 1] += bucket[p];
+    std::vector<int32_t> tmp(pairLm.size());
+    {
+      std::vector<int64_t> fill(bucket.begin(), bucket.end() - 1);
+      for (size_t i = 0; i < pairLm.size(); i++) tmp[fill[pairLm[i]]++] = pairCam[i];
+    }
+    std::vector<int32_t>().swap(pairLm);
+    std::vector<int32_t>().swap(pairCam);
+    lmCam.reserve(tmp.size());
+    for (int64_t p = 0; p < nP; p++) {
+      int32_t* b = tmp.data() + bucket[p];
+      int32_t* e = tmp.data() + bucket[p + 1];
+      std::sort(b, e);
+      e = std::unique(b, e);
+      lmCam.insert(lmCam.end(), b, e);
+      lmPtr[p + 1] = (int64_t)lmCam.size();
+    }
+  }
+  stage("sort adjacency keys");
   // cam -> landmarks CSR
   std::vector<int64_t> clPtr(nC + 1, 0);
   for (int32_t c : lmCam) clPtr[c + 1]++;
@@ -152,6 +197,7 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
     }
   }
 
+  stage("adjacency CSR");
   // ---- ordering of the camera side -----------------------------------------------------------
   // Nested dissection by BFS level structures on the Schur-filled graph (walked through the
   // landmark adjacency, never materialised): the visual-inertial graph is a chain in time, so a
@@ -249,6 +295,7 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
     }
     if ((int64_t)orderC.size() != nC) throw std::runtime_error("ordering lost camera blocks");
   }
+  stage("nested dissection ordering");
   std::vector<int32_t> cpos(nC); // camera registration c -> camera position
   for (int64_t i = 0; i < nC; i++) cpos[orderC[i]] = (int32_t)i;
 
@@ -282,6 +329,7 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
     S.lmDataSize = off;
   }
 
+  stage("landmark panels");
   // ---- symbolic Cholesky of the reduced camera system (column structures via the etree) ------
   std::vector<std::vector<int32_t>> cstruct(nC);
   std::vector<int32_t> parent(nC, -1);
@@ -315,6 +363,7 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
     }
   }
 
+  stage("column structures");
   // ---- supernodes ("lumps"): chains of columns merged under a width cap and a fill budget ----
   auto csize = [&](int32_t c) { return S.camStart[c + 1] - S.camStart[c]; };
   S.camLump.assign(nC, 0);
@@ -385,6 +434,7 @@ void buildSymbolic(const HostGraph& g, const SymbolicOptions& opt, Symbolic* Sp)
   }
   S.levels.assign(S.nL ? maxLevel + 1 : 0, {});
   for (int64_t L = 0; L < S.nL; L++) S.levels[S.lumpLevel[L]].push_back((int32_t)L);
+  stage("supernodes and levels");
 }
 
 } // namespace vb

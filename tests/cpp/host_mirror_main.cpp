@@ -12,6 +12,7 @@
 //              | int32 vars[count*nvars] | double consts[count*cpf] | double aux[auxLen]
 #include <small_thing/Optimizer.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <deque>
@@ -233,6 +234,13 @@ int run(int argc, char** argv) {
           f.diagSqrtH = arr<6>(c);
           f.priorInverse.q = arr<4>(c + 6);
           f.priorInverse.t = arr<3>(c + 10);
+          {  // the helper a user calls with the prior itself: inverting twice must give the payload back
+            const SE3 back = SE3PriorFactor::inverse(SE3PriorFactor::inverse(f.priorInverse));
+            for (int i = 0; i < 4; i++)
+              if (std::abs(back.q[i] - f.priorInverse.q[i]) > 1e-14) throw std::runtime_error("SE3PriorFactor::inverse: rotation");
+            for (int i = 0; i < 3; i++)
+              if (std::abs(back.t[i] - f.priorInverse.t[i]) > 1e-13) throw std::runtime_error("SE3PriorFactor::inverse: translation");
+          }
           opt.addFactor(f, as<SE3>(vars, v[0]));
           break;
         }

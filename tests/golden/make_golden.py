@@ -62,6 +62,17 @@ def golden_for(name, lib):
     o.damp(LAMBDA); o.factor(); o.solve()
     out["step"] = o.step
     out["model_decrease"] = np.float64(0.5 * o.step @ o.grad)
+    if any(st.type == G.F_VISUAL_RS for st in g.stores):
+        # rolling-shutter tables recomputed from raw IMU samples with the session's initial calibration
+        # (RollingShutterData::compute, oracle/rs_refresh.hpp) and the cost evaluated on them
+        d = synth.imu0_samples(s)
+        o3 = Oracle(lib, g)
+        o3.rs_set_imu(d["store"], d["time_ns"], d["gyro"], d["accel"], d["rig_mid_time_us"], d["rig_calib_var"], d["half_length_us"])
+        o3.rs_refresh()
+        rigs = np.flatnonzero(d["rig_calib_var"] >= 0)
+        out["rs_tables_refreshed"] = o3.store_aux(d["store"])[4:].reshape(-1, synth.RS_STRIDE)[rigs]
+        out["rs_cost_after_refresh"] = np.float64(o3.eval_cost(False)[0])
+        out["imu_digest"] = np.array(hashlib.sha256(d["time_ns"].tobytes() + d["gyro"].tobytes() + d["accel"].tobytes()).hexdigest())
     o2 = Oracle(lib, g)
     summ, tp, tn = o2.optimize(G.default_settings(ITERS))
     out["opt_iterations"] = np.int64(summ.num_iterations)

@@ -73,7 +73,82 @@ std::array<double, N> arr(const double* p) {
 
 }  // namespace
 
+// host-side contract of the mirror, no device: every misuse the reference rejects with BASPACHO_CHECK / a
+// compile error is a std::runtime_error here
+template <typename Fn>
+static bool throwsRuntimeError(Fn&& fn) {
+  try {
+    fn();
+  } catch (const std::runtime_error&) {
+    return true;
+  }
+  return false;
+}
+
+static int selftest() {
+  int bad = 0;
+  auto expect = [&](bool ok, const char* what) {
+    if (!ok) {
+      std::fprintf(stderr, "selftest failed: %s\n", what);
+      bad++;
+    }
+  };
+  Variable<Vec3> X, X2, vel;
+  Variable<SE3> T_bw, T_cb;
+  Variable<CameraModelParam> cam;
+  Variable<ImuCalibParam> imu;
+  Variable<S2> g;
+  HuberLossWithCutoff loss(1.0, 3.0), otherLoss(2.0, 3.0);
+  const VisualFactor vf{{{10.0, 20.0}}, {{0.7, 0.0, 0.0, 0.7}}};
+  {
+    Optimizer opt;
+    auto [store, k] = opt.addFactor(vf, loss, X, T_bw, T_cb, cam);
+    expect(k == 0 && store->numCosts() == 1 && store->name() == "VisualFactor" && store->costVar(0, 1) == &T_bw, "store introspection");
+    expect(opt.addFactor(vf, loss, X2, T_bw, T_cb, cam).second == 1, "second factor lands in the same store");
+    expect(opt.factorStores.size() == 1, "one store per factor type");
+    expect(throwsRuntimeError([&] { opt.addFactor(vf, otherLoss, X, T_bw, T_cb, cam); }), "two different losses in one store");
+    expect(throwsRuntimeError([&] { opt.addFactor(vf, loss, X, T_bw, T_cb); }), "wrong arity");
+    expect(throwsRuntimeError([&] { opt.addFactor(vf, loss, T_bw, X, T_cb, cam); }), "wrong variable types");
+    const double info[81] = {};
+    expect(throwsRuntimeError([&] { opt.addFactor(vf, info, loss, X, T_bw, T_cb, cam); }), "precision matrix on a factor that takes none");
+    PreIntegrationData pre;
+    Variable<SE3> T2;
+    Variable<Vec3> v2;
+    expect(throwsRuntimeError([&] { opt.addFactor(InertialFactor{&pre}, loss, imu, T_bw, vel, T2, v2, g); }), "inertial factor without precision matrix");
+    // registration: points first, then per store / argument / factor; constants keep kConstantVar
+    g.setConstant();
+    opt.registerVariable(X);
+    opt.registerVariable(X2);
+    opt.registeredVariablesToEliminationRange();
+    opt.registerAllVariables();
+    expect(X.index == 0 && X2.index == 1 && T_bw.index == 2 && T_cb.index == 3 && cam.index == 4, "registration order");
+    expect(opt.elimRanges.size() == 2 && opt.elimRanges[1] == 2, "elimination range");
+    expect(opt.totalVarDimensionality() == 3 + 3 + 6 + 6 + 15 && opt.totalErrorDimensionality() == 4, "dimensionalities");
+    expect(throwsRuntimeError([&] { X.setConstant(); }), "setConstant on a registered variable");
+    expect(g.isSetToConstant() && !g.isRegistered(), "constant variable");
+    auto ex = opt.exportGraph();
+    expect(ex->desc.num_vars == 5 && ex->desc.num_points == 2 && ex->stores[0].count == 2 && ex->stores[0].loss_a == 1.0 && ex->stores[0].loss_k == 3.0, "exported graph");
+    loss.setSize(1.5, 4.0);   // the loss is held by pointer: later changes are what the device sees (Factor.h:141)
+    expect(opt.exportGraph()->stores[0].loss_a == 1.5, "loss read at export time");
+    opt.unregisterAllVariables();
+    expect(X.isUnset() && cam.isUnset() && opt.paramSizes.empty() && g.isSetToConstant(), "unregisterAllVariables");
+  }
+  {
+    Optimizer opt;   // the elimination range must hold 3-D points only, and there is one range
+    opt.registerVariable(T_bw);
+    opt.registeredVariablesToEliminationRange();
+    opt.addFactor(vf, X, T_bw, T_cb, cam);
+    expect(throwsRuntimeError([&] { opt.exportGraph(); }), "pose inside the elimination range");
+    opt.unregisterAllVariables();
+  }
+  expect(throwsRuntimeError([] { HuberLossWithCutoff l(0.0, 1.0); }) && throwsRuntimeError([] { HuberLossWithCutoff l(2.0, 1.0); }), "loss parameter checks");
+  expect(HuberLossWithCutoff(1.0, 3.0).val(0.5) == 0.5 && HuberLossWithCutoff(1.0, 3.0).val(4.0) == 3.0 && HuberLossWithCutoff(1.0, 3.0).val(100.0) == 5.0, "loss values");
+  std::printf("selftest: %s\n", bad ? "FAILED" : "ok");
+  return bad ? 1 : 0;
+}
+
 int run(int argc, char** argv) {
+  if (argc >= 2 && std::string(argv[1]) == "--selftest") return selftest();
   if (argc < 3) {
     std::fprintf(stderr, "usage: %s in.bin out.bin [--optimize N]\n", argv[0]);
     return 2;

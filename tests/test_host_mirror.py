@@ -165,6 +165,13 @@ def test_mirror_builds_the_same_graph(name, mirror_bin, tmp_path):
     assert c["err_dim"] == sum(st.count * G.ERR_SIZE[st.type] for st in g.stores)
 
 
+def test_mirror_host_contract(mirror_bin):
+    """addFactor argument checks, store introspection, registration order, constants, loss-by-pointer semantics,
+    elimination-range checks: std::runtime_error wherever the reference's BASPACHO_CHECK would throw"""
+    r = subprocess.run([mirror_bin, "--selftest"], capture_output=True, text=True)
+    assert r.returncode == 0 and "selftest: ok" in r.stdout, r.stdout + r.stderr
+
+
 def test_mirror_compute_call_throws_without_device(mirror_bin, tmp_path):
     import torch
     if torch.cuda.is_available():

@@ -198,7 +198,7 @@ class Optimizer {
   // ---- compute entry points ---------------------------------------------------------------------
   // Optimizer.h:232-235 / Optimizer.cpp:88-97 -> vb_eval_cost
   double computeCost(bool makeComparableWithStored = false, CostStats* stats = nullptr) {
-    ensureBackend(0);
+    ensureBackend(ctx_ ? device_ : 0);   // stay on the device optimize() was last asked to use
     double cost = 0.0;
     vb_cost_stats cs{};
     check(vb_eval_cost(problem_, makeComparableWithStored ? 1 : 0, &cost, &cs));

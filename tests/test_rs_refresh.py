@@ -38,7 +38,7 @@ def tables_of(aux):
 def compare_tables(a, b, rigs, tol):
     for r in rigs:
         n = int(a[r, 0])
-        assert n == int(b[r, 0]) and 20 <= n <= synth.RS_MAX_SAMPLES
+        assert n == int(b[r, 0]) and 15 <= n <= synth.RS_MAX_SAMPLES
         sa, sb = a[r, 1:1 + n * 11], b[r, 1:1 + n * 11]
         assert np.abs(sa - sb).max() <= tol
         ia, ib = a[r, IOFF:IOFF + (n - 1) * 9], b[r, IOFF:IOFF + (n - 1) * 9]
@@ -110,6 +110,55 @@ def test_device_routine_on_host_matches_oracle(name, oracle, host_refresh):
     # the refreshed tables keep every rolling-shutter observation inside the sampled window
     c, stats = o.eval_cost(False)
     assert np.isfinite(c) and stats[1] == 0
+
+
+def test_device_routine_irregular_samples_and_time_offsets(oracle, host_refresh):
+    """BASELINE C4 ingredients: an 800 Hz IMU with jittered time stamps and separate gyro / accelerometer time
+    offsets of 2-4 ms (ImuUtils.cpp:46-47), so that integration pieces end at gyro and at accel boundaries that
+    do not coincide and windows start between samples; device routine (as host code) against the oracle"""
+    s = synth.make_session(**synth.CONFIGS["tiny_rs"])
+    d = synth.imu0_samples(s, rate_hz=800.0)
+    rng = np.random.default_rng(3)
+    t = d["time_ns"] + rng.integers(-100_000, 100_000, d["time_ns"].size)
+    assert np.all(np.diff(t) > 0)
+    d["time_ns"] = np.ascontiguousarray(t, np.int64)
+    d["half_length_us"] = 12000
+    g = s.graph
+    o = Oracle(oracle, g)
+    v = o.vars
+    for w, vid in enumerate(s.ids["imu"]):
+        v[g.var_off[vid] + 30] = 3.1e-3 + 1e-4 * w   # accel reference time offset
+        v[g.var_off[vid] + 31] = 2.3e-3 - 1e-4 * w   # gyro reference time offset
+    o.set(4, v)
+    set_imu(o, d)
+    o.rs_refresh()
+    want = tables_of(o.store_aux(d["store"]))
+    n_rigs = d["rig_mid_time_us"].size
+    calib_off = np.where(d["rig_calib_var"] >= 0, g.var_off[np.maximum(d["rig_calib_var"], 0)], -1).astype(np.int64)
+    got = np.zeros((n_rigs, STRIDE))
+    ip, fp, dp = C.POINTER(C.c_int64), C.POINTER(C.c_float), C.POINTER(C.c_double)
+    gy, ac = np.ascontiguousarray(d["gyro"]), np.ascontiguousarray(d["accel"])
+    host_refresh.rf_refresh_rigs.argtypes = [ip, fp, fp, C.c_int64, dp, ip, ip, C.c_int64, C.c_int64, dp]
+    st = host_refresh.rf_refresh_rigs(d["time_ns"].ctypes.data_as(ip), gy.ctypes.data_as(fp), ac.ctypes.data_as(fp), d["time_ns"].size,
+                                      v.ctypes.data_as(dp), calib_off.ctypes.data_as(ip), d["rig_mid_time_us"].ctypes.data_as(ip),
+                                      d["half_length_us"], n_rigs, got.ctypes.data_as(dp))
+    assert st == 0
+    rigs = np.flatnonzero(d["rig_calib_var"] >= 0)
+    compare_tables(got, want, rigs, 1e-12)
+    for r in rigs:   # the window still spans exactly +-half length around the rig's own time
+        n = int(got[r, 0])
+        dts = got[r, 1:1 + n * 11].reshape(n, 11)[:, 10]
+        assert dts[0] == pytest.approx(-0.012, abs=1e-9) and dts[-1] == pytest.approx(0.012, abs=1e-9) and np.all(np.diff(dts) > 0)
+    # too wide a window for the table: the oracle throws, the device routine reports kTooManySamples
+    d2 = dict(d, half_length_us=25000)
+    o2 = Oracle(oracle, g)
+    set_imu(o2, d2)
+    with pytest.raises(RuntimeError, match="more than 32 samples"):
+        o2.rs_refresh()
+    st = host_refresh.rf_refresh_rigs(d["time_ns"].ctypes.data_as(ip), gy.ctypes.data_as(fp), ac.ctypes.data_as(fp), d["time_ns"].size,
+                                      v.ctypes.data_as(dp), calib_off.ctypes.data_as(ip), d["rig_mid_time_us"].ctypes.data_as(ip),
+                                      25000, n_rigs, got.ctypes.data_as(dp))
+    assert st == 2
 
 
 def test_refresh_errors(oracle):

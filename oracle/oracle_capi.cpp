@@ -207,6 +207,20 @@ int orc_rs_set_imu(OrcHandle* h, int store, int64_t n_rigs, const int64_t* rig_m
   h->eng.preStep = [h]() { rsRefresh(h, -1); };
   ORC_CATCH
 }
+// integrateMeasurements (PreIntegration.cpp:277-306) on raw samples: out = q(4) dV(3) dP(3) dt
+int orc_integrate_measurements(int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel,
+                               const double* calib32, int64_t start_us, int64_t end_us, double* out11) {
+  ORC_TRY
+  ImuSamples m;
+  m.timeNs.assign(sample_time_ns, sample_time_ns + n_samples);
+  m.gyro.assign(gyro, gyro + 3 * n_samples);
+  m.accel.assign(accel, accel + 3 * n_samples);
+  const Rvp r = integrateMeasurements(m, measModelFromCalib(calib32), start_us, end_us);
+  for (int i = 0; i < 4; i++) out11[i] = r.q[i];
+  for (int i = 0; i < 3; i++) { out11[4 + i] = r.dV[i]; out11[7 + i] = r.dP[i]; }
+  out11[10] = r.dt;
+  ORC_CATCH
+}
 int orc_rs_refresh(OrcHandle* h, int store) {
   ORC_TRY
   rsRefresh(h, store);

@@ -151,6 +151,22 @@ inline void forEachIntegratedMeasurement(const ImuSamples& meas, const MeasModel
   fn(prev, true, true);
 }
 
+// PreIntegration.cpp:277-306: the preintegrated rotation / velocity / position over [start, end]
+inline Rvp integrateMeasurements(const ImuSamples& meas, const MeasModel& model, int64_t timeStartUs, int64_t timeEndUs) {
+  Rvp total{{0, 0, 0, 1}, {0, 0, 0}, {0, 0, 0}, 0.0};
+  bool first = true;
+  enumIntegrationSteps(meas, model, timeStartUs, timeEndUs, [&](const float* g, const float* a, double dtSec, bool, bool) {
+    double gd[3] = {g[0], g[1], g[2]}, ad[3] = {a[0], a[1], a[2]}, gc[3], ac[3];
+    mat3vec(model.gyroScaleInv, gd, gc);
+    mat3vec(model.accelScaleInv, ad, ac);
+    for (int i = 0; i < 3; i++) { gc[i] -= model.gyroBias[i]; ac[i] -= model.accelBias[i]; }
+    const Rvp piece = integrate(gc, ac, dtSec);
+    total = first ? piece : combine(total, piece);
+    first = false;
+  });
+  return total;
+}
+
 // RollingShutterData::compute -> the per-rig table of motion.hpp
 inline void rsCompute(const ImuSamples& meas, const double* calib32, int64_t midpointUs, int64_t halfLengthUs, double* table) {
   const MeasModel model = measModelFromCalib(calib32);

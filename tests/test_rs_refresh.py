@@ -83,9 +83,9 @@ def test_oracle_refresh_follows_the_true_motion(oracle):
         for row in smp:   # closed-form table is sampled every ms: compare where the times coincide
             k = np.argmin(np.abs(rs[:, 10] - row[10]))
             if abs(rs[k, 10] - row[10]) < 1e-9:
-                assert np.abs(row[:4] - rs[k, :4]).max() < 2e-6      # rotation
-                assert np.abs(row[4:7] - rs[k, 4:7]).max() < 2e-4    # velocity increment
-                assert np.abs(row[7:10] - rs[k, 7:10]).max() < 2e-6  # position increment
+                assert np.abs(row[:4] - rs[k, :4]).max() < 1e-6      # rotation (float32 samples)
+                assert np.abs(row[4:7] - rs[k, 4:7]).max() < 2e-6    # velocity increment
+                assert np.abs(row[7:10] - rs[k, 7:10]).max() < 2e-8  # position increment
 
 
 @pytest.mark.parametrize("name", ["tiny_rs", "small_rs"])
@@ -202,3 +202,29 @@ def test_gpu_refresh_matches_oracle(name, oracle):
         p.rs_refresh()
     assert e.value.code == 3
     p.close(); ctx.close()
+
+
+def test_oracle_preintegration_of_raw_samples_matches_the_true_motion(oracle):
+    """integrateMeasurements (PreIntegration.cpp:277-306, restated in oracle/rs_refresh.hpp) over consecutive rigs,
+    on noise-free samples with the ground-truth calibration, against the closed form the inertial factor expects
+    (InertialFactor.cpp:47-70): R = R_bw(prev) R_wb(next), dV = R_bw(prev)(v_n - v_p - g dt),
+    dP = p_p - R p_n - R_bw(prev)(v_p dt + g dt^2/2) with p = translation of T_bodyImu_world."""
+    s = synth.make_session(**synth.CONFIGS["tiny_rs"])
+    d = synth.imu0_samples(s, noise=False)
+    T, vel, grav = s.gt["T_bw"], s.gt["vel"], np.array([0.0, 0.0, -9.81])
+    ip, fp, dp = C.POINTER(C.c_int64), C.POINTER(C.c_float), C.POINTER(C.c_double)
+    oracle.orc_integrate_measurements.argtypes = [C.c_int64, ip, fp, fp, dp, C.c_int64, C.c_int64, dp]
+    t, gy, ac, mid = d["time_ns"], np.ascontiguousarray(d["gyro"]), np.ascontiguousarray(d["accel"]), d["rig_mid_time_us"]
+    for k in range(0, s.n_rigs - 1, 3):
+        calib = np.ascontiguousarray(s.gt["imu"][s.win[k]])
+        out = np.zeros(11)
+        assert oracle.orc_integrate_measurements(t.size, t.ctypes.data_as(ip), gy.ctypes.data_as(fp), ac.ctypes.data_as(fp),
+                                                 calib.ctypes.data_as(dp), int(mid[k]), int(mid[k + 1]), out.ctypes.data_as(dp)) == 0
+        dt = (mid[k + 1] - mid[k]) * 1e-6
+        qp, qn = T[k, :4], T[k + 1, :4]
+        R = synth.quat_mul(qp, synth.quat_conj(qn))
+        dV = synth.quat_rotate(qp, vel[k + 1] - vel[k] - grav * dt)
+        dP = T[k, 4:] - synth.quat_rotate(R, T[k + 1, 4:]) - synth.quat_rotate(qp, vel[k] * dt + grav * (0.5 * dt * dt))
+        assert out[10] == pytest.approx(dt, abs=1e-12)
+        assert min(np.abs(out[:4] - R).max(), np.abs(out[:4] + R).max()) < 5e-7   # float32 samples, 1 kHz midpoint rule
+        assert np.abs(out[4:7] - dV).max() < 1e-6 and np.abs(out[7:10] - dP).max() < 2e-8

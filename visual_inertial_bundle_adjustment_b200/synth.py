@@ -485,8 +485,8 @@ def imu0_samples(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
     the session's IMU CSV, lib/motion/imu_types/ImuDataFormat.h:14-23): time stamps in ns, float32 gyro
     (rad/s) and accelerometer (m/s^2) readings at `rate_hz`, each the mean of the true body rate / specific
     force over the sample's interval, distorted by the ground-truth calibration of its window
-    (measured = scale_matrix * (true + bias), the inverse of getCompensatedImuMeasurement) plus white noise
-    (ImuNoiseModelParameters defaults).  Returns dict(time_ns, gyro, accel, rig_mid_time_us, rig_calib_var,
+    (measured = scale_matrix * (true + bias), the inverse of getCompensatedImuMeasurement, read at the true time
+    shifted by the window's gyro / accelerometer reference time offsets) plus a little white noise.  Returns dict(time_ns, gyro, accel, rig_mid_time_us, rig_calib_var,
     half_length_us) ready for vb_rs_set_imu; rigs without rolling-shutter observations get calib var -1."""
     global _LOOP_PERIOD
     g = session.graph
@@ -496,17 +496,20 @@ def imu0_samples(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
     t_end = times[0] - margin_s + dt * np.arange(n)          # a sample closes the interval (t - dt, t]
     t_mid = t_end - 0.5 * dt
     h = 1e-4
+    w_idx = np.clip(np.searchsorted(times, t_mid, side="right") - 1, 0, times.size - 1)
+    calib = session.gt["imu"][win[w_idx]]                   # (n, 32): gs, as, gb, ab, Gn(col-major), An, dta, dtg
+    # a sample stamped tau carries the gyro reading of true time tau - dtReferenceGyro and the accelerometer
+    # reading of tau - dtReferenceAccel (enumIntegrationSteps subtracts them again, PreIntegration.cpp:36-43)
+    t_g, t_a = t_mid - calib[:, 31], t_mid - calib[:, 30]
     _LOOP_PERIOD = session.loop_period_s
     try:
-        qm = _traj(t_mid)[2]
-        w_body = so3_log(quat_mul(quat_conj(_traj(t_mid - h)[2]), _traj(t_mid + h)[2])) / (2 * h)
-        a_world = (_traj(t_mid + h)[1] - _traj(t_mid - h)[1]) / (2 * h)
+        w_body = so3_log(quat_mul(quat_conj(_traj(t_g - h)[2]), _traj(t_g + h)[2])) / (2 * h)
+        a_world = (_traj(t_a + h)[1] - _traj(t_a - h)[1]) / (2 * h)
+        qa = _traj(t_a)[2]
     finally:
         _LOOP_PERIOD = None
     grav = np.array([0.0, 0.0, -9.81])
-    f_body = quat_rotate(quat_conj(qm), a_world - grav)
-    w_idx = np.clip(np.searchsorted(times, t_mid, side="right") - 1, 0, times.size - 1)
-    calib = session.gt["imu"][win[w_idx]]                   # (n, 32): gs, as, gb, ab, Gn(col-major), An, dta, dtg
+    f_body = quat_rotate(quat_conj(qa), a_world - grav)
     Gn = calib[:, 12:21].reshape(n, 3, 3).transpose(0, 2, 1)
     An = calib[:, 21:30].reshape(n, 3, 3).transpose(0, 2, 1)
     gyro = calib[:, 0:3] * np.einsum("nij,nj->ni", Gn, w_body + calib[:, 6:9])

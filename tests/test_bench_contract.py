@@ -28,3 +28,18 @@ def test_reference_arm_other_ranks_exit_quietly():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2"],
                          capture_output=True, text=True, timeout=120, cwd=ROOT, env=env)
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_bench_attaches_imu_samples_to_rolling_shutter_sessions(oracle):
+    """the refresher is part of the timed iteration on both arms: bench.attach_rs_imu on the CPU arm's oracle"""
+    import bench
+    from tests.oracle_lib import Oracle
+    from visual_inertial_bundle_adjustment_b200 import synth
+    s = synth.make_session(**synth.CONFIGS["tiny_rs"])
+    o = Oracle(oracle, s.graph)
+    note = bench.attach_rs_imu(o, s)
+    assert note.startswith("RollingShutterData::compute for ") and "inside every iteration" in note
+    ms, c0, c1 = o.lm_iteration_timed(1e-5)   # runs the refresh first (preStepCallback)
+    assert c1 < c0
+    s2 = synth.make_session(**synth.CONFIGS["tiny"])
+    assert bench.attach_rs_imu(Oracle(oracle, s2.graph), s2) == "no rolling-shutter camera"

@@ -1,14 +1,23 @@
 #!/usr/bin/env python
 """bench.py — ms per LM iteration (Jacobian+Hessian build, Schur + Cholesky solve) on synthetic
 Aria-like sessions, the metric of BASELINE.json.  One "step" = one accepted-path LM iteration
-(Optimizer.cpp:800-1076): grad/Hess build, damping, factor, solve, backup+apply, cost.
+(Optimizer.cpp:800-1076): RS-table refresh, grad/Hess build, damping, factor, solve, backup+apply, cost.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
 
-N>1 is launched by torchrun (one rank per GPU): every rank holds the SAME session, landmarks (with
-all of their observations), factors and the subtrees of the reduced system's elimination tree are
-split over the ranks; the shared top of the reduced system, the camera right-hand side / step and the
-landmark steps are summed over NCCL at the exchange points of the C ABI's collective hook.  Total work is fixed as N grows: "scaling": "strong".
+Default workload: c3_20min_rs, BASELINE.json configs[2] (the 20-minute session the metric is quoted on "at
+1/2/4/8 B200"); it fits one GPU.  Both arms run the SAME session: `--impl reference` times the CPU port of
+the reference path (oracle/, OpenMP + OpenBLAS) on that session, no sampling, no extrapolation.
+
+N>1 is launched by torchrun (one rank per GPU): every rank holds the same session; landmarks (with all of
+their observations), factors and the subtrees of the reduced system's elimination tree are split over the
+ranks; the shared top of the reduced system, the camera right-hand side / step and the landmark steps are
+exchanged over NCCL at the exchange points of the C ABI's collective hook.  Total work is
+fixed as N grows: "scaling": "strong".
+
+Parity inside the line: `parity` holds cost before / cost after / step.grad of the timed iteration and their
+relative differences against the CPU port (N=1, when the CPU leg runs) or against an unsharded problem rank 0
+builds after the timed region (N>1); the run FAILS (exit 3) when a cost differs by more than 1e-9 relative.
 """
 import argparse
 import json
@@ -23,8 +32,10 @@ sys.path.insert(0, ROOT)
 
 import numpy as np  # noqa: E402
 
-DEFAULT_WORKLOAD = "c2_5min_rs"
-SAMPLE_WORKLOAD = "c1_60s_rs"  # bounded CPU sample: 60 s of the same kind of session
+DEFAULT_WORKLOAD = "c3_20min_rs"
+METRIC = "ms per LM iteration (Jacobian+Hessian build, Schur+Cholesky solve)"
+PARITY_TOL = 1e-9           # north star: per-iteration cost, FP64 relative
+REFERENCE_THREADS = 8       # viba/common/Settings.h:87 (numThreads = 8)
 
 
 def read_peaks():
@@ -66,10 +77,26 @@ class ClockSampler(threading.Thread):
 
 
 def make_workload(name, rank=0):
+    """the session of a named workload; generated once per box and cached on disk (synth.cached_session), so the
+    ranks of a torchrun job and the two bench arms read the same bytes"""
     from visual_inertial_bundle_adjustment_b200 import synth
-    cfg = dict(synth.CONFIGS[name])
-    cfg["seed"] = 42  # every rank builds the same session (rank is kept for callers that want replicas)
-    return synth.make_session(**cfg), cfg
+    if name.startswith("c5_"):
+        return synth.cached_session(name, seed=42)
+    return synth.cached_session(name, seed=42)
+
+
+def workload_config(name, s, cfg, rs_note):
+    """`config` of the JSON line: what the workload IS — identical on both arms and at every N"""
+    rs_obs = int(s.ext.get("rs_obs", 0))
+    cams = "2 global-shutter SLAM cameras" + (" + RGB rolling-shutter camera with readout/time-offset states" if cfg.get("rgb") else "")
+    extra = ""
+    if cfg.get("loop_period_s"):
+        extra = f", closed walk with {100 * cfg.get('lc_frac', 0):g} % loop-closure tracks"
+    return {"workload": f"synthetic {name}: {cfg['duration_s']:g} s Aria-like session, the same session on both arms and at every N "
+                        f"({cams}, {cfg.get('n_imus', 1)} IMU(s), 5 s calibration windows, RW + factory priors{extra})",
+            "observations": int(s.n_obs + rs_obs), "rs_observations": rs_obs, "landmarks": int(s.n_points), "rigs": int(s.n_rigs),
+            "rs_refresh": rs_note, "lambda": 1e-5,
+            "l2": "inputs larger than L2 (Hessian + factor tables exceed 126 MB); no flush needed"}
 
 
 def attach_rs_imu(target, session):
@@ -89,34 +116,42 @@ def attach_rs_imu(target, session):
         return "off (%s)" % str(ex)[:120]
 
 
-def cpu_leg(workload, steps, warmup):
-    """The reference's CPU path cannot be built offline (BaSpaCho/Eigen/Sophus absent: SURVEY.md
-    F1,F3), so the CPU arm is the oracle port in its baseline mode — factor loops and landmark
-    elimination on every host core (OpenMP, atomic block adds, as the reference's thread pool does
-    with locked adds) and the reduced-system Cholesky through LAPACK dpbtrf on the multi-threaded
-    OpenBLAS that ships with scipy (the reference: BaSpaCho's BLAS backend on OpenBLAS) — timed on
-    a bounded sample (60 s of the same kind of session) and scaled by session duration."""
+def cpu_leg(s, workload, steps, warmup, thread_counts):
+    """The reference's CPU path cannot be built offline (BaSpaCho/Eigen/Sophus absent: SURVEY.md F1,F3), so
+    the CPU arm is the oracle port in its baseline mode — factor loops and landmark elimination on T host
+    threads (OpenMP, atomic block adds, as the reference's thread pool does with locked adds) and the
+    reduced-system Cholesky through LAPACK dpbtrf on the multi-threaded OpenBLAS that ships with scipy (the
+    reference: BaSpaCho's BLAS backend on OpenBLAS) — timed on the SAME session as the GPU arm, whole
+    iterations, no sampling.  Returns (cpu_baseline dict for the first thread count, per-T results, rs note)."""
     from tests.oracle_lib import load_oracle, Oracle
-    from visual_inertial_bundle_adjustment_b200 import synth
-    sample = SAMPLE_WORKLOAD if synth.CONFIGS[workload].get("rgb") else "c1_60s"
-    s, _ = make_workload(sample)
+    t0 = time.time()
     o = Oracle(load_oracle(), s.graph)
-    cores = os.cpu_count() or 1
-    solver_kind = o.set_parallel(cores)
-    attach_rs_imu(o, s)
-    scale = synth.CONFIGS[workload]["duration_s"] / synth.CONFIGS[sample]["duration_s"]
-    ts = []
-    for i in range(warmup + steps):
-        ms, c0, c1 = o.lm_iteration_timed(1e-5)
-        if i >= warmup:
-            ts.append(ms)
-    ms = np.mean(np.array(ts), 0)
-    return {"value": float(ms[6] * scale), "unit": "ms/iteration", "cores": cores, "kind": "port",
-            "solver": solver_kind,
-            "sample": f"oracle port ({cores} OpenMP threads, reduced system by {solver_kind}) on the {sample} session ({s.n_obs + s.ext.get("rs_obs", 0)} observations, {s.n_rigs} rigs), "
-                      f"x{scale:g} by session duration to {workload}; split g/H {ms[0]:.0f} ms, factor {ms[2]:.0f} ms, "
-                      f"solve {ms[3]:.0f} ms, cost {ms[5]:.0f} ms on the sample",
-            "sample_ms": float(ms[6]), "scale": scale}
+    create_s = time.time() - t0
+    rs_note = attach_rs_imu(o, s)
+    runs = []
+    for T in thread_counts:
+        solver_kind = o.set_parallel(T)
+        ts, c0, c1 = [], None, None
+        for i in range(warmup + steps):
+            ms, c0, c1 = o.lm_iteration_timed(1e-5)
+            if i >= warmup:
+                ts.append(ms)
+        ms = np.mean(np.array(ts), 0)
+        runs.append({"threads": T, "value": float(ms[6]), "unit": "ms/iteration", "solver": solver_kind, "steps": steps, "warmup": warmup,
+                     "phases_ms": {"grad_hess": float(ms[0]), "damping": float(ms[1]), "factor": float(ms[2]), "solve": float(ms[3]),
+                                   "apply": float(ms[4]), "cost": float(ms[5])},
+                     "cost_before": c0, "cost_after": c1, "step_dot_grad": float(ms[7])})
+    head = runs[0]
+    n_obs = int(s.n_obs + s.ext.get("rs_obs", 0))
+    cb = {"value": head["value"], "unit": "ms/iteration", "cores": head["threads"], "kind": "port", "solver": head["solver"],
+          "sample": f"the whole {workload} session ({n_obs} observations, {s.n_rigs} rigs): {head['steps']} full iteration(s) of the oracle port after "
+                    f"{head['warmup']} warm-up, {head['threads']} OpenMP threads, reduced system by {head['solver']}; not a sample, not extrapolated",
+          "host_cores": os.cpu_count(), "setup_s": round(create_s, 1), "runs": runs}
+    return cb, runs, rs_note
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
 
 
 def main():
@@ -126,27 +161,58 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU leg of the b200 arm (and with it the N=1 parity check)")
+    ap.add_argument("--no-parity", action="store_true", help="N>1: skip the unsharded recomputation on rank 0")
+    ap.add_argument("--reference-budget-s", type=float, default=240.0, help="reference arm: stop adding timed steps beyond this")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
-    metric = "ms per LM iteration (Jacobian+Hessian build, Schur+Cholesky solve)"
-    config = {"workload": f"synthetic {a.workload} Aria Gen1-like session, the same session at every N (2 global-shutter SLAM cameras + RGB rolling-shutter "
-                          "camera with readout/time-offset states, 2 IMUs, 5 s calibration windows, RW + factory priors)",
-              "l2": "inputs larger than L2 (Hessian + factor tables exceed 126 MB); no flush needed"}
 
     if a.impl == "reference":
         if rank != 0:
             return 0
-        k, w = min(a.steps, 3), min(a.warmup, 1)
-        cb = cpu_leg(a.workload, k, w)
-        line = {"impl": "reference", "metric": metric, "value": cb["value"], "unit": "ms/iteration", "n_gpus": a.gpus,
-                "steps": k, "warmup": w, "ms_per_step": cb["value"], "higher_is_better": False, "scaling": "strong",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config, "cpu_baseline": cb,
-                "e2e": {"value": cb["value"], "unit": "ms/iteration", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "gpu_launches": 0}
+        s, cfg = make_workload(a.workload)
+        cores = os.cpu_count() or 1
+        # the CPU port is deterministic work: after one warm-up iteration every iteration costs the same, so the
+        # arm runs as many of the requested steps as fit the time budget (at least 1) and says how many
+        from tests.oracle_lib import load_oracle, Oracle
+        t0 = time.time()
+        o = Oracle(load_oracle(), s.graph)
+        create_s = time.time() - t0
+        rs_note = attach_rs_imu(o, s)
+        runs = []
+        for T in dict.fromkeys([cores, min(REFERENCE_THREADS, cores)]):  # all host threads first (the arm's value), then the reference default
+            kind = o.set_parallel(T)
+            w = min(a.warmup, 1)
+            t_start = time.time()
+            ts, c0, c1 = [], None, None
+            for i in range(w + max(1, a.steps)):
+                ms, c0, c1 = o.lm_iteration_timed(1e-5)
+                if i >= w:
+                    ts.append(ms)
+                if i >= w and time.time() - t_start > a.reference_budget_s / 2:
+                    break
+            m = np.mean(np.array(ts), 0)
+            runs.append({"threads": T, "value": float(m[6]), "unit": "ms/iteration", "solver": kind, "steps": len(ts), "warmup": w,
+                         "phases_ms": {"grad_hess": float(m[0]), "damping": float(m[1]), "factor": float(m[2]), "solve": float(m[3]),
+                                       "apply": float(m[4]), "cost": float(m[5])},
+                         "cost_before": c0, "cost_after": c1, "step_dot_grad": float(m[7])})
+        head = runs[0]
+        n_obs = int(s.n_obs + s.ext.get("rs_obs", 0))
+        cb = {"value": head["value"], "unit": "ms/iteration", "cores": head["threads"], "kind": "port", "solver": head["solver"],
+              "sample": f"the whole {a.workload} session ({n_obs} observations, {s.n_rigs} rigs): {head['steps']} full iteration(s) of the oracle port "
+                        f"after {head['warmup']} warm-up on {head['threads']} OpenMP threads (all host threads), reduced system by {head['solver']}; "
+                        f"also timed at T={runs[-1]['threads']} (the reference default, viba/common/Settings.h:87): {runs[-1]['value']:.0f} ms/iteration; "
+                        "not a sample, not extrapolated",
+              "host_cores": cores, "setup_s": round(create_s, 1), "runs": runs}
+        line = {"impl": "reference", "metric": METRIC, "value": head["value"], "unit": "ms/iteration", "n_gpus": a.gpus,
+                "steps": head["steps"], "warmup": head["warmup"], "ms_per_step": head["value"], "higher_is_better": False, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(a.workload, s, cfg, rs_note),
+                "cpu_baseline": cb, "parity": {"cost_before": head["cost_before"], "cost_after": head["cost_after"], "step_dot_grad": head["step_dot_grad"]},
+                "e2e": {"value": head["value"], "unit": "ms/iteration", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0, "session": getattr(s, "cache_note", "")}
         print(json.dumps(line))
         return 0
 
@@ -191,8 +257,10 @@ def main():
     barrier()
     phases, tot = {}, []
     wall0 = time.perf_counter()
+    c0 = c1 = sdg = None
     for _ in range(a.steps):
         t, c0, c1 = p.lm_iteration_timed(lam)
+        sdg = t.pop("step_dot_grad")
         tot.append(t["total"])
         for k_, v in t.items():
             phases[k_] = phases.get(k_, 0.0) + v / a.steps
@@ -230,6 +298,7 @@ def main():
     if rank != 0:
         p.close(); ctx.close()
         if dist is not None:
+            dist.barrier()   # rank 0 may still be recomputing the unsharded iteration
             dist.destroy_process_group()
         return 0
 
@@ -238,56 +307,110 @@ def main():
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     gh_ms = phases["grad_hess"]
     dmma = ctx.dmma_peak_tflops()
-    roof_gh = {"bound": "hbm", "achieved": work["visual_bytes"] / (gh_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s",
-               "traffic": None, "kernel": "gradHessVisualChunkKernel<GS>+<RS>", "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
-               "algorithmic_bytes": work["visual_bytes"], "ms": gh_ms}
+    # per-GPU rooflines: the whole job's algorithmic bytes / flops over the max-rank phase time, divided by N
+    roof_gh = {"bound": "hbm", "achieved": work["visual_bytes"] / (gh_ms * 1e-3) / 1e9 / world, "peak": hbm, "unit": "GB/s",
+               "traffic": None, "kernel": "visual eval+assemble kernels (GS + RS)", "peak_source": f"{which} (MEASURED_PEAKS.json hbm_gbs)",
+               "algorithmic_bytes": work["visual_bytes"], "ms": gh_ms, "per_gpu": True}
     roof_gh["frac"] = roof_gh["achieved"] / hbm
     fac_ms = phases["factor_schur"] + phases["factor_chol"]
-    roof_fac = {"bound": "tensor", "achieved": (work["schur_flops"] + work["chol_flops"]) / (fac_ms * 1e-3) / 1e12, "peak": dmma,
-                "unit": "TFLOP/s", "traffic": None, "kernel": "schurKernel + lumpFactor/lumpUpdate",
-                "peak_source": "FP64 mma.sync m8n8k4 probe measured in this run (no FP64 entry in MEASURED_PEAKS.json)",
-                "algorithmic_flops": work["schur_flops"] + work["chol_flops"], "ms": fac_ms}
+    flops = work["schur_flops"] + work["chol_flops"]
+    roof_fac = {"bound": "tensor", "achieved": flops / (fac_ms * 1e-3) / 1e12 / world, "peak": dmma,
+                "unit": "TFLOP/s", "traffic": None, "kernel": "landmark Schur + supernodal Cholesky kernels",
+                "peak_source": "builder-measured: FP64 mma.sync m8n8k4 issue-bound probe in this run (no FP64 entry in MEASURED_PEAKS.json; nominal 40)",
+                "algorithmic_flops": flops, "schur_flops": work["schur_flops"], "chol_flops": work["chol_flops"], "ms": fac_ms, "per_gpu": True}
     roof_fac["frac"] = roof_fac["achieved"] / dmma if dmma > 0 else None
+    low = low_fill_flops(a.workload, s)
+    if low is not None:   # the flops of the low-fill (plain RCM chain) ordering: what a sequential band factorisation would need
+        roof_fac["chol_flops_low_fill"] = low
+        roof_fac["frac_low_fill"] = (work["schur_flops"] + low) / (fac_ms * 1e-3) / 1e12 / world / dmma if dmma > 0 else None
+        roof_fac["flops_note"] = ("algorithmic_flops counts the nested-dissection ordering this library factors (parallel subtrees, more fill); "
+                                  "frac_low_fill recounts the same time against the plain-RCM chain's Cholesky flops")
     # DRAM traffic of the same kernels from the committed ncu --set full capture of this workload (N=1)
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            tr = json.load(f).get(a.workload)
-        if tr and world == 1:
-            roof_gh["traffic"] = tr["gradHessVisualChunkKernel<GS>+<RS>"]
-            roof_gh["traffic_note"] = "bytes per iteration (one launch of each visual kernel); " + tr["source"]
-            roof_fac["traffic"] = tr["schurGroupUpdateKernel"]
-            roof_fac["traffic_note"] = "schurGroupUpdateKernel only, bytes per launch; " + tr["source"]
-    except Exception:
-        pass
+    for fn in ("r02_traffic.json", "r01_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", fn)) as f:
+                tr = json.load(f).get(a.workload)
+            if tr and world == 1:
+                roof_gh["traffic"] = tr.get("visual")
+                roof_gh["traffic_note"] = "bytes per iteration (one launch of each visual kernel); " + tr["source"]
+                roof_fac["traffic"] = tr.get("schur")
+                roof_fac["traffic_note"] = "Schur update kernel only, bytes per launch; " + tr["source"]
+                break
+        except Exception:
+            pass
     dominant = roof_gh if gh_ms >= fac_ms else roof_fac
-    line = {"metric": metric, "value": ms_dev, "unit": "ms/iteration", "n_gpus": a.gpus, "steps": a.steps, "warmup": warmup,
+    config = workload_config(a.workload, s, cfg, rs_note)
+    parity = {"cost_before": c0, "cost_after": c1, "step_dot_grad": sdg, "tolerance": PARITY_TOL}
+    line = {"metric": METRIC, "value": ms_dev, "unit": "ms/iteration", "n_gpus": a.gpus, "steps": a.steps, "warmup": warmup,
             "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic", "config": dict(config, observations=int(s.n_obs + s.ext.get("rs_obs", 0)), rs_observations=int(s.ext.get("rs_obs", 0)), landmarks=int(s.n_points), rigs=int(s.n_rigs), rs_refresh=rs_note,
-                                                order=int(p.order), hess_doubles=int(p.data_size), lumps=int(p.num_lumps),
-                                                levels=int(p.num_levels), setup_s=round(setup_s, 2)),
+            "data": "synthetic", "config": config,
+            "problem": {"order": int(p.order), "hess_doubles": int(p.data_size), "lumps": int(p.num_lumps), "levels": int(p.num_levels),
+                        "setup_s": round(setup_s, 2), "session": getattr(s, "cache_note", "")},
             "phases_ms": {k_: round(v, 4) for k_, v in phases.items()}, "wall_ms_per_step": wall_ms,
             "roofline": dominant, "roofline_other": roof_fac if dominant is roof_gh else roof_gh,
             "e2e": {"value": e2e_ms, "unit": "ms/iteration", "h2d_bytes_per_step": int(host_vars.nbytes),
                     "d2h_bytes_per_step": int(out_vars.nbytes + 8 * (64 + 4 * len(s.graph.stores)))},
-            "gpu_launches": int(p.launches_per_iteration * a.steps * world), "clocks": sampler.summary()}
+            "gpu_launches": int(p.launches_per_iteration * a.steps * world), "clocks": sampler.summary(), "parity": parity}
     if world > 1:
         per_it = coll.calls / max(1, (warmup + 2 * a.steps + 2))
-        line["sharding"] = {"plan": "elimination-tree subtrees of the reduced camera system dealt to the ranks under a replicated "
-                                    "shared top; landmarks (with all their observations) and factors follow the rank whose subtree "
-                                    "they touch; only the shared top, the camera rhs/step and the landmark steps are summed over NCCL", "per_rank_landmarks": shard["per_rank_landmarks"],
+        line["sharding"] = {"plan": "elimination-tree subtrees of the reduced camera system dealt to the ranks under a shared top; landmarks "
+                                    "(with all their observations) and factors follow the rank whose subtree they touch",
+                            "per_rank_landmarks": shard["per_rank_landmarks"],
                             "per_rank_observations": shard["per_rank_observations"],
-                            "allreduce_bytes_per_iteration": int(coll.bytes / max(1, (warmup + 2 * a.steps + 2))),
+                            "collective_bytes_per_iteration": int(coll.bytes / max(1, (warmup + 2 * a.steps + 2))),
                             "collectives_per_iteration": round(per_it, 2)}
+    p.close()
+    ok = True
+    if world > 1 and not a.no_parity:
+        # real-NCCL correctness, driver side: rank 0 recomputes the same iteration unsharded on its own GPU
+        p1 = capi.Problem(ctx, s.graph)
+        attach_rs_imu(p1, s)
+        t1, u0, u1 = p1.lm_iteration_timed(lam)
+        p1.close()
+        parity.update({"against": "the same iteration recomputed unsharded on rank 0's GPU", "ref_cost_before": u0, "ref_cost_after": u1,
+                       "ref_step_dot_grad": t1["step_dot_grad"], "rel_cost_before": rel(c0, u0), "rel_cost_after": rel(c1, u1),
+                       "rel_step_dot_grad": rel(sdg, t1["step_dot_grad"])})
+        ok = parity["rel_cost_before"] <= PARITY_TOL and parity["rel_cost_after"] <= PARITY_TOL and parity["rel_step_dot_grad"] <= 1e-7
     if world == 1 and not a.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_leg(a.workload, 2, 1)
+        cb, runs, _ = cpu_leg(s, a.workload, 1, 0, [os.cpu_count() or 1])
+        line["cpu_baseline"] = cb
+        r0 = runs[0]
+        parity.update({"against": "the CPU oracle port on the same session (cpu_baseline leg)", "ref_cost_before": r0["cost_before"],
+                       "ref_cost_after": r0["cost_after"], "ref_step_dot_grad": r0["step_dot_grad"],
+                       "rel_cost_before": rel(c0, r0["cost_before"]), "rel_cost_after": rel(c1, r0["cost_after"]),
+                       "rel_step_dot_grad": rel(sdg, r0["step_dot_grad"])})
+        ok = parity["rel_cost_before"] <= PARITY_TOL and parity["rel_cost_after"] <= PARITY_TOL and parity["rel_step_dot_grad"] <= 1e-7
+    parity["ok"] = bool(ok) if "against" in parity else None
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
-    p.close()
     ctx.close()
     if dist is not None:
+        dist.barrier()
         dist.destroy_process_group()
+    if not ok:
+        print("bench.py: PARITY FAILURE " + json.dumps(parity), file=sys.stderr)
+        return 3
     return 0
+
+
+def low_fill_flops(workload, s):
+    """Cholesky flops of the reduced camera system under the plain RCM chain (vb_symbolic_stats with nested dissection
+    off): a host-only symbolic phase, cached beside the session"""
+    from visual_inertial_bundle_adjustment_b200 import capi
+    path = os.path.join(os.environ.get("VIBA_SESSION_CACHE", "/tmp/viba_b200_sessions"), f"{workload}_lowfill.json")
+    try:
+        with open(path) as f:
+            return json.load(f)["chol_flops"]
+    except Exception:
+        pass
+    try:
+        st = capi.symbolic_stats(s.graph, 0, 0)
+        with open(path, "w") as f:
+            json.dump({"chol_flops": st["chol_flops"], "levels": st["levels"]}, f)
+        return st["chol_flops"]
+    except Exception:
+        return None
 
 
 if __name__ == "__main__":

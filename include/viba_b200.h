@@ -105,7 +105,7 @@ typedef struct vb_settings {
 typedef struct vb_summary {  /* Optimizer::Summary, Optimizer.h:93-99 */
   double initial_cost, final_cost;
   int32_t num_troubled_seqs, largest_troubled_seq, num_iterations;
-  int32_t stop_reason; /* 0 converged, 1 iteration limit, 2 damping out of range */
+  int32_t stop_reason; /* 0 converged, 1 iteration limit, 2 damping out of range, 3 numeric failure (VB_ERR_NUMERIC; variables left at the current iterate) */
 } vb_summary;
 
 typedef struct vb_cost_stats { /* CostStats, Factor.h:25-31 */
@@ -114,7 +114,50 @@ typedef struct vb_cost_stats { /* CostStats, Factor.h:25-31 */
 
 typedef struct vb_iter_times { /* ms, CUDA-event timed; the split the reference logs (Optimizer.cpp:1062-1067) */
   double grad_hess, damping, factor_schur, factor_chol, solve, apply, cost, total;
+  double step_dot_grad; /* step.dot(grad) before the sign flip (Optimizer.cpp:833): 2 x modelCostReduction */
 } vb_iter_times;
+
+/* One LM iteration as the reference logs it (Optimizer.cpp:1058-1076), plus which branches of the loop ran.
+ * `damping` is the value AFTER this iteration's adjustment (what the reference prints as "lmbd"),
+ * `damping_used` the value the linear system was damped with. */
+#define VB_BR_MODEL_NEGATIVE 1     /* Q1: modelCostReduction < 0, g/H recomputed, damping bumped, fell through (:835-855) */
+#define VB_BR_STEP_FACTOR 2        /* step-factor loop entered (:907-1011) */
+#define VB_BR_ACCEPT_AT_FACTOR 4   /* accepted after scaling the step (:941-957) */
+#define VB_BR_SUB_STEP 8           /* sub-step solved on the gradient at the scaled step (:962-975) */
+#define VB_BR_ACCEPT_AT_SUB 16     /* accepted after the sub-step (:985-1000) */
+#define VB_BR_LATCH_NO_RETRY 32    /* Q5: dontRetryFailed latched in this iteration (:1002-1007) */
+#define VB_BR_REJECTED 64          /* newCost > prevCost or failure rate: restore, damping x fail (:1019-1035) */
+#define VB_BR_GOOD 128             /* damping x good (:1043-1047) */
+#define VB_BR_AVERAGE 256          /* damping x average (:1048-1051) */
+#define VB_BR_TOLERANCE_HIT 512    /* one of the three tolerances was hit (:1013-1018) */
+#define VB_BR_TROUBLED_SEQ_END 1024 /* a troubled sequence ended and was counted (:1037-1042) */
+typedef struct vb_iter_trace {
+  double prev_cost, new_cost, damping, damping_used, model_cost_reduction, applied_step_factor;
+  double ratio_reduction_to_expected, cost_reduction, grad_norm, step_norm;
+  double ratio_s2v_inf, ratio_s2v_2, ratio_s2v_1;   /* applyStep statistics (Optimizer.cpp:886) */
+  double ms_total, ms_grad_hess, ms_factor, ms_solve; /* host wall clock, as the reference measures them */
+  int64_t num_total, num_invalid, num_prev_invalid; /* CostStats the decision used (Q3: last store) */
+  int32_t branch;                                   /* VB_BR_* bits */
+  int32_t step_factor_attempts;
+} vb_iter_trace;
+
+/* Hooks of Optimizer::Settings (lib/small_thing/Optimizer.h:81,90): `log` receives the reference's
+ * per-iteration text (same layout as Optimizer.cpp:1058-1076 and the convergence / limit / damping lines),
+ * `pre_step` runs on the calling thread at the top of every iteration where Optimizer.cpp:803-805 calls
+ * settings.preStepCallback.  The device is the source of truth inside vb_optimize (SURVEY.md 8b
+ * "Ownership"): before each pre_step call the variables whose kind is in `sync_kinds` (bit k = VB_VAR_k;
+ * the reference's callbacks read IMU calibrations and gravity) are copied into `host_vars` (caller-owned,
+ * var_data_len doubles, same layout as vb_graph_desc.var_data).  The callback may call vb_upload_store_aux /
+ * vb_upload_store_consts / vb_upload_vars / vb_rs_refresh on the same problem; nothing else. */
+typedef void (*vb_pre_step_fn)(void* user, int32_t iteration);
+typedef void (*vb_log_fn)(void* user, const char* text);
+typedef struct vb_optimize_hooks {
+  vb_pre_step_fn pre_step; void* pre_step_user;
+  uint32_t sync_kinds; double* host_vars;
+  vb_log_fn log; void* log_user;
+  vb_iter_trace* trace; int32_t trace_cap; /* first trace_cap iterations are recorded */
+  int32_t trace_len;                       /* out: iterations recorded */
+} vb_optimize_hooks;
 
 typedef struct vb_ctx vb_ctx;
 typedef struct vb_problem vb_problem;
@@ -217,6 +260,9 @@ int vb_eval_grad_new(vb_problem* p, int dont_retry_failed);
 
 /* Optimizer::optimize (Optimizer.cpp:768-1106): the whole LM loop, host-controlled, device-resident */
 int vb_optimize(vb_problem* p, const vb_settings* s, vb_summary* out);
+/* same loop with the Settings hooks: preStepCallback (Optimizer.h:90, called at Optimizer.cpp:803-805),
+ * log (Optimizer.h:81) and a per-iteration trace; hooks may be NULL */
+int vb_optimize_ex(vb_problem* p, const vb_settings* s, vb_optimize_hooks* hooks, vb_summary* out);
 /* one accepted-path LM iteration with per-phase CUDA-event timing (bench / profiling) */
 int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times* t, double* cost_before, double* cost_after);
 

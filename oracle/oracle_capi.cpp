@@ -168,7 +168,23 @@ int orc_optimize(OrcHandle* h, const vb_settings* s, vb_summary* out, double* tr
   }
   ORC_CATCH
 }
-
+// same run with the full per-iteration trace (the fields of the reference's log line, Optimizer.cpp:1058-1076,
+// and the branches taken) and an optional Settings::preStepCallback stand-in: `cb(user, iteration)` may
+// rewrite store aux data / variables through orc_set_store_aux / orc_set before the linearisation
+typedef void (*orc_pre_step_fn)(void* user, int32_t iteration);
+int orc_optimize_ex(OrcHandle* h, const vb_settings* s, vb_summary* out, vb_iter_trace* trace, int traceCap, int* traceLen,
+                    orc_pre_step_fn cb, void* user) {
+  ORC_TRY
+  if (!h->analyzed) { h->sol.analyze(h->eng); h->analyzed = true; }
+  LmTrace tr;
+  std::function<void(int)> pre;
+  if (cb) pre = [&](int it) { cb(user, it); };
+  optimize(h->eng, h->sol, *s, out, &tr, pre);
+  int n = 0;
+  for (; n < traceCap && n < (int)tr.full.size(); n++) if (trace) trace[n] = tr.full[n];
+  if (traceLen) *traceLen = n;
+  ORC_CATCH
+}
 static void rsRefresh(OrcHandle* h, int store) {
   for (const RsSource& src : h->rs) {
     if (store >= 0 && src.store != store) continue;
@@ -276,6 +292,7 @@ int orc_lm_iteration_timed(OrcHandle* h, double lambda, double* ms, double* cost
   h->sol.solveOnly(e.hess.data(), e.grad.data(), e.step.data());
   ms[3] = ms_since(t1);
   t1 = clk::now();
+  ms[7] = vdot(e.step, e.grad); // step.dot(grad) before the sign flip (Optimizer.cpp:833)
   for (double& s : e.step) s = -s;
   e.backup();
   double rr[3];

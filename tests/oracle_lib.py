@@ -152,8 +152,25 @@ class Oracle:
         n = summ.num_iterations
         return summ, tp[:n], tn[:n]
 
+    def optimize_ex(self, settings, trace_cap=300, pre_step=None):
+        """optimize with the full per-iteration trace (vb_iter_trace records) and an optional
+        pre_step(iteration) callback (Settings::preStepCallback stand-in)"""
+        summ = G.vb_summary(); tr = (G.vb_iter_trace * trace_cap)(); n = C.c_int()
+        CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int32)
+        cb = CB((lambda user, it: pre_step(it)) if pre_step else 0)
+        self.lib.orc_optimize_ex.argtypes = [C.c_void_p, C.POINTER(G.vb_settings), C.POINTER(G.vb_summary),
+                                             C.POINTER(G.vb_iter_trace), C.c_int, C.POINTER(C.c_int), CB, C.c_void_p]
+        self._ck(self.lib.orc_optimize_ex(self.h, C.byref(settings), C.byref(summ), tr, trace_cap, C.byref(n), cb, None))
+        return summ, G.trace_records(tr, n.value)
+
+    def set_store_aux(self, store, aux):
+        aux = np.ascontiguousarray(aux, np.float64)
+        self.lib.orc_set_store_aux.argtypes = [C.c_void_p, C.c_int, _dp, C.c_int64]
+        self._ck(self.lib.orc_set_store_aux(self.h, int(store), dptr(aux), aux.size))
+
     def lm_iteration_timed(self, lam):
-        ms = np.zeros(7); c0 = C.c_double(); c1 = C.c_double()
+        """ms[0..6] = g/H, damping, factor, solve, apply, cost, total; ms[7] = step.dot(grad)"""
+        ms = np.zeros(8); c0 = C.c_double(); c1 = C.c_double()
         self._ck(self.lib.orc_lm_iteration_timed(self.h, lam, dptr(ms), C.byref(c0), C.byref(c1)))
         return ms, c0.value, c1.value
 

@@ -20,7 +20,7 @@ EXPORTS = [
     "vb_get_param_start", "vb_get_perm", "vb_get_lump_start", "vb_block_offset", "vb_get_work",
     "vb_eval_grad_hess", "vb_eval_cost", "vb_damp", "vb_step_from_grad", "vb_factor", "vb_solve",
     "vb_step_stats", "vb_scale_vec", "vb_dot", "vb_apply_step", "vb_backup", "vb_restore", "vb_eval_grad_new",
-    "vb_optimize", "vb_lm_iteration_timed", "vb_download_vars", "vb_upload_vars", "vb_download_grad",
+    "vb_optimize", "vb_optimize_ex", "vb_lm_iteration_timed", "vb_download_vars", "vb_upload_vars", "vb_download_grad",
     "vb_download_step", "vb_download_hess", "vb_upload_hess", "vb_upload_grad", "vb_download_factor_cache",
     "vb_upload_store_aux", "vb_upload_store_consts", "vb_measure_dmma_peak",
     "vb_download_store_aux", "vb_rs_set_imu", "vb_rs_refresh",
@@ -75,6 +75,7 @@ def load():
     lib.vb_restore.argtypes = [C.c_void_p]
     lib.vb_eval_grad_new.argtypes = [C.c_void_p, C.c_int]
     lib.vb_optimize.argtypes = [C.c_void_p, C.POINTER(G.vb_settings), C.POINTER(G.vb_summary)]
+    lib.vb_optimize_ex.argtypes = [C.c_void_p, C.POINTER(G.vb_settings), C.POINTER(G.vb_optimize_hooks), C.POINTER(G.vb_summary)]
     lib.vb_lm_iteration_timed.argtypes = [C.c_void_p, C.c_double, C.c_int, C.POINTER(G.vb_iter_times), _dp, _dp]
     for f in ("vb_download_vars", "vb_upload_vars", "vb_download_grad", "vb_download_step", "vb_download_hess",
               "vb_upload_hess", "vb_upload_grad"):
@@ -275,6 +276,32 @@ class Problem:
         s = G.vb_summary()
         _ck(self.lib, self.lib.vb_optimize(self.h, C.byref(settings), C.byref(s)))
         return s
+
+    def optimize_ex(self, settings, trace_cap=300, pre_step=None, sync_kinds=0, log=None):
+        """Optimizer::optimize with the Settings hooks (vb_optimize_ex): `pre_step(iteration, host_vars)` runs at
+        the top of every iteration with the variables of the kinds in `sync_kinds` (bit k = VB_VAR_k) fresh in
+        `host_vars`; `log(text)` receives the reference's per-iteration text.  Returns (summary, trace records)."""
+        s = G.vb_summary()
+        h = G.vb_optimize_hooks()
+        tr = (G.vb_iter_trace * max(1, trace_cap))()
+        h.trace, h.trace_cap = tr, trace_cap
+        host = np.array(self.g.var_data, dtype=np.float64, copy=True)
+        err = []
+        if pre_step is not None:
+            def _pre(user, it):
+                try:
+                    pre_step(it, host)
+                except BaseException as ex:   # never let an exception cross the C ABI
+                    err.append(ex)
+            h.pre_step = G.PRE_STEP_FN(_pre)
+            h.sync_kinds, h.host_vars = sync_kinds, _d(host)
+        if log is not None:
+            h.log = G.LOG_FN(lambda user, text: log(text.decode("utf-8", "replace")))
+        rc = self.lib.vb_optimize_ex(self.h, C.byref(settings), C.byref(h), C.byref(s))
+        if err:
+            raise err[0]
+        _ck(self.lib, rc)
+        return s, G.trace_records(tr, h.trace_len)
 
     def lm_iteration_timed(self, lam, apply=False):
         t, c0, c1 = G.vb_iter_times(), C.c_double(), C.c_double()

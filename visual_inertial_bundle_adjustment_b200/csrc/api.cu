@@ -5,6 +5,8 @@
 #include <cmath>
 #include <algorithm>
 #include <memory>
+#include <chrono>
+#include <string>
 #include "vb_internal.hpp"
 
 using namespace vb;
@@ -601,7 +603,11 @@ static void collective(vb_problem* p, int op, double* ptr, int64_t n) {
   p->collCalls++; p->collBytes += 8.0 * n;
 }
 static double* vecOf(vb_problem* p, int which) { return which == 0 ? p->step : which == 1 ? p->gradNew : p->grad; }
-static void requireProblem(const vb_problem* p) { if (!p) throw std::invalid_argument("null problem"); }
+// every ABI entry runs on the problem's device, whatever the calling thread's current device is
+static void requireProblem(const vb_problem* p) {
+  if (!p) throw std::invalid_argument("null problem");
+  VB_CUDA(cudaSetDevice(p->ctx->device));
+}
 static void syncCheck(vb_problem* p) { VB_CUDA(cudaStreamSynchronize(p->ctx->stream)); }
 
 constexpr int64_t kRsTableStride = 1 + 32 * 11 + 31 * 9; // per-rig table (dev_factors_ext.cuh)
@@ -1079,39 +1085,119 @@ int vb_restore(vb_problem* p) {
   VB_CATCH
 }
 
+// text helpers of the per-iteration log (the layout of lib/small_thing/Print.cpp: a duration as
+// "123μs" / "1.23ms" / "0.12s" / "1m5s" / "1h2m", a ratio as a percentage with fixed precision)
+static std::string fmtDuration(double seconds) {
+  char buf[64];
+  const long long us = (long long)std::llround(seconds * 1e6);
+  if (us < 1000) std::snprintf(buf, sizeof buf, "%lld\xce\xbcs", us);
+  else if (us < 100000) std::snprintf(buf, sizeof buf, "%.2fms", us / 1e3);
+  else if (us < 60000000ll) std::snprintf(buf, sizeof buf, "%.2fs", us / 1e6);
+  else if (us < 3600000000ll) {
+    const long long m = us / 60000000ll, sec = std::llround((us % 60000000ll) / 1e6);
+    if (sec > 0) std::snprintf(buf, sizeof buf, "%lldm%llds", m, sec); else std::snprintf(buf, sizeof buf, "%lldm", m);
+  } else {
+    const long long h = us / 3600000000ll, m = (us % 3600000000ll) / 60000000ll;
+    if (m > 0) std::snprintf(buf, sizeof buf, "%lldh%lldm", h, m); else std::snprintf(buf, sizeof buf, "%lldh", h);
+  }
+  return buf;
+}
+static std::string fmtPercent(double ratio, int precision = 1) {
+  char buf[64];
+  std::snprintf(buf, sizeof buf, "%.*f%%", precision, ratio * 100.0);
+  return buf;
+}
+static std::string fmtG(double v) { // operator<< of a double on a default stream: %g with 6 significant digits
+  char buf[64];
+  std::snprintf(buf, sizeof buf, "%g", v);
+  return buf;
+}
+
 // Optimizer::optimize — lib/small_thing/Optimizer.cpp:768-1106, host control over device state.
-// Quirks Q1-Q5 of SURVEY.md App. A are kept (see the inline notes).
-int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) {
-  VB_TRY
+// Quirks Q1-Q5 of SURVEY.md App. A are kept (see the inline notes).  Hooks: Settings::preStepCallback
+// (Optimizer.h:90, Optimizer.cpp:803-805), Settings::log (Optimizer.h:81) and a per-iteration trace.
+int vb_optimize_ex(vb_problem* p, const vb_settings* st, vb_optimize_hooks* hooks, vb_summary* out) {
+  double initialCost = 0, finalCost = 0;
+  int numTroubledSeqs = 0, largestTroubledSeq = 0, stopReason = 1, iterationNum = 0;
+  auto fillSummary = [&]() {
+    if (!out) return;
+    out->initial_cost = initialCost; out->final_cost = finalCost;
+    out->num_troubled_seqs = numTroubledSeqs; out->largest_troubled_seq = largestTroubledSeq;
+    out->num_iterations = iterationNum; out->stop_reason = stopReason;
+  };
+  try {
   requireProblem(p);
   if (!st) throw std::invalid_argument("null settings");
+  if (hooks && hooks->pre_step && hooks->sync_kinds && !hooks->host_vars) throw std::invalid_argument("sync_kinds without host_vars");
+  if (hooks) hooks->trace_len = 0;
+  using clk = std::chrono::steady_clock;
+  auto since = [](clk::time_point a) { return std::chrono::duration<double>(clk::now() - a).count(); };
   cudaStream_t s = p->ctx->stream;
   const int64_t n = p->S.order;
+  const bool wantLog = hooks && hooks->log;
+  const bool wantTrace = hooks && hooks->trace && hooks->trace_cap > 0;
+  auto say = [&](const std::string& text) { if (wantLog) hooks->log(hooks->log_user, text.c_str()); };
   double damping = st->damping;
-  int iterationNum = 0, lastImprovementIteration = 0, lastTroubledIteration = -10;
-  double initialCost = 0, finalCost = 0, troubledSeqStartDamping = damping;
-  int troubledSeqStart = 0, numTroubledSeqs = 0, largestTroubledSeq = 0, stopReason = 1;
+  int lastImprovementIteration = 0, lastTroubledIteration = -10;
+  double troubledSeqStartDamping = damping;
+  int troubledSeqStart = 0;
   bool dontRetryFailed = false;
   auto acceptable = [](const vb_cost_stats& c) {
     const double rate = c.num_invalid / (c.num_total + 1.0);
     return rate < 0.03 && (c.num_invalid < c.num_prev_invalid * 2.0 + 50);
   };
   while (true) {
-    if (!p->rsSources.empty()) refreshRsTables(p, -1); // preStepCallback (Optimizer.cpp:801-805)
+    const auto startIt = clk::now();
+    int branch = 0, attempts = 0;
+    if (hooks && hooks->pre_step) { // Optimizer.cpp:803-805; the host copy of the kinds the callback reads comes first
+      if (hooks->sync_kinds) {
+        syncCheck(p);
+        const HostGraph& g = p->g;
+        int64_t runBeg = -1, runEnd = -1; // contiguous runs of selected variables -> one copy each
+        auto flush = [&]() {
+          if (runBeg >= 0) VB_CUDA(cudaMemcpyAsync(hooks->host_vars + runBeg, p->dv.data + runBeg, (runEnd - runBeg) * sizeof(double), cudaMemcpyDeviceToHost, s));
+          runBeg = -1;
+        };
+        for (int64_t v = 0; v < g.nv; v++) {
+          if (!((hooks->sync_kinds >> g.kind[v]) & 1u)) continue;
+          const int64_t b = g.off[v], e = v + 1 < g.nv ? g.off[v + 1] : p->varDataLen;
+          if (b != runEnd) { flush(); runBeg = b; }
+          runEnd = e;
+        }
+        flush();
+        syncCheck(p);
+      }
+      hooks->pre_step(hooks->pre_step_user, iterationNum);
+    }
+    if (!p->rsSources.empty()) refreshRsTables(p, -1); // the reference's own preStepCallback (InitCalibration.cpp:316-325)
     const double prevCost = evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
+    const double secGradHess = since(startIt); // includes the callback, as Optimizer.cpp:801,816 measures it
     finalCost = prevCost;
     if (iterationNum == 0) initialCost = prevCost;
+    const double dampingUsed = damping;
     launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, damping, p->dampMask, s);
     launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
+    const auto startFactor = clk::now();
     factorAsync(p, nullptr);
     checkNumeric(p);
+    const double secFactor = since(startFactor);
+    const auto startSolve = clk::now();
     solveAsync(p, p->step);
     const double modelCostReduction = dotVec(p, p->step, p->grad) * 0.5;
+    const double secSolve = since(startSolve);
     if (modelCostReduction < 0) { // Q1: recompute, bump damping, fall through with the bad step
       evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
       damping *= st->damping_adjust_on_fail;
+      branch |= VB_BR_MODEL_NEGATIVE;
+      say(" ?:# quadratic model failing numerically, retrying... (damping: " + fmtG(damping) + ")");
     }
     launchVecOp(1, p->step, nullptr, -1.0, n, nullptr, s);
+    double gradNorm = 0, stepNorm = 0;
+    if (wantLog || wantTrace) { // Optimizer.cpp:858-859 (only the log reads them)
+      if (p->partial[2]) { collective(p, VB_COLL_SUM, p->grad, n); p->partial[2] = false; }
+      gradNorm = std::sqrt(dotVec(p, p->grad, p->grad));
+      stepNorm = std::sqrt(dotVec(p, p->step, p->step));
+    }
     VB_CUDA(cudaMemcpyAsync(p->backup, p->dv.data, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
     double ratios[3];
     applyStep(p, p->step, ratios);
@@ -1124,10 +1210,12 @@ int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) {
     bool failureRateIsAcceptable = acceptable(stats);
     if (st->max_step_factor_attempts > 0 &&
         (ratioReductionToExpected < st->min_relative_cost_reduction || !failureRateIsAcceptable)) {
+      branch |= VB_BR_STEP_FACTOR;
       evalGradHess(p, p->gradNew, 0, 0, dontRetryFailed, false);
       const double backRed = -dotVec(p, p->gradNew, p->step) * 0.5;
       double stepFactor = backRed > 0 ? (modelCostReduction / (modelCostReduction + backRed)) : st->step_factor_decrease;
       for (int i = 0; i < st->max_step_factor_attempts; i++) {
+        attempts++;
         appliedStepFactor *= stepFactor;
         launchVecOp(1, p->step, nullptr, stepFactor, n, nullptr, s);
         VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
@@ -1136,69 +1224,130 @@ int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) {
         const double newCostAtF = evalCost(p, 1, &statsAtF);
         const double costReductionAtF = prevCost - newCost; // Q2: stale newCost, as in the reference
         const double ratioAtF = costReductionAtF / (modelCostReduction * appliedStepFactor);
+        char fbuf[32];
+        std::snprintf(fbuf, sizeof fbuf, "%.2f", appliedStepFactor);
         if (ratioAtF >= st->min_relative_cost_reduction && acceptable(statsAtF)) {
           newCost = newCostAtF; stats = statsAtF; costReduction = costReductionAtF;
           ratioReductionToExpected = ratioAtF; failureRateIsAcceptable = true;
+          branch |= VB_BR_ACCEPT_AT_FACTOR;
+          say(std::string("\\!/ cost reduction obtained applying factor ") + fbuf);
           break;
         }
         if (st->try_sub_step) {
+          branch |= VB_BR_SUB_STEP;
           evalGradHess(p, p->gradNew, 0, 0, dontRetryFailed, false);
+          const auto startSub = clk::now();
           solveAsync(p, p->gradNew);
           launchVecOp(1, p->gradNew, nullptr, -1.0, n, nullptr, s);
           applyStep(p, p->gradNew, nullptr);
           vb_cost_stats statsAtSub{};
           const double newCostAtSub = evalCost(p, 1, &statsAtSub);
+          const double secSub = since(startSub);
           const double costReductionAtSub = prevCost - newCostAtSub;
           const double ratioAtSub = costReductionAtSub / (modelCostReduction * appliedStepFactor);
           if (ratioAtSub >= st->min_relative_cost_reduction && acceptable(statsAtSub)) {
             newCost = newCostAtSub; stats = statsAtSub; costReduction = costReductionAtSub;
             ratioReductionToExpected = ratioAtSub; failureRateIsAcceptable = true;
+            branch |= VB_BR_ACCEPT_AT_SUB;
+            say(std::string("\\!/ cost reduction obtained applying factor ") + fbuf + " + sub-step:\n    solve: " + fmtDuration(secSub));
             break;
           }
         }
-        dontRetryFailed = true; // Q5 latch
+        if (!dontRetryFailed) { // Q5 latch
+          dontRetryFailed = true;
+          branch |= VB_BR_LATCH_NO_RETRY;
+          say("\\!/ failing factors will no longer be retried!");
+        }
         stepFactor = st->step_factor_decrease;
       }
     }
-    const bool toleranceHit = ratioReductionToCost < st->relative_cost_tolerance ||
-        costReduction < st->absolute_cost_tolerance || ratios[1] < st->variables_tolerance;
+    const char* toleranceHit = ratioReductionToCost < st->relative_cost_tolerance ? "relative cost"
+        : costReduction < st->absolute_cost_tolerance ? "absolute cost"
+        : ratios[1] < st->variables_tolerance ? "variable" : nullptr;
+    if (toleranceHit) branch |= VB_BR_TOLERANCE_HIT;
     if (st->verbose)
       std::printf("[viba_b200] it %d cost %.12g -> %.12g lambda %.3g model %.6g\n", iterationNum, prevCost, newCost, damping, modelCostReduction);
+    const char* smiley;
+    bool stopDamping = false;
     if (newCost > prevCost || !failureRateIsAcceptable) {
       if (lastTroubledIteration != iterationNum - 1) { troubledSeqStartDamping = damping; troubledSeqStart = iterationNum; }
+      smiley = ":'(";
+      branch |= VB_BR_REJECTED;
       damping *= st->damping_adjust_on_fail;
       VB_CUDA(cudaMemcpyAsync(p->dv.data, p->backup, p->varDataLen * sizeof(double), cudaMemcpyDeviceToDevice, s));
-      if (damping > st->damping_max) { stopReason = 2; break; }
-      lastTroubledIteration = iterationNum;
+      if (damping > st->damping_max) { stopDamping = true; say("damping out of range, quadratic model failing?!"); }
+      else lastTroubledIteration = iterationNum;
     } else {
       if (lastTroubledIteration == iterationNum - 1) {
         if (troubledSeqStartDamping < 1e1 && damping > 1e-3) {
           numTroubledSeqs++;
           largestTroubledSeq = std::max(largestTroubledSeq, iterationNum - troubledSeqStart);
+          branch |= VB_BR_TROUBLED_SEQ_END;
         }
       }
       if (ratioReductionToExpected >= st->min_relative_cost_reduction && appliedStepFactor > st->min_step_factor_for_good) {
+        smiley = toleranceHit ? ";-|" : ":-)";
+        branch |= VB_BR_GOOD;
         damping *= st->damping_adjust_on_good;
         damping = std::max(damping, st->damping_min);
       } else {
+        smiley = ":-/";
+        branch |= VB_BR_AVERAGE;
         damping *= st->damping_adjust_on_average;
       }
       finalCost = newCost;
     }
+    const double secTotal = since(startIt);
+    if (wantTrace && hooks->trace_len < hooks->trace_cap) {
+      vb_iter_trace& t = hooks->trace[hooks->trace_len++];
+      t.prev_cost = prevCost; t.new_cost = newCost; t.damping = damping; t.damping_used = dampingUsed;
+      t.model_cost_reduction = modelCostReduction; t.applied_step_factor = appliedStepFactor;
+      t.ratio_reduction_to_expected = ratioReductionToExpected; t.cost_reduction = costReduction;
+      t.grad_norm = gradNorm; t.step_norm = stepNorm;
+      t.ratio_s2v_inf = ratios[0]; t.ratio_s2v_2 = ratios[1]; t.ratio_s2v_1 = ratios[2];
+      t.ms_total = secTotal * 1e3; t.ms_grad_hess = secGradHess * 1e3; t.ms_factor = secFactor * 1e3; t.ms_solve = secSolve * 1e3;
+      t.num_total = stats.num_total; t.num_invalid = stats.num_invalid; t.num_prev_invalid = stats.num_prev_invalid;
+      t.branch = branch; t.step_factor_attempts = attempts;
+    }
+    if (stopDamping) { stopReason = 2; break; } // Optimizer.cpp:1027-1034 leaves before the iteration is counted
     iterationNum++;
+    if (wantLog) { // Optimizer.cpp:1058-1076
+      const double prevFailing = stats.num_prev_invalid / std::max((double)stats.num_total, 1.0);
+      const double newFailing = stats.num_invalid / std::max((double)stats.num_total, 1.0);
+      std::string t;
+      t += std::string(" ") + smiley + " cost: " + fmtG(prevCost) + " -> " + fmtG(newCost) + " (" + fmtPercent(newCost / prevCost - 1.0, 2) +
+           "), t: " + fmtDuration(secTotal) + "\n";
+      t += "     n." + std::to_string(iterationNum) + "; g/H: " + fmtDuration(secGradHess) + ", solver:\n";
+      t += "    direct, factor: " + fmtDuration(secFactor) + ", solve: " + fmtDuration(secSolve) + "\n";
+      t += "     lmbd: " + fmtG(damping) + ", relRed: " + fmtPercent(ratioReductionToExpected) + ", improv: " + fmtG(costReduction) +
+           ", modelImprov: " + fmtG(modelCostReduction) + "\n";
+      t += "    |G|: " + fmtG(gradNorm) + ", |S|: " + fmtG(stepNorm) + ", |s/v|_inf: " + fmtG(ratios[0]) + ", |_2: " + fmtG(ratios[1]) +
+           ", |_1: " + fmtG(ratios[2]) + "\n";
+      t += "    Failing factors: " + fmtG(prevFailing) + " (" + fmtPercent(prevFailing) + ") -> " + fmtG(newFailing) + " (" + fmtPercent(newFailing) + ")";
+      say(t);
+    }
     if (!toleranceHit) lastImprovementIteration = iterationNum;
     if (iterationNum >= lastImprovementIteration + st->stop_if_no_improvement_for &&
-        iterationNum >= lastTroubledIteration + st->distance_from_troubled_iteration) { stopReason = 0; break; }
-    else if (iterationNum >= st->max_num_iterations) { stopReason = 1; break; }
+        iterationNum >= lastTroubledIteration + st->distance_from_troubled_iteration) {
+      stopReason = 0;
+      say(std::string(" >_< converged! (hit ") + (toleranceHit ? toleranceHit : "(null)") + " tolerance, for " +
+          std::to_string(st->stop_if_no_improvement_for) + " iterations)");
+      break;
+    } else if (iterationNum >= st->max_num_iterations) {
+      stopReason = 1;
+      say(" X-| iteration limit reached! (" + std::to_string(st->max_num_iterations) + " iterations)");
+      break;
+    }
   }
   syncCheck(p);
-  if (out) {
-    out->initial_cost = initialCost; out->final_cost = finalCost;
-    out->num_troubled_seqs = numTroubledSeqs; out->largest_troubled_seq = largestTroubledSeq;
-    out->num_iterations = iterationNum; out->stop_reason = stopReason;
+  fillSummary();
   }
-  VB_CATCH_NUMERIC
+  catch (const std::domain_error& ex) { g_err = ex.what(); stopReason = 3; fillSummary(); return VB_ERR_NUMERIC; } // the variables stay at the current iterate
+  catch (const std::invalid_argument& ex) { g_err = ex.what(); return VB_ERR_ARG; }
+  catch (const std::exception& ex) { g_err = ex.what(); return VB_ERR_CUDA; }
+  return VB_OK;
 }
+int vb_optimize(vb_problem* p, const vb_settings* st, vb_summary* out) { return vb_optimize_ex(p, st, nullptr, out); }
 
 // one accepted-path LM iteration (Optimizer.cpp:800-1076 on the good-step path) with CUDA-event
 // timing of the phases the reference logs (g/H, factor, solve: Optimizer.cpp:1062-1067).
@@ -1239,6 +1388,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   if (t) {
     t->grad_hess = ms(0, 1); t->damping = ms(1, 2); t->factor_schur = ms(2, 3); t->factor_chol = ms(3, 4);
     t->solve = ms(4, 5); t->apply = ms(5, 6); t->cost = ms(6, 7); t->total = ms(0, 7);
+    t->step_dot_grad = p->accHost[kAccDot];
   }
   if (cost_before) *cost_before = p->accHost[kAccCost];
   if (cost_after) { double c = 0; for (size_t i = 0; i < ns; i++) c += p->accHost[kAccStores + 4 * i]; *cost_after = c; }

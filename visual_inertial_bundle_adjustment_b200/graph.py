@@ -60,7 +60,36 @@ class vb_cost_stats(C.Structure):
 
 class vb_iter_times(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("grad_hess", "damping", "factor_schur", "factor_chol",
-                                          "solve", "apply", "cost", "total")]
+                                          "solve", "apply", "cost", "total", "step_dot_grad")]
+
+
+# VB_BR_* bits of vb_iter_trace.branch (include/viba_b200.h)
+BR_MODEL_NEGATIVE, BR_STEP_FACTOR, BR_ACCEPT_AT_FACTOR, BR_SUB_STEP, BR_ACCEPT_AT_SUB = 1, 2, 4, 8, 16
+BR_LATCH_NO_RETRY, BR_REJECTED, BR_GOOD, BR_AVERAGE, BR_TOLERANCE_HIT, BR_TROUBLED_SEQ_END = 32, 64, 128, 256, 512, 1024
+
+
+class vb_iter_trace(C.Structure):
+    _fields_ = [(n, C.c_double) for n in (
+        "prev_cost", "new_cost", "damping", "damping_used", "model_cost_reduction", "applied_step_factor",
+        "ratio_reduction_to_expected", "cost_reduction", "grad_norm", "step_norm",
+        "ratio_s2v_inf", "ratio_s2v_2", "ratio_s2v_1", "ms_total", "ms_grad_hess", "ms_factor", "ms_solve")] + [
+        (n, C.c_int64) for n in ("num_total", "num_invalid", "num_prev_invalid")] + [
+        ("branch", C.c_int32), ("step_factor_attempts", C.c_int32)]
+
+
+PRE_STEP_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int32)
+LOG_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_char_p)
+
+
+class vb_optimize_hooks(C.Structure):
+    _fields_ = [("pre_step", PRE_STEP_FN), ("pre_step_user", C.c_void_p), ("sync_kinds", C.c_uint32),
+                ("host_vars", C.POINTER(C.c_double)), ("log", LOG_FN), ("log_user", C.c_void_p),
+                ("trace", C.POINTER(vb_iter_trace)), ("trace_cap", C.c_int32), ("trace_len", C.c_int32)]
+
+
+def trace_records(arr, n):
+    """list of dicts from the first n vb_iter_trace records"""
+    return [{name: getattr(arr[i], name) for name, _ in vb_iter_trace._fields_} for i in range(n)]
 
 
 def default_settings(max_iterations=250):

@@ -667,3 +667,52 @@ def _extend_session(g, rng, L, rgb, n_imus, rgb_obs_frac):
         g.add_store(G.FactorStore(G.F_OMEGA_PRIOR_SEC, np.stack([v_om, v_iext[win]], -1), meas1))
         ext.update(v_omega=v_om, v_imu_extr=v_iext, v_imu1=v_imu1)
     return ext
+
+
+# ---- on-disk cache of generated sessions -------------------------------------------------------------
+# Generating the 20-minute session takes minutes of single-threaded numpy; bench.py runs it once per box
+# (every rank of a torchrun job and both bench arms share the file).  The key covers the configuration,
+# the seed and this file's contents, so an edited generator never reads a stale session.
+def cached_session(name, seed=42, cache_dir=None):
+    import fcntl
+    import hashlib
+    import os
+    import pickle
+    import time
+    cfg = dict(CONFIGS[name])
+    cfg["seed"] = seed
+    with open(os.path.abspath(__file__), "rb") as f:
+        src = hashlib.sha256(f.read()).hexdigest()[:12]
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "graph.py"), "rb") as f:
+        src += hashlib.sha256(f.read()).hexdigest()[:6]
+    key = hashlib.sha256(repr(sorted(cfg.items())).encode()).hexdigest()[:12]
+    cache_dir = cache_dir or os.environ.get("VIBA_SESSION_CACHE", "/tmp/viba_b200_sessions")
+    os.makedirs(cache_dir, exist_ok=True)
+    path = os.path.join(cache_dir, f"{name}_{key}_{src}.pkl")
+    t0 = time.time()
+    with open(path + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)   # one generator per box; the others wait here and then load
+        try:
+            if os.path.exists(path):
+                fcntl.flock(lock, fcntl.LOCK_SH)
+                with open(path, "rb") as f:
+                    s = pickle.load(f)
+                s.cache_note = f"loaded from {path} in {time.time() - t0:.1f} s"
+                return s, cfg
+            s = make_session(**cfg)
+            s.graph._keep = []
+            tmp = path + f".tmp{os.getpid()}"
+            try:
+                with open(tmp, "wb") as f:
+                    pickle.dump(s, f, protocol=pickle.HIGHEST_PROTOCOL)
+                os.replace(tmp, path)
+                s.cache_note = f"generated in {time.time() - t0:.1f} s, cached at {path}"
+            except OSError as ex:          # a full /tmp must not kill the bench
+                s.cache_note = f"generated in {time.time() - t0:.1f} s (not cached: {ex})"
+                try:
+                    os.remove(tmp)
+                except OSError:
+                    pass
+            return s, cfg
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)

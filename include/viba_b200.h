@@ -211,6 +211,9 @@ int vb_shard_info(const vb_problem* p, double* out8);
 /* host-only symbolic statistics for a given supernode width cap / nested-dissection leaf size:
  * out8 = {order, dataSize, lumps, levels, maxLumpRows, cholFlops, schurFlops, widest level} */
 int vb_symbolic_stats(const vb_graph_desc* g, int max_lump_width, int nd_leaf_blocks, double* out8);
+/* host-only: padding of the landmark-group Schur update for a grouping: out8 = {groups, tile tasks, executed DMMA
+ * flops, algorithmic Schur flops, mean landmarks per group, mean union rows, levels, algorithmic Cholesky flops} */
+int vb_schur_plan_stats(const vb_graph_desc* g, int max_rows, int chunks, int nd_leaf_blocks, double* out8);
 int64_t vb_order(const vb_problem* p);
 int64_t vb_data_size(const vb_problem* p);
 int64_t vb_num_blocks(const vb_problem* p);
@@ -300,6 +303,8 @@ int vb_rs_refresh(vb_problem* p, int32_t store); /* store < 0: every store that 
 
 /* FP64 DMMA peak probe (mma.sync m8n8k4 f64) used as the tensor roofline denominator */
 int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops);
+/* the same probe for every FP64 mma.sync shape: tflops4 = {m8n8k4, m16n8k4, m16n8k8, m16n8k16} */
+int vb_measure_dmma_shapes(vb_ctx* ctx, double* tflops4);
 
 #ifdef __cplusplus
 }

@@ -18,16 +18,16 @@ from visual_inertial_bundle_adjustment_b200 import synth, graph as G
 
 # name -> (session config, init_noise, settings overrides, branch bits the run must contain, stop reason)
 SCENARIOS = {
-    "far_start": ("tiny", 60.0, dict(max_num_iterations=20),
-                  G.BR_STEP_FACTOR | G.BR_SUB_STEP | G.BR_LATCH_NO_RETRY | G.BR_AVERAGE | G.BR_GOOD, 1),
-    "far_start_rs": ("tiny_rs", 60.0, dict(max_num_iterations=30),
-                     G.BR_STEP_FACTOR | G.BR_ACCEPT_AT_FACTOR | G.BR_SUB_STEP | G.BR_ACCEPT_AT_SUB | G.BR_LATCH_NO_RETRY | G.BR_AVERAGE, 1),
-    "strict_ratio": ("tiny", 20.0, dict(max_num_iterations=14, min_relative_cost_reduction=0.9, damping=1e-9),
-                     G.BR_STEP_FACTOR | G.BR_ACCEPT_AT_FACTOR | G.BR_SUB_STEP | G.BR_REJECTED | G.BR_LATCH_NO_RETRY, 1),
-    "troubled_seq": ("tiny_rs", 60.0, dict(max_num_iterations=20, min_relative_cost_reduction=0.9, damping=1e-2, damping_adjust_on_good=0.05,
-                                           damping_adjust_on_fail=1e5),
-                     G.BR_REJECTED | G.BR_TROUBLED_SEQ_END | G.BR_ACCEPT_AT_SUB, 1),
-    "damping_max": ("tiny", 20.0, dict(max_num_iterations=30, min_relative_cost_reduction=0.9, damping=1e-9, damping_max=2e-9),
+    # damping never falls below 1e-6: with smaller values the damped system is so ill-conditioned (the gauge
+    # freedom is held by the priors only) that two correct solvers differ by 1e-4 in the step
+    "all_branches": ("tiny_rs", 40.0, dict(max_num_iterations=25, damping_min=1e-6),
+                     G.BR_STEP_FACTOR | G.BR_ACCEPT_AT_FACTOR | G.BR_SUB_STEP | G.BR_ACCEPT_AT_SUB | G.BR_LATCH_NO_RETRY |
+                     G.BR_REJECTED | G.BR_TROUBLED_SEQ_END | G.BR_AVERAGE | G.BR_GOOD, 1),
+    "strict_ratio": ("tiny", 40.0, dict(max_num_iterations=16, min_relative_cost_reduction=0.9, damping_min=1e-6),
+                     G.BR_STEP_FACTOR | G.BR_SUB_STEP | G.BR_REJECTED | G.BR_LATCH_NO_RETRY | G.BR_AVERAGE, 1),
+    "troubled_seq": ("tiny", 40.0, dict(max_num_iterations=16, min_relative_cost_reduction=0.9, damping_min=1e-6, damping_adjust_on_fail=1e3),
+                     G.BR_REJECTED | G.BR_TROUBLED_SEQ_END | G.BR_TOLERANCE_HIT, 0),
+    "damping_max": ("tiny", 40.0, dict(max_num_iterations=30, min_relative_cost_reduction=0.9, damping_min=1e-5, damping_max=2e-5),
                     G.BR_REJECTED, 2),
 }
 
@@ -115,10 +115,12 @@ def test_gpu_trace_matches_oracle_on_hard_branches(oracle, name):
         assert lines[-1] == "damping out of range, quadratic model failing?!"
     elif stop == 1:
         assert lines[-1].startswith(" X-| iteration limit reached!")
+    else:
+        assert lines[-1].startswith(" >_< converged! (hit ")
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["far_start_rs", "strict_ratio"])
+@pytest.mark.parametrize("name", ["all_branches", "strict_ratio"])
 def test_sharded_trace_matches_oracle_on_hard_branches(oracle, name):
     """2 threaded shards: gradNew is rank-partial, the sub-step solves it through the distributed solve, the
     partial/full dot products decide — same trace, same bits of the variables on both ranks"""

@@ -24,7 +24,7 @@ EXPORTS = [
     "vb_download_step", "vb_download_hess", "vb_upload_hess", "vb_upload_grad", "vb_download_factor_cache",
     "vb_upload_store_aux", "vb_upload_store_consts", "vb_measure_dmma_peak",
     "vb_download_store_aux", "vb_rs_set_imu", "vb_rs_refresh",
-    "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info", "vb_shard_factor_owners",
+    "vb_schur_plan_stats", "vb_measure_dmma_shapes", "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info", "vb_shard_factor_owners",
 ]
 # int fn(void* user, int op, double* dev_ptr, int64_t count, void* cuda_stream)  (include/viba_b200.h)
 COLLECTIVE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p)
@@ -87,6 +87,7 @@ def load():
                                   C.POINTER(C.c_float), C.POINTER(C.c_float)]
     lib.vb_rs_refresh.argtypes = [C.c_void_p, C.c_int32]
     lib.vb_symbolic_only.argtypes = [C.POINTER(G.vb_graph_desc), _ip, _ip, _ip, _ip, C.c_int64]
+    lib.vb_schur_plan_stats.argtypes = [C.POINTER(G.vb_graph_desc), C.c_int, C.c_int, C.c_int, _dp]
     lib.vb_symbolic_stats.argtypes = [C.POINTER(G.vb_graph_desc), C.c_int, C.c_int, _dp]
     _lib = lib
     return lib
@@ -125,6 +126,15 @@ def symbolic_stats(graph, max_lump_width=0, nd_leaf_blocks=600):
     return dict(zip(["order", "data_size", "lumps", "levels", "max_lump_rows", "chol_flops", "schur_flops", "widest_level"], out))
 
 
+def schur_plan_stats(graph, max_rows=1024, chunks=4, nd_leaf_blocks=0):
+    """Host-only: executed vs algorithmic flops of the landmark-group Schur update for a grouping."""
+    lib = load()
+    desc = graph.desc()
+    out = np.zeros(8)
+    _ck(lib, lib.vb_schur_plan_stats(C.byref(desc), max_rows, chunks, nd_leaf_blocks, _d(out)))
+    return dict(zip(["groups", "tasks", "executed_flops", "schur_flops", "landmarks_per_group", "union_rows", "levels", "chol_flops"], out))
+
+
 def shard_plan(graph, nranks):
     """Host-only: owner rank of every landmark (registration index) for an nranks-way split."""
     lib = load()
@@ -160,6 +170,12 @@ class Context:
         t = C.c_double()
         _ck(self.lib, self.lib.vb_measure_dmma_peak(self.h, C.byref(t)))
         return t.value
+
+    def dmma_shapes_tflops(self):
+        out = np.zeros(4)
+        self.lib.vb_measure_dmma_shapes.argtypes = [C.c_void_p, _dp]
+        _ck(self.lib, self.lib.vb_measure_dmma_shapes(self.h, _d(out)))
+        return dict(zip(["m8n8k4", "m16n8k4", "m16n8k8", "m16n8k16"], out.tolist()))
 
     def close(self):
         if self.h:

@@ -5,6 +5,7 @@
 #include <cmath>
 #include <algorithm>
 #include <memory>
+#include <climits>
 #include <chrono>
 #include <string>
 #include "vb_internal.hpp"
@@ -246,6 +247,151 @@ static std::vector<int32_t> planFactorOwners(const HostGraph& g, const Symbolic&
   return out;
 }
 
+// ---- landmark groups of the Schur update (K9b) -------------------------------------------------------
+// Landmarks sorted by their first camera block are packed greedily while the union of their row blocks stays
+// <= maxRows scalars and the group holds <= 32 x maxChunks landmarks; each chunk of a group is one dense
+// [union rows] x [3 members] operand.  Host-only, so the padding (executed vs algorithmic flops) can be studied
+// without a device (vb_schur_plan_stats).
+struct SchurPlan {
+  std::vector<int64_t> grpBlkPtr{0}, grpMaskPtr{0}, uniPtr{0};
+  std::vector<int32_t> grpBlkOff, grpRowBlk, grpRowSub, grpRows, grpChunks, grpBlks, uniCams;
+  std::vector<uint32_t> grpTileMask;
+  std::vector<SchurTask> tasks;
+  int64_t nGrpLm = 0;
+  double executedFlops = 0; // 2 x 64 x 64 x K4 per (task, chunk with common members)
+};
+static void planSchurGroups(const Symbolic& S, const std::vector<int32_t>& lmOrder, int kGrpMaxRows, int kGrpChunks, SchurPlan& sp) {
+  constexpr int kGrpMax = 32;
+  std::vector<int32_t> uni, merged, members;
+  auto scal = [&](const std::vector<int32_t>& v) { int64_t s = 0; for (int32_t c : v) s += S.camStart[c + 1] - S.camStart[c]; return s; };
+  static const int kOrderMode = getenv("VB_GRP_ROW_ORDER") ? atoi(getenv("VB_GRP_ROW_ORDER")) : 1;
+  static const int kMemberMode = getenv("VB_GRP_MEMBER_ORDER") ? atoi(getenv("VB_GRP_MEMBER_ORDER")) : 0;
+  std::vector<int32_t> uniOrd, slotOf, useLo, useHi, useCnt, perm;
+  auto flush = [&]() {
+    if (members.empty()) return;
+    const int32_t g = (int32_t)sp.grpRows.size();
+    const int32_t r = (int32_t)scal(uni);
+    const size_t nblk = uni.size();
+    // Row order of the union.  Every 64-row tile a landmark touches costs it a full tile of DMMA work, and in
+    // elimination order a member uses only ~60 % of the rows of the tiles it touches (members see different
+    // subsets of rigs; velocity rows exist only for rolling-shutter observations).  Sorting the row blocks by
+    // how many members use them packs the shared rows into dense leading tiles and leaves sparse tail tiles that
+    // only few members are gathered for (executed / algorithmic flops at C2: 3.5 -> 2.6).  The kernel resolves
+    // the triangle of every entry from the rows' elimination positions (updGlobal).
+    useLo.assign(nblk, INT32_MAX); useHi.assign(nblk, -1); useCnt.assign(nblk, 0);
+    for (size_t mi = 0; mi < members.size(); mi++) {
+      const int32_t p = members[mi];
+      size_t b = 0;
+      for (int64_t k = S.lmRowPtr[p]; k < S.lmRowPtr[p + 1]; k++) {
+        while (uni[b] != S.lmRowCam[k]) b++;
+        useLo[b] = std::min(useLo[b], (int32_t)mi); useHi[b] = std::max(useHi[b], (int32_t)mi); useCnt[b]++;
+      }
+    }
+    perm.resize(nblk);
+    for (size_t b = 0; b < nblk; b++) perm[b] = (int32_t)b;
+    if (kOrderMode == 1) { // most-shared rows first: dense leading tiles, sparse tails that few members pay for
+      std::stable_sort(perm.begin(), perm.end(), [&](int32_t a, int32_t b) {
+        if (useCnt[a] != useCnt[b]) return useCnt[a] > useCnt[b];
+        return useLo[a] + useHi[a] < useLo[b] + useHi[b];
+      });
+    } else if (kOrderMode == 2) {
+      std::stable_sort(perm.begin(), perm.end(), [&](int32_t a, int32_t b) { return useLo[a] + useHi[a] < useLo[b] + useHi[b]; });
+    }
+    uniOrd.resize(nblk); slotOf.resize(nblk);
+    for (size_t i = 0; i < nblk; i++) { uniOrd[i] = uni[perm[i]]; slotOf[perm[i]] = (int32_t)i; }
+    if (kMemberMode >= 1) {
+      // chunks of similar extent: members re-sorted by the last (then first) slot of the sliding part of the
+      // union they use, so that a chunk's 32 landmarks end in the same tiles (the tile masks are per chunk)
+      int32_t nCommon = 0;
+      if (kOrderMode == 1) {
+        const int32_t n = (int32_t)members.size();
+        for (size_t i = 0; i < nblk; i++) { if (4 * useCnt[perm[i]] >= 3 * n) nCommon++; else break; }
+      }
+      std::vector<std::pair<int64_t, int32_t>> keyed(members.size());
+      for (size_t mi = 0; mi < members.size(); mi++) {
+        const int32_t p = members[mi];
+        int32_t lo = INT32_MAX, hi = -1;
+        size_t b = 0;
+        for (int64_t k = S.lmRowPtr[p]; k < S.lmRowPtr[p + 1]; k++) {
+          while (uni[b] != S.lmRowCam[k]) b++;
+          const int32_t sl = slotOf[b];
+          if (sl < nCommon) continue;
+          lo = std::min(lo, sl); hi = std::max(hi, sl);
+        }
+        keyed[mi] = {kMemberMode == 1 ? ((int64_t)hi << 32) + lo : ((int64_t)(lo + hi) << 32) + hi, p};
+      }
+      std::stable_sort(keyed.begin(), keyed.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+      for (size_t mi = 0; mi < members.size(); mi++) members[mi] = keyed[mi].second;
+    }
+    sp.uniCams.insert(sp.uniCams.end(), uniOrd.begin(), uniOrd.end());
+    sp.uniPtr.push_back((int64_t)sp.uniCams.size());
+    sp.grpRows.push_back(r);
+    sp.nGrpLm += (int64_t)members.size();
+    const int nch = ((int)members.size() + kGrpMax - 1) / kGrpMax;
+    sp.grpChunks.push_back(nch);
+    sp.grpBlks.push_back((int32_t)nblk);
+    for (size_t b = 0; b < nblk; b++) {
+      const int32_t dc = S.camStart[uniOrd[b] + 1] - S.camStart[uniOrd[b]];
+      for (int32_t s = 0; s < dc; s++) { sp.grpRowBlk.push_back((int32_t)b); sp.grpRowSub.push_back(s); }
+    }
+    // offsets table: row (c * nblk + b), 32 member slots each
+    const size_t base = sp.grpBlkOff.size();
+    sp.grpBlkOff.resize(base + (size_t)nch * nblk * kGrpMax, -1);
+    for (size_t mi = 0; mi < members.size(); mi++) {
+      const int32_t p = members[mi];
+      const int c = (int)(mi / kGrpMax), l = (int)(mi % kGrpMax);
+      size_t b = 0;
+      for (int64_t k = S.lmRowPtr[p]; k < S.lmRowPtr[p + 1]; k++) { // both lists ascend
+        while (uni[b] != S.lmRowCam[k]) b++;
+        sp.grpBlkOff[base + ((size_t)c * nblk + slotOf[b]) * kGrpMax + l] = (int32_t)(S.lmOff[p] + (int64_t)S.lmRowOff[k] * 3);
+      }
+    }
+    sp.grpBlkPtr.push_back(sp.grpBlkPtr.back() + (int64_t)nch * (int64_t)nblk);
+    // per chunk and 64-row tile: which member slots have rows in it; a tile pair only needs, chunk by
+    // chunk, the landmarks present in both tiles (the others contribute exact zeros)
+    const int nt = (r + 63) / 64;
+    const size_t mbase = sp.grpTileMask.size();
+    sp.grpTileMask.resize(mbase + (size_t)nch * nt, 0u);
+    {
+      int32_t q = 0;
+      for (size_t b = 0; b < nblk; b++) {
+        const int32_t dc = S.camStart[uniOrd[b] + 1] - S.camStart[uniOrd[b]];
+        for (int c = 0; c < nch; c++) {
+          uint32_t m = 0;
+          for (int l = 0; l < kGrpMax; l++) if (sp.grpBlkOff[base + ((size_t)c * nblk + b) * kGrpMax + l] >= 0) m |= 1u << l;
+          for (int32_t s = 0; s < dc; s++) sp.grpTileMask[mbase + (size_t)c * nt + (q + s) / 64] |= m;
+        }
+        q += dc;
+      }
+    }
+    sp.grpMaskPtr.push_back((int64_t)sp.grpTileMask.size());
+    for (int ti = 0; ti < nt; ti++)
+      for (int tj = 0; tj <= ti; tj++) {
+        uint32_t any = 0;
+        for (int c = 0; c < nch; c++) {
+          const uint32_t m = sp.grpTileMask[mbase + (size_t)c * nt + ti] & sp.grpTileMask[mbase + (size_t)c * nt + tj];
+          any |= m;
+          if (m) sp.executedFlops += 2.0 * 64 * 64 * ((3 * __builtin_popcount(m) + 3) & ~3);
+        }
+        if (any) sp.tasks.push_back({g, ti, tj, any});
+      }
+    uni.clear(); members.clear();
+  };
+  for (int32_t p : lmOrder) {
+    const int32_t* bb = S.lmRowCam.data() + S.lmRowPtr[p];
+    const int32_t* ee = S.lmRowCam.data() + S.lmRowPtr[p + 1];
+    merged.clear();
+    std::set_union(uni.begin(), uni.end(), bb, ee, std::back_inserter(merged));
+    if (!members.empty() && ((int)members.size() == kGrpMax * kGrpChunks || scal(merged) > kGrpMaxRows)) {
+      flush();
+      merged.assign(bb, ee);
+    }
+    uni.swap(merged);
+    members.push_back(p);
+  }
+  flush();
+}
+
 static void buildDeviceProblem(vb_problem& P) {
   const HostGraph& g = P.g;
   const Symbolic& S = P.S;
@@ -387,8 +533,10 @@ static void buildDeviceProblem(vb_problem& P) {
       for (int64_t k = 0; k < n; k++) {
         const int32_t c = cams[k];
         const int32_t T = S.camLump[c];
-        if (targets.empty() || targets.back() != T) targets.push_back(T);
-        const int32_t t = (int32_t)targets.size() - 1;
+        int32_t t = -1; // group unions are not in elimination order: look the target up
+        if (!targets.empty() && targets.back() == T) t = (int32_t)targets.size() - 1;
+        else { for (size_t z = 0; z < targets.size(); z++) if (targets[z] == T) { t = (int32_t)z; break; } }
+        if (t < 0) { targets.push_back(T); t = (int32_t)targets.size() - 1; }
         const int32_t dc = S.camStart[c + 1] - S.camStart[c];
         for (int32_t s = 0; s < dc; s++) {
           colOff.push_back(S.lumpOff[T] + (S.camStart[c] + s - S.camStart[S.lumpFirst[T]]));
@@ -426,7 +574,6 @@ static void buildDeviceProblem(vb_problem& P) {
     // A group is the scatter unit: up to kGrpChunks chunks of <= 32 landmarks that share one union of
     // row blocks.  The kernel accumulates the chunks of a tile pair in registers (K loop) and scatters
     // once, so the reductions per target entry drop with the number of chunks.
-    constexpr int kGrpMax = 32;
     int kGrpMaxRows = 1024, kGrpChunks = 4; // measured on B200 at C2: 1 chunk 5.8 ms, 4: 4.9, 8: 5.0, 16: 5.3
     if (const char* e = getenv("VB_GRP_MAX_ROWS")) kGrpMaxRows = std::max(64, atoi(e));
     if (const char* e = getenv("VB_GRP_CHUNKS")) kGrpChunks = std::max(1, std::min(32, atoi(e)));
@@ -441,81 +588,18 @@ static void buildDeviceProblem(vb_problem& P) {
       d.lmActive = P.upload(mine);
     }
     P.ownedLandmarks = d.nLmActive;
-    std::vector<int64_t> grpBlkPtr(1, 0), grpMaskPtr(1, 0);
-    std::vector<int32_t> grpBlkOff, grpRowBlk, grpRowSub, grpRows, grpChunks, grpBlks;
-    std::vector<uint32_t> grpTileMask;
-    std::vector<SchurTask> schurTasks;
-    int64_t nGrpLm = 0;
-    {
-      std::vector<int32_t> uni, merged, members;
-      auto scal = [&](const std::vector<int32_t>& v) { int64_t s = 0; for (int32_t c : v) s += S.camStart[c + 1] - S.camStart[c]; return s; };
-      auto flush = [&]() {
-        if (members.empty()) return;
-        const int32_t g = (int32_t)grpRows.size();
-        const int32_t r = appendSource(uni.data(), (int64_t)uni.size(), false);
-        grpRows.push_back(r);
-        nGrpLm += (int64_t)members.size();
-        const int nch = ((int)members.size() + kGrpMax - 1) / kGrpMax;
-        grpChunks.push_back(nch);
-        const size_t nblk = uni.size();
-        grpBlks.push_back((int32_t)nblk);
-        for (size_t b = 0; b < nblk; b++) {
-          const int32_t dc = S.camStart[uni[b] + 1] - S.camStart[uni[b]];
-          for (int32_t s = 0; s < dc; s++) { grpRowBlk.push_back((int32_t)b); grpRowSub.push_back(s); }
-        }
-        // offsets table: row (c * nblk + b), 32 member slots each
-        const size_t base = grpBlkOff.size();
-        grpBlkOff.resize(base + (size_t)nch * nblk * kGrpMax, -1);
-        for (size_t mi = 0; mi < members.size(); mi++) {
-          const int32_t p = members[mi];
-          const int c = (int)(mi / kGrpMax), l = (int)(mi % kGrpMax);
-          size_t b = 0;
-          for (int64_t k = S.lmRowPtr[p]; k < S.lmRowPtr[p + 1]; k++) { // both lists ascend
-            while (uni[b] != S.lmRowCam[k]) b++;
-            grpBlkOff[base + ((size_t)c * nblk + b) * kGrpMax + l] = (int32_t)(S.lmOff[p] + (int64_t)S.lmRowOff[k] * 3);
-          }
-        }
-        grpBlkPtr.push_back(grpBlkPtr.back() + (int64_t)nch * (int64_t)nblk);
-        // per chunk and 64-row tile: which member slots have rows in it; a tile pair only needs, chunk by
-        // chunk, the landmarks present in both tiles (the others contribute exact zeros)
-        const int nt = (r + 63) / 64;
-        const size_t mbase = grpTileMask.size();
-        grpTileMask.resize(mbase + (size_t)nch * nt, 0u);
-        {
-          int32_t q = 0;
-          for (size_t b = 0; b < nblk; b++) {
-            const int32_t dc = S.camStart[uni[b] + 1] - S.camStart[uni[b]];
-            for (int c = 0; c < nch; c++) {
-              uint32_t m = 0;
-              for (int l = 0; l < kGrpMax; l++) if (grpBlkOff[base + ((size_t)c * nblk + b) * kGrpMax + l] >= 0) m |= 1u << l;
-              for (int32_t s = 0; s < dc; s++) grpTileMask[mbase + (size_t)c * nt + (q + s) / 64] |= m;
-            }
-            q += dc;
-          }
-        }
-        grpMaskPtr.push_back((int64_t)grpTileMask.size());
-        for (int ti = 0; ti < nt; ti++)
-          for (int tj = 0; tj <= ti; tj++) {
-            uint32_t any = 0;
-            for (int c = 0; c < nch; c++) any |= grpTileMask[mbase + (size_t)c * nt + ti] & grpTileMask[mbase + (size_t)c * nt + tj];
-            if (any) schurTasks.push_back({g, ti, tj, any});
-          }
-        uni.clear(); members.clear();
-      };
-      for (int32_t p : lmOrder) {
-        const int32_t* bb = S.lmRowCam.data() + S.lmRowPtr[p];
-        const int32_t* ee = S.lmRowCam.data() + S.lmRowPtr[p + 1];
-        merged.clear();
-        std::set_union(uni.begin(), uni.end(), bb, ee, std::back_inserter(merged));
-        if (!members.empty() && ((int)members.size() == kGrpMax * kGrpChunks || scal(merged) > kGrpMaxRows)) {
-          flush();
-          merged.assign(bb, ee);
-        }
-        uni.swap(merged);
-        members.push_back(p);
-      }
-      flush();
+    SchurPlan sp;
+    planSchurGroups(S, lmOrder, kGrpMaxRows, kGrpChunks, sp);
+    for (size_t g = 0; g < sp.grpRows.size(); g++) {
+      const int32_t r = appendSource(sp.uniCams.data() + sp.uniPtr[g], sp.uniPtr[g + 1] - sp.uniPtr[g], false);
+      if (r != sp.grpRows[g]) throw std::runtime_error("schur plan: union row count mismatch");
     }
+    std::vector<int64_t>& grpBlkPtr = sp.grpBlkPtr; std::vector<int64_t>& grpMaskPtr = sp.grpMaskPtr;
+    std::vector<int32_t>&grpBlkOff = sp.grpBlkOff, &grpRowBlk = sp.grpRowBlk, &grpRowSub = sp.grpRowSub, &grpRows = sp.grpRows,
+                        &grpChunks = sp.grpChunks, &grpBlks = sp.grpBlks;
+    std::vector<uint32_t>& grpTileMask = sp.grpTileMask;
+    std::vector<SchurTask>& schurTasks = sp.tasks;
+    const int64_t nGrpLm = sp.nGrpLm;
     updPtr.push_back((int64_t)colOff.size()); relPtr.push_back((int64_t)rel.size());
     d.diagLOff = P.upload(diagLOff); d.diagL = P.alloc<double>(dl);
     d.diagInv = P.alloc<double>((size_t)(S.camStart[S.nC] + 1) * 32);
@@ -785,6 +869,25 @@ int vb_symbolic_stats(const vb_graph_desc* g, int max_lump_width, int nd_leaf_bl
   for (const auto& lv : S.levels) widest = std::max(widest, lv.size());
   out8[0] = (double)S.order; out8[1] = (double)S.dataSize; out8[2] = (double)S.nL; out8[3] = (double)S.levels.size();
   out8[4] = S.maxLumpRows; out8[5] = S.cholFlops; out8[6] = S.schurFlops; out8[7] = (double)widest;
+  VB_CATCH
+}
+
+// host-only: padding of the Schur update for a grouping (max union rows, chunks of 32 landmarks per group):
+// out8 = {groups, tasks, executed DMMA flops, algorithmic Schur flops, mean landmarks per group, mean union rows,
+//         levels, algorithmic Cholesky flops}
+int vb_schur_plan_stats(const vb_graph_desc* g, int max_rows, int chunks, int nd_leaf_blocks, double* out8) {
+  VB_TRY
+  HostGraph hg; hg.load(g);
+  SymbolicOptions opt;
+  if (nd_leaf_blocks != 0) opt.ndLeafBlocks = nd_leaf_blocks;
+  if (const char* e = getenv("VB_MAX_LUMP_WIDTH")) opt.maxLumpWidth = std::max(8, std::min(128, atoi(e)));
+  Symbolic S; buildSymbolic(hg, opt, &S);
+  SchurPlan sp;
+  planSchurGroups(S, landmarkOrder(S), max_rows, chunks, sp);
+  double rs = 0; for (int32_t r : sp.grpRows) rs += r;
+  const double ng = std::max<double>(1, (double)sp.grpRows.size());
+  out8[0] = (double)sp.grpRows.size(); out8[1] = (double)sp.tasks.size(); out8[2] = sp.executedFlops; out8[3] = S.schurFlops;
+  out8[4] = sp.nGrpLm / ng; out8[5] = rs / ng; out8[6] = (double)S.levels.size(); out8[7] = S.cholFlops;
   VB_CATCH
 }
 
@@ -1483,6 +1586,13 @@ int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops) {
   if (!ctx || !tflops) throw std::invalid_argument("null argument");
   VB_CUDA(cudaSetDevice(ctx->device));
   *tflops = measureDmmaPeak(ctx->stream);
+  VB_CATCH
+}
+int vb_measure_dmma_shapes(vb_ctx* ctx, double* tflops4) {
+  VB_TRY
+  if (!ctx || !tflops4) throw std::invalid_argument("null argument");
+  VB_CUDA(cudaSetDevice(ctx->device));
+  measureDmmaPeak(ctx->stream, tflops4);
   VB_CATCH
 }
 

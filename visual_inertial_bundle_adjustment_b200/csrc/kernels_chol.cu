@@ -338,8 +338,20 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
     dmmaABt<2, 4>(As, ld, Bs, ld, K4, rowBase, colBase, acc);
   }
   const int32_t* rel = d.rel + d.relPtr[src];
-  // two-phase scatter: every index lookup first (independent loads in flight together), then the reductions
+  // two-phase scatter: every index lookup first (independent loads in flight together), then the reductions.
+  // The union rows are not in elimination order (most-shared rows first), so which of the two rows is the
+  // column of the lower-triangular target is decided per entry from their reduced-system positions.
   double* dst[4][2][2];
+  int64_t rowCol[2]; int rowStride[2], rowGlob[2]; const int32_t* rowRel[2];
+#pragma unroll
+  for (int m = 0; m < 2; m++) {
+    const int qi = i0 + rowBase + m * 8 + (lane >> 2);
+    const bool rv = qi < r;
+    rowCol[m] = rv ? d.updColOff[q0 + qi] : 0;
+    rowStride[m] = rv ? d.updStride[q0 + qi] : 0;
+    rowGlob[m] = rv ? d.updGlobal[q0 + qi] : -1;
+    rowRel[m] = rel + (int64_t)(rv ? d.updTgt[q0 + qi] : 0) * r;
+  }
 #pragma unroll
   for (int n = 0; n < 4; n++)
 #pragma unroll
@@ -348,12 +360,17 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
       const bool cv = qj < r;
       const int64_t colOff = cv ? d.updColOff[q0 + qj] : 0;
       const int stride = cv ? d.updStride[q0 + qj] : 0;
+      const int gj = cv ? d.updGlobal[q0 + qj] : 0;
       const int32_t* relT = rel + (int64_t)(cv ? d.updTgt[q0 + qj] : 0) * r;
 #pragma unroll
       for (int m = 0; m < 2; m++) {
         const int qi = i0 + rowBase + m * 8 + (lane >> 2);
-        const int rr = (cv && qi < r && qi >= qj) ? relT[qi] : -1;
-        dst[n][e][m] = rr >= 0 ? hess + colOff + (int64_t)rr * stride : nullptr;
+        double* p = nullptr;
+        if (cv && qi < r && qi >= qj) {
+          if (rowGlob[m] >= gj) { const int rr = relT[qi]; if (rr >= 0) p = hess + colOff + (int64_t)rr * stride; }
+          else { const int rr = rowRel[m][qj]; if (rr >= 0) p = hess + rowCol[m] + (int64_t)rr * rowStride[m]; }
+        }
+        dst[n][e][m] = p;
       }
     }
 #pragma unroll

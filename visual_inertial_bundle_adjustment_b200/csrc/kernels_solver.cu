@@ -4,6 +4,8 @@
 // Cholesky of the camera system level by level over the elimination tree; then the solves.
 #include "vb_internal.hpp"
 #include "dev_math.cuh"
+#include <cstdio>
+#include <cstdlib>
 
 namespace vb {
 
@@ -132,22 +134,71 @@ __global__ void dmmaProbeKernel(double* out, int iters) {
   }
   if (c0[0] + c1[0] + c2[0] + c3[0] + c0[1] + c1[1] + c2[1] + c3[1] == 12345.678) out[0] = 1.0;
 }
-double measureDmmaPeak(cudaStream_t s) {
-  double* dummy;
-  VB_CUDA(cudaMalloc(&dummy, 8));
-  const int iters = 20000, blocks = 148 * 4, threads = 256;
-  dmmaProbeKernel<<<blocks, threads, 0, s>>>(dummy, 100);
+// the sm_90+ shapes (m16n8k4 / k8 / k16), probed the same way: SHAPE = K; operands per lane A: K/2, B: K/4, C: 4
+template <int K>
+__global__ void dmmaProbeWideKernel(double* out, int iters) {
+  double c[2][4] = {{0, 0, 0, 0}, {0, 0, 0, 0}};
+  double a[8], b[4];
+#pragma unroll
+  for (int i = 0; i < 8; i++) a[i] = 1.0 + (threadIdx.x + i) * 1e-9;
+#pragma unroll
+  for (int i = 0; i < 4; i++) b[i] = 1.0 - (threadIdx.x + i) * 1e-9;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int u = 0; u < 2; u++) {
+      if (K == 4)
+        asm volatile("mma.sync.aligned.m16n8k4.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                     : "+d"(c[u][0]), "+d"(c[u][1]), "+d"(c[u][2]), "+d"(c[u][3]) : "d"(a[0]), "d"(a[1]), "d"(b[0]));
+      else if (K == 8)
+        asm volatile("mma.sync.aligned.m16n8k8.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                     : "+d"(c[u][0]), "+d"(c[u][1]), "+d"(c[u][2]), "+d"(c[u][3])
+                     : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(b[0]), "d"(b[1]));
+      else
+        asm volatile("mma.sync.aligned.m16n8k16.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7,%8,%9,%10,%11}, {%12,%13,%14,%15}, {%0,%1,%2,%3};"
+                     : "+d"(c[u][0]), "+d"(c[u][1]), "+d"(c[u][2]), "+d"(c[u][3])
+                     : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(a[4]), "d"(a[5]), "d"(a[6]), "d"(a[7]),
+                       "d"(b[0]), "d"(b[1]), "d"(b[2]), "d"(b[3]));
+    }
+  }
+  double s = 0;
+#pragma unroll
+  for (int u = 0; u < 2; u++)
+#pragma unroll
+    for (int i = 0; i < 4; i++) s += c[u][i];
+  if (s == 12345.678) out[0] = 1.0;
+}
+template <typename F>
+static double timeProbe(F launch, double flopsPerLaunch, cudaStream_t s) {
   cudaEvent_t e0, e1;
   VB_CUDA(cudaEventCreate(&e0)); VB_CUDA(cudaEventCreate(&e1));
+  launch(100);
   VB_CUDA(cudaEventRecord(e0, s));
-  dmmaProbeKernel<<<blocks, threads, 0, s>>>(dummy, iters);
+  launch(20000);
   VB_CUDA(cudaEventRecord(e1, s));
   VB_CUDA(cudaEventSynchronize(e1));
   float ms = 0;
   VB_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(dummy);
-  const double flops = (double)blocks * (threads / 32) * iters * 4.0 * (2.0 * 8 * 8 * 4);
-  return flops / (ms * 1e-3) * 1e-12;
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return flopsPerLaunch / (ms * 1e-3) * 1e-12;
+}
+// FP64 tensor-pipe peak: the m8n8k4 shape every kernel here uses; VB_VERBOSE also prints the sm_90+ shapes
+// m16n8k4 / k8 / k16 measured the same way (perShape[0..3], may be null)
+double measureDmmaPeak(cudaStream_t s, double* perShape) {
+  double* dummy;
+  VB_CUDA(cudaMalloc(&dummy, 8));
+  const int blocks = 148 * 4, threads = 256;
+  const double warps = (double)blocks * (threads / 32);
+  double r[4];
+  r[0] = timeProbe([&](int it) { dmmaProbeKernel<<<blocks, threads, 0, s>>>(dummy, it); }, warps * 20000 * 4.0 * (2.0 * 8 * 8 * 4), s);
+  r[1] = timeProbe([&](int it) { dmmaProbeWideKernel<4><<<blocks, threads, 0, s>>>(dummy, it); }, warps * 20000 * 2.0 * (2.0 * 16 * 8 * 4), s);
+  r[2] = timeProbe([&](int it) { dmmaProbeWideKernel<8><<<blocks, threads, 0, s>>>(dummy, it); }, warps * 20000 * 2.0 * (2.0 * 16 * 8 * 8), s);
+  r[3] = timeProbe([&](int it) { dmmaProbeWideKernel<16><<<blocks, threads, 0, s>>>(dummy, it); }, warps * 20000 * 2.0 * (2.0 * 16 * 8 * 16), s);
+  VB_CUDA(cudaGetLastError());
+  cudaFree(dummy);
+  if (perShape) for (int i = 0; i < 4; i++) perShape[i] = r[i];
+  if (getenv("VB_VERBOSE"))
+    std::fprintf(stderr, "[viba_b200] FP64 mma.sync probes (TFLOP/s): m8n8k4 %.2f, m16n8k4 %.2f, m16n8k8 %.2f, m16n8k16 %.2f\n", r[0], r[1], r[2], r[3]);
+  return r[0];
 }
 
 // ---- launchers ----------------------------------------------------------------------------------------

@@ -121,6 +121,6 @@ void launchVecOp(int op, double* a, const double* b, double s, int64_t n, double
 void launchRsRefresh(const int64_t* timeNs, const float* gyro, const float* accel, int64_t nSamples, const double* varData,
                      const int64_t* calibOff, const int64_t* midUs, int64_t halfUs, int64_t nRigs, double* tables, int* status,
                      cudaStream_t st);
-double measureDmmaPeak(cudaStream_t s);
+double measureDmmaPeak(cudaStream_t s, double* perShape = nullptr);
 
 } // namespace vb

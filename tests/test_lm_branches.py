@@ -76,8 +76,12 @@ def test_model_negative_branch_is_unreachable(oracle):
 def assert_traces_match(tg, to, rel=1e-9):
     assert len(tg) == len(to)
     for i, (a, b) in enumerate(zip(tg, to)):
-        for k in ("prev_cost", "new_cost", "model_cost_reduction", "cost_reduction"):
+        for k in ("prev_cost", "new_cost", "model_cost_reduction"):
             assert abs(a[k] - b[k]) <= rel * max(abs(b[k]), abs(b["prev_cost"]) * 1e-3), (i, k, a[k], b[k])
+        # a difference of two costs that are each gated at `rel`: absolute tolerance from the costs, not from the
+        # (possibly tiny, on a rejected step) difference
+        assert abs(a["cost_reduction"] - b["cost_reduction"]) <= rel * (abs(b["prev_cost"]) + abs(b["new_cost"])), \
+            (i, "cost_reduction", a["cost_reduction"], b["cost_reduction"])
         for k in ("damping", "damping_used", "applied_step_factor"):
             assert abs(a[k] - b[k]) <= 1e-9 * abs(b[k]), (i, k, a[k], b[k])
         for k in ("grad_norm", "step_norm", "ratio_s2v_inf", "ratio_s2v_2", "ratio_s2v_1"):

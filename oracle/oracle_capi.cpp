@@ -7,6 +7,7 @@
 #include <chrono>
 #include "lm.hpp"
 #include "rs_refresh.hpp"
+#include "preint.hpp"
 
 using namespace orc;
 
@@ -18,8 +19,18 @@ struct RsSource {   // raw IMU-0 samples + per-rig windows of one rolling-shutte
   int64_t halfUs = 0;
 };
 
+struct PreintSource {   // raw samples of one IMU + the integration interval of every factor of one inertial store
+  int store = -1;
+  ImuSamples meas;
+  std::vector<int64_t> startUs, endUs;
+  std::vector<int32_t> calibVar;
+  double gyroVar[3], accelVar[3];
+  std::vector<double> cov, omegaAtEnd;   // per factor: 81 / 3 doubles, filled by the refresh
+};
+
 struct OrcHandle {
   std::vector<RsSource> rs;
+  std::vector<PreintSource> preint;
   Engine eng;
   SchurSkylineSolver sol;
   bool analyzed = false;
@@ -185,6 +196,30 @@ int orc_optimize_ex(OrcHandle* h, const vb_settings* s, vb_summary* out, vb_iter
   if (traceLen) *traceLen = n;
   ORC_CATCH
 }
+static void preintRefresh(OrcHandle* h, int store) {
+  for (PreintSource& src : h->preint) {
+    if (store >= 0 && src.store != store) continue;
+    Problem& P = h->eng.P;
+    double* recs = P.stores[src.store].aux.data();
+    const int threads = h->eng.threads;
+    std::string failure;
+#pragma omp parallel for schedule(dynamic, 16) num_threads(threads) if (threads > 1)
+    for (int64_t k = 0; k < (int64_t)src.startUs.size(); k++) {
+      if (src.calibVar[k] < 0) continue;
+      try {
+        const int32_t v = src.calibVar[k];
+        const PreintResult r = preintCompute(src.meas, P.data.data() + P.off[v], P.flags[v], src.gyroVar, src.accelVar, src.startUs[k], src.endUs[k]);
+        std::memcpy(recs + k * kPreintRec, r.rec, sizeof r.rec);
+        std::memcpy(src.cov.data() + 81 * k, r.cov, sizeof r.cov);
+        std::memcpy(src.omegaAtEnd.data() + 3 * k, r.omegaAtEnd, sizeof r.omegaAtEnd);
+      } catch (const std::exception& ex) {
+#pragma omp critical
+        failure = ex.what();
+      }
+    }
+    if (!failure.empty()) throw std::runtime_error(failure);
+  }
+}
 static void rsRefresh(OrcHandle* h, int store) {
   for (const RsSource& src : h->rs) {
     if (store >= 0 && src.store != store) continue;
@@ -220,7 +255,114 @@ int orc_rs_set_imu(OrcHandle* h, int store, int64_t n_rigs, const int64_t* rig_m
   src.meas.accel.assign(accel, accel + 3 * n_samples);
   if ((int64_t)h->eng.P.stores.at(store).aux.size() != 4 + n_rigs * kRsStride) throw std::runtime_error("rig count does not match the store's tables");
   h->rs.push_back(std::move(src));
-  h->eng.preStep = [h]() { rsRefresh(h, -1); };
+  h->eng.preStep = [h]() { preintRefresh(h, -1); rsRefresh(h, -1); };
+  ORC_CATCH
+}
+// SingleSessionAdapter::regenerateAllPreintegrationsFromImuMeasurements (InertialFactors.cpp:45-70): same arguments as vb_preint_set_imu
+int orc_preint_set_imu(OrcHandle* h, int store, int64_t n_factors, const int64_t* start_us, const int64_t* end_us, const int32_t* calib_var,
+                       int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel, const double* gyro_var3,
+                       const double* accel_var3) {
+  ORC_TRY
+  PreintSource src;
+  src.store = store;
+  src.startUs.assign(start_us, start_us + n_factors);
+  src.endUs.assign(end_us, end_us + n_factors);
+  src.calibVar.assign(calib_var, calib_var + n_factors);
+  src.meas.timeNs.assign(sample_time_ns, sample_time_ns + n_samples);
+  src.meas.gyro.assign(gyro, gyro + 3 * n_samples);
+  src.meas.accel.assign(accel, accel + 3 * n_samples);
+  for (int i = 0; i < 3; i++) { src.gyroVar[i] = gyro_var3[i]; src.accelVar[i] = accel_var3[i]; }
+  src.cov.assign(81 * n_factors, 0.0);
+  src.omegaAtEnd.assign(3 * n_factors, 0.0);
+  if ((int64_t)h->eng.P.stores.at(store).aux.size() != n_factors * kPreintRec) throw std::runtime_error("factor count does not match the store's records");
+  h->preint.push_back(std::move(src));
+  h->eng.preStep = [h]() { preintRefresh(h, -1); rsRefresh(h, -1); };
+  ORC_CATCH
+}
+int orc_preint_refresh(OrcHandle* h, int store) {
+  ORC_TRY
+  preintRefresh(h, store);
+  ORC_CATCH
+}
+int orc_preint_get_cov(OrcHandle* h, int store, double* cov, double* omega_at_end, int64_t n_factors) {
+  ORC_TRY
+  for (const PreintSource& src : h->preint) {
+    if (src.store != store) continue;
+    if ((int64_t)src.startUs.size() != n_factors) throw std::runtime_error("factor count mismatch");
+    if (cov) std::memcpy(cov, src.cov.data(), src.cov.size() * 8);
+    if (omega_at_end) std::memcpy(omega_at_end, src.omegaAtEnd.data(), src.omegaAtEnd.size() * 8);
+    return 0;
+  }
+  throw std::runtime_error("store has no IMU source");
+  ORC_CATCH
+}
+// computePreIntegration (PreIntegration.cpp:136-275) on raw samples, standalone
+int orc_preint_compute(int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel, const double* calib32,
+                       uint32_t flags, const double* gyro_var3, const double* accel_var3, int64_t start_us, int64_t end_us, double* rec250,
+                       double* cov81, double* omega3, int32_t* steps) {
+  ORC_TRY
+  ImuSamples m;
+  m.timeNs.assign(sample_time_ns, sample_time_ns + n_samples);
+  m.gyro.assign(gyro, gyro + 3 * n_samples);
+  m.accel.assign(accel, accel + 3 * n_samples);
+  const PreintResult r = preintCompute(m, calib32, flags, gyro_var3, accel_var3, start_us, end_us);
+  std::memcpy(rec250, r.rec, sizeof r.rec);
+  if (cov81) std::memcpy(cov81, r.cov, sizeof r.cov);
+  if (omega3) std::memcpy(omega3, r.omegaAtEnd, sizeof r.omegaAtEnd);
+  if (steps) *steps = r.steps;
+  ORC_CATCH
+}
+// pieces, for the reference's unit-test recipes: integrate + Jacobian (MotionIntegral.cpp:162-226), combineJacs (:52-75),
+// getCompensatedImuMeasurementAndJac (CompensateJac.cpp:146-249), combine / differentiate / integrate(interp)
+int orc_integrate_jac(const double* gyro3, const double* accel3, double dt, double* out11, double* J54) {
+  ORC_TRY
+  double J[54];
+  const Rvp r = integrateJac(gyro3, accel3, dt, J);
+  const Rvp r0 = integrate(gyro3, accel3, dt);
+  for (int i = 0; i < 4; i++) if (r.q[i] != r0.q[i]) throw std::runtime_error("integrate with and without Jacobian differ");
+  for (int i = 0; i < 4; i++) out11[i] = r.q[i];
+  for (int i = 0; i < 3; i++) { out11[4 + i] = r.dV[i]; out11[7 + i] = r.dP[i]; }
+  out11[10] = r.dt;
+  if (J54) std::memcpy(J54, J, sizeof J);
+  ORC_CATCH
+}
+static Rvp rvpFrom(const double* a) { Rvp r; for (int i = 0; i < 4; i++) r.q[i] = a[i]; for (int i = 0; i < 3; i++) { r.dV[i] = a[4 + i]; r.dP[i] = a[7 + i]; } r.dt = a[10]; return r; }
+static void rvpTo(const Rvp& r, double* a) { for (int i = 0; i < 4; i++) a[i] = r.q[i]; for (int i = 0; i < 3; i++) { a[4 + i] = r.dV[i]; a[7 + i] = r.dP[i]; } a[10] = r.dt; }
+int orc_combine(const double* a11, const double* b11, double* c11) {
+  ORC_TRY
+  rvpTo(combine(rvpFrom(a11), rvpFrom(b11)), c11);
+  ORC_CATCH
+}
+int orc_uncombine_left(const double* c11, const double* a11, double* b11) {
+  ORC_TRY
+  rvpTo(uncombineLeft(rvpFrom(c11), rvpFrom(a11)), b11);
+  ORC_CATCH
+}
+int orc_combine_jacs(const double* a11, const double* b11, const double* aJ, const double* bJ, int n, double* c11, double* cJ) {
+  ORC_TRY
+  rvpTo(combineJacs(rvpFrom(a11), rvpFrom(b11), aJ, bJ, cJ, n), c11);
+  ORC_CATCH
+}
+int orc_differentiate(const double* a11, double* interp9) {
+  ORC_TRY
+  differentiate(rvpFrom(a11), interp9);
+  ORC_CATCH
+}
+int orc_integrate_interp(const double* interp9, double dt, double* out11) {
+  ORC_TRY
+  rvpTo(integrateInterp(interp9, dt), out11);
+  ORC_CATCH
+}
+int orc_compensate_jac(const double* calib32, uint32_t flags, const double* raw_gyro3, const double* raw_accel3, double* gyro3, double* accel3,
+                       double* cmJ /* 6 x (6 + E) */) {
+  ORC_TRY
+  const ImuIdx ix(flags);
+  compensateAndJac(calibMats(calib32), ix, raw_gyro3, raw_accel3, gyro3, accel3, cmJ);
+  ORC_CATCH
+}
+int orc_imu_boxplus(double* calib32, const double* step, uint32_t flags) {
+  ORC_TRY
+  imuCalibBoxPlus(calib32, step, flags);
   ORC_CATCH
 }
 // integrateMeasurements (PreIntegration.cpp:277-306) on raw samples: out = q(4) dV(3) dP(3) dt

@@ -76,8 +76,12 @@ def test_model_negative_branch_is_unreachable(oracle):
 def assert_traces_match(tg, to, rel=1e-9):
     assert len(tg) == len(to)
     for i, (a, b) in enumerate(zip(tg, to)):
-        for k in ("prev_cost", "new_cost", "model_cost_reduction"):
+        for k in ("prev_cost", "new_cost"):
             assert abs(a[k] - b[k]) <= rel * max(abs(b[k]), abs(b["prev_cost"]) * 1e-3), (i, k, a[k], b[k])
+        # 0.5 step.grad is a function of the solved step, which is gated at 1e-7 (two correct solvers of these
+        # barely damped systems differ by more than 1e-9 in it)
+        assert abs(a["model_cost_reduction"] - b["model_cost_reduction"]) <= 1e-7 * max(abs(b["model_cost_reduction"]), abs(b["prev_cost"]) * 1e-3), \
+            (i, "model_cost_reduction", a["model_cost_reduction"], b["model_cost_reduction"])
         # a difference of two costs that are each gated at `rel`: absolute tolerance from the costs, not from the
         # (possibly tiny, on a rejected step) difference
         assert abs(a["cost_reduction"] - b["cost_reduction"]) <= rel * (abs(b["prev_cost"]) + abs(b["new_cost"])), \

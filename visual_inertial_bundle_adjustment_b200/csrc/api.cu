@@ -454,7 +454,7 @@ static void buildDeviceProblem(vb_problem& P) {
     }
     if (bad) throw std::runtime_error("scatter map: block missing from the structure");
     d.gOff = P.upload(gOff); d.hOff = P.upload(hOff); d.hStride = P.upload(hStride);
-    d.order = nullptr; d.chunkStart = nullptr; d.nChunks = 0; d.orderLm = nullptr;
+    d.order = nullptr; d.chunkStart = nullptr; d.nChunks = 0; d.orderLm = nullptr; d.pk = VisPack{}; d.visImpl = 0;
     // Two-pass visual schedule pays once the landmark panels no longer live in L2 (measured on B200:
     // C2, 0.7 GB of panels: 6.1 ms single pass vs 6.6 ms; C3, 3 GB: 35.5 ms vs 24.6 ms).
     // VB_VISUAL_TWO_PASS=0/1 overrides.
@@ -479,6 +479,7 @@ static void buildDeviceProblem(vb_problem& P) {
       if (sharded) d.active = P.upload(order); // ascending factor index: the cost kernel's order
       P.ownedVisual += nOwn;
       auto key = [&](int32_t k, int a) { return hs.vars[(int64_t)k * nv + a]; };
+      std::vector<int32_t> olmKeep;
       { // landmark-major order of the second pass
         std::vector<int32_t> olm(order);
         std::stable_sort(olm.begin(), olm.end(), [&](int32_t x, int32_t y) {
@@ -487,6 +488,7 @@ static void buildDeviceProblem(vb_problem& P) {
           return key(x, 3) < key(y, 3);
         });
         d.orderLm = P.upload(olm);
+        olmKeep.swap(olm);
       }
       std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
         if (key(x, 1) != key(y, 1)) return key(x, 1) < key(y, 1);
@@ -506,6 +508,48 @@ static void buildDeviceProblem(vb_problem& P) {
       chunkStart.push_back((int32_t)nOwn);
       d.nChunks = (int32_t)chunkStart.size() - 1;
       d.order = P.upload(order); d.chunkStart = P.upload(chunkStart);
+      // packed tables of kernels_visual.cu (VB_VISUAL_IMPL=0 keeps the round-1 kernels)
+      d.visImpl = 1;
+      if (const char* e = getenv("VB_VISUAL_IMPL")) d.visImpl = atoi(e);
+      if (d.visImpl && (S.dataSize >= 0xffffffffll || (int64_t)g.data.size() >= 0x7fffffffll)) d.visImpl = 0;  // 32-bit offsets
+      if (d.visImpl) {
+        const int cpf = hs.cpf;
+        const bool rs = hs.type == VB_F_VISUAL_RS;
+        auto off32 = [&](int32_t var) { return (int32_t)g.off[var]; };
+        std::vector<int32_t> hdr((size_t)d.nChunks * 8), cLm(nOwn);
+        std::vector<double> cConst((size_t)nOwn * cpf), lConst((size_t)nOwn * cpf);
+        for (int32_t c = 0; c < d.nChunks; c++) {
+          const int32_t f0 = order[chunkStart[c]];
+          const int32_t* v = &hs.vars[(int64_t)f0 * nv];
+          int32_t* h = &hdr[(size_t)c * 8];
+          h[0] = off32(v[1]); h[1] = off32(v[2]); h[2] = off32(v[3]); h[3] = rs ? off32(v[4]) : 0;
+          h[4] = (int32_t)g.flags[v[3]]; h[5] = g.tdim[v[3]]; h[6] = f0; h[7] = 0;
+        }
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < nOwn; i++) {
+          const int32_t f = order[i];
+          cLm[i] = off32(hs.vars[(int64_t)f * nv]);
+          for (int j = 0; j < cpf; j++) cConst[i * cpf + j] = hs.consts[(int64_t)f * cpf + j];
+        }
+        std::vector<int32_t> lVar((size_t)nOwn * 6);
+        std::vector<uint32_t> lOut((size_t)nOwn * 6);
+        auto o32 = [](int64_t o) { return o < 0 ? 0xffffffffu : (uint32_t)o; };
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < nOwn; i++) {
+          const int32_t f = olmKeep[i];
+          const int32_t* v = &hs.vars[(int64_t)f * nv];
+          int32_t* lv = &lVar[i * 6];
+          lv[0] = off32(v[0]); lv[1] = off32(v[1]); lv[2] = off32(v[2]); lv[3] = off32(v[3]); lv[4] = rs ? off32(v[4]) : 0;
+          lv[5] = (int32_t)g.flags[v[3]];
+          for (int j = 0; j < cpf; j++) lConst[i * cpf + j] = hs.consts[(int64_t)f * cpf + j];
+          const int64_t* ho = &hOff[(int64_t)f * np];
+          uint32_t* lo = &lOut[i * 6];
+          lo[0] = o32(gOff[(int64_t)f * nv]); lo[1] = o32(ho[0]); lo[2] = o32(ho[1]); lo[3] = o32(ho[3]); lo[4] = o32(ho[6]);
+          lo[5] = rs ? o32(ho[10]) : 0xffffffffu;
+        }
+        d.pk.chunkHdr = (const int4*)P.upload(hdr); d.pk.cLm = P.upload(cLm); d.pk.cConst = P.upload(cConst);
+        d.pk.lVar = P.upload(lVar); d.pk.lConst = P.upload(lConst); d.pk.lOut = P.upload(lOut);
+      }
     }
     if (hs.type == VB_F_VISUAL) P.visualBytes += 224.0 * hs.count; // SURVEY.md §8d algorithmic bytes/obs
     if (hs.type == VB_F_VISUAL_RS) P.visualBytes += 296.0 * hs.count;

@@ -705,6 +705,7 @@ void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* 
     case VB_F_VISUAL_RS: {
       if (!st.order) throw std::runtime_error("visual store without a chunk schedule");
       if (st.nChunks == 0) break; // a shard that owns none of this store's landmarks
+      if (st.visImpl) { launchVisualGradHess(st, v, grad, hess, updateCache, dontRetry, costAcc, s); break; }
       const bool rs = st.type == VB_F_VISUAL_RS;
       const size_t smem = (size_t)2 * kVisChunk * (rs ? 44 : 36) * sizeof(double);
       // two passes: camera side per (rig, camera) chunk on DMMA, landmark side in landmark-major order

@@ -21,6 +21,16 @@ constexpr int kMaxVars = 10;
 struct LevelTask { int32_t lump, ti, tj; };
 struct SchurTask { int32_t group, ti, tj; uint32_t mask; }; // mask: member landmarks present in both row tiles
 
+// visual stores: observation tables packed in the two processing orders of kernels_visual.cu
+struct VisPack {
+  const int4* chunkHdr;    // [2 nChunks] {pose, extr, intr, vel data offsets}, {camFlags, camDim, first factor, 0}
+  const int32_t* cLm;      // [nActive] chunk order: data offset of the landmark
+  const double* cConst;    // [nActive * cpf] chunk order
+  const int32_t* lVar;     // [nActive * 6] landmark-major order: data offsets {X, pose, extr, intr, vel}, camFlags
+  const double* lConst;    // [nActive * cpf] landmark-major order
+  const uint32_t* lOut;    // [nActive * 6] {g_p, H_pp, W_pose, W_extr, W_intr, W_vel} offsets, 0xffffffff = absent
+};
+
 // device view of one factor store (SoA tables + scatter map)
 struct DevStore {
   int32_t type, nvars, cpf, npairs;
@@ -45,6 +55,8 @@ struct DevStore {
   // whose landmark this rank owns).  Unsharded: kBegin = 0, nActive = count, active = null.
   int64_t kBegin, nActive;
   const int32_t* active;
+  VisPack pk;
+  int32_t visImpl;           // 1: kernels_visual.cu (packed tables), 0: the round-1 kernels of kernels_factors.cu
 };
 
 // device view of the variables
@@ -105,6 +117,9 @@ void launchCost(const DevStore& st, const DevVars& v, int comparable, double* ac
 void launchApplyStep(const DevVars& v, const int64_t* blockVar, int64_t nB, const double* step, double* ratioAcc, cudaStream_t s);
 void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStride, const int32_t* diagSize, int64_t nB,
                    double lambda, const double* addMask, cudaStream_t s);
+// kernels_visual.cu
+void launchVisualGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
+                          double* costAcc, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
 void launchZeroOwnedPanels(const DevSolver& d, double* hess, cudaStream_t s);

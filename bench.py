@@ -116,7 +116,19 @@ def attach_rs_imu(target, session):
         return "off (%s)" % str(ex)[:120]
 
 
-def cpu_leg(s, workload, steps, warmup, thread_counts):
+def attach_preint(target, session, on):
+    """--recompute-preint of the reference (off by default, viba/common/Settings.h:54): raw IMU-0 samples for the IMU-0
+    inertial store, so that computePreIntegration runs for every factor at the top of every iteration — on both arms"""
+    if not on:
+        return "off (the reference's default; --recompute-preint turns it on, on both arms)"
+    from visual_inertial_bundle_adjustment_b200 import synth
+    d = synth.imu0_preint_source(session)
+    target.preint_set_imu(d["store"], d["time_ns"], d["gyro"], d["accel"], d["start_us"], d["end_us"], d["calib_var"], d["gyro_var"], d["accel_var"])
+    target.preint_refresh(d["store"])
+    return "computePreIntegration for %d IMU-0 inertial factors over %d raw samples inside every iteration (grad_hess phase)" % (d["start_us"].size, d["time_ns"].size)
+
+
+def cpu_leg(s, workload, steps, warmup, thread_counts, recompute_preint=False):
     """The reference's CPU path cannot be built offline (BaSpaCho/Eigen/Sophus absent: SURVEY.md F1,F3), so
     the CPU arm is the oracle port in its baseline mode — factor loops and landmark elimination on T host
     threads (OpenMP, atomic block adds, as the reference's thread pool does with locked adds) and the
@@ -127,6 +139,7 @@ def cpu_leg(s, workload, steps, warmup, thread_counts):
     t0 = time.time()
     o = Oracle(load_oracle(), s.graph)
     create_s = time.time() - t0
+    attach_preint(o, s, recompute_preint)
     rs_note = attach_rs_imu(o, s)
     runs = []
     for T in thread_counts:
@@ -162,6 +175,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU leg of the b200 arm (and with it the N=1 parity check)")
+    ap.add_argument("--recompute-preint", action="store_true", help="the reference's --recompute-preint: refresh the IMU-0 preintegration records every iteration (both arms)")
     ap.add_argument("--no-parity", action="store_true", help="N>1: skip the unsharded recomputation on rank 0")
     ap.add_argument("--reference-budget-s", type=float, default=240.0, help="reference arm: stop adding timed steps beyond this")
     a = ap.parse_args()
@@ -181,6 +195,7 @@ def main():
         t0 = time.time()
         o = Oracle(load_oracle(), s.graph)
         create_s = time.time() - t0
+        pre_note = attach_preint(o, s, a.recompute_preint)
         rs_note = attach_rs_imu(o, s)
         runs = []
         for T in dict.fromkeys([cores, min(REFERENCE_THREADS, cores)]):  # all host threads first (the arm's value), then the reference default
@@ -209,7 +224,7 @@ def main():
               "host_cores": cores, "setup_s": round(create_s, 1), "runs": runs}
         line = {"impl": "reference", "metric": METRIC, "value": head["value"], "unit": "ms/iteration", "n_gpus": a.gpus,
                 "steps": head["steps"], "warmup": head["warmup"], "ms_per_step": head["value"], "higher_is_better": False, "scaling": "strong",
-                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(a.workload, s, cfg, rs_note),
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": dict(workload_config(a.workload, s, cfg, rs_note), preint_refresh=pre_note),
                 "cpu_baseline": cb, "parity": {"cost_before": head["cost_before"], "cost_after": head["cost_after"], "step_dot_grad": head["step_dot_grad"]},
                 "e2e": {"value": head["value"], "unit": "ms/iteration", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0, "session": getattr(s, "cache_note", "")}
@@ -241,6 +256,7 @@ def main():
     lam = 1e-5
     # the reference refreshes the rolling-shutter tables from the raw IMU samples at the top of every iteration
     # (preStepCallback, Optimizer.cpp:801-805 -> InitCalibration.cpp:316-325): same here, on the device
+    pre_note = attach_preint(p, s, a.recompute_preint)
     rs_note = attach_rs_imu(p, s)
 
     def barrier():
@@ -339,7 +355,7 @@ def main():
         except Exception:
             pass
     dominant = roof_gh if gh_ms >= fac_ms else roof_fac
-    config = workload_config(a.workload, s, cfg, rs_note)
+    config = dict(workload_config(a.workload, s, cfg, rs_note), preint_refresh=pre_note)
     parity = {"cost_before": c0, "cost_after": c1, "step_dot_grad": sdg, "tolerance": PARITY_TOL}
     line = {"metric": METRIC, "value": ms_dev, "unit": "ms/iteration", "n_gpus": a.gpus, "steps": a.steps, "warmup": warmup,
             "ms_per_step": ms_dev, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -364,6 +380,7 @@ def main():
     if world > 1 and not a.no_parity:
         # real-NCCL correctness, driver side: rank 0 recomputes the same iteration unsharded on its own GPU
         p1 = capi.Problem(ctx, s.graph)
+        attach_preint(p1, s, a.recompute_preint)
         attach_rs_imu(p1, s)
         t1, u0, u1 = p1.lm_iteration_timed(lam)
         p1.close()
@@ -372,7 +389,7 @@ def main():
                        "rel_step_dot_grad": rel(sdg, t1["step_dot_grad"])})
         ok = parity["rel_cost_before"] <= PARITY_TOL and parity["rel_cost_after"] <= PARITY_TOL and parity["rel_step_dot_grad"] <= 1e-7
     if world == 1 and not a.no_cpu_baseline:
-        cb, runs, _ = cpu_leg(s, a.workload, 1, 0, [os.cpu_count() or 1])
+        cb, runs, _ = cpu_leg(s, a.workload, 1, 0, [os.cpu_count() or 1], a.recompute_preint)
         line["cpu_baseline"] = cb
         r0 = runs[0]
         parity.update({"against": "the CPU oracle port on the same session (cpu_baseline leg)", "ref_cost_before": r0["cost_before"],

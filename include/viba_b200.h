@@ -301,6 +301,26 @@ int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* r
                   const float* accel_m_s2);
 int vb_rs_refresh(vb_problem* p, int32_t store); /* store < 0: every store that has IMU samples */
 
+/* Per-iteration refresher of the preintegration records on the device (second half):
+ * computePreIntegration (lib/motion/preintegration/PreIntegration.cpp:136-275, with CompensateJac.cpp:146-249 and
+ * MotionIntegral.cpp:52-75,162-226), which the reference runs on the host for every inertial factor at the top of
+ * every LM iteration under --recompute-preint (SingleSessionAdapter::regenerateAllPreintegrationsFromImuMeasurements,
+ * viba/single_session/InertialFactors.cpp:19-70, from the preStepCallback of interfaces/ark/main_AriaKit_ViBa.cpp:95-101).
+ * vb_preint_set_imu hands the raw samples of the store's IMU and, per factor of a VB_F_INERTIAL* store, the interval
+ * [start_us, end_us] (previous / next rig timestamps) and the pool id of the IMU calibration variable whose current
+ * value is the measurement model (-1: leave that record alone); gyro_var3 / accel_var3 are
+ * ImuNoiseModelParameters::{gyroSampleVarianceRad2Sec2, accelSampleVarianceM2Sec4}.  From then on vb_optimize (and
+ * vb_lm_iteration_timed, inside its grad_hess phase) rewrites the store's records {R, dV, dP, dt, J(9x23), evalPoint}
+ * before the rolling-shutter tables, as the reference's callback does; vb_preint_refresh does it on request;
+ * vb_preint_download returns the 9x9 covariances (whose inverse is the factor's information matrix at creation,
+ * viba/problem/InertialFactor.cpp:313 - NOT refreshed, as in the reference) and omegaAtEnd of the last refresh.
+ * n_samples = 0 forgets the samples of that store.  VB_ERR_NUMERIC when an interval runs off the samples. */
+int vb_preint_set_imu(vb_problem* p, int32_t store, int64_t n_factors, const int64_t* start_us, const int64_t* end_us,
+                      const int32_t* calib_var, int64_t n_samples, const int64_t* sample_time_ns, const float* gyro_rad_s,
+                      const float* accel_m_s2, const double* gyro_var3, const double* accel_var3);
+int vb_preint_refresh(vb_problem* p, int32_t store); /* store < 0: every store that has IMU samples */
+int vb_preint_download(vb_problem* p, int32_t store, double* cov81_per_factor, double* omega_at_end3_per_factor, int64_t n_factors);
+
 /* FP64 DMMA peak probe (mma.sync m8n8k4 f64) used as the tensor roofline denominator */
 int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops);
 /* the same probe for every FP64 mma.sync shape: tflops4 = {m8n8k4, m16n8k4, m16n8k8, m16n8k16} */

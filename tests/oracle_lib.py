@@ -120,6 +120,25 @@ class Oracle:
         self._ck(self.lib.orc_rs_set_imu(self.h, int(store), mid.size, mid.ctypes.data_as(_ip), cv.ctypes.data_as(C.POINTER(C.c_int32)),
                                          int(half_length_us), t.size, t.ctypes.data_as(_ip), gy.ctypes.data_as(fp), ac.ctypes.data_as(fp)))
 
+    def preint_set_imu(self, store, time_ns, gyro, accel, start_us, end_us, calib_var, gyro_var, accel_var):
+        t = np.ascontiguousarray(time_ns, np.int64); gy = np.ascontiguousarray(gyro, np.float32); ac = np.ascontiguousarray(accel, np.float32)
+        t0 = np.ascontiguousarray(start_us, np.int64); t1 = np.ascontiguousarray(end_us, np.int64); cv = np.ascontiguousarray(calib_var, np.int32)
+        gv = np.ascontiguousarray(gyro_var, np.float64); av = np.ascontiguousarray(accel_var, np.float64)
+        fp = C.POINTER(C.c_float)
+        self.lib.orc_preint_set_imu.argtypes = [C.c_void_p, C.c_int, C.c_int64, _ip, _ip, C.POINTER(C.c_int32), C.c_int64, _ip, fp, fp, _dp, _dp]
+        self._ck(self.lib.orc_preint_set_imu(self.h, int(store), cv.size, t0.ctypes.data_as(_ip), t1.ctypes.data_as(_ip), cv.ctypes.data_as(C.POINTER(C.c_int32)),
+                                             t.size, t.ctypes.data_as(_ip), gy.ctypes.data_as(fp), ac.ctypes.data_as(fp), dptr(gv), dptr(av)))
+
+    def preint_refresh(self, store=-1):
+        self.lib.orc_preint_refresh.argtypes = [C.c_void_p, C.c_int]
+        self._ck(self.lib.orc_preint_refresh(self.h, int(store)))
+
+    def preint_download(self, store, n_factors):
+        cov, om = np.zeros((n_factors, 9, 9)), np.zeros((n_factors, 3))
+        self.lib.orc_preint_get_cov.argtypes = [C.c_void_p, C.c_int, _dp, _dp, C.c_int64]
+        self._ck(self.lib.orc_preint_get_cov(self.h, int(store), dptr(cov), dptr(om), n_factors))
+        return cov, om
+
     def rs_refresh(self, store=-1):
         self.lib.orc_rs_refresh.argtypes = [C.c_void_p, C.c_int]
         self._ck(self.lib.orc_rs_refresh(self.h, int(store)))

@@ -367,6 +367,33 @@ class Problem:
     def rs_refresh(self, store=-1):
         _ck(self.lib, self.lib.vb_rs_refresh(self.h, int(store)))
 
+    def preint_set_imu(self, store, time_ns, gyro, accel, start_us, end_us, calib_var, gyro_var, accel_var):
+        """raw samples of an inertial store's IMU + the interval and calibration variable of every factor (vb_preint_set_imu):
+        from now on optimize() recomputes the store's preintegration records at the top of every iteration"""
+        t = np.ascontiguousarray(time_ns, np.int64); gy = np.ascontiguousarray(gyro, np.float32); ac = np.ascontiguousarray(accel, np.float32)
+        t0 = np.ascontiguousarray(start_us, np.int64); t1 = np.ascontiguousarray(end_us, np.int64); cv = np.ascontiguousarray(calib_var, np.int32)
+        gv = np.ascontiguousarray(gyro_var, np.float64); av = np.ascontiguousarray(accel_var, np.float64)
+        assert gy.shape == (t.size, 3) and ac.shape == (t.size, 3) and t0.size == t1.size == cv.size and gv.size == 3 and av.size == 3
+        fp = C.POINTER(C.c_float)
+        self.lib.vb_preint_set_imu.argtypes = [C.c_void_p, C.c_int32, C.c_int64, _ip, _ip, C.POINTER(C.c_int32), C.c_int64, _ip, fp, fp, _dp, _dp]
+        _ck(self.lib, self.lib.vb_preint_set_imu(self.h, int(store), cv.size, t0.ctypes.data_as(_ip), t1.ctypes.data_as(_ip),
+                                                 cv.ctypes.data_as(C.POINTER(C.c_int32)), t.size, t.ctypes.data_as(_ip), gy.ctypes.data_as(fp),
+                                                 ac.ctypes.data_as(fp), _d(gv), _d(av)))
+
+    def preint_clear_imu(self, store):
+        self.lib.vb_preint_set_imu.argtypes = [C.c_void_p, C.c_int32, C.c_int64, _ip, _ip, C.POINTER(C.c_int32), C.c_int64, _ip,
+                                               C.POINTER(C.c_float), C.POINTER(C.c_float), _dp, _dp]
+        _ck(self.lib, self.lib.vb_preint_set_imu(self.h, int(store), 0, None, None, None, 0, None, None, None, None, None))
+
+    def preint_refresh(self, store=-1):
+        _ck(self.lib, self.lib.vb_preint_refresh(self.h, int(store)))
+
+    def preint_download(self, store, n_factors):
+        cov, om = np.zeros((n_factors, 9, 9)), np.zeros((n_factors, 3))
+        self.lib.vb_preint_download.argtypes = [C.c_void_p, C.c_int32, _dp, _dp, C.c_int64]
+        _ck(self.lib, self.lib.vb_preint_download(self.h, int(store), _d(cov), _d(om), n_factors))
+        return cov, om
+
     def upload_store_aux(self, store, aux):
         aux = np.ascontiguousarray(aux, np.float64)
         _ck(self.lib, self.lib.vb_upload_store_aux(self.h, store, _d(aux), aux.size))

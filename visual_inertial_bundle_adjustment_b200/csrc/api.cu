@@ -62,6 +62,18 @@ struct vb_problem {
     int* status = nullptr;
   };
   std::vector<RsSource> rsSources;
+  // raw samples of one IMU and the integration interval of every factor of an inertial store (vb_preint_set_imu):
+  // when present the preintegration records are recomputed on the device at the top of every LM iteration
+  struct PreintSource {
+    int store = -1;
+    int64_t nFactors = 0, nSamples = 0;
+    int64_t *timeNs = nullptr, *startUs = nullptr, *endUs = nullptr, *calibOff = nullptr;
+    uint32_t* calibFlags = nullptr;
+    float *gyro = nullptr, *accel = nullptr;
+    double *noise6 = nullptr, *scratch = nullptr, *cov = nullptr, *omegaAtEnd = nullptr;
+    int* status = nullptr;
+  };
+  std::vector<PreintSource> preintSources;
   cudaEvent_t ev[10];
 
   template <typename T>
@@ -266,6 +278,7 @@ static void planSchurGroups(const Symbolic& S, const std::vector<int32_t>& lmOrd
   auto scal = [&](const std::vector<int32_t>& v) { int64_t s = 0; for (int32_t c : v) s += S.camStart[c + 1] - S.camStart[c]; return s; };
   static const int kOrderMode = getenv("VB_GRP_ROW_ORDER") ? atoi(getenv("VB_GRP_ROW_ORDER")) : 1;
   static const int kMemberMode = getenv("VB_GRP_MEMBER_ORDER") ? atoi(getenv("VB_GRP_MEMBER_ORDER")) : 0;
+  static const int kTile = getenv("VB_GRP_TILE_STATS") ? atoi(getenv("VB_GRP_TILE_STATS")) : 64;  // != 64: plan statistics only
   std::vector<int32_t> uniOrd, slotOf, useLo, useHi, useCnt, perm;
   auto flush = [&]() {
     if (members.empty()) return;
@@ -349,7 +362,7 @@ static void planSchurGroups(const Symbolic& S, const std::vector<int32_t>& lmOrd
     sp.grpBlkPtr.push_back(sp.grpBlkPtr.back() + (int64_t)nch * (int64_t)nblk);
     // per chunk and 64-row tile: which member slots have rows in it; a tile pair only needs, chunk by
     // chunk, the landmarks present in both tiles (the others contribute exact zeros)
-    const int nt = (r + 63) / 64;
+    const int nt = (r + kTile - 1) / kTile;
     const size_t mbase = sp.grpTileMask.size();
     sp.grpTileMask.resize(mbase + (size_t)nch * nt, 0u);
     {
@@ -359,7 +372,7 @@ static void planSchurGroups(const Symbolic& S, const std::vector<int32_t>& lmOrd
         for (int c = 0; c < nch; c++) {
           uint32_t m = 0;
           for (int l = 0; l < kGrpMax; l++) if (sp.grpBlkOff[base + ((size_t)c * nblk + b) * kGrpMax + l] >= 0) m |= 1u << l;
-          for (int32_t s = 0; s < dc; s++) sp.grpTileMask[mbase + (size_t)c * nt + (q + s) / 64] |= m;
+          for (int32_t s = 0; s < dc; s++) sp.grpTileMask[mbase + (size_t)c * nt + (q + s) / kTile] |= m;
         }
         q += dc;
       }
@@ -371,7 +384,7 @@ static void planSchurGroups(const Symbolic& S, const std::vector<int32_t>& lmOrd
         for (int c = 0; c < nch; c++) {
           const uint32_t m = sp.grpTileMask[mbase + (size_t)c * nt + ti] & sp.grpTileMask[mbase + (size_t)c * nt + tj];
           any |= m;
-          if (m) sp.executedFlops += 2.0 * 64 * 64 * ((3 * __builtin_popcount(m) + 3) & ~3);
+          if (m) sp.executedFlops += 2.0 * kTile * kTile * ((3 * __builtin_popcount(m) + 3) & ~3);
         }
         if (any) sp.tasks.push_back({g, ti, tj, any});
       }
@@ -742,6 +755,31 @@ constexpr int64_t kRsTableStride = 1 + 32 * 11 + 31 * 9; // per-rig table (dev_f
 
 // RollingShutterData::compute for every rig of the stores that were given IMU samples
 // (InitCalibration.cpp:316-325, called from the preStepCallback: Optimizer.cpp:801-805)
+// computePreIntegration for every factor of the stores that have raw samples attached
+static bool launchPreint(vb_problem* p, int store) {
+  cudaStream_t s = p->ctx->stream;
+  bool any = false;
+  for (auto& src : p->preintSources) {
+    if (store >= 0 && src.store != store) continue;
+    any = true;
+    VB_CUDA(cudaMemsetAsync(src.status, 0, sizeof(int), s));
+    launchPreintRefresh(src.timeNs, src.gyro, src.accel, src.nSamples, p->dv.data, src.calibOff, src.calibFlags, src.startUs, src.endUs,
+                        src.nFactors, src.noise6, src.scratch, const_cast<double*>(p->ds[src.store].aux), src.cov, src.omegaAtEnd, src.status, s);
+    VB_CUDA(cudaGetLastError());
+  }
+  return any;
+}
+static void checkPreint(vb_problem* p, int store) {
+  cudaStream_t s = p->ctx->stream;
+  for (auto& src : p->preintSources) {
+    if (store >= 0 && src.store != store) continue;
+    int st = 0;
+    VB_CUDA(cudaMemcpyAsync(&st, src.status, sizeof(int), cudaMemcpyDeviceToHost, s));
+    VB_CUDA(cudaStreamSynchronize(s));
+    if (st == 1) throw std::domain_error("enumIntegrationSteps: not enough IMU samples around a preintegration interval");
+    if (st != 0) throw std::domain_error("computePreIntegration: empty interval");
+  }
+}
 static bool launchRsTables(vb_problem* p, int store) {
   cudaStream_t s = p->ctx->stream;
   bool any = false;
@@ -947,6 +985,7 @@ int64_t vb_num_launches_per_iteration(const vb_problem* p) { // kernels one vb_l
   int64_t lv = 0;
   for (const auto& sc : p->sched) for (size_t i = 0; i + 1 < sc.lumpOff.size(); i++) lv += sc.lumpOff[i + 1] > sc.lumpOff[i];
   n += (int64_t)p->rsSources.size(); // rolling-shutter table refresh
+  n += (int64_t)p->preintSources.size(); // preintegration refresh
   return n + 2 /*damp, step=grad*/ + 1 + 2 * lv /*factor*/ + 2 + 2 * lv /*solve*/ + 2 /*dot, negate*/ + 1 /*apply*/;
 }
 int vb_get_param_start(const vb_problem* p, int64_t* out, int64_t n) {
@@ -1316,7 +1355,9 @@ int vb_optimize_ex(vb_problem* p, const vb_settings* st, vb_optimize_hooks* hook
       }
       hooks->pre_step(hooks->pre_step_user, iterationNum);
     }
-    if (!p->rsSources.empty()) refreshRsTables(p, -1); // the reference's own preStepCallback (InitCalibration.cpp:316-325)
+    // the reference's own preStepCallback (main_AriaKit_ViBa.cpp:95-101): preintegrations first, then the RS tables
+    if (!p->preintSources.empty()) { launchPreint(p, -1); checkPreint(p, -1); }
+    if (!p->rsSources.empty()) refreshRsTables(p, -1); // InitCalibration.cpp:316-325
     const double prevCost = evalGradHess(p, p->grad, 1, 1, dontRetryFailed, true);
     const double secGradHess = since(startIt); // includes the callback, as Optimizer.cpp:801,816 measures it
     finalCost = prevCost;
@@ -1505,7 +1546,8 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   cudaEvent_t* e = p->ev;
   const int64_t n = p->S.order;
   VB_CUDA(cudaEventRecord(e[0], s));
-  launchRsTables(p, -1); // preStepCallback (Optimizer.cpp:801-805): part of the iteration, timed with grad/Hess
+  launchPreint(p, -1);   // preStepCallback (Optimizer.cpp:801-805): part of the iteration, timed with grad/Hess
+  launchRsTables(p, -1);
   evalGradHess(p, p->grad, 1, 1, 0, false); // also clears the evaluation error word
   VB_CUDA(cudaEventRecord(e[1], s));
   launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->dampMask, s);
@@ -1530,6 +1572,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, (64 + 4 * ns) * sizeof(double), cudaMemcpyDeviceToHost, s));
   checkNumeric(p);
   checkRsTables(p, -1);
+  checkPreint(p, -1);
   if (p->accHost[kAccErr] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift out of the sampled range");
   auto ms = [&](int a, int b) { float f = 0; cudaEventElapsedTime(&f, e[a], e[b]); return (double)f; };
   if (t) {
@@ -1623,6 +1666,75 @@ int vb_rs_refresh(vb_problem* p, int32_t store) {
   requireProblem(p);
   VB_CUDA(cudaSetDevice(p->ctx->device));
   refreshRsTables(p, store);
+  VB_CATCH
+}
+int vb_preint_set_imu(vb_problem* p, int32_t store, int64_t n_factors, const int64_t* start_us, const int64_t* end_us, const int32_t* calib_var,
+                      int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel, const double* gyro_var3,
+                      const double* accel_var3) {
+  VB_TRY
+  requireProblem(p);
+  if (store < 0 || store >= (int)p->ds.size()) throw std::invalid_argument("store index out of range");
+  const int type = p->g.stores[store].type;
+  if (type != VB_F_INERTIAL && type != VB_F_INERTIAL_SEC && type != VB_F_INERTIAL_SEC_SPLIT) throw std::invalid_argument("not an inertial store");
+  auto forget = [&]() { for (auto it = p->preintSources.begin(); it != p->preintSources.end();) it = it->store == store ? p->preintSources.erase(it) : it + 1; };
+  if (n_samples == 0) { forget(); return VB_OK; }
+  const auto& hs = p->g.stores[store];
+  if (!start_us || !end_us || !calib_var || !sample_time_ns || !gyro || !accel || !gyro_var3 || !accel_var3 || n_samples < 2)
+    throw std::invalid_argument("null or empty IMU data");
+  if (n_factors != hs.count || (int64_t)hs.aux.size() != n_factors * kPreintStride) throw std::invalid_argument("factor count does not match the store's records");
+  for (int64_t i = 1; i < n_samples; i++)
+    if (sample_time_ns[i] <= sample_time_ns[i - 1]) throw std::invalid_argument("IMU sample times must increase");
+  std::vector<int64_t> calibOff((size_t)n_factors, -1);
+  std::vector<uint32_t> calibFlags((size_t)n_factors, 0);
+  for (int64_t k = 0; k < n_factors; k++) {
+    const int32_t v = calib_var[k];
+    if (v < 0) continue;
+    if (v >= p->g.nv || p->g.kind[v] != VB_VAR_IMUCALIB) throw std::invalid_argument("calib_var must name IMU calibration variables");
+    if (!(start_us[k] < end_us[k])) throw std::invalid_argument("empty preintegration interval");
+    calibOff[(size_t)k] = p->g.off[v];
+    calibFlags[(size_t)k] = p->g.flags[v];
+  }
+  VB_CUDA(cudaSetDevice(p->ctx->device));
+  vb_problem::PreintSource src;
+  src.store = store; src.nFactors = n_factors; src.nSamples = n_samples;
+  src.timeNs = p->upload(std::vector<int64_t>(sample_time_ns, sample_time_ns + n_samples));
+  src.gyro = p->upload(std::vector<float>(gyro, gyro + 3 * n_samples));
+  src.accel = p->upload(std::vector<float>(accel, accel + 3 * n_samples));
+  src.startUs = p->upload(std::vector<int64_t>(start_us, start_us + n_factors));
+  src.endUs = p->upload(std::vector<int64_t>(end_us, end_us + n_factors));
+  src.calibOff = p->upload(calibOff);
+  src.calibFlags = p->upload(calibFlags);
+  src.noise6 = p->upload(std::vector<double>{gyro_var3[0], gyro_var3[1], gyro_var3[2], accel_var3[0], accel_var3[1], accel_var3[2]});
+  src.scratch = p->alloc<double>((size_t)n_factors * 9 * 38);
+  src.cov = p->alloc<double>((size_t)n_factors * 81);
+  src.omegaAtEnd = p->alloc<double>((size_t)n_factors * 3);
+  VB_CUDA(cudaMemset(src.cov, 0, (size_t)n_factors * 81 * sizeof(double)));
+  VB_CUDA(cudaMemset(src.omegaAtEnd, 0, (size_t)n_factors * 3 * sizeof(double)));
+  src.status = p->alloc<int>(1);
+  forget();
+  p->preintSources.push_back(src);
+  VB_CATCH
+}
+int vb_preint_refresh(vb_problem* p, int32_t store) {
+  VB_TRY
+  requireProblem(p);
+  VB_CUDA(cudaSetDevice(p->ctx->device));
+  if (!launchPreint(p, store) && store >= 0) throw std::invalid_argument("store has no IMU samples (vb_preint_set_imu)");
+  checkPreint(p, store);
+  VB_CATCH
+}
+int vb_preint_download(vb_problem* p, int32_t store, double* cov, double* omega_at_end, int64_t n_factors) {
+  VB_TRY
+  requireProblem(p);
+  for (auto& src : p->preintSources) {
+    if (src.store != store) continue;
+    if (n_factors != src.nFactors) throw std::invalid_argument("factor count mismatch");
+    VB_CUDA(cudaStreamSynchronize(p->ctx->stream));
+    if (cov) VB_CUDA(cudaMemcpy(cov, src.cov, (size_t)n_factors * 81 * sizeof(double), cudaMemcpyDeviceToHost));
+    if (omega_at_end) VB_CUDA(cudaMemcpy(omega_at_end, src.omegaAtEnd, (size_t)n_factors * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+    return VB_OK;
+  }
+  throw std::invalid_argument("store has no IMU samples (vb_preint_set_imu)");
   VB_CATCH
 }
 int vb_measure_dmma_peak(vb_ctx* ctx, double* tflops) {

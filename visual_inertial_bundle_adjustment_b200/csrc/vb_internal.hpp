@@ -136,6 +136,9 @@ void launchVecOp(int op, double* a, const double* b, double s, int64_t n, double
 void launchRsRefresh(const int64_t* timeNs, const float* gyro, const float* accel, int64_t nSamples, const double* varData,
                      const int64_t* calibOff, const int64_t* midUs, int64_t halfUs, int64_t nRigs, double* tables, int* status,
                      cudaStream_t st);
+void launchPreintRefresh(const int64_t* timeNs, const float* gyro, const float* accel, int64_t nSamples, const double* varData,
+                         const int64_t* calibOff, const uint32_t* calibFlags, const int64_t* startUs, const int64_t* endUs, int64_t nFactors,
+                         const double* noise6, double* scratch, double* records, double* cov, double* omegaAtEnd, int* status, cudaStream_t st);
 double measureDmmaPeak(cudaStream_t s, double* perShape = nullptr);
 
 } // namespace vb

@@ -480,16 +480,14 @@ def rs_tables(times, grav, half_ms=14):
     return tab
 
 
-def imu0_samples(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
-    """Raw IMU-0 samples for the per-iteration refreshers (the reference reads them from
-    the session's IMU CSV, lib/motion/imu_types/ImuDataFormat.h:14-23): time stamps in ns, float32 gyro
-    (rad/s) and accelerometer (m/s^2) readings at `rate_hz`, each the mean of the true body rate / specific
-    force over the sample's interval, distorted by the ground-truth calibration of its window
-    (measured = scale_matrix * (true + bias), the inverse of getCompensatedImuMeasurement, read at the true time
-    shifted by the window's gyro / accelerometer reference time offsets) plus a little white noise.  Returns dict(time_ns, gyro, accel, rig_mid_time_us, rig_calib_var,
-    half_length_us) ready for vb_rs_set_imu; rigs without rolling-shutter observations get calib var -1."""
+def _imu0_raw(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
+    """Raw IMU-0 samples of a session (the reference reads them from the session's IMU CSV,
+    lib/motion/imu_types/ImuDataFormat.h:14-23): time stamps in ns, float32 gyro (rad/s) and accelerometer (m/s^2)
+    readings at `rate_hz`, each the mean of the true body rate / specific force over the sample's interval, distorted by
+    the ground-truth calibration of its window (measured = scale_matrix * (true + bias), the inverse of
+    getCompensatedImuMeasurement, read at the true time shifted by the window's gyro / accelerometer reference time
+    offsets) plus a little white noise."""
     global _LOOP_PERIOD
-    g = session.graph
     times, win = session.times, session.win
     dt = 1.0 / rate_hz
     n = int(round((times[-1] - times[0] + 2 * margin_s) * rate_hz)) + 1
@@ -518,13 +516,39 @@ def imu0_samples(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
         rng = np.random.default_rng(seed)
         gyro = gyro + rng.normal(0, np.sqrt(2.74e-5 * rate_hz) * 1e-2, gyro.shape)
         accel = accel + rng.normal(0, np.sqrt(6.63e-3 * rate_hz) * 1e-2, accel.shape)
+    return np.round(t_end * 1e9).astype(np.int64), gyro.astype(np.float32), accel.astype(np.float32)
+
+
+def imu0_samples(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
+    """Raw IMU-0 samples for the rolling-shutter refresher.  Returns dict(time_ns, gyro, accel,
+    rig_mid_time_us, rig_calib_var, half_length_us) ready for vb_rs_set_imu; rigs without rolling-shutter observations
+    get calib var -1."""
+    g = session.graph
+    times, win = session.times, session.win
+    time_ns, gyro, accel = _imu0_raw(session, rate_hz, margin_s, seed, noise)
     rs_store = next(i for i, st in enumerate(g.stores) if st.type == G.F_VISUAL_RS)
     rigs = np.unique(g.stores[rs_store].consts[:, 6].astype(np.int64))
     calib_var = np.full(times.size, -1, np.int32)
     calib_var[rigs] = session.ids["imu"][win[rigs]]
-    return dict(store=rs_store, time_ns=np.round(t_end * 1e9).astype(np.int64), gyro=gyro.astype(np.float32),
-                accel=accel.astype(np.float32), rig_mid_time_us=np.round(times * 1e6).astype(np.int64),
+    return dict(store=rs_store, time_ns=time_ns, gyro=gyro, accel=accel, rig_mid_time_us=np.round(times * 1e6).astype(np.int64),
                 rig_calib_var=calib_var, half_length_us=13000)
+
+
+def imu0_preint_source(session, rate_hz=1000.0, margin_s=0.05, seed=7, noise=True):
+    """Raw IMU-0 samples and the integration interval of every IMU-0 inertial factor, ready for vb_preint_set_imu
+    (SingleSessionAdapter::regenerateAllPreintegrationsFromImuMeasurements, viba/single_session/InertialFactors.cpp:19-70:
+    interval = previous / next rig timestamps, measurement model = the calibration variable of the PREVIOUS rig's window,
+    noise = ImuNoiseModelParameters defaults)."""
+    g = session.graph
+    times, win = session.times, session.win
+    time_ns, gyro, accel = _imu0_raw(session, rate_hz, margin_s, seed, noise)
+    store = next(i for i, st in enumerate(g.stores) if st.type == G.F_INERTIAL)
+    n = g.stores[store].vars.shape[0]
+    assert n == times.size - 1
+    t_us = np.round(times * 1e6).astype(np.int64)
+    return dict(store=store, time_ns=time_ns, gyro=gyro, accel=accel, start_us=t_us[:-1], end_us=t_us[1:],
+                calib_var=np.ascontiguousarray(g.stores[store].vars[:, 0], np.int32),
+                gyro_var=np.full(3, 2.7415568e-05), accel_var=np.full(3, 6.6297049e-3))
 
 
 def _synth_preint(T_iw, vel_iw, prev, nxt, dt, grav, eval_point, rng):

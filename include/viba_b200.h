@@ -301,6 +301,19 @@ int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* r
                   const float* accel_m_s2);
 int vb_rs_refresh(vb_problem* p, int32_t store); /* store < 0: every store that has IMU samples */
 
+/* refinePoints pre-pass: viba/problem/PointRefinement.cpp:96-196 — a 3x3 Levenberg-Marquardt per
+ * landmark (lambda 1e-5, <= 5 iterations, reduced step on a poor one) over its visual factors with every other variable
+ * held fixed (FactorStore::varGradHess / singleCost, lib/small_thing/Factor.h:230-232,419-468).  Updates the landmark
+ * variables on the device; `out` receives the totals the reference logs (:180-193); per_point (may be null) receives
+ * {startCost, endCost, nIts (-1: failed)} for each of the vb_refine_num_points landmarks that have visual factors, in
+ * ascending variable id.  Not available on a sharded problem. */
+typedef struct vb_refine_stats {
+  double total_start_cost, total_end_cost;
+  int64_t num_points, num_failures, num_total_iterations, num_at_least_one_iteration;
+} vb_refine_stats;
+int vb_refine_points(vb_problem* p, vb_refine_stats* out, double* per_point, int64_t n_points);
+int64_t vb_refine_num_points(const vb_problem* p);
+
 /* Per-iteration refresher of the preintegration records on the device (second half):
  * computePreIntegration (lib/motion/preintegration/PreIntegration.cpp:136-275, with CompensateJac.cpp:146-249 and
  * MotionIntegral.cpp:52-75,162-226), which the reference runs on the host for every inertial factor at the top of

@@ -8,6 +8,7 @@
 #include "lm.hpp"
 #include "rs_refresh.hpp"
 #include "preint.hpp"
+#include "refine.hpp"
 
 using namespace orc;
 
@@ -256,6 +257,15 @@ int orc_rs_set_imu(OrcHandle* h, int store, int64_t n_rigs, const int64_t* rig_m
   if ((int64_t)h->eng.P.stores.at(store).aux.size() != 4 + n_rigs * kRsStride) throw std::runtime_error("rig count does not match the store's tables");
   h->rs.push_back(std::move(src));
   h->eng.preStep = [h]() { preintRefresh(h, -1); rsRefresh(h, -1); };
+  ORC_CATCH
+}
+// refinePoints (viba/problem/PointRefinement.cpp:171-196): stats6 = {totalStartCost, totalEndCost, nPoints, nFailures,
+// nTotalIterations, nAtLeastOneIt}; per_point (may be null) = {startCost, endCost, nIts} per refined landmark
+int orc_refine_points(OrcHandle* h, double* stats6, double* per_point) {
+  ORC_TRY
+  const RefineStats r = refinePoints(h->eng, per_point);
+  stats6[0] = r.totalStartCost; stats6[1] = r.totalEndCost; stats6[2] = (double)r.nPoints; stats6[3] = (double)r.nFailures;
+  stats6[4] = (double)r.nTotalIterations; stats6[5] = (double)r.nAtLeastOneIt;
   ORC_CATCH
 }
 // SingleSessionAdapter::regenerateAllPreintegrationsFromImuMeasurements (InertialFactors.cpp:45-70): same arguments as vb_preint_set_imu

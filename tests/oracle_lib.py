@@ -139,6 +139,15 @@ class Oracle:
         self._ck(self.lib.orc_preint_get_cov(self.h, int(store), dptr(cov), dptr(om), n_factors))
         return cov, om
 
+    def refine_points(self):
+        """refinePoints on the oracle: (stats dict, per-point [n, 3]); the landmark variables are updated"""
+        n = len(set(int(v) for st in self.g.stores if st.type in (G.F_VISUAL, G.F_VISUAL_RS) for v in st.vars[:, 0]))
+        pp, st = np.zeros((n, 3)), np.zeros(6)
+        self.lib.orc_refine_points.argtypes = [C.c_void_p, _dp, _dp]
+        self._ck(self.lib.orc_refine_points(self.h, dptr(st), dptr(pp)))
+        keys = ["total_start_cost", "total_end_cost", "num_points", "num_failures", "num_total_iterations", "num_at_least_one_iteration"]
+        return {k: (float(v) if i < 2 else int(v)) for i, (k, v) in enumerate(zip(keys, st))}, pp
+
     def rs_refresh(self, store=-1):
         self.lib.orc_rs_refresh.argtypes = [C.c_void_p, C.c_int]
         self._ck(self.lib.orc_rs_refresh(self.h, int(store)))

@@ -23,7 +23,7 @@ SCENARIOS = {
     "all_branches": ("tiny_rs", 40.0, dict(max_num_iterations=25, damping_min=1e-6),
                      G.BR_STEP_FACTOR | G.BR_ACCEPT_AT_FACTOR | G.BR_SUB_STEP | G.BR_ACCEPT_AT_SUB | G.BR_LATCH_NO_RETRY |
                      G.BR_REJECTED | G.BR_TROUBLED_SEQ_END | G.BR_AVERAGE | G.BR_GOOD, 1),
-    "strict_ratio": ("tiny", 40.0, dict(max_num_iterations=16, min_relative_cost_reduction=0.9, damping_min=1e-6),
+    "strict_ratio": ("tiny", 40.0, dict(max_num_iterations=16, min_relative_cost_reduction=0.9, damping_min=1e-5),
                      G.BR_STEP_FACTOR | G.BR_SUB_STEP | G.BR_REJECTED | G.BR_LATCH_NO_RETRY | G.BR_AVERAGE, 1),
     "troubled_seq": ("tiny", 40.0, dict(max_num_iterations=16, min_relative_cost_reduction=0.9, damping_min=1e-6, damping_adjust_on_fail=1e3),
                      G.BR_REJECTED | G.BR_TROUBLED_SEQ_END | G.BR_TOLERANCE_HIT, 0),

@@ -394,6 +394,20 @@ class Problem:
         _ck(self.lib, self.lib.vb_preint_download(self.h, int(store), _d(cov), _d(om), n_factors))
         return cov, om
 
+    def refine_points(self, per_point=True):
+        """refinePoints pre-pass (vb_refine_points): returns (stats dict, per-point array [n, 3] = startCost, endCost, nIts)"""
+        class _S(C.Structure):
+            _fields_ = [("total_start_cost", C.c_double), ("total_end_cost", C.c_double), ("num_points", C.c_int64),
+                        ("num_failures", C.c_int64), ("num_total_iterations", C.c_int64), ("num_at_least_one_iteration", C.c_int64)]
+        self.lib.vb_refine_num_points.restype = C.c_int64
+        self.lib.vb_refine_num_points.argtypes = [C.c_void_p]
+        n = self.lib.vb_refine_num_points(self.h)
+        pp = np.zeros((n, 3)) if per_point else None
+        st = _S()
+        self.lib.vb_refine_points.argtypes = [C.c_void_p, C.POINTER(_S), _dp, C.c_int64]
+        _ck(self.lib, self.lib.vb_refine_points(self.h, C.byref(st), _d(pp) if per_point else None, n))
+        return {k: getattr(st, k) for k, _ in _S._fields_}, pp
+
     def upload_store_aux(self, store, aux):
         aux = np.ascontiguousarray(aux, np.float64)
         _ck(self.lib, self.lib.vb_upload_store_aux(self.h, store, _d(aux), aux.size))

@@ -74,6 +74,9 @@ struct vb_problem {
     int* status = nullptr;
   };
   std::vector<PreintSource> preintSources;
+  RefineArgs refine{};            // refinePoints (vb_refine_points): landmark-major view of the visual stores
+  bool refineReady = false;
+  double* refinePerPoint = nullptr;
   cudaEvent_t ev[10];
 
   template <typename T>
@@ -435,6 +438,7 @@ static void buildDeviceProblem(vb_problem& P) {
   const bool sharded = P.nranks > 1;
   // factor stores + scatter maps
   P.ds.resize(g.stores.size());
+  std::vector<std::vector<int32_t>> refLmVar(g.stores.size());   // visual stores: landmark variable of every landmark-major slot
   for (size_t s = 0; s < g.stores.size(); s++) {
     const HostGraph::Store& hs = g.stores[s];
     DevStore& d = P.ds[s];
@@ -562,10 +566,46 @@ static void buildDeviceProblem(vb_problem& P) {
         }
         d.pk.chunkHdr = (const int4*)P.upload(hdr); d.pk.cLm = P.upload(cLm); d.pk.cConst = P.upload(cConst);
         d.pk.lVar = P.upload(lVar); d.pk.lConst = P.upload(lConst); d.pk.lOut = P.upload(lOut);
+        refLmVar[s].resize(nOwn);
+        for (int64_t i = 0; i < nOwn; i++) refLmVar[s][i] = hs.vars[(int64_t)olmKeep[i] * nv];
       }
     }
     if (hs.type == VB_F_VISUAL) P.visualBytes += 224.0 * hs.count; // SURVEY.md §8d algorithmic bytes/obs
     if (hs.type == VB_F_VISUAL_RS) P.visualBytes += 296.0 * hs.count;
+  }
+  // refinePoints: the landmarks that have visual factors, and their range in every visual store's landmark-major tables
+  if (!sharded) {
+    std::vector<int32_t> lms;
+    for (auto& v : refLmVar) lms.insert(lms.end(), v.begin(), v.end());
+    std::sort(lms.begin(), lms.end());
+    lms.erase(std::unique(lms.begin(), lms.end()), lms.end());
+    int ns = 0;
+    bool ok = true;
+    for (size_t s = 0; s < g.stores.size(); s++) {
+      if (refLmVar[s].empty()) continue;
+      if (!P.ds[s].visImpl || ns >= 4) { ok = false; break; }
+      const auto& lv = refLmVar[s];
+      std::vector<int64_t> ptr(lms.size() + 1, 0);
+      size_t i = 0;
+      for (size_t j = 0; j < lms.size(); j++) {
+        ptr[j] = (int64_t)i;
+        while (i < lv.size() && lv[i] == lms[j]) i++;
+      }
+      ptr[lms.size()] = (int64_t)i;
+      if (i != lv.size()) throw std::runtime_error("refinePoints: landmark-major table is not sorted by landmark");
+      RefineStore& rs = P.refine.st[ns++];
+      rs.lVar = P.ds[s].pk.lVar; rs.lConst = P.ds[s].pk.lConst; rs.lmPtr = P.upload(ptr);
+      rs.backup = P.alloc<double>(lv.size());
+      rs.aux = P.ds[s].aux; rs.loss_a = P.ds[s].loss_a; rs.loss_k = P.ds[s].loss_k; rs.cpf = P.ds[s].cpf;
+      rs.rs = g.stores[s].type == VB_F_VISUAL_RS;
+    }
+    if (ok && ns > 0) {
+      std::vector<int64_t> lmOff(lms.size());
+      for (size_t j = 0; j < lms.size(); j++) lmOff[j] = g.off[lms[j]];
+      P.refine.nStores = ns; P.refine.nLm = (int64_t)lms.size(); P.refine.lmOff = P.upload(lmOff);
+      P.refinePerPoint = P.alloc<double>(3 * lms.size());
+      P.refineReady = true;
+    }
   }
   P.alignedPlan = aligned;
   if (sharded && !aligned && getenv("VB_VERBOSE")) std::fprintf(stderr, "[viba_b200] shard plan not aligned with the elimination tree: subtree panels are summed too\n");
@@ -1668,6 +1708,30 @@ int vb_rs_refresh(vb_problem* p, int32_t store) {
   refreshRsTables(p, store);
   VB_CATCH
 }
+int vb_refine_points(vb_problem* p, vb_refine_stats* out, double* per_point, int64_t n_points) {
+  VB_TRY
+  requireProblem(p);
+  if (p->nranks > 1) throw std::logic_error("vb_refine_points: not available on a sharded problem");
+  if (!p->refineReady) throw std::logic_error("vb_refine_points: the problem has no visual factors in the packed layout");
+  if (per_point && n_points != p->refine.nLm) throw std::invalid_argument("per_point must hold 3 doubles per refined landmark");
+  VB_CUDA(cudaSetDevice(p->ctx->device));
+  cudaStream_t s = p->ctx->stream;
+  VB_CUDA(cudaMemsetAsync(p->acc, 0, 8 * sizeof(double), s));
+  VB_CUDA(cudaMemsetAsync(p->acc + kAccErrSlot, 0, sizeof(double), s));
+  launchRefinePoints(p->refine, p->dv, p->refinePerPoint, p->acc, s);
+  VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, 8 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  VB_CUDA(cudaMemcpyAsync(p->accHost + kAccErrSlot, p->acc + kAccErrSlot, sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (per_point) VB_CUDA(cudaMemcpyAsync(per_point, p->refinePerPoint, 3 * p->refine.nLm * sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  if (p->accHost[kAccErrSlot] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift outside the sampled window");
+  if (out) {
+    out->total_start_cost = p->accHost[0]; out->total_end_cost = p->accHost[1];
+    out->num_points = (int64_t)p->accHost[2]; out->num_failures = (int64_t)p->accHost[3];
+    out->num_total_iterations = (int64_t)p->accHost[4]; out->num_at_least_one_iteration = (int64_t)p->accHost[5];
+  }
+  VB_CATCH
+}
+int64_t vb_refine_num_points(const vb_problem* p) { return p && p->refineReady ? p->refine.nLm : 0; }
 int vb_preint_set_imu(vb_problem* p, int32_t store, int64_t n_factors, const int64_t* start_us, const int64_t* end_us, const int32_t* calib_var,
                       int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel, const double* gyro_var3,
                       const double* accel_var3) {
@@ -1705,7 +1769,6 @@ int vb_preint_set_imu(vb_problem* p, int32_t store, int64_t n_factors, const int
   src.calibOff = p->upload(calibOff);
   src.calibFlags = p->upload(calibFlags);
   src.noise6 = p->upload(std::vector<double>{gyro_var3[0], gyro_var3[1], gyro_var3[2], accel_var3[0], accel_var3[1], accel_var3[2]});
-  src.scratch = p->alloc<double>((size_t)n_factors * 9 * 38);
   src.cov = p->alloc<double>((size_t)n_factors * 81);
   src.omegaAtEnd = p->alloc<double>((size_t)n_factors * 3);
   VB_CUDA(cudaMemset(src.cov, 0, (size_t)n_factors * 81 * sizeof(double)));

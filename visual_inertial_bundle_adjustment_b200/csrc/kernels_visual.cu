@@ -409,6 +409,162 @@ __global__ void __launch_bounds__(128, RS ? 2 : 4) visualLandmarkKernel(DevStore
   }
 }
 
+// ---- refinePoints -------------------------------------------------------------------------------
+// viba/problem/PointRefinement.cpp:96-196: a 3x3 Levenberg-Marquardt per landmark (<= 5 iterations) over its visual
+// factors only — pointGradHess / pointCost (:49-86) through FactorStore::varGradHess (Factor.h:419-468) and singleCost
+// (:230-232).  One warp per landmark: lanes take the landmark's observations (landmark-major tables of VisPack, store
+// by store), cost / gradient / 3x3 Hessian are summed with shuffles, and every lane takes the same decisions.
+// backups = the per-observation costBackups of the reference (a per-store scratch array).
+VB_DEV bool solve3v(const double* H, const double* g, double* x) {   // H x = g, H SPD (lower entries used)
+  if (!(H[0] > 0)) return false;
+  const double l00 = sqrt(H[0]);
+  const double l10 = H[3] / l00, l20 = H[6] / l00;
+  const double d1 = H[4] - l10 * l10;
+  if (!(d1 > 0)) return false;
+  const double l11 = sqrt(d1), l21 = (H[7] - l20 * l10) / l11;
+  const double d2 = H[8] - l20 * l20 - l21 * l21;
+  if (!(d2 > 0)) return false;
+  const double l22 = sqrt(d2);
+  const double y0 = g[0] / l00, y1 = (g[1] - l10 * y0) / l11, y2 = (g[2] - l20 * y0 - l21 * y1) / l22;
+  x[2] = y2 / l22;
+  x[1] = (y1 - l21 * x[2]) / l11;
+  x[0] = (y0 - l10 * x[1] - l20 * x[2]) / l00;
+  return true;
+}
+VB_DEV double warpSum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// residual (+ J_X) of observation i of store S at landmark position X
+template <bool WANT_J>
+VB_DEV int refineEval(const RefineStore& S, const DevVars& V, int64_t i, const double* X, double* r, double* JX) {
+  const int32_t* lv = S.lVar + i * 6;
+  const double* cst = S.lConst + i * S.cpf;
+  double JT[12], JE[12], JC[34], JV[6];
+  if (S.rs) {
+    double cl[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) cl[j] = cst[j];
+    return rs_visual_factor<WANT_J>(X, V.data + lv[1], V.data + lv[2], V.data + lv[3], (uint32_t)lv[5], V.data + lv[4], cl, S.aux, r, JX, JT, JE, JC, JV);
+  }
+  double cl[6];
+#pragma unroll
+  for (int j = 0; j < 6; j++) cl[j] = cst[j];
+  return visual_factor<WANT_J>(X, V.data + lv[1], V.data + lv[2], V.data + lv[3], cl, r, JX, JT, JE, JC) ? 0 : 1;
+}
+
+__global__ void __launch_bounds__(128) refinePointsKernel(RefineArgs A, DevVars V, double* perPoint, double* statsAcc) {
+  constexpr double kLambda = 1e-5, kCostTolerance = 1e-8, kStepTolerance = 1e-6, kMinImprovementRatio = 0.2, kStepReduction = 0.3;
+  constexpr int kMaxNumIterations = 5;
+  const int lane = threadIdx.x & 31;
+  const int64_t j = blockIdx.x * 4ll + (threadIdx.x >> 5);
+  if (j >= A.nLm) return;
+  double* Xg = V.data + A.lmOff[j];
+  double X[3] = {Xg[0], Xg[1], Xg[2]};
+  // (cost, grad, hess) at X; update: write the backups
+  auto gradHess = [&](bool update, double* grad, double* hess) {
+    double acc[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // cost, g(3), lower H (6)
+    for (int s = 0; s < A.nStores; s++) {
+      const RefineStore& S = A.st[s];
+      for (int64_t i = S.lmPtr[j] + lane; i < S.lmPtr[j + 1]; i += 32) {
+        double r[2], JX[6];
+        const int status = refineEval<true>(S, V, i, X, r, JX);
+        if (status == 2) V.errAcc[0] = 1.0;
+        if (status != 0) { if (update) S.backup[i] = -1.0; continue; }
+        double soft, d;
+        loss_jet2(S.loss_a, S.loss_k, r[0] * r[0] + r[1] * r[1], soft, d);
+        acc[0] += 0.5 * soft;
+        if (update) S.backup[i] = 0.5 * soft;
+        int q = 4;
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+          acc[1 + a] += d * (r[0] * JX[a] + r[1] * JX[3 + a]);
+#pragma unroll
+          for (int b = 0; b <= a; b++) acc[q++] += d * (JX[a] * JX[b] + JX[3 + a] * JX[3 + b]);
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 10; q++) acc[q] = warpSum(acc[q]);
+    grad[0] = acc[1]; grad[1] = acc[2]; grad[2] = acc[3];
+    hess[0] = acc[4]; hess[3] = hess[1] = acc[5]; hess[4] = acc[6]; hess[6] = hess[2] = acc[7]; hess[7] = hess[5] = acc[8]; hess[8] = acc[9];
+    return acc[0];
+  };
+  auto pointCost = [&]() {
+    double c = 0.0;
+    for (int s = 0; s < A.nStores; s++) {
+      const RefineStore& S = A.st[s];
+      for (int64_t i = S.lmPtr[j] + lane; i < S.lmPtr[j + 1]; i += 32) {
+        const double bk = S.backup[i];
+        if (bk < 0) continue;
+        double r[2];
+        const int status = refineEval<false>(S, V, i, X, r, nullptr);
+        if (status != 0) { c += bk; continue; }
+        double soft, d;
+        loss_jet2(S.loss_a, S.loss_k, r[0] * r[0] + r[1] * r[1], soft, d);
+        c += 0.5 * soft;
+      }
+    }
+    return warpSum(c);
+  };
+  double startCost = 0, endCost = 0;
+  int nIts = 0;
+  for (int it = 0; it < kMaxNumIterations; it++) {
+    double grad[3], hess[9];
+    const double cost = gradHess(true, grad, hess);
+    __syncwarp();   // the backups written above are read by other lanes' loops only at the same indices, but keep the order explicit
+    if (it == 0) startCost = endCost = cost;
+#pragma unroll
+    for (int a = 0; a < 3; a++) hess[a * 4] = hess[a * 4] * (1.0 + kLambda) + kLambda;
+    double step[3];
+    if (!solve3v(hess, grad, step)) { nIts = -1; break; }
+#pragma unroll
+    for (int a = 0; a < 3; a++) step[a] = -step[a];
+    const double bak[3] = {X[0], X[1], X[2]};
+    bool success = false;
+#pragma unroll
+    for (int a = 0; a < 3; a++) X[a] += step[a];
+    double newCost = pointCost();
+    const double modelCostDelta = step[0] * grad[0] + step[1] * grad[1] + step[2] * grad[2];
+    if (-modelCostDelta < kCostTolerance) break;   // the step stays applied, as in the reference
+    if (newCost < cost + modelCostDelta * kMinImprovementRatio) {
+      success = true;
+    } else {
+      double nGrad[3], nHess[9];
+      gradHess(false, nGrad, nHess);
+#pragma unroll
+      for (int a = 0; a < 3; a++) X[a] = bak[a];
+      const double newDelta = step[0] * nGrad[0] + step[1] * nGrad[1] + step[2] * nGrad[2];
+      const double f = newDelta > 0 ? -modelCostDelta / (newDelta - modelCostDelta) : kStepReduction;
+#pragma unroll
+      for (int a = 0; a < 3; a++) { step[a] *= f; X[a] += step[a]; }
+      newCost = pointCost();
+      if (newCost < cost + (step[0] * grad[0] + step[1] * grad[1] + step[2] * grad[2]) * kMinImprovementRatio) success = true;
+      else {
+#pragma unroll
+        for (int a = 0; a < 3; a++) X[a] = bak[a];
+      }
+    }
+    if (success) { nIts++; endCost = newCost; }
+    else { nIts = -1; break; }
+    if (step[0] * step[0] + step[1] * step[1] + step[2] * step[2] < kStepTolerance * kStepTolerance) break;
+  }
+  if (lane == 0) {
+    Xg[0] = X[0]; Xg[1] = X[1]; Xg[2] = X[2];
+    if (perPoint) { perPoint[3 * j] = startCost; perPoint[3 * j + 1] = endCost; perPoint[3 * j + 2] = (double)nIts; }
+    red_add(statsAcc + 0, startCost); red_add(statsAcc + 1, endCost); red_add(statsAcc + 2, 1.0);
+    if (nIts < 0) red_add(statsAcc + 3, 1.0);
+    else { if (nIts > 0) { red_add(statsAcc + 4, (double)nIts); red_add(statsAcc + 5, 1.0); } }
+  }
+}
+
+void launchRefinePoints(const RefineArgs& A, const DevVars& v, double* perPoint, double* statsAcc, cudaStream_t s) {
+  if (A.nLm <= 0) return;
+  refinePointsKernel<<<(unsigned)((A.nLm + 3) / 4), 128, 0, s>>>(A, v, perPoint, statsAcc);
+  VB_CUDA(cudaGetLastError());
+}
+
 // ---- launcher ---------------------------------------------------------------------------------------------------
 void launchVisualGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
                           double* costAcc, cudaStream_t s) {

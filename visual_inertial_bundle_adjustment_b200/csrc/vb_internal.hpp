@@ -31,6 +31,17 @@ struct VisPack {
   const uint32_t* lOut;    // [nActive * 6] {g_p, H_pp, W_pose, W_extr, W_intr, W_vel} offsets, 0xffffffff = absent
 };
 
+// refinePoints (kernels_visual.cu): the visual stores seen landmark by landmark
+struct RefineStore {
+  const int32_t* lVar; const double* lConst; const int64_t* lmPtr;   // [nLm + 1] range of landmark j in the store's landmark-major tables
+  double* backup;                                                    // [nActive] costBackups of PointRefinement.cpp:49-86
+  const double* aux; double loss_a, loss_k; int32_t cpf, rs;
+};
+struct RefineArgs {
+  RefineStore st[4]; int32_t nStores; int64_t nLm;
+  const int64_t* lmOff;                                              // [nLm] data offset of landmark j
+};
+
 // device view of one factor store (SoA tables + scatter map)
 struct DevStore {
   int32_t type, nvars, cpf, npairs;
@@ -120,6 +131,7 @@ void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStri
 // kernels_visual.cu
 void launchVisualGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
                           double* costAcc, cudaStream_t s);
+void launchRefinePoints(const RefineArgs& A, const DevVars& v, double* perPoint, double* statsAcc, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
 void launchZeroOwnedPanels(const DevSolver& d, double* hess, cudaStream_t s);

@@ -400,6 +400,10 @@ CONFIGS = {
     # C4 ingredients at the C2 scale: RS camera, two IMUs and loop closures (three 100 s laps, 2 % of the
     # landmarks seen again on every later lap): 9x the Cholesky flops of c2_5min_rs through loop-closure fill
     "c4_5min_lc": dict(duration_s=300.0, n_landmarks=100000, n_obs=5_000_000, rgb=True, n_imus=2, loop_period_s=100.0, lc_frac=0.02),
+    # BASELINE configs[3]: 30 min, RGB rolling-shutter camera, two IMUs with their own gyro / accelerometer reference time
+    # offsets (2-4 ms, ImuUtils.cpp:46-47), a closed walk of three 10-minute laps with 2 % of the landmarks observed again
+    # on every later lap (loop closures >= 600 s apart): 18 000 rigs, 450 k landmarks, ~30 M SLAM observations + RGB
+    "c4_30min_gen2": dict(duration_s=1800.0, n_landmarks=450000, n_obs=30_000_000, rgb=True, n_imus=2, loop_period_s=600.0, lc_frac=0.02),
     "c3_20min": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000),
     "c3_20min_rs": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000, rgb=True, n_imus=2),
 }

@@ -404,6 +404,12 @@ CONFIGS = {
     # offsets (2-4 ms, ImuUtils.cpp:46-47), a closed walk of three 10-minute laps with 2 % of the landmarks observed again
     # on every later lap (loop closures >= 600 s apart): 18 000 rigs, 450 k landmarks, ~30 M SLAM observations + RGB
     "c4_30min_gen2": dict(duration_s=1800.0, n_landmarks=450000, n_obs=30_000_000, rgb=True, n_imus=2, loop_period_s=600.0, lc_frac=0.02),
+    # BASELINE configs[4], the factorisation-only sweep: reduced camera systems of 5 k - 50 k poses (walks at 10 Hz, ~500
+    # observations per rig, sparse landmark field); bench.py times Schur + Cholesky + solves only on these
+    "c5_5k": dict(duration_s=500.0, n_landmarks=50000, n_obs=2_500_000),
+    "c5_10k": dict(duration_s=1000.0, n_landmarks=100000, n_obs=5_000_000),
+    "c5_20k": dict(duration_s=2000.0, n_landmarks=200000, n_obs=10_000_000),
+    "c5_50k": dict(duration_s=5000.0, n_landmarks=500000, n_obs=25_000_000),
     "c3_20min": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000),
     "c3_20min_rs": dict(duration_s=1200.0, n_landmarks=300000, n_obs=20_000_000, rgb=True, n_imus=2),
 }

@@ -20,12 +20,16 @@
 // There is no host implementation of any of the numerics: without a usable sm_100 device the first
 // compute call throws.
 //
+// Settings::preStepCallback (Optimizer.h:90, called at Optimizer.cpp:803-805) runs on the calling thread at the top of
+// every iteration: the values of the IMU-calibration, camera-model and gravity variables (what the reference's callbacks
+// read: InitCalibration.cpp:316-325, InertialFactors.cpp:19-43) are pulled from the device into the user's Variables
+// first, and whatever the callback changed in the user-owned records (preintegration records, rolling-shutter tables,
+// factor constants) is pushed to the device after it.  Settings::log receives the reference's per-iteration text
+// (Optimizer.cpp:1058-1076).  Settings::solverType: only Solver_Direct runs on the device; the PCG types throw.
+//
 // Differences, all forced by the device path: (1) factor types come from the catalogue of
 // small_thing/Factor.h, not arbitrary functors; (2) store order is first-use order (the reference's is
-// libstdc++ unordered_map order over type_index); (3) Settings::numThreads is ignored,
-// Settings::preStepCallback is not offered — data the callback would refresh is re-read from the
-// user's records at every optimize()/computeCost() call, and within one optimize() through
-// vb_upload_store_aux.
+// libstdc++ unordered_map order over type_index); (3) Settings::numThreads is ignored.
 #pragma once
 
 #include <cstdint>
@@ -48,6 +52,7 @@
 namespace small_thing {
 
 using LogFunc = std::function<void(const std::string&)>;
+using PreStepCallback = std::function<void(int)>;   // Optimizer.h:24
 
 struct CostStats {   // Factor.h:25-31
   int64_t numTotal = 0, numInvalid = 0, numPrevInvalid = 0;
@@ -68,9 +73,20 @@ struct ExportedGraph {
 
 class Optimizer {
  public:
+  enum SolverType {   // Optimizer.h:30-36
+    Solver_Direct,
+    Solver_PCG_Trivial,
+    Solver_PCG_Jacobi,
+    Solver_PCG_GaussSeidel,
+    Solver_PCG_LowerPrecSolve,
+  };
+
   struct Settings {   // Optimizer.h:40-91, same defaults
     int maxNumIterations = 50;
     unsigned int numThreads = 8;   // ignored: one host thread drives one GPU context
+    SolverType solverType = Solver_Direct;   // the PCG types throw (SURVEY §8 f3 is not on the device path)
+    int pcgMaxIterations = 40;
+    double pcgDesiredResidual = 1e-10;
     double absoluteCostTolerance = 1e-8;
     double relativeCostTolerance = 1e-10;
     double variablesTolerance = 1e-5;
@@ -88,6 +104,7 @@ class Optimizer {
     bool trySubStep = true;
     double minStepFactorForGood = 0.7;
     LogFunc log = [](const std::string& str) { std::cout << str << std::endl; };
+    PreStepCallback preStepCallback;   // Optimizer.h:90
     bool verbose = false;          // per-iteration lines from the library (stderr)
     int device = 0;                // CUDA device ordinal
   };
@@ -236,13 +253,35 @@ class Optimizer {
     vs.distance_from_troubled_iteration = s.distanceFromTroubledIteration;
     vs.max_num_iterations = s.maxNumIterations;
     vs.verbose = s.verbose ? 1 : 0;
+    if (s.solverType != Solver_Direct)
+      throw std::runtime_error("small_thing: only Settings::Solver_Direct runs on the device path (PCG: SURVEY.md §8 f3)");
     vb_summary out{};
-    check(vb_optimize(problem_, &vs, &out));
-    pullValues();
-    if (s.log) {
-      s.log("optimize: cost " + std::to_string(out.initial_cost) + " -> " + std::to_string(out.final_cost) + ", " +
-            std::to_string(out.num_iterations) + " iterations");
+    struct Hook { Optimizer* self; const Settings* s; std::string err; } hk{this, &s, {}};
+    vb_optimize_hooks hooks{};
+    if (s.preStepCallback) {
+      hooks.pre_step_user = &hk;
+      hooks.sync_kinds = (1u << VB_VAR_IMUCALIB) | (1u << VB_VAR_CAM) | (1u << VB_VAR_S2);
+      hooks.host_vars = graph_->data.data();
+      hooks.pre_step = [](void* u, int32_t it) {
+        Hook& h = *static_cast<Hook*>(u);
+        if (!h.err.empty()) return;
+        try {
+          ExportedGraph& g = *h.self->graph_;
+          for (size_t i = 0; i < g.pool.size(); i++)   // the kinds the library just synchronised into host_vars
+            if (g.index[i] >= 0 && (g.kind[i] == VB_VAR_IMUCALIB || g.kind[i] == VB_VAR_CAM || g.kind[i] == VB_VAR_S2))
+              g.pool[i]->setData(g.data.data() + g.off[i]);
+          h.s->preStepCallback((int)it);
+          h.self->pushStoreData();
+        } catch (const std::exception& ex) { h.err = ex.what(); }   // no exception may cross the C ABI
+      };
     }
+    if (s.log) {
+      hooks.log_user = &hk;
+      hooks.log = [](void* u, const char* text) { static_cast<Hook*>(u)->s->log(text); };
+    }
+    check(vb_optimize_ex(problem_, &vs, &hooks, &out));
+    if (!hk.err.empty()) throw std::runtime_error("small_thing: preStepCallback threw: " + hk.err);
+    pullValues();
     return Summary{out.initial_cost, out.final_cost, out.num_troubled_seqs, out.largest_troubled_seq, out.num_iterations};
   }
 
@@ -397,6 +436,21 @@ class Optimizer {
         if (!graph_->storeAux[s].empty())
           check(vb_upload_store_aux(problem_, (int32_t)s, graph_->storeAux[s].data(), (int64_t)graph_->storeAux[s].size()));
       }
+    }
+  }
+
+  // user-owned per-store data (factor constants, preintegration records, rolling-shutter tables) -> device
+  void pushStoreData() {
+    for (size_t s = 0; s < factorStores.size(); s++) {
+      FactorStoreBase& st = *factorStores[s];
+      if (!graph_->storeConsts[s].empty()) {
+        st.fillConsts(graph_->storeConsts[s].data());
+        check(vb_upload_store_consts(problem_, (int32_t)s, graph_->storeConsts[s].data(), (int64_t)graph_->storeConsts[s].size()));
+      }
+      const size_t before = graph_->storeAux[s].size();
+      st.fillAux(graph_->storeAux[s]);
+      if (graph_->storeAux[s].size() != before) throw std::runtime_error("small_thing: a callback changed the size of a store's records");
+      if (before) check(vb_upload_store_aux(problem_, (int32_t)s, graph_->storeAux[s].data(), (int64_t)before));
     }
   }
 

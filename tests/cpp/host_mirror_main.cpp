@@ -155,6 +155,7 @@ int run(int argc, char** argv) {
   }
   int optimizeIters = -1;
   if (argc >= 5 && std::string(argv[3]) == "--optimize") optimizeIters = std::atoi(argv[4]);
+  const bool withCallback = argc >= 6 && std::string(argv[5]) == "--callback";
 
   Reader in(argv[1]);
   const int64_t nv = in.one<int64_t>();
@@ -336,6 +337,29 @@ int run(int argc, char** argv) {
     st.maxNumIterations = optimizeIters;
     st.log = nullptr;
     const double cost0 = opt.computeCost();
+    int logLines = 0, callbacks = 0;
+    double calibSeen = 0.0;
+    if (withCallback) {
+      // Settings::preStepCallback as interfaces/ark/main_AriaKit_ViBa.cpp:95-101 uses it: user code runs at the top of
+      // every iteration, reads the CURRENT calibration from its own Variable and rewrites a preintegration record
+      // (here: at iteration 2 record 0 of the first inertial store gets dV[0] += 1e-3 and the calibration of that
+      // iteration as evalPoint).  The test drives the oracle the same way and compares.
+      st.log = [&](const std::string& line) { logLines += (line.find(" cost: ") != std::string::npos); };
+      st.preStepCallback = [&](int it) {
+        callbacks++;
+        if (it != 2 || preints.empty()) return;
+        PreIntegrationData& rec = preints.front()[0];
+        rec.dV[0] += 1e-3;
+        VarBase* calib = nullptr;
+        for (auto& v : vars) if (v->kind() == VB_VAR_IMUCALIB && v->index >= 0) { calib = v.get(); break; }
+        if (calib) { calib->getData(rec.evalPoint.data()); calibSeen = rec.evalPoint[6]; }
+      };
+      Optimizer::Settings bad = st;
+      bad.solverType = Optimizer::Solver_PCG_Jacobi;
+      bool threw = false;
+      try { opt.optimize(bad); } catch (const std::runtime_error&) { threw = true; }
+      if (!threw) throw std::runtime_error("Solver_PCG_Jacobi was accepted");
+    }
     Optimizer::Summary sm = opt.optimize(st);
     const double cost1 = opt.computeCost();
     out.one<double>(sm.initialCost);
@@ -343,6 +367,7 @@ int run(int argc, char** argv) {
     out.one<double>((double)sm.numIterations);
     out.one<double>(cost0);
     out.one<double>(cost1);
+    if (withCallback) { out.one<double>((double)logLines); out.one<double>((double)callbacks); out.one<double>(calibSeen); }
     std::vector<double> buf(32);
     for (auto& v : vars) {   // the user's own Variables now hold the optimised values
       v->getData(buf.data());

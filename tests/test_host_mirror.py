@@ -206,3 +206,40 @@ def test_mirror_optimize_matches_python_path(name, iters, mirror_bin, tmp_path):
     assert abs(cost1 - final_cost) <= 1e-9 * abs(final_cost)     # and after: values went back and forth intact
     assert vals.size == ref.size and np.abs(vals - ref).max() <= 1e-6
     assert final_cost < 0.9 * init_cost
+
+
+@pytest.mark.gpu
+def test_mirror_pre_step_callback_matches_oracle(oracle, mirror_bin, tmp_path):
+    """Settings::preStepCallback through the C++ mirror: user code rewrites a preintegration record at iteration 2 from
+    the calibration it reads in its own Variable at that moment; the oracle driven the same way gives the same run"""
+    from tests.oracle_lib import Oracle
+    iters = 6
+    s = synth.make_session(**synth.CONFIGS["small_rs"])
+    g = merged(s.graph, s.ids["point"])
+    dump(g, s.ids["point"], tmp_path / "in.bin")
+    r = subprocess.run([mirror_bin, str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "--optimize", str(iters), "--callback"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = np.fromfile(tmp_path / "out.bin", np.float64)
+    init_cost, final_cost, n_it, cost0, cost1, log_lines, callbacks, calib_seen = out[:8]
+    vals = out[8:]
+    # the oracle with the same callback
+    o = Oracle(oracle, g)
+    store = next(i for i, st in enumerate(g.stores) if st.type == G.F_INERTIAL)
+    calib_var = next(v for v in range(g.nv) if g.var_kind[v] == G.VAR_IMUCALIB and g.var_index[v] >= 0)
+    seen = []
+
+    def pre(it):
+        if it != 2:
+            return
+        aux = o.store_aux(store)
+        aux[4] += 1e-3
+        cur = o.vars[g.var_off[calib_var]:g.var_off[calib_var] + 32]
+        aux[218:250] = cur
+        seen.append(cur[6])
+        o.set_store_aux(store, aux)
+    so, _ = o.optimize_ex(G.default_settings(iters), pre_step=pre)
+    assert int(n_it) == so.num_iterations and int(log_lines) == so.num_iterations and int(callbacks) >= so.num_iterations
+    assert abs(final_cost - so.final_cost) <= 1e-9 * abs(so.final_cost)
+    assert abs(calib_seen - seen[0]) <= 1e-9 * max(1e-3, abs(seen[0])) and calib_seen != g.var_data[g.var_off[calib_var] + 6]
+    assert vals.size == o.vars.size and np.abs(vals - o.vars).max() <= 1e-6

@@ -273,7 +273,7 @@ def main():
     coll = None
     if world > 1:
         from visual_inertial_bundle_adjustment_b200 import sharding
-        ctx, p, coll = sharding.make_sharded_problem(s.graph, rank, world, local_rank)
+        ctx, p, coll = sharding.make_sharded_problem(s.graph, rank, world, local_rank, native=os.environ.get("VB_PY_COLLECTIVE", "0") != "1")
     else:
         ctx = capi.Context(local_rank)
         p = capi.Problem(ctx, s.graph)
@@ -398,6 +398,7 @@ def main():
                                     "(with all their observations) and factors follow the rank whose subtree they touch",
                             "per_rank_landmarks": shard["per_rank_landmarks"],
                             "per_rank_observations": shard["per_rank_observations"],
+                            "hook": "C++ (csrc/nccl_hook.cpp: ncclAllReduce on the problem's stream)" if os.environ.get("VB_PY_COLLECTIVE", "0") != "1" else "Python (torch.distributed)",
                             "collective_bytes_per_iteration": int(coll.bytes / max(1, (warmup + 2 * a.steps + 2))),
                             "collectives_per_iteration": round(per_it, 2)}
     p.close()

@@ -227,6 +227,13 @@ class Optimizer {
     return cost;
   }
 
+  // the device problem behind this optimizer, built / refreshed from the current graph (for BaSpaCho::Solver of
+  // include/baspacho/baspacho/Solver.h: the reference's `solver` member, Optimizer.h:267)
+  vb_problem* backendProblem(int device = 0) {
+    ensureBackend(ctx_ ? device_ : device);
+    return problem_;
+  }
+
   Summary optimize() { return optimize(Settings{}); }
 
   // Optimizer.cpp:768-1106 -> vb_optimize (same control flow, device resident), then the values

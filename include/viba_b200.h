@@ -197,6 +197,19 @@ int vb_problem_destroy(vb_problem* p);
 typedef int (*vb_collective_fn)(void* user, int op, double* dev_ptr, int64_t count, void* cuda_stream);
 int vb_problem_create_sharded(vb_ctx* ctx, const vb_graph_desc* g, int rank, int nranks,
                               vb_collective_fn fn, void* user, vb_problem** out);
+/* The same with the hook implemented inside the library, in C++, over NCCL (csrc/nccl_hook.cpp): no Python and no torch on
+ * the collective path.  NCCL is bound at run time (libnccl.so.2).  Rank 0 makes the 128-byte id (vb_nccl_unique_id) and
+ * hands it to the other ranks by whatever means the host has (MPI, a file, torch.distributed in bench.py); every rank
+ * then calls vb_nccl_comm_create (collective: ncclCommInitRank) with its CUDA device current, and creates its problem
+ * with vb_problem_create_sharded_nccl.  The context must have been created on the stream the caller wants the
+ * collectives ordered on (vb_ctx_create_on_stream) or on its own stream (vb_ctx_create). */
+int vb_nccl_version(int* version);
+int vb_nccl_unique_id(char* id128);
+int vb_nccl_comm_create(int rank, int nranks, const char* id128, void** comm_out);
+int vb_nccl_comm_destroy(void* comm);
+int vb_nccl_comm_stats(void* comm, int64_t* calls, double* bytes);
+const char* vb_nccl_last_error(void);
+int vb_problem_create_sharded_nccl(vb_ctx* ctx, const vb_graph_desc* g, int rank, int nranks, void* comm, vb_problem** out);
 /* host-only: owner rank of every landmark (indexed by registration index, n = num_points) */
 int vb_shard_plan(const vb_graph_desc* g, int nranks, int32_t* landmark_owner, int64_t n);
 /* host-only: owner rank of every factor of one store (n = its count); *aligned = 1 when no landmark or

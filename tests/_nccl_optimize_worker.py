@@ -19,7 +19,8 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl")
     s = synth.make_session(**synth.CONFIGS[sys.argv[1]])
-    ctx, p, coll = sharding.make_sharded_problem(s.graph, rank, world, local)
+    native = len(sys.argv) < 5 or sys.argv[4] != "python"   # the library's C++ NCCL hook, or the Python / torch.distributed one
+    ctx, p, coll = sharding.make_sharded_problem(s.graph, rank, world, local, native=native)
     summ = p.optimize(G.default_settings(int(sys.argv[2])))
     v = p.vars
     t = torch.from_numpy(v.copy()).cuda()

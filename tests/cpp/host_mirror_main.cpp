@@ -11,6 +11,8 @@
 //   per store: int32 type, nvars | int64 count | int32 cpf | double lossA, lossK | int64 auxLen
 //              | int32 vars[count*nvars] | double consts[count*cpf] | double aux[auxLen]
 #include <small_thing/Optimizer.h>
+#include <baspacho/baspacho/Solver.h>
+#include <baspacho/baspacho/Utils.h>
 
 #include <cmath>
 #include <cstdio>
@@ -156,6 +158,7 @@ int run(int argc, char** argv) {
   int optimizeIters = -1;
   if (argc >= 5 && std::string(argv[3]) == "--optimize") optimizeIters = std::atoi(argv[4]);
   const bool withCallback = argc >= 6 && std::string(argv[5]) == "--callback";
+  const bool withFacade = argc >= 4 && std::string(argv[3]) == "--facade";
 
   Reader in(argv[1]);
   const int64_t nv = in.one<int64_t>();
@@ -332,6 +335,45 @@ int run(int argc, char** argv) {
   }
 
   Writer out(argv[2]);
+  if (withFacade) {
+    // include/baspacho/baspacho/{Solver,Accessor}.h over the mirror's device problem: the calls of the reference's direct
+    // path — order / dataSize / accessor().paramStart, paramSize, block, diagBlock / factor / solve
+    vb_problem* p = opt.backendProblem();
+    BaSpaCho::Solver solver(p);
+    const auto& acc = solver.accessor();
+    const int64_t n = solver.order(), ds = solver.dataSize();
+    double cost = 0;
+    if (vb_eval_grad_hess(p, 1, 1, 0, &cost) != VB_OK || vb_damp(p, 1e-5) != VB_OK) throw std::runtime_error(vb_last_error());
+    std::vector<double> hess((size_t)ds), grad((size_t)n), step((size_t)n), ref((size_t)n);
+    if (vb_download_hess(p, hess.data(), ds) != VB_OK || vb_download_grad(p, grad.data(), n) != VB_OK) throw std::runtime_error(vb_last_error());
+    // accessor: every registered variable's segment has its tangent size, diagonal blocks are symmetric and positive
+    int64_t checked = 0, total = 0;
+    for (auto& v : vars) {
+      if (v->index < 0) continue;
+      BASPACHO_CHECK_EQ(acc.paramSize(v->index), (int64_t)v->getTangentDim());
+      BASPACHO_CHECK_LE(acc.paramStart(v->index) + acc.paramSize(v->index), n);
+      total += acc.paramSize(v->index);
+      auto D = acc.diagBlock(hess.data(), v->index);
+      for (int64_t a = 0; a < D.rows; a++) { BASPACHO_CHECK_GT(D(a, a), 0.0); checked++; }
+    }
+    BASPACHO_CHECK_EQ(total, n);
+    step = grad;
+    std::vector<double> factored = hess;
+    solver.factor(factored.data());
+    solver.solve(factored.data(), step.data(), n, 1);
+    // the same through the plain ABI
+    if (vb_upload_hess(p, hess.data(), ds) != VB_OK || vb_upload_grad(p, grad.data(), n) != VB_OK || vb_step_from_grad(p) != VB_OK ||
+        vb_factor(p) != VB_OK || vb_solve(p, 0) != VB_OK || vb_download_step(p, ref.data(), n) != VB_OK)
+      throw std::runtime_error(vb_last_error());
+    double worst = 0, scale = 0, resid = 0;
+    for (int64_t i = 0; i < n; i++) { worst = std::max(worst, std::fabs(step[(size_t)i] - ref[(size_t)i])); scale = std::max(scale, std::fabs(ref[(size_t)i])); }
+    (void)resid;
+    bool threw = false;
+    try { solver.factorUpTo(factored.data(), 1); } catch (const std::runtime_error&) { threw = true; }
+    out.one<double>((double)n); out.one<double>((double)ds); out.one<double>((double)checked); out.one<double>(worst); out.one<double>(scale);
+    out.one<double>(threw ? 1.0 : 0.0); out.one<double>(cost);
+    return 0;
+  }
   if (optimizeIters >= 0) {
     Optimizer::Settings st;
     st.maxNumIterations = optimizeIters;

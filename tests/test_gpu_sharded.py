@@ -135,9 +135,12 @@ def test_sharded_c1_scale_matches_single():
         assert np.array_equal(o["vars"], outs[0]["vars"])
 
 
-def test_nccl_optimize_two_processes(tmp_path):
+@pytest.mark.parametrize("hook", ["native", "python"])
+def test_nccl_optimize_two_processes(tmp_path, hook):
     """A whole LM run as a real 2-process torchrun/NCCL job (needs 2 GPUs; skipped otherwise): same
-    iteration count and final cost as one GPU, final state within 1e-6, identical bits on both ranks."""
+    iteration count and final cost as one GPU, final state within 1e-6, identical bits on both ranks.
+    hook = native: the exchange steps go through the library's C++ NCCL hook (csrc/nccl_hook.cpp); python: through
+    torch.distributed."""
     import json, os, subprocess, sys, socket
     import torch
     if torch.cuda.device_count() < 2:
@@ -148,7 +151,7 @@ def test_nccl_optimize_two_processes(tmp_path):
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
                           "127.0.0.1", "--master-port", str(port), os.path.join(root, "tests", "_nccl_optimize_worker.py"),
-                          name, str(iters), str(tmp_path / "vars.npy")], capture_output=True, text=True, timeout=900, cwd=root)
+                          name, str(iters), str(tmp_path / "vars.npy"), hook], capture_output=True, text=True, timeout=900, cwd=root)
     assert out.returncode == 0, out.stderr[-3000:]
     d = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
     s = synth.make_session(**synth.CONFIGS[name])

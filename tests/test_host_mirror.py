@@ -243,3 +243,21 @@ def test_mirror_pre_step_callback_matches_oracle(oracle, mirror_bin, tmp_path):
     assert abs(final_cost - so.final_cost) <= 1e-9 * abs(so.final_cost)
     assert abs(calib_seen - seen[0]) <= 1e-9 * max(1e-3, abs(seen[0])) and calib_seen != g.var_data[g.var_off[calib_var] + 6]
     assert vals.size == o.vars.size and np.abs(vals - o.vars).max() <= 1e-6
+
+
+@pytest.mark.gpu
+def test_baspacho_facade_over_the_mirror(mirror_bin, tmp_path):
+    """include/baspacho/baspacho/{Solver,Accessor}.h: order / dataSize / accessor / factor / solve over the mirror's device
+    problem give the plain ABI's result bit for bit; the partial-factor family throws"""
+    s = synth.make_session(**synth.CONFIGS["small_rs"])
+    g = merged(s.graph, s.ids["point"])
+    dump(g, s.ids["point"], tmp_path / "in.bin")
+    r = subprocess.run([mirror_bin, str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "--facade"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    n, ds, checked, worst, scale, threw, cost = np.fromfile(tmp_path / "out.bin", np.float64)
+    ctx = capi.Context(0)
+    p = capi.Problem(ctx, g)
+    assert (int(n), int(ds)) == (p.order, p.data_size) and int(checked) == p.order
+    assert abs(cost - p.compute_grad_hess()) <= 1e-12 * abs(cost)
+    p.close(); ctx.close()
+    assert worst == 0.0 and scale > 0 and threw == 1.0

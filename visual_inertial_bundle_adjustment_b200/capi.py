@@ -183,19 +183,62 @@ class Context:
             self.h = C.c_void_p()
 
 
+def nccl_unique_id():
+    """128-byte NCCL id for vb_nccl_comm_create (rank 0 makes it, every rank needs it)"""
+    lib = load()
+    buf = C.create_string_buffer(128)
+    if lib.vb_nccl_unique_id(buf) != 0:
+        lib.vb_nccl_last_error.restype = C.c_char_p
+        raise RuntimeError("NCCL: " + lib.vb_nccl_last_error().decode())
+    return buf.raw
+
+
+class NcclComm:
+    """an NCCL communicator owned by the library's C++ hook (csrc/nccl_hook.cpp); creation is collective"""
+
+    def __init__(self, rank, nranks, id128):
+        self.lib = load()
+        self.h = C.c_void_p()
+        self.lib.vb_nccl_comm_create.argtypes = [C.c_int, C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]
+        if self.lib.vb_nccl_comm_create(rank, nranks, id128, C.byref(self.h)) != 0:
+            self.lib.vb_nccl_last_error.restype = C.c_char_p
+            raise RuntimeError("NCCL: " + self.lib.vb_nccl_last_error().decode())
+
+    @property
+    def stats(self):
+        calls, nbytes = C.c_int64(0), C.c_double(0)
+        self.lib.vb_nccl_comm_stats.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_double)]
+        self.lib.vb_nccl_comm_stats(self.h, C.byref(calls), C.byref(nbytes))
+        return calls.value, nbytes.value
+
+    calls = property(lambda s: s.stats[0])
+    bytes = property(lambda s: s.stats[1])
+
+    def close(self):
+        if self.h:
+            self.lib.vb_nccl_comm_destroy.argtypes = [C.c_void_p]
+            self.lib.vb_nccl_comm_destroy(self.h)
+            self.h = C.c_void_p()
+
+
 class Problem:
     """Thin object wrapper over vb_problem; method names follow small_thing::Optimizer
     (lib/small_thing/Optimizer.h:115-335) where one exists."""
 
-    def __init__(self, ctx, graph, rank=0, nranks=1, collective=None):
+    def __init__(self, ctx, graph, rank=0, nranks=1, collective=None, nccl_comm=None):
         """`collective(op, dev_ptr, count, stream) -> None` performs the in-place exchange of a sharded
-        problem (sharding.TorchCollective for torch.distributed/NCCL)."""
+        problem (sharding.TorchCollective for torch.distributed/NCCL); `nccl_comm` (a capi.NcclComm) selects the
+        library's own C++ NCCL hook instead: no Python on the collective path."""
         self.ctx, self.lib, self.g = ctx, ctx.lib, graph
         self.h = C.c_void_p()
         desc = graph.desc()
         self.rank, self.nranks = rank, nranks
         if nranks == 1:
             _ck(self.lib, self.lib.vb_problem_create(ctx.h, C.byref(desc), C.byref(self.h)))
+        elif nccl_comm is not None:
+            self._comm = nccl_comm
+            self.lib.vb_problem_create_sharded_nccl.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+            _ck(self.lib, self.lib.vb_problem_create_sharded_nccl(ctx.h, C.byref(desc), rank, nranks, nccl_comm.h, C.byref(self.h)))
         else:
             self._coll_error = None
 

@@ -699,7 +699,7 @@ static void buildDeviceProblem(vb_problem& P) {
     const int64_t nGrpLm = sp.nGrpLm;
     updPtr.push_back((int64_t)colOff.size()); relPtr.push_back((int64_t)rel.size());
     d.diagLOff = P.upload(diagLOff); d.diagL = P.alloc<double>(dl);
-    d.diagInv = P.alloc<double>(dl);   // the full inverse of every factored diagonal block (same offsets as diagL)
+    d.diagInv = P.alloc<double>((size_t)(S.camStart[S.nC] + 1) * 32);
     d.solveAcc = P.alloc<double>(S.camStart[S.nC] + 1); d.solveCnt = P.alloc<int>(S.nL + 1);
     VB_CUDA(cudaMemset(d.solveAcc, 0, (S.camStart[S.nC] + 1) * sizeof(double)));
     VB_CUDA(cudaMemset(d.solveCnt, 0, (S.nL + 1) * sizeof(int)));

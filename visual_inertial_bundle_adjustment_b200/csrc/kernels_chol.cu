@@ -122,11 +122,11 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
   double* out = d.diagL + d.diagLOff[L];
   for (int a = warp; a < w; a += 8)
     for (int b = lane; b < w; b += 32) out[a * w + b] = b <= a ? A[a * ld + b] : 0.0;
-  // ---- the full inverse of L (w x w, lower), for the trsm (its 32x32 diagonal blocks) and for the solves (x = Linv b
-  // instead of a 96-step substitution on the critical path of every level).  Linv^T is built in the strict upper
-  // triangle of A, which the factorisation no longer needs: U[k][i] = Linv[i][k] for k < i; its diagonal is dinvAll.
-  // (1) diagonal blocks: thread c owns column c of its 32x32 block, forward substitution on e_c in registers
+  // inverses of the 32x32 diagonal blocks of L (for the DMMA trsm): thread c owns column c
+  double* inv = d.diagInv + (int64_t)d.camStart[d.lumpFirst[L]] * 32;
   if (tid < w) {
+    // column-oriented forward substitution on e_c with the column in registers (compile-time indices
+    // only: no local memory); the updates of one step are independent FMAs, L is read by broadcast
     const int c = tid, b0 = c & ~31, nbk = min(32, w - b0), cc = c - b0;
     const double* Lb = A + b0 * ld + b0;
     double z[32];
@@ -141,46 +141,9 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
         for (int k = i + 1; k < 32; k++) if (k < nbk) z[k] = fma(-zi, Lb[k * ld + i], z[k]);
       }
     }
-    // L sits in the lower triangle, these writes go to the strict upper one: no hazard with the other columns' reads
 #pragma unroll
-    for (int i = 0; i < 32; i++) if (i < nbk && i > cc) A[c * ld + b0 + i] = z[i];   // U[c][b0 + i] = Linv[b0 + i][c]
+    for (int i = 0; i < 32; i++) if (i < nbk) inv[(int64_t)(b0 + i) * 32 + cc] = z[i];
   }
-  __syncthreads();
-  // (2) off-diagonal blocks by increasing block distance: Linv_ij = -D_i sum_{k=j}^{i-1} L_ik Linv_kj
-  {
-    __shared__ double Mb[32][33];
-    const int nbl = (w + 31) >> 5;
-    auto linvAt = [&](int r, int c) -> double { return r > c ? A[c * ld + r] : (r == c ? dinvAll[r] : 0.0); };
-    for (int dd = 1; dd < nbl; dd++)
-      for (int bi = dd; bi < nbl; bi++) {
-        const int bj = bi - dd, i0 = bi * 32, j0b = bj * 32, ni = min(32, w - i0);
-        for (int e = tid; e < 1024; e += 256) {   // M = sum_k L_ik Linv_kj
-          const int r = e >> 5, c = e & 31;
-          double sacc = 0.0;
-          if (r < ni) {
-            for (int kb = bj; kb < bi; kb++) {
-              const int k0 = kb * 32;
-              if (kb == bj) { for (int k = c; k < 32; k++) sacc = fma(A[(i0 + r) * ld + k0 + k], linvAt(k0 + k, j0b + c), sacc); }
-              else { for (int k = 0; k < 32; k++) sacc = fma(A[(i0 + r) * ld + k0 + k], A[(j0b + c) * ld + k0 + k], sacc); }
-            }
-          }
-          Mb[r][c] = sacc;
-        }
-        __syncthreads();
-        for (int e = tid; e < 1024; e += 256) {   // Linv_ij = -D_i M  (D_i lower triangular)
-          const int r = e >> 5, c = e & 31;
-          if (r < ni) {
-            double sacc = 0.0;
-            for (int k = 0; k <= r; k++) sacc = fma(linvAt(i0 + r, i0 + k), Mb[k][c], sacc);
-            A[(j0b + c) * ld + i0 + r] = -sacc;
-          }
-        }
-        __syncthreads();
-      }
-  }
-  double* inv = d.diagInv + d.diagLOff[L];
-  for (int a = warp; a < w; a += 8)
-    for (int b = lane; b < w; b += 32) inv[a * w + b] = b < a ? A[b * ld + a] : (b == a ? dinvAll[a] : 0.0);
 }
 
 // panel trsm X L^T = B by 32-column blocks: X_j <- (X_j - X_{<j} L_{j,<j}^T) Linv_jj^T, both products
@@ -201,7 +164,7 @@ __global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess,
   double* Li = Lr + (size_t)kTB * ldl;            // 32 x 36
   double* panel = hess + d.lumpOff[L];
   const double* Ld = d.diagL + d.diagLOff[L];
-  const double* inv = d.diagInv + d.diagLOff[L];   // full inverse of L, w x w
+  const double* inv = d.diagInv + (int64_t)d.camStart[d.lumpFirst[L]] * 32;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int row0 = tile * kPanelRows;
   const int nrows = min(kPanelRows, r - row0);
@@ -211,7 +174,7 @@ __global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess,
     const int c0 = jb * kTB, nb = min(kTB, w - c0);
     __syncthreads();
     loadTileAsync(Lr, ldl, kTB, c0, Ld + (int64_t)c0 * w, w, nb, c0);
-    loadTileAsync(Li, 36, kTB, 36, inv + (int64_t)c0 * w + c0, w, nb, nb);
+    loadTileAsync(Li, 36, kTB, 36, inv + (int64_t)c0 * 32, 32, nb, nb);
     cp_async_wait_all();
     __syncthreads();
     double acc[1][4][2];
@@ -422,12 +385,48 @@ __global__ void __launch_bounds__(256) schurGroupUpdateKernel(DevSolver d, doubl
 }
 
 // ---- K11 (supernode part) ---------------------------------------------------------------------------
+// Warp-level triangular solves: L (w x w, lower, row-major, odd leading dimension) and the
+// reciprocals of its diagonal in shared memory, x in shared memory.  32 columns at a time live in
+// registers (one per lane) and are eliminated with shuffles; earlier/later blocks enter as GEMVs.
+VB_DEV void warpSolveL(const double* Ls, int ld, const double* dinv, double* x, int w) {  // L y = x
+  const int lane = threadIdx.x & 31;
+  for (int b0 = 0; b0 < w; b0 += 32) {
+    const int k = b0 + lane;
+    double xk = k < w ? x[k] : 0.0;
+    if (k < w) for (int c = 0; c < b0; c++) xk = fma(-Ls[k * ld + c], x[c], xk);
+    const int nb = min(32, w - b0);
+    for (int c = 0; c < nb; c++) {
+      const double xc = __shfl_sync(0xffffffffu, xk, c) * dinv[b0 + c];
+      if (lane == c) xk = xc;
+      else if (lane > c && k < w) xk = fma(-Ls[k * ld + b0 + c], xc, xk);
+    }
+    if (k < w) x[k] = xk;
+    __syncwarp();
+  }
+}
+VB_DEV void warpSolveLt(const double* Ls, int ld, const double* dinv, double* x, int w) { // L^T y = x
+  const int lane = threadIdx.x & 31;
+  for (int b0 = ((w - 1) / 32) * 32; b0 >= 0; b0 -= 32) {
+    const int k = b0 + lane;
+    double xk = k < w ? x[k] : 0.0;
+    if (k < w) for (int c = b0 + 32; c < w; c++) xk = fma(-Ls[c * ld + k], x[c], xk);
+    const int nb = min(32, w - b0);
+    for (int c = nb - 1; c >= 0; c--) {
+      const double xc = __shfl_sync(0xffffffffu, xk, c) * dinv[b0 + c];
+      if (lane == c) xk = xc;
+      else if (lane < c) xk = fma(-Ls[(b0 + c) * ld + k], xc, xk);
+    }
+    if (k < w) x[k] = xk;
+    __syncwarp();
+  }
+}
+
 constexpr int kSolveSlice = 128; // panel rows per CTA in the solves
 
-// forward over the lumps of one level: x_L = Linv b_L ; b_below -= P x_L.
-// grid = (row slices, lumps).  Every slice CTA forms x_L redundantly (a w x w triangular GEMV with the inverse that
-// lumpPotrfKernel published: no substitution chain on the critical path) and applies its 128 panel rows; the CTA that
-// finishes last (per-lump counter) publishes x_L, which guarantees every other slice has already read b_L.
+// forward over the lumps of one level: x_L = L^-1 b_L ; b_below -= P x_L.
+// grid = (row slices, lumps).  Every slice CTA solves the small triangular system redundantly and
+// applies its 128 panel rows; the CTA that finishes last (per-lump counter) publishes x_L, which
+// guarantees every other slice has already read b_L.
 template <bool STAGE>
 __global__ void __launch_bounds__(256) solveLumpFwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps, int useAtomics) {
   extern __shared__ double sm[];
@@ -437,26 +436,22 @@ __global__ void __launch_bounds__(256) solveLumpFwdKernel(DevSolver d, const dou
   const int nSlices = max(1, (r + kSolveSlice - 1) / kSolveSlice);
   const int slice = blockIdx.x;
   if (slice >= nSlices) return;
-  double* b = sm;            // w
-  double* x = sm + w;        // w
-  double* Ps = x + w;        // [kSolveSlice x w] staged panel rows (STAGE only)
+  const int ld = w | 1;
+  double* Ls = sm;
+  double* x = sm + (size_t)w * ld;
+  double* dinv = x + w;
   double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
-  const double* Li = d.diagInv + d.diagLOff[L];
+  const double* Ld = d.diagL + d.diagLOff[L];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
   const int rBeg = slice * kSolveSlice, rEnd = min(r, rBeg + kSolveSlice);
+  double* Ps = dinv + w; // [kSolveSlice x w] staged panel rows (STAGE only)
+  loadTileAsync(Ls, ld, w, w, Ld, w, w, w);
   if (STAGE && rEnd > rBeg) loadTileAsync(Ps, w, rEnd - rBeg, w, below + (int64_t)rBeg * w, w, rEnd - rBeg, w);
-  for (int i = tid; i < w; i += 256) b[i] = vL[i];
-  __syncthreads();
-  for (int i = warp; i < w; i += 8) {   // x_i = sum_{k <= i} Linv[i][k] b[k]
-    const double* row = Li + (int64_t)i * w;
-    double s0 = 0.0;
-    for (int k = lane; k <= i; k += 32) s0 = fma(row[k], b[k], s0);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s0 += __shfl_xor_sync(0xffffffffu, s0, o);
-    if (lane == 0) x[i] = s0;
-  }
+  for (int i = tid; i < w; i += 256) { x[i] = vL[i]; dinv[i] = 1.0 / Ld[i * w + i]; }
   cp_async_wait_all();
+  __syncthreads();
+  if (warp == 0) warpSolveL(Ls, ld, dinv, x, w);
   __syncthreads();
   const int64_t q0 = d.updPtr[L];
   for (int row = rBeg + warp * 2; row < rEnd; row += 16) { // two rows per warp pass
@@ -485,8 +480,8 @@ __global__ void __launch_bounds__(256) solveLumpFwdKernel(DevSolver d, const dou
   __syncthreads();
   if (isLast) for (int i = tid; i < w; i += 256) vL[i] = x[i];
 }
-// backward: x_L = Linv^T (b_L - P^T x_below).  Slice CTAs accumulate their part of P^T x_below into a per-lump scratch
-// with fp64 reductions; the last one to arrive applies Linv^T (warps take rows of Linv, lanes its columns).
+// backward: x_L = L^-T (b_L - P^T x_below).  Slice CTAs accumulate their part of P^T x_below into a
+// per-lump scratch with fp64 reductions; the last one to arrive finishes the triangular solve.
 __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const double* hess, double* vec, const int32_t* lumps) {
   extern __shared__ double sm[];
   __shared__ int isLast;
@@ -495,16 +490,19 @@ __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const dou
   const int nSlices = max(1, (r + kSolveSlice - 1) / kSolveSlice);
   const int slice = blockIdx.x;
   if (slice >= nSlices) return;
-  double* y = sm;                    // w
-  double* part = y + w;              // 8 x w (2 x w used by the panel phase)
-  double* xb = part + 8 * w;         // kSolveSlice
-  double* Ps = xb + kSolveSlice;     // kSolveSlice x w staged panel rows
+  const int ld = w | 1;
+  double* x = sm;                    // w
+  double* dinv = x + w;              // w
+  double* part = dinv + w;           // 2 x w
+  double* xb = part + 2 * w;         // kSolveSlice
+  double* Ls = xb + kSolveSlice;     // max(w x ld, kSolveSlice x w): staged panel rows first, then L
+  double* Ps = Ls;
   double* vL = vec + d.camVec0 + d.camStart[d.lumpFirst[L]];
   double* accL = d.solveAcc + d.camStart[d.lumpFirst[L]];
-  const double* Li = d.diagInv + d.diagLOff[L];
+  const double* Ld = d.diagL + d.diagLOff[L];
   const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
   const int64_t q0 = d.updPtr[L];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x;
   const int rBeg = slice * kSolveSlice, rEnd = min(r, rBeg + kSolveSlice);
   if (rEnd > rBeg) loadTileAsync(Ps, w, rEnd - rBeg, w, below + (int64_t)rBeg * w, w, rEnd - rBeg, w);
   for (int i = tid; i < rEnd - rBeg; i += 256) xb[i] = vec[d.camVec0 + d.updGlobal[q0 + rBeg + i]];
@@ -532,36 +530,18 @@ __global__ void __launch_bounds__(256) solveLumpBwdKernel(DevSolver d, const dou
   __syncthreads();
   if (!isLast) return;
   __threadfence();
+  loadTileAsync(Ls, ld, w, w, Ld, w, w, w);
   for (int i = tid; i < w; i += 256) {
     double s;
     if (nSlices > 1) { s = __ldcg(accL + i); accL[i] = 0.0; } else s = part[i] + part[w + i];
-    y[i] = vL[i] - s;
+    x[i] = vL[i] - s;
+    dinv[i] = 1.0 / Ld[i * w + i];
   }
+  cp_async_wait_all();
   __syncthreads();
-  // x_k = sum_{i >= k} Linv[i][k] y_i : warp takes rows i, lane owns columns k = lane + 32 j
-  {
-    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    for (int i = warp; i < w; i += 8) {
-      const double* row = Li + (int64_t)i * w;
-      const double yi = y[i];
-      if (lane <= i) a0 = fma(row[lane], yi, a0);
-      if (lane + 32 <= i) a1 = fma(row[lane + 32], yi, a1);
-      if (lane + 64 <= i) a2 = fma(row[lane + 64], yi, a2);
-      if (lane + 96 <= i) a3 = fma(row[lane + 96], yi, a3);
-    }
-    double* pw = part + warp * w;
-    if (lane < w) pw[lane] = a0;
-    if (lane + 32 < w) pw[lane + 32] = a1;
-    if (lane + 64 < w) pw[lane + 64] = a2;
-    if (lane + 96 < w) pw[lane + 96] = a3;
-  }
+  if (tid < 32) warpSolveLt(Ls, ld, dinv, x, w);
   __syncthreads();
-  for (int k = tid; k < w; k += 256) {
-    double s = 0.0;
-#pragma unroll
-    for (int q = 0; q < 8; q++) s += part[q * w + k];
-    vL[k] = s;
-  }
+  for (int i = tid; i < w; i += 256) vL[i] = x[i];
 }
 
 // ---- launchers ----------------------------------------------------------------------------------------
@@ -609,7 +589,7 @@ void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, 
 }
 void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, int useAtomics, cudaStream_t s) {
   const int slices = std::max(1, (maxBelow + kSolveSlice - 1) / kSolveSlice);
-  const size_t base = 2 * (size_t)maxWidth * sizeof(double);
+  const size_t base = ((size_t)maxWidth * (maxWidth | 1) + 2 * (size_t)maxWidth) * sizeof(double);
   const size_t staged = base + (size_t)kSolveSlice * maxWidth * sizeof(double);
   // narrow levels are latency bound: stage the panel slice with cp.async behind the triangular solve;
   // wide levels are throughput bound: keep the small footprint (2 CTAs per SM)
@@ -623,7 +603,8 @@ void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, co
   VB_CUDA(cudaGetLastError());
 }
 void launchSolveLumpsBwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, cudaStream_t s) {
-  const size_t smem = ((size_t)kSolveSlice * maxWidth + 9 * (size_t)maxWidth + kSolveSlice) * sizeof(double);
+  const size_t tile = std::max((size_t)maxWidth * (maxWidth | 1), (size_t)kSolveSlice * maxWidth);
+  const size_t smem = (tile + 4 * (size_t)maxWidth + kSolveSlice) * sizeof(double);
   ensureSmem((const void*)solveLumpBwdKernel, smem);
   const int slices = std::max(1, (maxBelow + kSolveSlice - 1) / kSolveSlice);
   solveLumpBwdKernel<<<dim3(slices, nLumps), 256, smem, s>>>(d, hess, vec, lumps);

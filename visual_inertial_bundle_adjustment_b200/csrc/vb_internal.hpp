@@ -92,7 +92,7 @@ struct DevSolver {
   const int64_t* lumpRowPtr; const int32_t* lumpRowCam; const int32_t* lumpRowOff;
   const int64_t* diagLOff;  // [nL] offset of the factored diagonal block in diagL
   double* diagL;
-  double* diagInv;          // the inverse of every L (w x w, lower, row-major) at diagLOff
+  double* diagInv;          // [reduced order x 32] inverses of the 32x32 diagonal blocks of every L
   // update tables (per lump, indexed by below-row scalar q)
   const int64_t* updPtr;    // [nL+1] start of the lump's below rows in the per-row arrays
   const int64_t* updColOff; // target address of column role: lumpOff[T] + col

@@ -92,14 +92,23 @@ class ThreadCollective:
         return call
 
 
-def make_sharded_problem(graph, rank, nranks, device, group=None):
-    """(ctx, problem, collective) for one rank of a torch.distributed job."""
+def make_sharded_problem(graph, rank, nranks, device, group=None, native=True):
+    """(ctx, problem, collective) for one rank of a torch.distributed job.  native: the library's own C++ NCCL hook
+    (csrc/nccl_hook.cpp) carries the exchange steps — torch.distributed only hands the 128-byte NCCL id from rank 0 to the
+    others; native=False keeps the Python hook (TorchCollective)."""
     import torch
     torch.cuda.set_device(device)
     stream = torch.cuda.Stream(device=device)
     ctx = capi.Context(device, stream=stream.cuda_stream)
-    coll = TorchCollective(device, stream, group) if nranks > 1 else None
-    p = capi.Problem(ctx, graph, rank, nranks, coll)
+    if nranks > 1 and native:
+        import torch.distributed as dist
+        box = [capi.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0 if group is None else dist.get_global_rank(group, 0), group=group)
+        coll = capi.NcclComm(rank, nranks, box[0])
+        p = capi.Problem(ctx, graph, rank, nranks, nccl_comm=coll)
+    else:
+        coll = TorchCollective(device, stream, group) if nranks > 1 else None
+        p = capi.Problem(ctx, graph, rank, nranks, coll)
     p._stream = stream  # keep the stream alive as long as the problem
     return ctx, p, coll
 

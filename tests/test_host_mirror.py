@@ -248,7 +248,8 @@ def test_mirror_pre_step_callback_matches_oracle(oracle, mirror_bin, tmp_path):
 @pytest.mark.gpu
 def test_baspacho_facade_over_the_mirror(mirror_bin, tmp_path):
     """include/baspacho/baspacho/{Solver,Accessor}.h: order / dataSize / accessor / factor / solve over the mirror's device
-    problem give the plain ABI's result bit for bit; the partial-factor family throws"""
+    problem give the plain ABI's result (to rounding: the Schur update sums with fp64 reductions in no fixed order); the
+    partial-factor family throws"""
     s = synth.make_session(**synth.CONFIGS["small_rs"])
     g = merged(s.graph, s.ids["point"])
     dump(g, s.ids["point"], tmp_path / "in.bin")
@@ -260,4 +261,4 @@ def test_baspacho_facade_over_the_mirror(mirror_bin, tmp_path):
     assert (int(n), int(ds)) == (p.order, p.data_size) and int(checked) == p.order
     assert abs(cost - p.compute_grad_hess()) <= 1e-12 * abs(cost)
     p.close(); ctx.close()
-    assert worst == 0.0 and scale > 0 and threw == 1.0
+    assert worst <= 1e-9 * scale and scale > 0 and threw == 1.0

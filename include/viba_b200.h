@@ -131,6 +131,7 @@ typedef struct vb_iter_times { /* ms, CUDA-event timed; the split the reference 
 #define VB_BR_AVERAGE 256          /* damping x average (:1048-1051) */
 #define VB_BR_TOLERANCE_HIT 512    /* one of the three tolerances was hit (:1013-1018) */
 #define VB_BR_TROUBLED_SEQ_END 1024 /* a troubled sequence ended and was counted (:1037-1042) */
+#define VB_BR_FACTOR_FAILED 2048   /* the damped system was not positive definite in floating point: counted as a rejected step */
 typedef struct vb_iter_trace {
   double prev_cost, new_cost, damping, damping_used, model_cost_reduction, applied_step_factor;
   double ratio_reduction_to_expected, cost_reduction, grad_norm, step_norm;

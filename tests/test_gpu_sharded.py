@@ -110,9 +110,9 @@ def test_sharded_timed_iteration():
         return a, b, p.shard_info()["coll_calls"]
     for a, b, calls in sharding.run_threaded(s.graph, 2, run):
         assert abs(a - c0) <= 1e-12 * abs(c0) and abs(b - c1) <= 1e-9 * abs(c1)
-        # shared panels, camera rhs, rhs after the subtree forward pass, camera step,
+        # shared panels, camera vector after the own subtrees (forward solve fused into the factorisation), camera step,
         # landmark steps, scalars, factorisation verdict
-        assert calls == 7
+        assert calls == 6
 
 
 def test_sharded_c1_scale_matches_single():

@@ -74,6 +74,7 @@ struct vb_problem {
     int* status = nullptr;
   };
   std::vector<PreintSource> preintSources;
+  double* fwdFused = nullptr;     // the vector whose forward solve the last factorAsync carried (consumed by solveAsync)
   RefineArgs refine{};            // refinePoints (vb_refine_points): landmark-major view of the visual stores
   bool refineReady = false;
   double* refinePerPoint = nullptr;
@@ -735,6 +736,8 @@ static void buildDeviceProblem(vb_problem& P) {
         mb = std::max(mb, r); mw = std::max(mw, S.lumpWidth[L]);
         const int nt = (r + 63) / 64;
         for (int ti = 0; ti < nt; ti++) for (int tj = 0; tj <= ti; tj++) tasks.push_back({L, ti, tj});
+        // fused forward solve (kernels_chol.cu, kGemvSlice = 256 panel rows per task): skipped by the kernel without a right-hand side
+        for (int sl = 0; sl * 256 < r; sl++) tasks.push_back({L, -1, sl});
       }
       sc.maxBelow.push_back(mb); sc.maxWidth.push_back(mw);
     }
@@ -1140,21 +1143,45 @@ int vb_step_from_grad(vb_problem* p) {
   VB_CATCH
 }
 
-static void factorLevels(vb_problem* p, int which) {
+static void factorLevels(vb_problem* p, int which, double* rhs = nullptr) {
   cudaStream_t s = p->ctx->stream;
   const vb_problem::Sched& sc = p->sched[which];
   for (size_t lv = 0; lv + 1 < sc.lumpOff.size(); lv++) {
     const int nl = (int)(sc.lumpOff[lv + 1] - sc.lumpOff[lv]);
     const int nt = (int)(sc.taskOff[lv + 1] - sc.taskOff[lv]);
     if (nl == 0) continue;
-    launchLumpFactor(p->sol, p->hess, sc.lumps + sc.lumpOff[lv], nl, sc.maxBelow[lv], sc.maxWidth[lv], p->errFlag, s);
-    launchLumpUpdate(p->sol, p->hess, sc.tasks + sc.taskOff[lv], nt, sc.maxWidth[lv], nl > 1, s);
+    launchLumpFactor(p->sol, p->hess, sc.lumps + sc.lumpOff[lv], nl, sc.maxBelow[lv], sc.maxWidth[lv], p->errFlag, s, rhs);
+    launchLumpUpdate(p->sol, p->hess, sc.tasks + sc.taskOff[lv], nt, sc.maxWidth[lv], nl > 1, s, rhs);
   }
 }
-static void factorAsync(vb_problem* p, cudaEvent_t afterSchur) {
+// rhs (one GPU only): the forward half of Solver::solve on that vector is fused into the factorisation — the landmark
+// forward solve runs between the landmark Cholesky and the Schur update, every supernode's segment rides through its trsm
+// and its panel product through the update kernel — so the 2 x levels dependent kernels of a separate forward pass
+// disappear from the iteration's critical path.  solveAsync then only runs the backward half (p->fwdFused).
+static void factorAsync(vb_problem* p, cudaEvent_t afterSchur, double* rhs = nullptr) {
   cudaStream_t s = p->ctx->stream;
   const Symbolic& S = p->S;
   VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
+  static const bool kFuse = !(getenv("VB_FUSE_FWD") && atoi(getenv("VB_FUSE_FWD")) == 0);
+  if ((p->nranks > 1 && !p->alignedPlan) || !kFuse) rhs = nullptr;
+  p->fwdFused = rhs;
+  if (rhs) {
+    launchSchurPrep(p->sol, p->hess, p->errFlag, s);
+    launchSolveLandmarksFwd(p->sol, p->hess, rhs, s);
+    launchSchurUpdate(p->sol, p->hess, p->schurTasks, p->nSchurTasks, s);
+    if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
+    if (p->nranks > 1) {
+      // Sharded, tree-aligned plan.  The right-hand side is rank-partial: an own-subtree camera entry is complete on its
+      // owner and exactly zero elsewhere (no factor and no landmark of another rank touches it), a shared-top entry holds
+      // this rank's part.  After the own subtrees are factored (forward solve fused) ONE sum of the camera vector gives
+      // every rank the solved subtrees of all ranks and the complete right-hand side of the shared top.
+      factorLevels(p, 0, rhs);
+      collective(p, VB_COLL_SUM, p->hess + S.sharedOff, S.dataSize - S.sharedOff);
+      collective(p, VB_COLL_SUM, rhs + p->sol.camVec0, S.order - p->sol.camVec0);
+    }
+    factorLevels(p, 1, rhs);
+    return;
+  }
   launchSchur(p->sol, p->hess, p->schurTasks, p->nSchurTasks, p->errFlag, s);
   // sharded: every rank eliminated its own landmarks from its own partial camera system; the sum over
   // ranks is the reduced camera system (the exchange step of SURVEY.md §8e).  With the tree-aligned
@@ -1200,6 +1227,19 @@ static void solveAsync(vb_problem* p, double* vec) {
   cudaStream_t s = p->ctx->stream;
   const int64_t nCam = p->S.order - p->sol.camVec0;
   double* cam = vec + p->sol.camVec0;
+  if (p->fwdFused == vec) {   // the forward half already happened inside factorAsync
+    p->fwdFused = nullptr;
+    solveLevels(p, vec, 1, false);
+    if (p->nranks > 1) {
+      solveLevels(p, vec, 0, false);
+      launchVecOp(4, cam, p->camKeep, 0, nCam, nullptr, s);   // every camera scalar from exactly one rank
+      collective(p, VB_COLL_SUM, cam, nCam);
+    }
+    launchSolveLandmarksBwd(p->sol, p->hess, vec, s);
+    collective(p, VB_COLL_SUM, vec, p->sol.camVec0);          // owned landmark steps -> full step everywhere
+    p->partial[vec == p->step ? 0 : vec == p->gradNew ? 1 : 2] = false;
+    return;
+  }
   launchSolveLandmarksFwd(p->sol, p->hess, vec, s);
   if (p->nranks > 1) {
     collective(p, VB_COLL_SUM, cam, nCam);           // partial camera gradients - owned landmark eliminations
@@ -1406,8 +1446,28 @@ int vb_optimize_ex(vb_problem* p, const vb_settings* st, vb_optimize_hooks* hook
     launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, damping, p->dampMask, s);
     launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
     const auto startFactor = clk::now();
-    factorAsync(p, nullptr);
-    checkNumeric(p);
+    factorAsync(p, nullptr, p->step);
+    try {
+      checkNumeric(p);
+    } catch (const std::domain_error& ex) {
+      // A pivot of the damped system was not positive in floating point.  The reference's loop never aborts: a useless
+      // step is rejected and the damping raised (Optimizer.cpp:1019-1035).  Same here — the variables were not touched
+      // yet — instead of returning VB_ERR_NUMERIC mid-run.
+      p->fwdFused = nullptr;
+      if (lastTroubledIteration != iterationNum - 1) { troubledSeqStartDamping = damping; troubledSeqStart = iterationNum; }
+      say(std::string("factorisation failed (") + ex.what() + "): step rejected, damping raised");
+      damping *= st->damping_adjust_on_fail;
+      if (wantTrace && hooks->trace_len < hooks->trace_cap) {
+        vb_iter_trace& t = hooks->trace[hooks->trace_len++];
+        std::memset(&t, 0, sizeof t);
+        t.prev_cost = prevCost; t.new_cost = prevCost; t.damping = damping; t.damping_used = dampingUsed;
+        t.branch = VB_BR_REJECTED | VB_BR_FACTOR_FAILED;
+      }
+      if (damping > st->damping_max) { say("damping out of range, quadratic model failing?!"); stopReason = 2; break; }
+      lastTroubledIteration = iterationNum;
+      iterationNum++;
+      continue;
+    }
     const double secFactor = since(startFactor);
     const auto startSolve = clk::now();
     solveAsync(p, p->step);
@@ -1593,7 +1653,7 @@ int vb_lm_iteration_timed(vb_problem* p, double lambda, int apply, vb_iter_times
   launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, p->S.nB, lambda, p->dampMask, s);
   launchVecOp(0, p->step, p->grad, 0, n, nullptr, s);
   VB_CUDA(cudaEventRecord(e[2], s));
-  factorAsync(p, e[3]);
+  factorAsync(p, e[3], p->step);
   VB_CUDA(cudaEventRecord(e[4], s));
   solveAsync(p, p->step);
   VB_CUDA(cudaMemsetAsync(p->acc + kAccDot, 0, sizeof(double), s));

@@ -150,12 +150,15 @@ __global__ void __launch_bounds__(256) lumpPotrfKernel(DevSolver d, const double
 // on DMMA.  Only the 32x32 diagonal blocks are inverted (by lumpPotrfKernel).  64 panel rows per CTA,
 // one 8-row tile per warp (a warp only touches its own rows of X).
 constexpr int kTB = 32;
-__global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess, const int32_t* lumps) {
+// rhs != null: one more tile per lump carries the lump's segment of the right-hand side through the same
+// substitution (x = b^T L^-T, i.e. the forward solve y_L = L^-1 b_L of Solver::solve falls out of the factorisation)
+__global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess, const int32_t* lumps, double* rhs) {
   extern __shared__ double sm[];
   const int L = lumps[blockIdx.y];
   const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  const bool rhsTile = rhs != nullptr && blockIdx.x == gridDim.x - 1;
   const int tile = blockIdx.x;
-  if (tile * kPanelRows >= r) return;
+  if (!rhsTile && tile * kPanelRows >= r) return;
   const int nblk = (w + kTB - 1) / kTB;
   const int ld = ldFor(kTB * nblk);              // X (padded to whole 32-column blocks)
   const int ldl = ldFor(max(kTB * (nblk - 1), 8)); // L row block [32 x 32 jb]
@@ -166,9 +169,9 @@ __global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess,
   const double* Ld = d.diagL + d.diagLOff[L];
   const double* inv = d.diagInv + (int64_t)d.camStart[d.lumpFirst[L]] * 32;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int row0 = tile * kPanelRows;
-  const int nrows = min(kPanelRows, r - row0);
-  double* below = panel + (int64_t)(w + row0) * w;
+  const int row0 = rhsTile ? 0 : tile * kPanelRows;
+  const int nrows = rhsTile ? 1 : min(kPanelRows, r - row0);
+  double* below = rhsTile ? rhs + d.camVec0 + d.camStart[d.lumpFirst[L]] : panel + (int64_t)(w + row0) * w;
   loadTileAsync(X, ld, kPanelRows, ld, below, w, nrows, w);
   for (int jb = 0; jb < nblk; jb++) {
     const int c0 = jb * kTB, nb = min(kTB, w - c0);
@@ -207,11 +210,42 @@ __global__ void __launch_bounds__(256) lumpTrsmKernel(DevSolver d, double* hess,
 // One CTA per 64x64 tile pair of the lump's below-diagonal rows; 8 warps, each a 16x32 sub-tile
 // (2x4 DMMA tiles).  The scatter uses the per-lump relative-index tables built by the symbolic phase.
 constexpr int kUpdTile = 64;
-__global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hess, const LevelTask* tasks, int useAtomics) {
+constexpr int kGemvSlice = 256;   // panel rows per fused forward-solve task (must match api.cu)
+// Tasks with ti < 0 belong to the fused forward solve (rhs != null): slice tj of b_below -= P y_L, with y_L the
+// lump's solved segment that lumpTrsmKernel left in rhs.
+__global__ void __launch_bounds__(256) lumpUpdateKernel(DevSolver d, double* hess, const LevelTask* tasks, int useAtomics, double* rhs) {
   extern __shared__ double sm[];
   const LevelTask t = tasks[blockIdx.x];
   const int L = t.lump;
   const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
+  if (t.ti < 0) {
+    if (!rhs) return;
+    double* x = sm;
+    const double* vL = rhs + d.camVec0 + d.camStart[d.lumpFirst[L]];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < w; i += 256) x[i] = vL[i];
+    __syncthreads();
+    const double* below = hess + d.lumpOff[L] + (int64_t)w * w;
+    const int64_t q0 = d.updPtr[L];
+    const int rBeg = t.tj * kGemvSlice, rEnd = min(r, rBeg + kGemvSlice);
+    for (int row = rBeg + warp * 2; row < rEnd; row += 16) {   // two rows per warp pass
+      const double* P0 = below + (int64_t)row * w;
+      const bool two = row + 1 < rEnd;
+      const double* P1 = two ? P0 + w : P0;
+      double s0 = 0, s1 = 0;
+      for (int c = lane; c < w; c += 32) { const double xc = x[c]; s0 = fma(P0[c], xc, s0); s1 = fma(P1[c], xc, s1); }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) { s0 += __shfl_xor_sync(0xffffffffu, s0, o); s1 += __shfl_xor_sync(0xffffffffu, s1, o); }
+      if (lane == 0) {
+        double* out = rhs + d.camVec0 + d.updGlobal[q0 + row];
+        if (useAtomics) red_add(out, -s0); else *out -= s0;
+      } else if (lane == 1 && two) {
+        double* out = rhs + d.camVec0 + d.updGlobal[q0 + row + 1];
+        if (useAtomics) red_add(out, -s1); else *out -= s1;
+      }
+    }
+    return;
+  }
   const int ld = ldFor(w);
   double* As = sm;
   double* Bs = (t.ti == t.tj) ? sm : sm + (size_t)kUpdTile * ld;
@@ -562,29 +596,32 @@ static void ensureSmem(const void* fn, size_t bytes) {
 }
 void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s) {
   launchSchurPrep(d, hess, errFlag, s);
+  launchSchurUpdate(d, hess, tasks, nTasks, s);
+}
+void launchSchurUpdate(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, cudaStream_t s) {
   if (nTasks == 0) return;
   const size_t smem = (size_t)2 * kUpdTile * (3 * kGrpMax + 4) * sizeof(double);
   ensureSmem((const void*)schurGroupUpdateKernel, smem);
   schurGroupUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks);
   VB_CUDA(cudaGetLastError());
 }
-void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s) {
+void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s, double* rhs) {
   const size_t smemP = (size_t)((maxWidth + 7) & ~7) * ldFor(maxWidth) * sizeof(double);
   ensureSmem((const void*)lumpPotrfKernel, smemP);
   lumpPotrfKernel<<<nLumps, 256, smemP, s>>>(d, hess, lumps, errFlag);
   VB_CUDA(cudaGetLastError());
-  if (maxRows <= 0) return;
+  if (maxRows <= 0 && !rhs) return;
   const int nblk = (maxWidth + kTB - 1) / kTB;
   const size_t smemT = ((size_t)kPanelRows * ldFor(kTB * nblk) + (size_t)kTB * ldFor(std::max(kTB * (nblk - 1), 8)) + kTB * 36) * sizeof(double);
   ensureSmem((const void*)lumpTrsmKernel, smemT);
-  lumpTrsmKernel<<<dim3((maxRows + kPanelRows - 1) / kPanelRows, nLumps), 256, smemT, s>>>(d, hess, lumps);
+  lumpTrsmKernel<<<dim3((std::max(maxRows, 0) + kPanelRows - 1) / kPanelRows + (rhs ? 1 : 0), nLumps), 256, smemT, s>>>(d, hess, lumps, rhs);
   VB_CUDA(cudaGetLastError());
 }
-void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s) {
+void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s, double* rhs) {
   if (nTasks == 0) return;
   const size_t smem = (size_t)2 * kUpdTile * ldFor(maxWidth) * sizeof(double);
   ensureSmem((const void*)lumpUpdateKernel, smem);
-  lumpUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks, useAtomics);
+  lumpUpdateKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks, useAtomics, rhs);
   VB_CUDA(cudaGetLastError());
 }
 void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, int useAtomics, cudaStream_t s) {

@@ -746,6 +746,7 @@ void launchGradHess(const DevStore& st, const DevVars& v, double* grad, double* 
 
 void launchCost(const DevStore& st, const DevVars& v, int comparable, double* acc, cudaStream_t s) {
   if (st.nActive == 0) return;
+  if ((st.type == VB_F_VISUAL || st.type == VB_F_VISUAL_RS) && st.visImpl && st.pk.lVar) { launchVisualCost(st, v, comparable, acc, s); return; }
 #define COST(E) costKernel<E><<<gridFor(st.nActive, 128), 128, 0, s>>>(st, v, comparable, acc)
   switch (errSize(st.type)) {
     case 2: COST(2); break;

@@ -565,6 +565,51 @@ void launchRefinePoints(const RefineArgs& A, const DevVars& v, double* perPoint,
   VB_CUDA(cudaGetLastError());
 }
 
+// ---- cost only: computeSingleCost (Factor.h:390-417) + CostStats for the visual stores, over the packed landmark-major
+// tables (coalesced constants, one index level).  acc = {cost, numTotal, numInvalid, numPrevInvalid}
+template <bool RS>
+__global__ void __launch_bounds__(256) visualCostKernel(DevStore st, DevVars V, int comparable, double* accOut) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  double acc[4] = {0, 0, 0, 0};
+  if (i < st.nActive) {
+    const int32_t* lv = st.pk.lVar + i * 6;
+    const double* cst = st.pk.lConst + i * st.cpf;
+    const int f = st.orderLm[i];
+    const double prev = st.cache[f];
+    double cl[8], r[2];
+#pragma unroll
+    for (int j = 0; j < (RS ? 8 : 6); j++) cl[j] = cst[j];
+    int status;
+    if (RS) status = rs_visual_factor<false>(V.data + lv[0], V.data + lv[1], V.data + lv[2], V.data + lv[3], (uint32_t)lv[5], V.data + lv[4], cl, st.aux, r,
+                                             nullptr, nullptr, nullptr, nullptr, nullptr);
+    else status = visual_factor<false>(V.data + lv[0], V.data + lv[1], V.data + lv[2], V.data + lv[3], cl, r, nullptr, nullptr, nullptr, nullptr) ? 0 : 1;
+    if (status == 2) V.errAcc[0] = 1.0;
+    const bool valid = status == 0, prevInvalid = prev < 0.0;
+    acc[1] = 1.0;
+    acc[2] = valid ? 0.0 : 1.0;
+    acc[3] = prevInvalid ? 1.0 : 0.0;
+    bool has = true;
+    if (comparable) {
+      if (prevInvalid) has = false;
+      else if (!valid) { has = false; acc[0] = prev; }
+    }
+    if (has && valid) {
+      double soft, d;
+      loss_jet2(st.loss_a, st.loss_k, r[0] * r[0] + r[1] * r[1], soft, d);
+      acc[0] = 0.5 * soft;
+    }
+  }
+  blockReduceAddV<4>(acc, accOut);
+}
+
+void launchVisualCost(const DevStore& st, const DevVars& v, int comparable, double* acc, cudaStream_t s) {
+  if (st.nActive == 0) return;
+  const int grid = (int)((st.nActive + 255) / 256);
+  if (st.type == VB_F_VISUAL_RS) visualCostKernel<true><<<grid, 256, 0, s>>>(st, v, comparable, acc);
+  else visualCostKernel<false><<<grid, 256, 0, s>>>(st, v, comparable, acc);
+  VB_CUDA(cudaGetLastError());
+}
+
 // ---- launcher ---------------------------------------------------------------------------------------------------
 void launchVisualGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
                           double* costAcc, cudaStream_t s) {

@@ -131,13 +131,17 @@ void launchDamping(double* hess, const int64_t* diagOff, const int32_t* diagStri
 // kernels_visual.cu
 void launchVisualGradHess(const DevStore& st, const DevVars& v, double* grad, double* hess, int updateCache, int dontRetry,
                           double* costAcc, cudaStream_t s);
+void launchVisualCost(const DevStore& st, const DevVars& v, int comparable, double* acc, cudaStream_t s);
 void launchRefinePoints(const RefineArgs& A, const DevVars& v, double* perPoint, double* statsAcc, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
 void launchZeroOwnedPanels(const DevSolver& d, double* hess, cudaStream_t s);
 void launchSchur(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, int* errFlag, cudaStream_t s);
-void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s);
-void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s);
+// rhs (nullable): the forward solve of that vector is fused into the factorisation (its lump segments ride through the trsm,
+// the panel products through the update kernel's gemv tasks)
+void launchLumpFactor(const DevSolver& d, double* hess, const int32_t* lumps, int nLumps, int maxRows, int maxWidth, int* errFlag, cudaStream_t s, double* rhs = nullptr);
+void launchLumpUpdate(const DevSolver& d, double* hess, const LevelTask* tasks, int nTasks, int maxWidth, int useAtomics, cudaStream_t s, double* rhs = nullptr);
+void launchSchurUpdate(const DevSolver& d, double* hess, const SchurTask* tasks, int nTasks, cudaStream_t s);
 void launchSolveLandmarksFwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);
 void launchSolveLandmarksBwd(const DevSolver& d, const double* hess, double* vec, cudaStream_t s);
 void launchSolveLumpsFwd(const DevSolver& d, const double* hess, double* vec, const int32_t* lumps, int nLumps, int maxWidth, int maxBelow, int useAtomics, cudaStream_t s);

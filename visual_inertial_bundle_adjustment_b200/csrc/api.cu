@@ -508,16 +508,21 @@ static void buildDeviceProblem(vb_problem& P) {
         d.orderLm = P.upload(olm);
         olmKeep.swap(olm);
       }
+      // rolling shutter: the chunk also shares the velocity variable (argument 4) — one rig, one velocity in the
+      // reference's builder, but the ABI does not promise it, so it is part of the key
+      const bool rsStore = hs.type == VB_F_VISUAL_RS;
       std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
         if (key(x, 1) != key(y, 1)) return key(x, 1) < key(y, 1);
         if (key(x, 2) != key(y, 2)) return key(x, 2) < key(y, 2);
-        return key(x, 3) < key(y, 3);
+        if (key(x, 3) != key(y, 3)) return key(x, 3) < key(y, 3);
+        return rsStore && key(x, 4) < key(y, 4);
       });
       std::vector<int32_t> chunkStart;
       int64_t groupStart = 0;
       for (int64_t i = 0; i <= nOwn; i++) {
         const bool boundary = i == nOwn || (i > 0 && (key(order[i], 1) != key(order[i - 1], 1) ||
-                              key(order[i], 2) != key(order[i - 1], 2) || key(order[i], 3) != key(order[i - 1], 3)));
+                              key(order[i], 2) != key(order[i - 1], 2) || key(order[i], 3) != key(order[i - 1], 3) ||
+                              (rsStore && key(order[i], 4) != key(order[i - 1], 4))));
         if (boundary || i - groupStart == 128) {
           if (i > groupStart) chunkStart.push_back((int32_t)groupStart);
           groupStart = i;

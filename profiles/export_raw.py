@@ -6,7 +6,11 @@ KEYS = ['gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'la
         'sm__throughput.avg.pct_of_peak_sustained_elapsed', 'smsp__inst_executed.sum',
         'sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active',
         'sm__inst_executed_pipe_tensor_subpipe_dmma.avg.pct_of_peak_sustained_active',
-        'SM_C.TriageCompute.smsp__pipe_tensor_subpipe_dmma_cycles_active.avg', 'lts__t_sectors_op_red.sum', 'lts__t_bytes.sum']
+        'SM_C.TriageCompute.smsp__pipe_tensor_subpipe_dmma_cycles_active.avg', 'lts__t_sectors_op_red.sum', 'lts__t_bytes.sum',
+        'smsp__issue_active.avg.pct_of_peak_sustained_active', 'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum',
+        'smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_wait_per_issue_active.ratio',
+        'smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio',
+        'smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio', 'smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio']
 def main(path):
     out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))

@@ -48,9 +48,16 @@ VB_DEV void rvp_integrate(const double* interp, double dt, double* q, double* dV
 VB_DEV bool rs_estimate(const double* table, const double* grav, double tDelta, const double* velW, const double* Tbw, double* Tmid_atT) {
   const int n = (int)table[0];
   const double* smp = table + 1;
-  int lo = 0, hi = n; // first sample with dt > tDelta
-  while (lo < hi) { const int mid = (lo + hi) >> 1; if (tDelta < smp[mid * 11 + 10]) hi = mid; else lo = mid + 1; }
-  if (n <= 0 || lo == n || lo == 0) return false;
+  if (n <= 0) return false;
+  // first sample with dt > tDelta (upper_bound, as the reference searches): the samples sit on the gyro boundaries,
+  // almost uniformly spaced, so start from the proportional guess and walk — two independent loads and usually one
+  // or two checks instead of the five dependent loads of a bisection
+  const double tFirst = smp[10], tLast = smp[(n - 1) * 11 + 10];
+  int lo = tLast > tFirst ? (int)((tDelta - tFirst) / (tLast - tFirst) * (double)(n - 1)) + 1 : 0;
+  lo = lo < 0 ? 0 : (lo > n ? n : lo);
+  while (lo > 0 && tDelta < smp[(lo - 1) * 11 + 10]) lo--;
+  while (lo < n && !(tDelta < smp[lo * 11 + 10])) lo++;
+  if (lo == n || lo == 0) return false;
   const double* s = smp + (lo - 1) * 11;
   double q[4], dV[3], dP[3];
   const double dtb = tDelta - s[10];

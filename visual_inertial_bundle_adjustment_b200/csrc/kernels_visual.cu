@@ -271,7 +271,7 @@ VB_DEV int segEndOfV(uint32_t heads, int lane) {
 // Observations in landmark-major order (sorted by landmark, extrinsics, intrinsics).  lOut per observation:
 // {g_p offset, H_pp, W_pose, W_extr, W_intr, W_vel} as 32-bit offsets into grad / hess (0xffffffff = absent).
 template <bool RS>
-__global__ void __launch_bounds__(128, RS ? 2 : 4) visualLandmarkKernel(DevStore st, DevVars V, double* grad, double* hess, int dontRetry) {
+__global__ void __launch_bounds__(128, RS ? 3 : 4) visualLandmarkKernel(DevStore st, DevVars V, double* grad, double* hess, int dontRetry) {
   constexpr int CI = RS ? 17 : 15;
   constexpr int NE = 6 + CI;            // rows of [W_extr ; W_intr]: 21 / 23
   constexpr int NCOL = 2 * NE + 6;      // per-warp tile: JE, JC of residual row 0, of row 1, then w J_X (2 x 3)

@@ -39,6 +39,7 @@ struct vb_problem {
   struct Sched {
     int32_t* lumps = nullptr; LevelTask* tasks = nullptr;
     std::vector<int64_t> lumpOff, taskOff;
+    std::vector<int64_t> taskMid;   // per level: tasks [taskOff, taskMid) feed the NEXT level (urgent), [taskMid, taskOff+1) later ones
     std::vector<int32_t> maxBelow, maxWidth;
   } sched[2];
   double* dampMask = nullptr; // multi-GPU: 1 on the blocks whose diagonal gets this rank's "+ lambda"
@@ -74,6 +75,11 @@ struct vb_problem {
     int* status = nullptr;
   };
   std::vector<PreintSource> preintSources;
+  // one-level lookahead of the supernodal factorisation: potrf / trsm / urgent updates on a high-priority stream, the
+  // bulk of a level's updates (targets two or more levels up) on the context's stream underneath them
+  cudaStream_t hiStream = nullptr;
+  std::vector<cudaEvent_t> evTrsm, evLater;
+  cudaEvent_t evFork = nullptr, evJoin = nullptr;
   double* fwdFused = nullptr;     // the vector whose forward solve the last factorAsync carried (consumed by solveAsync)
   RefineArgs refine{};            // refinePoints (vb_refine_points): landmark-major view of the visual stores
   bool refineReady = false;
@@ -94,6 +100,11 @@ struct vb_problem {
     return p;
   }
   ~vb_problem() {
+    for (cudaEvent_t e : evTrsm) cudaEventDestroy(e);
+    for (cudaEvent_t e : evLater) cudaEventDestroy(e);
+    if (evFork) cudaEventDestroy(evFork);
+    if (evJoin) cudaEventDestroy(evJoin);
+    if (hiStream) cudaStreamDestroy(hiStream);
     for (void* p : allocs) cudaFree(p);
     if (accHost) cudaFreeHost(accHost);
   }
@@ -729,9 +740,13 @@ static void buildDeviceProblem(vb_problem& P) {
   for (int which = 0; which < 2; which++) {
     vb_problem::Sched& sc = P.sched[which];
     std::vector<int32_t> lumps; std::vector<LevelTask> tasks;
-    for (const auto& lv : S.levels) {
+    std::vector<LevelTask> later;
+    std::vector<char> tileUrgent;
+    for (size_t li = 0; li < S.levels.size(); li++) {
+      const auto& lv = S.levels[li];
       sc.lumpOff.push_back((int64_t)lumps.size());
       sc.taskOff.push_back((int64_t)tasks.size());
+      later.clear();
       int32_t mb = 0, mw = 0;
       for (int32_t L : lv) {
         const int32_t own = S.lumpOwner.empty() ? -1 : S.lumpOwner[L];
@@ -740,10 +755,27 @@ static void buildDeviceProblem(vb_problem& P) {
         const int r = S.lumpRows[L] - S.lumpWidth[L];
         mb = std::max(mb, r); mw = std::max(mw, S.lumpWidth[L]);
         const int nt = (r + 63) / 64;
-        for (int ti = 0; ti < nt; ti++) for (int tj = 0; tj <= ti; tj++) tasks.push_back({L, ti, tj});
-        // fused forward solve (kernels_chol.cu, kGemvSlice = 256 panel rows per task): skipped by the kernel without a right-hand side
+        // a tile task (ti, tj) writes into the supernodes that own the columns of tile tj: it is urgent when one of them
+        // is factored at the very next level (everything else is only needed one level later: lookahead)
+        tileUrgent.assign((size_t)nt, 0);
+        {
+          int32_t q = 0;
+          for (int64_t k = S.lumpRowPtr[L]; k < S.lumpRowPtr[L + 1]; k++) {
+            const int32_t c = S.lumpRowCam[k];
+            const int32_t dc = S.camStart[c + 1] - S.camStart[c];
+            if (S.lumpLevel[S.camLump[c]] <= (int32_t)li + 1)
+              for (int32_t t = q / 64; t <= (q + dc - 1) / 64; t++) tileUrgent[(size_t)t] = 1;
+            q += dc;
+          }
+        }
+        for (int ti = 0; ti < nt; ti++)
+          for (int tj = 0; tj <= ti; tj++) (tileUrgent[(size_t)tj] ? tasks : later).push_back({L, ti, tj});
+        // fused forward solve (kernels_chol.cu, kGemvSlice = 256 panel rows per task): skipped by the kernel without a
+        // right-hand side; cheap, so always with the urgent part
         for (int sl = 0; sl * 256 < r; sl++) tasks.push_back({L, -1, sl});
       }
+      sc.taskMid.push_back((int64_t)tasks.size());
+      tasks.insert(tasks.end(), later.begin(), later.end());
       sc.maxBelow.push_back(mb); sc.maxWidth.push_back(mw);
     }
     sc.lumpOff.push_back((int64_t)lumps.size());
@@ -1151,13 +1183,62 @@ int vb_step_from_grad(vb_problem* p) {
 static void factorLevels(vb_problem* p, int which, double* rhs = nullptr) {
   cudaStream_t s = p->ctx->stream;
   const vb_problem::Sched& sc = p->sched[which];
-  for (size_t lv = 0; lv + 1 < sc.lumpOff.size(); lv++) {
-    const int nl = (int)(sc.lumpOff[lv + 1] - sc.lumpOff[lv]);
-    const int nt = (int)(sc.taskOff[lv + 1] - sc.taskOff[lv]);
-    if (nl == 0) continue;
-    launchLumpFactor(p->sol, p->hess, sc.lumps + sc.lumpOff[lv], nl, sc.maxBelow[lv], sc.maxWidth[lv], p->errFlag, s, rhs);
-    launchLumpUpdate(p->sol, p->hess, sc.tasks + sc.taskOff[lv], nt, sc.maxWidth[lv], nl > 1, s, rhs);
+  const size_t nLv = sc.lumpOff.size() - 1;
+  static const bool kLookahead = !(getenv("VB_LOOKAHEAD") && atoi(getenv("VB_LOOKAHEAD")) == 0);
+  if (!kLookahead) {
+    for (size_t lv = 0; lv < nLv; lv++) {
+      const int nl = (int)(sc.lumpOff[lv + 1] - sc.lumpOff[lv]);
+      const int nt = (int)(sc.taskOff[lv + 1] - sc.taskOff[lv]);
+      if (nl == 0) continue;
+      launchLumpFactor(p->sol, p->hess, sc.lumps + sc.lumpOff[lv], nl, sc.maxBelow[lv], sc.maxWidth[lv], p->errFlag, s, rhs);
+      launchLumpUpdate(p->sol, p->hess, sc.tasks + sc.taskOff[lv], nt, sc.maxWidth[lv], nl > 1, s, rhs);
+    }
+    return;
   }
+  // One-level lookahead.  The potrf -> trsm -> urgent-update chain of level k runs on a high-priority stream; the rest of
+  // level k's update tasks (targets at level k + 2 and above) run on the context's stream underneath the chain of level
+  // k + 1, which only waits for the "later" tasks of level k - 1.  Targets may now be hit by two levels at once: always
+  // fp64 reductions.
+  if (!p->hiStream) {
+    int least = 0, greatest = 0;
+    VB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    VB_CUDA(cudaStreamCreateWithPriority(&p->hiStream, cudaStreamNonBlocking, greatest));
+    VB_CUDA(cudaEventCreateWithFlags(&p->evFork, cudaEventDisableTiming));
+    VB_CUDA(cudaEventCreateWithFlags(&p->evJoin, cudaEventDisableTiming));
+  }
+  while (p->evTrsm.size() < nLv) {
+    cudaEvent_t a, b;
+    VB_CUDA(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+    VB_CUDA(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+    p->evTrsm.push_back(a); p->evLater.push_back(b);
+  }
+  cudaStream_t h = p->hiStream;
+  VB_CUDA(cudaEventRecord(p->evFork, s));
+  VB_CUDA(cudaStreamWaitEvent(h, p->evFork, 0));
+  std::vector<long> laterLevels;   // levels whose "later" tasks were queued on s, ascending
+  size_t waited = 0;               // laterLevels[0 .. waited) have been waited for by h
+  for (size_t lv = 0; lv < nLv; lv++) {
+    const int nl = (int)(sc.lumpOff[lv + 1] - sc.lumpOff[lv]);
+    if (nl == 0) continue;
+    const int nUrgent = (int)(sc.taskMid[lv] - sc.taskOff[lv]);
+    const int nLater = (int)(sc.taskOff[lv + 1] - sc.taskMid[lv]);
+    // this level's supernodes need every update from two or more levels below: s is in order, so waiting for the most
+    // recent such batch of later tasks covers the older ones
+    size_t upTo = waited;
+    while (upTo < laterLevels.size() && laterLevels[upTo] + 2 <= (long)lv) upTo++;
+    if (upTo > waited) { VB_CUDA(cudaStreamWaitEvent(h, p->evLater[(size_t)laterLevels[upTo - 1]], 0)); waited = upTo; }
+    launchLumpFactor(p->sol, p->hess, sc.lumps + sc.lumpOff[lv], nl, sc.maxBelow[lv], sc.maxWidth[lv], p->errFlag, h, rhs);
+    if (nLater > 0) VB_CUDA(cudaEventRecord(p->evTrsm[lv], h));
+    launchLumpUpdate(p->sol, p->hess, sc.tasks + sc.taskOff[lv], nUrgent, sc.maxWidth[lv], 1, h, rhs);
+    if (nLater > 0) {
+      VB_CUDA(cudaStreamWaitEvent(s, p->evTrsm[lv], 0));
+      launchLumpUpdate(p->sol, p->hess, sc.tasks + sc.taskMid[lv], nLater, sc.maxWidth[lv], 1, s, nullptr);
+      VB_CUDA(cudaEventRecord(p->evLater[lv], s));
+      laterLevels.push_back((long)lv);
+    }
+  }
+  VB_CUDA(cudaEventRecord(p->evJoin, h));
+  VB_CUDA(cudaStreamWaitEvent(s, p->evJoin, 0));
 }
 // rhs (one GPU only): the forward half of Solver::solve on that vector is fused into the factorisation — the landmark
 // forward solve runs between the landmark Cholesky and the Schur update, every supernode's segment rides through its trsm

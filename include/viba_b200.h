@@ -315,6 +315,15 @@ int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* r
                   const float* accel_m_s2);
 int vb_rs_refresh(vb_problem* p, int32_t store); /* store < 0: every store that has IMU samples */
 
+/* Optimizer::computeJointCovariances / computeCovariances (lib/small_thing/Optimizer.cpp:503-696; used by
+ * SingleSessionProblem::computeCovariances, viba/problem/SingleSessionProblem.cpp:66-138) for ONE list of registered
+ * variables (registration indices): cov = the block of (H + damping)^-1 of those variables, row-major D x D with
+ * D = sum of their tangent dims in list order (offsets[n + 1], may be null); damping follows Settings::damping
+ * (1e-5 by default in the reference) and is raised as the reference does when the factorisation fails (*damping_used,
+ * may be null).  Linearises at the current values without touching the ResultCache; overwrites grad / hess / step. */
+int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* cov, int64_t cov_len,
+                                int64_t* offsets, double* damping_used);
+
 /* refinePoints pre-pass: viba/problem/PointRefinement.cpp:96-196 — a 3x3 Levenberg-Marquardt per
  * landmark (lambda 1e-5, <= 5 iterations, reduced step on a poor one) over its visual factors with every other variable
  * held fixed (FactorStore::varGradHess / singleCost, lib/small_thing/Factor.h:230-232,419-468).  Updates the landmark

@@ -437,6 +437,17 @@ class Problem:
         _ck(self.lib, self.lib.vb_preint_download(self.h, int(store), _d(cov), _d(om), n_factors))
         return cov, om
 
+    def joint_covariance(self, indices, damping=1e-5):
+        """Optimizer::computeJointCovariances for one list of registration indices: (cov [D, D], offsets [n + 1], damping used)"""
+        idx = np.ascontiguousarray(indices, np.int64)
+        dims = [int(self.g.var_tdim[np.flatnonzero(self.g.var_index == i)[0]]) for i in idx]
+        D = int(sum(dims))
+        cov, off, used = np.zeros((D, D)), np.zeros(idx.size + 1, np.int64), C.c_double(0)
+        self.lib.vb_compute_joint_covariance.argtypes = [C.c_void_p, C.c_double, C.c_int64, _ip, _dp, C.c_int64, _ip, C.POINTER(C.c_double)]
+        _ck(self.lib, self.lib.vb_compute_joint_covariance(self.h, damping, idx.size, idx.ctypes.data_as(_ip), _d(cov), D * D,
+                                                           off.ctypes.data_as(_ip), C.byref(used)))
+        return cov, off, used.value
+
     def refine_points(self, per_point=True):
         """refinePoints pre-pass (vb_refine_points): returns (stats dict, per-point array [n, 3] = startCost, endCost, nIts)"""
         class _S(C.Structure):

@@ -1854,6 +1854,56 @@ int vb_rs_refresh(vb_problem* p, int32_t store) {
   refreshRsTables(p, store);
   VB_CATCH
 }
+// Optimizer::computeJointCovariances (Optimizer.cpp:503-612) for one list of registered variables: linearise at the
+// current values (ResultCache untouched, :343-349), damp (:351-353), factor — with the reference's retry on a failed
+// factorisation (:516-533: damping += 1e-9, then doubled) — and read the block of H^-1 column by column: one solve per
+// tangent scalar of the listed variables (the reference restricts each solve to the trailing part of the factor;
+// here the full forward / backward passes run, one right-hand side at a time).
+int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* cov, int64_t cov_len,
+                                int64_t* offsets, double* damping_used) {
+  VB_TRY
+  requireProblem(p);
+  if (p->nranks > 1) throw std::logic_error("vb_compute_joint_covariance: not available on a sharded problem");
+  if (n <= 0 || !indices || !cov) throw std::invalid_argument("null or empty index list");
+  const Symbolic& S = p->S;
+  std::vector<int64_t> start((size_t)n), size((size_t)n), off((size_t)n + 1, 0);
+  for (int64_t i = 0; i < n; i++) {
+    if (indices[i] < 0 || indices[i] >= S.nB) throw std::invalid_argument("taking index from an unregistered variable?");
+    for (int64_t j = 0; j < i; j++) if (indices[j] == indices[i]) throw std::invalid_argument("duplicated indices");
+    start[(size_t)i] = S.vecStart[S.pos[indices[i]]];
+    size[(size_t)i] = S.bsize[indices[i]];
+    off[(size_t)i + 1] = off[(size_t)i] + size[(size_t)i];
+  }
+  const int64_t D = off[(size_t)n];
+  if (cov_len != D * D) throw std::invalid_argument("cov must hold (sum of tangent dims)^2 doubles");
+  if (offsets) for (int64_t i = 0; i <= n; i++) offsets[i] = off[(size_t)i];
+  cudaStream_t s = p->ctx->stream;
+  while (true) {
+    evalGradHess(p, p->grad, 1, 0, 0, true);
+    if (damping > 0) launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, S.nB, damping, p->dampMask, s);
+    factorAsync(p, nullptr);
+    bool ok = true;
+    try { checkNumeric(p); } catch (const std::domain_error&) { ok = false; }
+    if (ok) break;
+    if (damping < 1e-9) damping += 1e-9; else damping *= 2.0;
+    if (damping > 1e12) throw std::domain_error("unable to compute covariances: the system stays singular");
+  }
+  if (damping_used) *damping_used = damping;
+  std::vector<double> col((size_t)S.order);
+  const double one = 1.0;
+  for (int64_t i = 0; i < n; i++)
+    for (int64_t k = 0; k < size[(size_t)i]; k++) {
+      VB_CUDA(cudaMemsetAsync(p->step, 0, S.order * sizeof(double), s));
+      VB_CUDA(cudaMemcpyAsync(p->step + start[(size_t)i] + k, &one, sizeof(double), cudaMemcpyHostToDevice, s));
+      p->partial[0] = false;
+      solveAsync(p, p->step);
+      for (int64_t j = 0; j < n; j++)
+        VB_CUDA(cudaMemcpyAsync(col.data() + off[(size_t)j], p->step + start[(size_t)j], size[(size_t)j] * sizeof(double), cudaMemcpyDeviceToHost, s));
+      syncCheck(p);
+      for (int64_t r = 0; r < D; r++) cov[r * D + off[(size_t)i] + k] = col[(size_t)r];
+    }
+  VB_CATCH_NUMERIC
+}
 int vb_refine_points(vb_problem* p, vb_refine_stats* out, double* per_point, int64_t n_points) {
   VB_TRY
   requireProblem(p);

@@ -314,6 +314,10 @@ int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* r
                   int64_t half_length_us, int64_t n_samples, const int64_t* sample_time_ns, const float* gyro_rad_s,
                   const float* accel_m_s2);
 int vb_rs_refresh(vb_problem* p, int32_t store); /* store < 0: every store that has IMU samples */
+/* updateRollingShutterData also re-snapshots gravityWorld from the gravity variable (InitCalibration.cpp:317 ->
+ * RollingShutterData.cpp:21): name that S2 variable here and every refresh of the store copies its current value into the
+ * store's aux[0..2]; -1 keeps the value uploaded with the store (single-session runs hold gravity constant) */
+int vb_rs_set_gravity_var(vb_problem* p, int32_t store, int32_t gravity_var);
 
 /* Optimizer::computeJointCovariances / computeCovariances (lib/small_thing/Optimizer.cpp:503-696; used by
  * SingleSessionProblem::computeCovariances, viba/problem/SingleSessionProblem.cpp:66-138) for ONE list of registered

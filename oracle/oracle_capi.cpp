@@ -18,6 +18,7 @@ struct RsSource {   // raw IMU-0 samples + per-rig windows of one rolling-shutte
   std::vector<int64_t> midUs;
   std::vector<int32_t> calibVar;
   int64_t halfUs = 0;
+  int32_t gravityVar = -1;   // re-read at every refresh (InitCalibration.cpp:317), -1: keep the stored value
 };
 
 struct PreintSource {   // raw samples of one IMU + the integration interval of every factor of one inertial store
@@ -225,6 +226,7 @@ static void rsRefresh(OrcHandle* h, int store) {
   for (const RsSource& src : h->rs) {
     if (store >= 0 && src.store != store) continue;
     Problem& P = h->eng.P;
+    if (src.gravityVar >= 0) for (int i = 0; i < 3; i++) P.stores[src.store].aux[i] = P.data[P.off[src.gravityVar] + i];
     double* tables = P.stores[src.store].aux.data() + 4;
     const int threads = h->eng.threads;
     std::string failure;   // exceptions must not leave the OpenMP region
@@ -387,6 +389,11 @@ int orc_integrate_measurements(int64_t n_samples, const int64_t* sample_time_ns,
   for (int i = 0; i < 4; i++) out11[i] = r.q[i];
   for (int i = 0; i < 3; i++) { out11[4 + i] = r.dV[i]; out11[7 + i] = r.dP[i]; }
   out11[10] = r.dt;
+  ORC_CATCH
+}
+int orc_rs_set_gravity_var(OrcHandle* h, int store, int gravity_var) {
+  ORC_TRY
+  for (RsSource& src : h->rs) if (src.store == store) src.gravityVar = gravity_var;
   ORC_CATCH
 }
 int orc_rs_refresh(OrcHandle* h, int store) {

@@ -148,6 +148,10 @@ class Oracle:
         keys = ["total_start_cost", "total_end_cost", "num_points", "num_failures", "num_total_iterations", "num_at_least_one_iteration"]
         return {k: (float(v) if i < 2 else int(v)) for i, (k, v) in enumerate(zip(keys, st))}, pp
 
+    def rs_set_gravity_var(self, store, gravity_var):
+        self.lib.orc_rs_set_gravity_var.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        self._ck(self.lib.orc_rs_set_gravity_var(self.h, int(store), int(gravity_var)))
+
     def rs_refresh(self, store=-1):
         self.lib.orc_rs_refresh.argtypes = [C.c_void_p, C.c_int]
         self._ck(self.lib.orc_rs_refresh(self.h, int(store)))

@@ -217,3 +217,33 @@ def test_two_pass_visual_schedule(name, ctx, oracle, monkeypatch):
         assert np.abs(to_reg(p, o, p.grad) - o.grad).max() <= 1e-10 * np.abs(o.grad).max()
     finally:
         p.close()
+
+
+def test_c1_full_size_parity_with_the_serial_oracle(ctx, oracle):
+    """BASELINE configs[0] at full size (c1_60s_rs: 600 rigs, 20 k landmarks, ~1.3 M observations with the RGB rolling-shutter
+    camera, two IMUs) against the serial oracle: cost 1e-12, gradient 1e-10, damped step 1e-7, and a 3-iteration optimize
+    with the per-iteration trace (cost 1e-9, same branches) and the final state at 1e-6"""
+    from tests.test_lm_branches import assert_traces_match
+    s = synth.make_session(**synth.CONFIGS["c1_60s_rs"])
+    o = Oracle(oracle, s.graph)
+    p = capi.Problem(ctx, s.graph)
+    co, cg = o.eval_grad_hess(), p.compute_grad_hess()
+    assert abs(cg - co) <= 1e-12 * abs(co)
+    go, gg = o.grad, to_reg(p, o, p.grad)
+    assert np.abs(gg - go).max() <= 1e-10 * np.abs(go).max()
+    c1, st1 = o.eval_cost(True); c2, st2 = p.compute_cost(True)
+    assert abs(c1 - c2) <= 1e-12 * abs(c1) and st1 == st2
+    o.damp(1e-4); p.add_damping(1e-4)
+    o.factor(); o.solve()
+    p.step_from_grad(); p.factor(); p.solve(0)
+    so_, sg_ = o.step, to_reg(p, o, p.step)
+    assert np.abs(sg_ - so_).max() <= 1e-7 * np.abs(so_).max()
+    p.close()
+    st = G.default_settings(3)
+    o2 = Oracle(oracle, s.graph); p2 = capi.Problem(ctx, s.graph)
+    so, to = o2.optimize_ex(st)
+    sg, tg = p2.optimize_ex(st)
+    assert_traces_match(tg, to)
+    assert sg.num_iterations == so.num_iterations and abs(sg.final_cost - so.final_cost) <= 1e-9 * so.final_cost
+    assert np.abs(p2.vars - o2.vars).max() <= 1e-6
+    p2.close()

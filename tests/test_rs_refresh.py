@@ -228,3 +228,47 @@ def test_oracle_preintegration_of_raw_samples_matches_the_true_motion(oracle):
         assert out[10] == pytest.approx(dt, abs=1e-12)
         assert min(np.abs(out[:4] - R).max(), np.abs(out[:4] + R).max()) < 5e-7   # float32 samples, 1 kHz midpoint rule
         assert np.abs(out[4:7] - dV).max() < 1e-6 and np.abs(out[7:10] - dP).max() < 2e-8
+
+
+def test_oracle_refresh_resnapshots_gravity(oracle):
+    """updateRollingShutterData copies the CURRENT gravity variable into every RollingShutterData (InitCalibration.cpp:317,
+    RollingShutterData.cpp:21): with the variable named, a changed gravity reaches the store's aux[0..2] and the cost"""
+    s, d = session_with_imu("tiny_rs")
+    g = s.graph
+    o = Oracle(oracle, g)
+    set_imu(o, d)
+    gv = int(s.ids["gravity"][0])
+    o.rs_refresh()
+    c0 = o.eval_cost(False)[0]
+    v = o.vars
+    v[g.var_off[gv]:g.var_off[gv] + 3] = [0.3, -0.2, -9.80]
+    o.set(4, v)
+    o.rs_refresh()
+    assert np.array_equal(o.store_aux(d["store"])[:3], [0.0, 0.0, -9.81])      # not named: the stored value stays
+    o.rs_set_gravity_var(d["store"], gv)
+    o.rs_refresh()
+    assert np.array_equal(o.store_aux(d["store"])[:3], [0.3, -0.2, -9.80])
+    assert o.eval_cost(False)[0] != c0
+
+
+@pytest.mark.gpu
+def test_gpu_refresh_resnapshots_gravity(oracle):
+    s, d = session_with_imu("tiny_rs")
+    g = s.graph
+    gv = int(s.ids["gravity"][0])
+    o = Oracle(oracle, g)
+    ctx = capi.Context(0)
+    p = capi.Problem(ctx, g)
+    for t in (o, p):
+        set_imu(t, d)
+        t.rs_set_gravity_var(d["store"], gv)
+    v = o.vars
+    v[g.var_off[gv]:g.var_off[gv] + 3] = [0.3, -0.2, -9.80]
+    o.set(4, v); p.set_vars(v)
+    o.rs_refresh(); p.rs_refresh()
+    assert np.array_equal(p.store_aux(d["store"])[:3], [0.3, -0.2, -9.80])
+    co, cg = o.eval_cost(False)[0], p.compute_cost(False)[0]
+    assert abs(co - cg) <= 1e-12 * abs(co)
+    with pytest.raises(capi.VbError):
+        p.rs_set_gravity_var(d["store"], int(s.ids["pose"][0]))
+    p.close(); ctx.close()

@@ -410,6 +410,9 @@ class Problem:
     def rs_refresh(self, store=-1):
         _ck(self.lib, self.lib.vb_rs_refresh(self.h, int(store)))
 
+    def rs_set_gravity_var(self, store, gravity_var):
+        _ck(self.lib, self.lib.vb_rs_set_gravity_var(self.h, int(store), int(gravity_var)))
+
     def preint_set_imu(self, store, time_ns, gyro, accel, start_us, end_us, calib_var, gyro_var, accel_var):
         """raw samples of an inertial store's IMU + the interval and calibration variable of every factor (vb_preint_set_imu):
         from now on optimize() recomputes the store's preintegration records at the top of every iteration"""

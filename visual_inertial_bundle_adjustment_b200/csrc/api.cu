@@ -58,6 +58,7 @@ struct vb_problem {
   struct RsSource {
     int store = -1;
     int64_t nRigs = 0, nSamples = 0, halfUs = 0;
+    int64_t gravOff = -1;   // data offset of the gravity variable re-read at every refresh (vb_rs_set_gravity_var), -1: keep
     int64_t *timeNs = nullptr, *midUs = nullptr, *calibOff = nullptr;
     float *gyro = nullptr, *accel = nullptr;
     int* status = nullptr;
@@ -867,6 +868,10 @@ static bool launchRsTables(vb_problem* p, int store) {
     if (store >= 0 && src.store != store) continue;
     any = true;
     VB_CUDA(cudaMemsetAsync(src.status, 0, sizeof(int), s));
+    // gravityWorld_ of every RollingShutterData is re-snapshotted from the gravity variable (InitCalibration.cpp:317,
+    // RollingShutterData.cpp:21): constant in single-session runs, a free S2 variable in multi-session ones
+    if (src.gravOff >= 0)
+      VB_CUDA(cudaMemcpyAsync(const_cast<double*>(p->ds[src.store].aux), p->dv.data + src.gravOff, 3 * sizeof(double), cudaMemcpyDeviceToDevice, s));
     double* tables = const_cast<double*>(p->ds[src.store].aux) + 4;
     launchRsRefresh(src.timeNs, src.gyro, src.accel, src.nSamples, p->dv.data, src.calibOff, src.midUs, src.halfUs, src.nRigs,
                     tables, src.status, s);
@@ -1845,6 +1850,16 @@ int vb_rs_set_imu(vb_problem* p, int32_t store, int64_t n_rigs, const int64_t* r
   for (auto it = p->rsSources.begin(); it != p->rsSources.end();)
     it = it->store == store ? p->rsSources.erase(it) : it + 1;
   p->rsSources.push_back(src);
+  VB_CATCH
+}
+int vb_rs_set_gravity_var(vb_problem* p, int32_t store, int32_t gravity_var) {
+  VB_TRY
+  requireProblem(p);
+  if (gravity_var >= 0 && (gravity_var >= p->g.nv || p->g.kind[gravity_var] != VB_VAR_S2)) throw std::invalid_argument("gravity_var must name an S2 variable");
+  bool found = false;
+  for (auto& src : p->rsSources)
+    if (src.store == store) { src.gravOff = gravity_var < 0 ? -1 : p->g.off[gravity_var]; found = true; }
+  if (!found) throw std::invalid_argument("store has no IMU samples (vb_rs_set_imu)");
   VB_CATCH
 }
 int vb_rs_refresh(vb_problem* p, int32_t store) {

@@ -100,7 +100,20 @@ typedef struct vb_settings {
   int32_t max_step_factor_attempts, try_sub_step;
   int32_t stop_if_no_improvement_for, distance_from_troubled_iteration, max_num_iterations;
   int32_t verbose;
+  /* Optimizer::Settings::{solverType, pcgMaxIterations, pcgDesiredResidual} (Optimizer.h:43-45).  solver_type:
+   * VB_SOLVER_DIRECT (0), VB_SOLVER_PCG_TRIVIAL (1), VB_SOLVER_PCG_JACOBI (2) run on the device (SURVEY.md 8 f3:
+   * landmark Schur elimination, then preconditioned conjugate gradients on the reduced camera system,
+   * Optimizer.cpp:232-331, PCG.cpp:15-97, Preconditioner.h:29-116); VB_SOLVER_PCG_GAUSS_SEIDEL (3) and
+   * VB_SOLVER_PCG_LOWER_PREC_SOLVE (4) are BaSpaCho's pseudoFactorFrom / float factorFrom, whose source is not in the
+   * reference tree: VB_ERR_ARG. */
+  int32_t solver_type, pcg_max_iterations;
+  double pcg_desired_residual;
 } vb_settings;
+#define VB_SOLVER_DIRECT 0
+#define VB_SOLVER_PCG_TRIVIAL 1
+#define VB_SOLVER_PCG_JACOBI 2
+#define VB_SOLVER_PCG_GAUSS_SEIDEL 3
+#define VB_SOLVER_PCG_LOWER_PREC_SOLVE 4
 
 typedef struct vb_summary {  /* Optimizer::Summary, Optimizer.h:93-99 */
   double initial_cost, final_cost;
@@ -275,6 +288,12 @@ int vb_restore(vb_problem* p);
 /* compute grad only into the secondary vector (Optimizer.cpp:912-919) */
 int vb_eval_grad_new(vb_problem* p, int dont_retry_failed);
 
+/* Linear solver of vb_factor / vb_solve (vb_optimize sets it from its settings): see vb_settings.solver_type.  With a PCG
+ * type vb_factor eliminates the landmarks and initialises the preconditioner (Optimizer.cpp:289-300), vb_solve runs the
+ * landmark forward solve, PCG on the reduced system and the landmark back-substitution (:301-327); vb_pcg_last returns
+ * the iteration count and relative residual of the last PCG run.  Not available on a sharded problem. */
+int vb_set_linear_solver(vb_problem* p, int32_t solver_type, int32_t pcg_max_iterations, double pcg_desired_residual);
+int vb_pcg_last(const vb_problem* p, int32_t* iterations, double* relative_residual);
 /* Optimizer::optimize (Optimizer.cpp:768-1106): the whole LM loop, host-controlled, device-resident */
 int vb_optimize(vb_problem* p, const vb_settings* s, vb_summary* out);
 /* same loop with the Settings hooks: preStepCallback (Optimizer.h:90, called at Optimizer.cpp:803-805),

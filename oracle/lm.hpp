@@ -34,6 +34,7 @@ inline int optimize(Engine& e, SchurSkylineSolver& sol, const vb_settings& st, v
     const double rate = s.numInvalid / (s.numTotal + 1.0);
     return rate < 0.03 && (s.numInvalid < s.numPrevInvalid * 2.0 + 50);
   };
+  sol.setLinearSolver(st.solver_type, st.pcg_max_iterations, st.pcg_desired_residual);   // Settings::solverType (Optimizer.h:43)
   while (true) {
     int branch = 0, attempts = 0;
     if (userPreStep) userPreStep(iterationNum); // Settings::preStepCallback (Optimizer.cpp:803-805)

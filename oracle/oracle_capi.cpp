@@ -261,6 +261,16 @@ int orc_rs_set_imu(OrcHandle* h, int store, int64_t n_rigs, const int64_t* rig_m
   h->eng.preStep = [h]() { preintRefresh(h, -1); rsRefresh(h, -1); };
   ORC_CATCH
 }
+// Settings::solverType for orc_factor / orc_solve (orc_optimize takes it from its settings); last PCG run's statistics
+int orc_set_linear_solver(OrcHandle* h, int solver_type, int pcg_max_iterations, double pcg_desired_residual) {
+  ORC_TRY
+  h->sol.setLinearSolver(solver_type, pcg_max_iterations, pcg_desired_residual);
+  ORC_CATCH
+}
+int orc_pcg_last(OrcHandle* h, int* iterations, double* residual) {
+  *iterations = h->sol.pcgLastIterations; *residual = h->sol.pcgLastResidual;
+  return 0;
+}
 // refinePoints (viba/problem/PointRefinement.cpp:171-196): stats6 = {totalStartCost, totalEndCost, nPoints, nFailures,
 // nTotalIterations, nAtLeastOneIt}; per_point (may be null) = {startCost, endCost, nIts} per refined landmark
 int orc_refine_points(OrcHandle* h, double* stats6, double* per_point) {

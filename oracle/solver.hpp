@@ -192,6 +192,9 @@ struct SchurSkylineSolver {
     }
     flopsSchur = fl;
     bandFactored = false;
+    factoredDirect = false;
+    if (schurOnly) { initPrecond(); return; }   // iterative path (Optimizer.cpp:291-292: factorUpTo the elimination range only)
+    factoredDirect = true;
     if (pbtrf && e.threads > 1) { // CPU-baseline mode: band storage (lower), AB[(i-j) + j*ldab] = A(i,j)
       kd = 0;
       for (int64_t i = 0; i < nr; i++) kd = std::max<int>(kd, (int)(i - first[i]));
@@ -229,6 +232,92 @@ struct SchurSkylineSolver {
     }
   }
 
+  // ---- iterative path: Optimizer.cpp:232-331 (PCG on the reduced camera system), PCG.cpp:15-97, and the two
+  // preconditioners whose definition is in the reference tree: IdentityPrecond and BlockJacobiPrecond
+  // (Preconditioner.h:52-116: the param-sized diagonal blocks, Cholesky-factored).  BlockGaussSeidelPrecond is
+  // Solver::pseudoFactorFrom and LowerPrecSolvePrecond a float factorFrom of BaSpaCho, whose source is absent.
+  bool schurOnly = false, factoredDirect = false;
+  int pcgPrecond = 0;            // 0 identity, 1 block Jacobi
+  int pcgMaxIterations = 40; double pcgDesiredResidual = 1e-10;
+  int pcgLastIterations = 0; double pcgLastResidual = 0;
+  // Optimizer::Settings::solverType (Optimizer.h:30-36,43): 0 direct, 1 PCG identity, 2 PCG block Jacobi
+  void setLinearSolver(int solverType, int maxIterations, double desiredResidual) {
+    if (solverType < 0 || solverType > 2)
+      throw std::runtime_error("oracle: Solver_PCG_GaussSeidel / LowerPrecSolve need BaSpaCho's pseudoFactorFrom / float factorFrom (source absent)");
+    schurOnly = solverType != 0; pcgPrecond = solverType == 2 ? 1 : 0;
+    pcgMaxIterations = maxIterations; pcgDesiredResidual = desiredResidual;
+  }
+  std::vector<double> jac;       // per camera block: Cholesky factor of its diagonal block (d x d, lower), at jacOff
+  std::vector<int64_t> jacOff;
+
+  void reducedMatVec(const std::vector<double>& v, std::vector<double>& u) const {   // u = S v, S symmetric in skyline
+    u.assign(nr, 0.0);
+    for (int64_t i = 0; i < nr; i++) {
+      const double* Si = &S[rowStart[i]];
+      const int64_t fi = first[i];
+      double s = 0;
+      for (int64_t j = fi; j < i; j++) { s += Si[j - fi] * v[j]; u[j] += Si[j - fi] * v[i]; }
+      u[i] += s + Si[i - fi] * v[i];
+    }
+  }
+  void initPrecond() {
+    const Engine& e = *E;
+    jacOff.assign(nC + 1, 0);
+    for (int64_t c = 0; c < nC; c++) jacOff[c + 1] = jacOff[c] + (int64_t)e.P.blockSize[nP + c] * e.P.blockSize[nP + c];
+    jac.assign(jacOff[nC], 0.0);
+    if (pcgPrecond != 1) return;
+    for (int64_t c = 0; c < nC; c++) {
+      const int d = e.P.blockSize[nP + c];
+      double* L = &jac[jacOff[c]];
+      for (int a = 0; a < d; a++) for (int b = 0; b <= a; b++) L[a * d + b] = S[rowStart[cstart[c] + a] + (cstart[c] + b - first[cstart[c] + a])];
+      for (int a = 0; a < d; a++) {   // in-place LLT
+        for (int b = 0; b < a; b++) { double t = L[a * d + b]; for (int k = 0; k < b; k++) t -= L[a * d + k] * L[b * d + k]; L[a * d + b] = t / L[b * d + b]; }
+        double t = L[a * d + a];
+        for (int k = 0; k < a; k++) t -= L[a * d + k] * L[a * d + k];
+        if (!(t > 0)) throw std::runtime_error("oracle: Jacobi block not positive definite");
+        L[a * d + a] = std::sqrt(t);
+      }
+    }
+  }
+  void applyPrecond(const std::vector<double>& r, std::vector<double>& z) const {
+    z = r;
+    if (pcgPrecond != 1) return;
+    const Engine& e = *E;
+    for (int64_t c = 0; c < nC; c++) {
+      const int d = e.P.blockSize[nP + c];
+      const double* L = &jac[jacOff[c]];
+      double* x = &z[cstart[c]];
+      for (int a = 0; a < d; a++) { double t = x[a]; for (int k = 0; k < a; k++) t -= L[a * d + k] * x[k]; x[a] = t / L[a * d + a]; }
+      for (int a = d - 1; a >= 0; a--) { double t = x[a]; for (int k = a + 1; k < d; k++) t -= L[k * d + a] * x[k]; x[a] = t / L[a * d + a]; }
+    }
+  }
+  // PCG::solve (PCG.cpp:15-97): x0 = 0, stops on |r_k| / |r_0| < desired or at maxIterations
+  void pcgSolve(const std::vector<double>& b, std::vector<double>& x) {
+    std::vector<double> xk(nr, 0.0), rk(b), zk, pk, Apk, zk1;
+    applyPrecond(rk, zk);
+    pk = zk;
+    auto dot = [&](const std::vector<double>& a, const std::vector<double>& c) { double s = 0; for (int64_t i = 0; i < nr; i++) s += a[i] * c[i]; return s; };
+    const double rk0norm = std::sqrt(dot(rk, rk));
+    double zk_rk = dot(zk, rk), rel = 0.0;
+    int k = 0;
+    while (true) {
+      reducedMatVec(pk, Apk);
+      const double alpha = zk_rk / dot(pk, Apk);
+      for (int64_t i = 0; i < nr; i++) { xk[i] += pk[i] * alpha; rk[i] -= Apk[i] * alpha; }
+      rel = std::sqrt(dot(rk, rk)) / rk0norm;
+      if (rel < pcgDesiredResidual) break;
+      if (k + 1 >= pcgMaxIterations) break;
+      applyPrecond(rk, zk1);
+      const double zk1_rk1 = dot(zk1, rk);
+      const double beta = zk1_rk1 / zk_rk;
+      for (int64_t i = 0; i < nr; i++) pk[i] = zk1[i] + pk[i] * beta;
+      zk_rk = zk1_rk1;
+      k++;
+    }
+    x = xk;
+    pcgLastIterations = k + 1; pcgLastResidual = rel;
+  }
+
   // Solver::solve (Optimizer.cpp:228) with the factor computed by factor(H)
   void solveOnly(const double* H, const double* g, double* x) {
     const Engine& e = *E;
@@ -246,7 +335,11 @@ struct SchurSkylineSolver {
     }
     // solve L y = gr ; L^T z = y
     std::vector<double> y(gr);
-    if (bandFactored) {
+    if (!factoredDirect) {   // iterative path: PCG on the reduced system (Optimizer.cpp:308-310)
+      std::vector<double> sol;
+      pcgSolve(gr, sol);
+      y = sol;
+    } else if (bandFactored) {
       const int n = (int)nr, ld = kd + 1, one = 1;
       int info = 0;
       pbtrs("L", &n, &kd, &one, AB.data(), &ld, y.data(), &n, &info);

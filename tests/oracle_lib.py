@@ -139,6 +139,16 @@ class Oracle:
         self._ck(self.lib.orc_preint_get_cov(self.h, int(store), dptr(cov), dptr(om), n_factors))
         return cov, om
 
+    def set_linear_solver(self, solver_type, max_iterations=40, residual=1e-10):
+        self.lib.orc_set_linear_solver.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
+        self._ck(self.lib.orc_set_linear_solver(self.h, int(solver_type), int(max_iterations), float(residual)))
+
+    def pcg_last(self):
+        it, res = C.c_int(0), C.c_double(0)
+        self.lib.orc_pcg_last.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        self.lib.orc_pcg_last(self.h, C.byref(it), C.byref(res))
+        return it.value, res.value
+
     def refine_points(self):
         """refinePoints on the oracle: (stats dict, per-point [n, 3]); the landmark variables are updated"""
         n = len(set(int(v) for st in self.g.stores if st.type in (G.F_VISUAL, G.F_VISUAL_RS) for v in st.vars[:, 0]))

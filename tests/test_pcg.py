@@ -1,0 +1,204 @@
+"""The iterative path of the linear solve: lib/small_thing/Optimizer.cpp:232-331 — eliminate the
+landmarks, run preconditioned conjugate gradients (PCG.cpp:15-97) on the reduced camera system, back-substitute —
+with IdentityPrecond (Solver_PCG_Trivial) and BlockJacobiPrecond (Solver_PCG_Jacobi), Preconditioner.h:29-116.
+Solver_PCG_GaussSeidel / Solver_PCG_LowerPrecSolve call BaSpaCho's pseudoFactorFrom / float factorFrom, whose source
+is not in the reference tree: they are refused, here and in the library.
+
+CPU part: the oracle's PCG converges to the oracle's direct solve; its iteration count obeys PCG.cpp's two exits.
+GPU part: the device PCG against the oracle's PCG (same algorithm, same stopping rule: iteration counts equal, steps
+at 1e-6 of scale — CG amplifies rounding differences by the condition number, so the gate is looser than the direct
+solve's 1e-7) and against the device's own direct solve; a whole optimize() through the PCG path against the oracle's."""
+import numpy as np
+import pytest
+from tests.oracle_lib import Oracle
+from visual_inertial_bundle_adjustment_b200 import synth, graph as G
+
+DAMP = 1e-4
+
+
+def prepared_oracle(oracle, name):
+    s = synth.make_session(**synth.CONFIGS[name])
+    o = Oracle(oracle, s.graph)
+    o.eval_grad_hess(); o.damp(DAMP)
+    return s, o
+
+
+def oracle_step(o, solver_type, max_it=40, res=1e-10):
+    o.set_linear_solver(solver_type, max_it, res)
+    o.factor(); o.solve()
+    return o.step.copy()
+
+
+# Trivial (no preconditioner) needs ~14 000 iterations on "tiny" and does not get there in 40 000 on the "small" sessions
+# (the damped reduced system is badly conditioned: IMU information against a 1e-4 damping): convergence of the identity
+# path is tested on "tiny", the "small" sessions compare cut-short iterates.
+CONVERGING = [("tiny", G.SOLVER_PCG_JACOBI, 4000), ("tiny", G.SOLVER_PCG_TRIVIAL, 40000),
+              ("small_rs", G.SOLVER_PCG_JACOBI, 6000), ("small_lc_rs", G.SOLVER_PCG_JACOBI, 6000)]
+
+
+@pytest.mark.parametrize("name,solver_type,max_it", CONVERGING[:3])
+def test_oracle_pcg_converges_to_the_direct_solve(oracle, name, solver_type, max_it):
+    s, o = prepared_oracle(oracle, name)
+    direct = oracle_step(o, G.SOLVER_DIRECT)
+    x = oracle_step(o, solver_type, max_it, 1e-12)
+    it, res = o.pcg_last()
+    assert it < max_it and res < 1e-12
+    assert np.abs(x - direct).max() <= 1e-7 * np.abs(direct).max()
+
+
+def test_block_jacobi_needs_fewer_iterations_than_identity(oracle):
+    s, o = prepared_oracle(oracle, "tiny")
+    oracle_step(o, G.SOLVER_PCG_JACOBI, 40000, 1e-10); it_j = o.pcg_last()[0]
+    oracle_step(o, G.SOLVER_PCG_TRIVIAL, 40000, 1e-10); it_t = o.pcg_last()[0]
+    assert it_j < it_t
+
+
+def test_oracle_pcg_exits(oracle):
+    """PCG.cpp:60-66: stop when |r|/|r0| < desired or after maxIterations matrix-vector products"""
+    s, o = prepared_oracle(oracle, "tiny")
+    oracle_step(o, G.SOLVER_PCG_JACOBI, 3, 1e-30)
+    assert o.pcg_last()[0] == 3 and o.pcg_last()[1] > 1e-30
+    oracle_step(o, G.SOLVER_PCG_JACOBI, 5000, 1e-3)
+    it, res = o.pcg_last()
+    assert it < 5000 and res < 1e-3
+
+
+def test_oracle_refuses_the_pseudo_factor_preconditioners(oracle):
+    s, o = prepared_oracle(oracle, "tiny")
+    for t in (G.SOLVER_PCG_GAUSS_SEIDEL, G.SOLVER_PCG_LOWER_PREC_SOLVE, 7):
+        with pytest.raises(RuntimeError):
+            o.set_linear_solver(t)
+
+
+def test_oracle_optimize_through_pcg_matches_direct(oracle):
+    s = synth.make_session(**synth.CONFIGS["tiny_rs"])
+    st = G.default_settings(6)
+    a = Oracle(oracle, s.graph); sa = a.optimize(st)[0]
+    st.solver_type, st.pcg_max_iterations, st.pcg_desired_residual = G.SOLVER_PCG_JACOBI, 2000, 1e-12
+    b = Oracle(oracle, s.graph); sb = b.optimize(st)[0]
+    assert sa.num_iterations == sb.num_iterations
+    assert abs(sa.final_cost - sb.final_cost) <= 1e-6 * abs(sa.final_cost)
+
+
+# ---- device ----------------------------------------------------------------------------------------------------------
+def to_reg(p, o, vec):
+    ps_g = p.param_start(); _, _, _, ps_o = o.structure()
+    out = np.zeros(o.order)
+    d = np.diff(ps_o)
+    for b in range(o.nblocks):
+        out[ps_o[b]:ps_o[b] + d[b]] = vec[ps_g[b]:ps_g[b] + d[b]]
+    return out
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from visual_inertial_bundle_adjustment_b200 import capi
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+def device_step(p, solver_type, max_it=40, res=1e-10):
+    p.set_linear_solver(solver_type, max_it, res)
+    p.step_from_grad(); p.factor(); p.solve(0)
+    return p.step.copy()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,solver_type,max_it", CONVERGING)
+def test_device_pcg_converges_where_the_oracle_pcg_does(ctx, oracle, name, solver_type, max_it):
+    from visual_inertial_bundle_adjustment_b200 import capi
+    s, o = prepared_oracle(oracle, name)
+    p = capi.Problem(ctx, s.graph)
+    try:
+        p.compute_grad_hess(); p.add_damping(DAMP)
+        so = oracle_step(o, solver_type, max_it, 1e-12)
+        sg = to_reg(p, o, device_step(p, solver_type, max_it, 1e-12))
+        it_o, res_o = o.pcg_last(); it_g, res_g = p.pcg_last()
+        assert res_o < 1e-12 and res_g < 1e-12
+        assert np.abs(sg - so).max() <= 1e-6 * np.abs(so).max()
+        assert abs(it_g - it_o) <= max(3, it_o // 4), (it_g, it_o)   # rounding moves the exit by a few percent
+        # against the device's own direct factorisation
+        p.compute_grad_hess(); p.add_damping(DAMP)
+        sd = to_reg(p, o, device_step(p, G.SOLVER_DIRECT))
+        assert np.abs(sg - sd).max() <= 1e-6 * np.abs(sd).max()
+    finally:
+        p.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["tiny", "small_rs", "small_lc_rs"])
+@pytest.mark.parametrize("solver_type", [G.SOLVER_PCG_TRIVIAL, G.SOLVER_PCG_JACOBI])
+def test_device_pcg_iterates_match_the_oracle_pcg(ctx, oracle, name, solver_type):
+    """cut short at the reference's default maxIterations and before: the same iterate after the same number of
+    iterations (rounding differences have not been amplified yet)"""
+    from visual_inertial_bundle_adjustment_b200 import capi
+    s, o = prepared_oracle(oracle, name)
+    p = capi.Problem(ctx, s.graph)
+    try:
+        for n_it, tol in ((1, 1e-11), (5, 1e-9), (40, 1e-6)):
+            p.compute_grad_hess(); p.add_damping(DAMP)
+            so = oracle_step(o, solver_type, n_it, 1e-30)
+            sg = to_reg(p, o, device_step(p, solver_type, n_it, 1e-30))
+            assert o.pcg_last()[0] == n_it and p.pcg_last()[0] == n_it
+            assert abs(p.pcg_last()[1] - o.pcg_last()[1]) <= 100 * tol * o.pcg_last()[1], (n_it, p.pcg_last(), o.pcg_last())
+            assert np.abs(sg - so).max() <= tol * np.abs(so).max(), n_it
+    finally:
+        p.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,solver_type,max_it", [("tiny_rs", G.SOLVER_PCG_TRIVIAL, 40000), ("small_rs", G.SOLVER_PCG_JACOBI, 8000)])
+def test_device_optimize_through_pcg_matches_the_oracle(ctx, oracle, name, solver_type, max_it):
+    from visual_inertial_bundle_adjustment_b200 import capi
+    s = synth.make_session(**synth.CONFIGS[name])
+    st = G.default_settings(6)
+    st.solver_type, st.pcg_max_iterations, st.pcg_desired_residual = solver_type, max_it, 1e-12
+    o = Oracle(oracle, s.graph); so, to = o.optimize_ex(st)
+    p = capi.Problem(ctx, s.graph)
+    try:
+        lines = []
+        sg, tg = p.optimize_ex(st, log=lines.append)
+        assert sg.num_iterations == so.num_iterations and sg.stop_reason == so.stop_reason
+        for a, b in zip(tg, to):
+            assert abs(a["new_cost"] - b["new_cost"]) <= 1e-8 * abs(b["new_cost"])
+            assert a["branch"] == b["branch"]
+        assert np.abs(p.vars - o.vars).max() <= 1e-6
+        label = "jacobi" if solver_type == G.SOLVER_PCG_JACOBI else "trivial"
+        assert any(f"semi-precond({label})" in l and "iters: " in l and "residual: " in l for l in lines)
+        # and lands where the direct solver lands
+        st.solver_type = G.SOLVER_DIRECT
+        q = capi.Problem(ctx, s.graph)
+        sd = q.optimize(st)
+        q.close()
+        assert abs(sd.final_cost - sg.final_cost) <= 1e-6 * abs(sd.final_cost)
+    finally:
+        p.close()
+
+
+@pytest.mark.gpu
+def test_device_refuses_what_it_does_not_build(ctx):
+    from visual_inertial_bundle_adjustment_b200 import capi, sharding
+    s = synth.make_session(**synth.CONFIGS["tiny"])
+    p = capi.Problem(ctx, s.graph)
+    try:
+        for t in (G.SOLVER_PCG_GAUSS_SEIDEL, G.SOLVER_PCG_LOWER_PREC_SOLVE, 9, -1):
+            with pytest.raises(capi.VbError) as e:
+                p.set_linear_solver(t)
+            assert e.value.code == 1
+        st = G.default_settings(2)
+        st.solver_type = G.SOLVER_PCG_GAUSS_SEIDEL
+        with pytest.raises(capi.VbError):
+            p.optimize(st)
+        with pytest.raises(capi.VbError):
+            p.set_linear_solver(G.SOLVER_PCG_JACOBI, 0, 1e-10)
+    finally:
+        p.close()
+
+    def run(q, rank):
+        try:
+            q.set_linear_solver(G.SOLVER_PCG_JACOBI)
+        except capi.VbError as ex:
+            return ex.code
+        return 0
+    assert sharding.run_threaded(s.graph, 2, run) == [1, 1]

@@ -66,6 +66,8 @@ def load():
     lib.vb_damp.argtypes = [C.c_void_p, C.c_double]
     lib.vb_step_from_grad.argtypes = [C.c_void_p]
     lib.vb_factor.argtypes = [C.c_void_p]
+    lib.vb_set_linear_solver.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_double]
+    lib.vb_pcg_last.argtypes = [C.c_void_p, C.POINTER(C.c_int32), _dp]
     lib.vb_solve.argtypes = [C.c_void_p, C.c_int]
     lib.vb_step_stats.argtypes = [C.c_void_p, _dp, _dp, _dp]
     lib.vb_scale_vec.argtypes = [C.c_void_p, C.c_int, C.c_double]
@@ -409,6 +411,17 @@ class Problem:
 
     def rs_refresh(self, store=-1):
         _ck(self.lib, self.lib.vb_rs_refresh(self.h, int(store)))
+
+    def set_linear_solver(self, solver_type, max_iterations=40, desired_residual=1e-10):
+        """Settings::solverType for vb_factor / vb_solve (optimize() takes it from its settings): graph.SOLVER_DIRECT,
+        SOLVER_PCG_TRIVIAL, SOLVER_PCG_JACOBI; the two BaSpaCho-pseudo-factor preconditioners raise"""
+        _ck(self.lib, self.lib.vb_set_linear_solver(self.h, int(solver_type), int(max_iterations), float(desired_residual)))
+
+    def pcg_last(self):
+        """(iterations, relative residual) of the last PCG solve (PCG::solve's return, PCG.cpp:95)"""
+        it = C.c_int32(0); res = C.c_double(0.0)
+        _ck(self.lib, self.lib.vb_pcg_last(self.h, C.byref(it), C.byref(res)))
+        return it.value, res.value
 
     def rs_set_gravity_var(self, store, gravity_var):
         _ck(self.lib, self.lib.vb_rs_set_gravity_var(self.h, int(store), int(gravity_var)))

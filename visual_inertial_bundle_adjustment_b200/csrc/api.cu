@@ -81,6 +81,11 @@ struct vb_problem {
   cudaStream_t hiStream = nullptr;
   std::vector<cudaEvent_t> evTrsm, evLater;
   cudaEvent_t evFork = nullptr, evJoin = nullptr;
+  // iterative path (vb_set_linear_solver): PCG on the reduced camera system
+  int solverType = VB_SOLVER_DIRECT, pcgMaxIterations = 40, pcgLastIterations = 0;
+  double pcgDesiredResidual = 1e-10, pcgLastResidual = 0.0;
+  double *pcgX = nullptr, *pcgR = nullptr, *pcgZ = nullptr, *pcgP = nullptr, *pcgAp = nullptr, *pcgJac = nullptr, *pcgDots = nullptr;
+  int64_t* pcgJacOff = nullptr;
   double* fwdFused = nullptr;     // the vector whose forward solve the last factorAsync carried (consumed by solveAsync)
   RefineArgs refine{};            // refinePoints (vb_refine_points): landmark-major view of the visual stores
   bool refineReady = false;
@@ -911,6 +916,7 @@ void vb_settings_default(vb_settings* s) { // lib/small_thing/Optimizer.h:40-78
   s->max_step_factor_attempts = 2; s->try_sub_step = 1;
   s->stop_if_no_improvement_for = 3; s->distance_from_troubled_iteration = 3; s->max_num_iterations = 50;
   s->verbose = 0;
+  s->solver_type = VB_SOLVER_DIRECT; s->pcg_max_iterations = 40; s->pcg_desired_residual = 1e-10;
 }
 
 int vb_ctx_create(int device, vb_ctx** out) {
@@ -1249,7 +1255,10 @@ static void factorLevels(vb_problem* p, int which, double* rhs = nullptr) {
 // forward solve runs between the landmark Cholesky and the Schur update, every supernode's segment rides through its trsm
 // and its panel product through the update kernel — so the 2 x levels dependent kernels of a separate forward pass
 // disappear from the iteration's critical path.  solveAsync then only runs the backward half (p->fwdFused).
+static void factorPcgAsync(vb_problem* p, cudaEvent_t afterSchur);
+static void solvePcg(vb_problem* p, double* vec);
 static void factorAsync(vb_problem* p, cudaEvent_t afterSchur, double* rhs = nullptr) {
+  if (p->solverType != VB_SOLVER_DIRECT) { factorPcgAsync(p, afterSchur); return; }
   cudaStream_t s = p->ctx->stream;
   const Symbolic& S = p->S;
   VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
@@ -1315,6 +1324,7 @@ static void solveLevels(vb_problem* p, double* vec, int which, bool forward) {
   }
 }
 static void solveAsync(vb_problem* p, double* vec) {
+  if (p->solverType != VB_SOLVER_DIRECT) { solvePcg(p, vec); return; }
   cudaStream_t s = p->ctx->stream;
   const int64_t nCam = p->S.order - p->sol.camVec0;
   double* cam = vec + p->sol.camVec0;
@@ -1353,6 +1363,83 @@ static void solveAsync(vb_problem* p, double* vec) {
   collective(p, VB_COLL_SUM, vec, p->sol.camVec0);   // owned landmark steps -> full step everywhere
   p->partial[vec == p->step ? 0 : vec == p->gradNew ? 1 : 2] = false;
 }
+// ---- iterative path (Optimizer.cpp:232-331) ---------------------------------------------------------------------------------
+static void pcgEnsureBuffers(vb_problem* p) {
+  if (p->pcgX) return;
+  const Symbolic& S = p->S;
+  const int64_t nCam = S.order - p->sol.camVec0;
+  p->pcgX = p->alloc<double>(nCam); p->pcgR = p->alloc<double>(nCam); p->pcgZ = p->alloc<double>(nCam);
+  p->pcgP = p->alloc<double>(nCam); p->pcgAp = p->alloc<double>(nCam);
+  p->pcgDots = p->alloc<double>(8);
+  std::vector<int64_t> off((size_t)S.nC + 1, 0);
+  for (int64_t c = 0; c < S.nC; c++) { const int64_t d = S.camStart[c + 1] - S.camStart[c]; off[(size_t)c + 1] = off[(size_t)c] + d * d; }
+  p->pcgJacOff = p->upload(off);
+  p->pcgJac = p->alloc<double>(off[(size_t)S.nC]);
+}
+// factorUpTo(elimination range) + precond->init (Optimizer.cpp:289-300)
+static void factorPcgAsync(vb_problem* p, cudaEvent_t afterSchur) {
+  if (p->nranks > 1) throw std::logic_error("the PCG path is not available on a sharded problem");
+  cudaStream_t s = p->ctx->stream;
+  pcgEnsureBuffers(p);
+  p->fwdFused = nullptr;
+  VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
+  launchSchur(p->sol, p->hess, p->schurTasks, p->nSchurTasks, p->errFlag, s);
+  if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
+  if (p->solverType == VB_SOLVER_PCG_JACOBI) launchJacobiInit(p->sol, p->hess, p->pcgJacOff, p->pcgJac, p->errFlag, s);
+}
+// solveLUpTo + PCG::solve on the reduced system + solveLtUpTo (Optimizer.cpp:301-327, PCG.cpp:15-97)
+static void solvePcg(vb_problem* p, double* vec) {
+  cudaStream_t s = p->ctx->stream;
+  const Symbolic& S = p->S;
+  const int64_t nCam = S.order - p->sol.camVec0;
+  double* cam = vec + p->sol.camVec0;
+  double *x = p->pcgX, *r = p->pcgR, *z = p->pcgZ, *pk = p->pcgP, *Ap = p->pcgAp, *dots = p->pcgDots;
+  const bool jacobi = p->solverType == VB_SOLVER_PCG_JACOBI;
+  auto precond = [&](const double* in, double* out) {
+    if (jacobi) launchJacobiApply(p->sol, p->pcgJacOff, p->pcgJac, in, out, s);
+    else VB_CUDA(cudaMemcpyAsync(out, in, nCam * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  };
+  auto readDots = [&](double* host, int n) {
+    VB_CUDA(cudaMemcpyAsync(host, dots, n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    syncCheck(p);
+  };
+  launchSolveLandmarksFwd(p->sol, p->hess, vec, s);
+  VB_CUDA(cudaMemsetAsync(x, 0, nCam * sizeof(double), s));
+  VB_CUDA(cudaMemcpyAsync(r, cam, nCam * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  precond(r, z);
+  VB_CUDA(cudaMemcpyAsync(pk, z, nCam * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  // dots: [0] z.r (current), [1] r.r, [2] p.Ap, [3] scratch, [4] z1.r1 (next)
+  VB_CUDA(cudaMemsetAsync(dots, 0, 8 * sizeof(double), s));
+  launchPcgDot2(z, r, r, r, nCam, dots, s);
+  double h[8];
+  readDots(h, 2);
+  const double rk0norm = std::sqrt(h[1]);
+  double rel = 0.0;
+  int k = 0;
+  if (!(rk0norm > 0.0)) { p->pcgLastIterations = 0; p->pcgLastResidual = 0.0; }
+  else while (true) {
+    VB_CUDA(cudaMemsetAsync(Ap, 0, nCam * sizeof(double), s));
+    launchCamSymMv(p->sol, p->hess, pk, Ap, (int)S.nL, S.maxLumpRows, S.maxLumpWidth, s);
+    VB_CUDA(cudaMemsetAsync(dots + 2, 0, 2 * sizeof(double), s));
+    launchPcgDot2(pk, Ap, pk, Ap, nCam, dots + 2, s);
+    launchPcgStep(x, r, pk, Ap, dots + 0, dots + 2, nCam, s);       // alpha = z.r / p.Ap, on the device
+    precond(r, z);                                                   // z_{k+1} (one more than the reference when it stops here)
+    VB_CUDA(cudaMemsetAsync(dots + 4, 0, 2 * sizeof(double), s));
+    launchPcgDot2(z, r, r, r, nCam, dots + 4, s);
+    readDots(h, 6);
+    rel = std::sqrt(h[5]) / rk0norm;
+    if (!std::isfinite(rel)) break;   // the reference's PCG does not check either; the LM loop rejects the useless step
+    if (rel < p->pcgDesiredResidual) break;
+    if (k + 1 >= p->pcgMaxIterations) break;
+    launchPcgDir(pk, z, dots + 4, dots + 0, nCam, s);                // beta = z1.r1 / z.r
+    VB_CUDA(cudaMemcpyAsync(dots, dots + 4, sizeof(double), cudaMemcpyDeviceToDevice, s));
+    k++;
+  }
+  if (rk0norm > 0.0) { p->pcgLastIterations = k + 1; p->pcgLastResidual = rel; }
+  VB_CUDA(cudaMemcpyAsync(cam, x, nCam * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  launchSolveLandmarksBwd(p->sol, p->hess, vec, s);
+  p->partial[vec == p->step ? 0 : vec == p->gradNew ? 1 : 2] = false;
+}
 #define VB_CATCH_NUMERIC                                                             \
   }                                                                                  \
   catch (const std::domain_error& ex) { g_err = ex.what(); return VB_ERR_NUMERIC; } \
@@ -1360,6 +1447,33 @@ static void solveAsync(vb_problem* p, double* vec) {
   catch (const std::exception& ex) { g_err = ex.what(); return VB_ERR_CUDA; }        \
   return VB_OK;
 
+static void setLinearSolver(vb_problem* p, int solverType, int maxIterations, double desiredResidual) {
+  if (solverType == VB_SOLVER_PCG_GAUSS_SEIDEL || solverType == VB_SOLVER_PCG_LOWER_PREC_SOLVE)
+    throw std::invalid_argument("Solver_PCG_GaussSeidel / Solver_PCG_LowerPrecSolve need BaSpaCho's pseudoFactorFrom / float factorFrom, whose source "
+                                "is not part of the reference tree: not built (DESIGN.md section 9)");
+  if (solverType < VB_SOLVER_DIRECT || solverType > VB_SOLVER_PCG_LOWER_PREC_SOLVE)
+    throw std::invalid_argument("Unknown preconditioner " + std::to_string(solverType));   // Optimizer.cpp:243-245
+  if (solverType != VB_SOLVER_DIRECT) {
+    if (p->nranks > 1) throw std::invalid_argument("the PCG path runs on an unsharded problem only");
+    if (maxIterations < 1 || !(desiredResidual >= 0.0)) throw std::invalid_argument("pcg_max_iterations >= 1 and pcg_desired_residual >= 0 required");
+    p->pcgMaxIterations = maxIterations; p->pcgDesiredResidual = desiredResidual;
+  }
+  if (solverType != p->solverType) p->fwdFused = nullptr;
+  p->solverType = solverType;
+}
+int vb_set_linear_solver(vb_problem* p, int32_t solver_type, int32_t pcg_max_iterations, double pcg_desired_residual) {
+  VB_TRY
+  requireProblem(p);
+  setLinearSolver(p, solver_type, pcg_max_iterations, pcg_desired_residual);
+  VB_CATCH_NUMERIC
+}
+int vb_pcg_last(const vb_problem* p, int32_t* iterations, double* residual) {
+  VB_TRY
+  requireProblem(const_cast<vb_problem*>(p));
+  if (iterations) *iterations = p->pcgLastIterations;
+  if (residual) *residual = p->pcgLastResidual;
+  VB_CATCH_NUMERIC
+}
 int vb_factor(vb_problem* p) {
   VB_TRY
   requireProblem(p);
@@ -1487,6 +1601,7 @@ int vb_optimize_ex(vb_problem* p, const vb_settings* st, vb_optimize_hooks* hook
   if (!st) throw std::invalid_argument("null settings");
   if (hooks && hooks->pre_step && hooks->sync_kinds && !hooks->host_vars) throw std::invalid_argument("sync_kinds without host_vars");
   if (hooks) hooks->trace_len = 0;
+  setLinearSolver(p, st->solver_type, st->pcg_max_iterations, st->pcg_desired_residual);   // Optimizer.cpp:774 (initSolverData)
   using clk = std::chrono::steady_clock;
   auto since = [](clk::time_point a) { return std::chrono::duration<double>(clk::now() - a).count(); };
   cudaStream_t s = p->ctx->stream;
@@ -1697,7 +1812,11 @@ int vb_optimize_ex(vb_problem* p, const vb_settings* st, vb_optimize_hooks* hook
       t += std::string(" ") + smiley + " cost: " + fmtG(prevCost) + " -> " + fmtG(newCost) + " (" + fmtPercent(newCost / prevCost - 1.0, 2) +
            "), t: " + fmtDuration(secTotal) + "\n";
       t += "     n." + std::to_string(iterationNum) + "; g/H: " + fmtDuration(secGradHess) + ", solver:\n";
-      t += "    direct, factor: " + fmtDuration(secFactor) + ", solve: " + fmtDuration(secSolve) + "\n";
+      if (p->solverType == VB_SOLVER_DIRECT) t += "    direct, factor: " + fmtDuration(secFactor) + ", solve: " + fmtDuration(secSolve) + "\n";
+      else   // Optimizer.cpp:298-327 (the per-stage split of the reference's report is folded into the two totals)
+        t += std::string("    semi-precond(") + (p->solverType == VB_SOLVER_PCG_JACOBI ? "jacobi" : "trivial") + "), factor[elims] + init precond: " +
+             fmtDuration(secFactor) + "\n    solve[elims] + reduced-PCG + backsubst: " + fmtDuration(secSolve) + " (iters: " +
+             std::to_string(p->pcgLastIterations) + ", residual: " + fmtG(p->pcgLastResidual) + ")\n";
       t += "     lmbd: " + fmtG(damping) + ", relRed: " + fmtPercent(ratioReductionToExpected) + ", improv: " + fmtG(costReduction) +
            ", modelImprov: " + fmtG(modelCostReduction) + "\n";
       t += "    |G|: " + fmtG(gradNorm) + ", |S|: " + fmtG(stepNorm) + ", |s/v|_inf: " + fmtG(ratios[0]) + ", |_2: " + fmtG(ratios[1]) +

@@ -45,7 +45,8 @@ class vb_settings(C.Structure):
         "min_step_factor_for_good", "absolute_cost_tolerance", "relative_cost_tolerance",
         "variables_tolerance")] + [(n, C.c_int32) for n in (
         "max_step_factor_attempts", "try_sub_step", "stop_if_no_improvement_for",
-        "distance_from_troubled_iteration", "max_num_iterations", "verbose")]
+        "distance_from_troubled_iteration", "max_num_iterations", "verbose",
+        "solver_type", "pcg_max_iterations")] + [("pcg_desired_residual", C.c_double)]
 
 
 class vb_summary(C.Structure):
@@ -92,11 +93,14 @@ def trace_records(arr, n):
     return [{name: getattr(arr[i], name) for name, _ in vb_iter_trace._fields_} for i in range(n)]
 
 
+SOLVER_DIRECT, SOLVER_PCG_TRIVIAL, SOLVER_PCG_JACOBI, SOLVER_PCG_GAUSS_SEIDEL, SOLVER_PCG_LOWER_PREC_SOLVE = range(5)
+
+
 def default_settings(max_iterations=250):
     """Optimizer::Settings defaults (lib/small_thing/Optimizer.h:40-78) with the ark_vi_ba
     overrides (viba/common/Settings.cpp:313-320); SURVEY.md App. A."""
     return vb_settings(1e-5, 2.5, 0.7, 1.5, 1e-9, 1e8, 0.3, 0.3, 0.7, 1e-8, 1e-10, 1e-5,
-                       2, 1, 3, 3, max_iterations, 0)
+                       2, 1, 3, 3, max_iterations, 0, SOLVER_DIRECT, 40, 1e-10)
 
 
 class FactorStore:

@@ -158,6 +158,7 @@ int run(int argc, char** argv) {
   int optimizeIters = -1;
   if (argc >= 5 && std::string(argv[3]) == "--optimize") optimizeIters = std::atoi(argv[4]);
   const bool withCallback = argc >= 6 && std::string(argv[5]) == "--callback";
+  const bool withPcg = argc >= 6 && std::string(argv[5]) == "--pcg-jacobi";   // Settings::solverType = Solver_PCG_Jacobi
   const bool withFacade = argc >= 4 && std::string(argv[3]) == "--facade";
 
   Reader in(argv[1]);
@@ -397,11 +398,12 @@ int run(int argc, char** argv) {
         if (calib) { calib->getData(rec.evalPoint.data()); calibSeen = rec.evalPoint[6]; }
       };
       Optimizer::Settings bad = st;
-      bad.solverType = Optimizer::Solver_PCG_Jacobi;
+      bad.solverType = Optimizer::Solver_PCG_GaussSeidel;   // BaSpaCho's pseudoFactorFrom: not built, must be refused up front
       bool threw = false;
       try { opt.optimize(bad); } catch (const std::runtime_error&) { threw = true; }
-      if (!threw) throw std::runtime_error("Solver_PCG_Jacobi was accepted");
+      if (!threw || callbacks != 0) throw std::runtime_error("Solver_PCG_GaussSeidel was accepted");
     }
+    if (withPcg) { st.solverType = Optimizer::Solver_PCG_Jacobi; st.pcgMaxIterations = 8000; st.pcgDesiredResidual = 1e-12; }
     Optimizer::Summary sm = opt.optimize(st);
     const double cost1 = opt.computeCost();
     out.one<double>(sm.initialCost);

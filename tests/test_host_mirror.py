@@ -209,6 +209,33 @@ def test_mirror_optimize_matches_python_path(name, iters, mirror_bin, tmp_path):
 
 
 @pytest.mark.gpu
+def test_mirror_optimize_with_pcg_jacobi(mirror_bin, tmp_path):
+    """Settings::solverType = Solver_PCG_Jacobi through the C++ mirror (Optimizer.cpp:232-331): the same run as the Python
+    path with the same settings, and the direct solver's optimum"""
+    iters = 6
+    s = synth.make_session(**synth.CONFIGS["small_rs"])
+    g = merged(s.graph, s.ids["point"])
+    dump(g, s.ids["point"], tmp_path / "in.bin")
+    r = subprocess.run([mirror_bin, str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "--optimize", str(iters), "--pcg-jacobi"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = np.fromfile(tmp_path / "out.bin", np.float64)
+    init_cost, final_cost, n_it = out[:3]
+    vals = out[5:]
+    ctx = capi.Context(0)
+    st = G.default_settings(iters)
+    p = capi.Problem(ctx, g); direct = p.optimize(st); p.close()
+    st.solver_type, st.pcg_max_iterations, st.pcg_desired_residual = G.SOLVER_PCG_JACOBI, 8000, 1e-12
+    p = capi.Problem(ctx, g); summ = p.optimize(st); ref = p.vars; last = p.pcg_last(); p.close()
+    ctx.close()
+    assert last[0] > 1 and last[1] < 1e-12
+    assert int(n_it) == summ.num_iterations == direct.num_iterations
+    assert abs(final_cost - summ.final_cost) <= 1e-8 * abs(summ.final_cost)
+    assert abs(final_cost - direct.final_cost) <= 1e-6 * abs(direct.final_cost)
+    assert vals.size == ref.size and np.abs(vals - ref).max() <= 1e-6
+
+
+@pytest.mark.gpu
 def test_mirror_pre_step_callback_matches_oracle(oracle, mirror_bin, tmp_path):
     """Settings::preStepCallback through the C++ mirror: user code rewrites a preintegration record at iteration 2 from
     the calibration it reads in its own Variable at that moment; the oracle driven the same way gives the same run"""

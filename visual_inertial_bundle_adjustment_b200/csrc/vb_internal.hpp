@@ -156,7 +156,8 @@ void launchPreintRefresh(const int64_t* timeNs, const float* gyro, const float* 
                          const int64_t* calibOff, const uint32_t* calibFlags, const int64_t* startUs, const int64_t* endUs, int64_t nFactors,
                          const double* noise6, double* scratch, double* records, double* cov, double* omegaAtEnd, int* status, cudaStream_t st);
 // kernels_pcg.cu (iterative path)
-void launchCamSymMv(const DevSolver& d, const double* hess, const double* v, double* u, int nLumps, int maxBelow, int maxWidth, cudaStream_t s);
+int camSymMvRows();
+void launchCamSymMv(const DevSolver& d, const double* hess, const int2* tasks, int nTasks, const double* v, double* u, int maxWidth, cudaStream_t s);
 void launchJacobiInit(const DevSolver& d, const double* hess, const int64_t* jacOff, double* jac, int* errFlag, cudaStream_t s);
 void launchJacobiApply(const DevSolver& d, const int64_t* jacOff, const double* jac, const double* in, double* out, cudaStream_t s);
 void launchPcgDot2(const double* a, const double* b, const double* c, const double* dd, int64_t n, double* out, cudaStream_t s);

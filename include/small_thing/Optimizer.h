@@ -25,9 +25,8 @@
 // read: InitCalibration.cpp:316-325, InertialFactors.cpp:19-43) are pulled from the device into the user's Variables
 // first, and whatever the callback changed in the user-owned records (preintegration records, rolling-shutter tables,
 // factor constants) is pushed to the device after it.  Settings::log receives the reference's per-iteration text
-// (Optimizer.cpp:1058-1076).  Settings::solverType: Solver_Direct, Solver_PCG_Trivial and Solver_PCG_Jacobi run on the
-// device (PCG on the reduced camera system, Optimizer.cpp:232-331); Solver_PCG_GaussSeidel / Solver_PCG_LowerPrecSolve
-// need BaSpaCho's pseudoFactorFrom / float factorFrom (source absent from the reference tree) and throw.
+// (Optimizer.cpp:1058-1076).  Settings::solverType: all five types run on the device (PCG on the reduced camera system,
+// Optimizer.cpp:232-331; for the Gauss-Seidel and lower-precision preconditioners see viba_b200.h, vb_settings).
 //
 // Differences, all forced by the device path: (1) factor types come from the catalogue of
 // small_thing/Factor.h, not arbitrary functors; (2) store order is first-use order (the reference's is
@@ -86,7 +85,7 @@ class Optimizer {
   struct Settings {   // Optimizer.h:40-91, same defaults
     int maxNumIterations = 50;
     unsigned int numThreads = 8;   // ignored: one host thread drives one GPU context
-    SolverType solverType = Solver_Direct;   // GaussSeidel / LowerPrecSolve throw (see the header comment)
+    SolverType solverType = Solver_Direct;
     int pcgMaxIterations = 40;
     double pcgDesiredResidual = 1e-10;
     double absoluteCostTolerance = 1e-8;
@@ -262,7 +261,7 @@ class Optimizer {
     vs.distance_from_troubled_iteration = s.distanceFromTroubledIteration;
     vs.max_num_iterations = s.maxNumIterations;
     vs.verbose = s.verbose ? 1 : 0;
-    vs.solver_type = (int32_t)s.solverType;   // same numbering as VB_SOLVER_*; the library rejects the two it does not build
+    vs.solver_type = (int32_t)s.solverType;   // same numbering as VB_SOLVER_*; the library rejects anything else
     vs.pcg_max_iterations = s.pcgMaxIterations;
     vs.pcg_desired_residual = s.pcgDesiredResidual;
     vb_summary out{};

@@ -101,11 +101,14 @@ typedef struct vb_settings {
   int32_t stop_if_no_improvement_for, distance_from_troubled_iteration, max_num_iterations;
   int32_t verbose;
   /* Optimizer::Settings::{solverType, pcgMaxIterations, pcgDesiredResidual} (Optimizer.h:43-45).  solver_type:
-   * VB_SOLVER_DIRECT (0), VB_SOLVER_PCG_TRIVIAL (1), VB_SOLVER_PCG_JACOBI (2) run on the device (SURVEY.md 8 f3:
-   * landmark Schur elimination, then preconditioned conjugate gradients on the reduced camera system,
-   * Optimizer.cpp:232-331, PCG.cpp:15-97, Preconditioner.h:29-116); VB_SOLVER_PCG_GAUSS_SEIDEL (3) and
-   * VB_SOLVER_PCG_LOWER_PREC_SOLVE (4) are BaSpaCho's pseudoFactorFrom / float factorFrom, whose source is not in the
-   * reference tree: VB_ERR_ARG. */
+   * VB_SOLVER_DIRECT (0) or one of the PCG types (landmark Schur elimination, then preconditioned
+   * conjugate gradients on the reduced camera system, Optimizer.cpp:232-331, PCG.cpp:15-97) with the preconditioners of
+   * Preconditioner.h: VB_SOLVER_PCG_TRIVIAL (1, identity, :29-47), VB_SOLVER_PCG_JACOBI (2, param-sized diagonal blocks,
+   * :52-116), VB_SOLVER_PCG_GAUSS_SEIDEL (3, :118-158: BaSpaCho's pseudo-factor, restated as the Cholesky sweep without
+   * Schur updates = symmetric block Gauss-Seidel over the supernode diagonal blocks; BaSpaCho's source is absent, so
+   * the block partition and sweep order are this library's), VB_SOLVER_PCG_LOWER_PREC_SOLVE (4, :160-245: complete
+   * factor of a float-rounded copy of the reduced system with the reference's diagonal-raise retry; the data and the
+   * preconditioned vectors are rounded to float, the arithmetic on them is fp64).  Anything else: VB_ERR_ARG. */
   int32_t solver_type, pcg_max_iterations;
   double pcg_desired_residual;
 } vb_settings;

@@ -271,6 +271,16 @@ int orc_pcg_last(OrcHandle* h, int* iterations, double* residual) {
   *iterations = h->sol.pcgLastIterations; *residual = h->sol.pcgLastResidual;
   return 0;
 }
+// PCG on a dense symmetric system, identity (0) or block-Jacobi (1) preconditioner: the reduced system of the reference's
+// own PCG test (lib/small_thing/tests/TestPCG.cpp:29-131), whose recipe tests/test_pcg.py restates
+int orc_pcg_dense(int64_t n, const double* A, const double* b, const int32_t* block_size, int64_t n_blocks, int precond,
+                  double desired_residual, int max_iterations, double* x, int* iterations, double* residual) {
+  try {
+    const orc::PcgResult r = orc::pcgDense(n, A, b, block_size, n_blocks, precond, desired_residual, max_iterations, x);
+    *iterations = r.numIterations; *residual = r.relativeResidual;
+    return 0;
+  } catch (const std::exception&) { return 1; }
+}
 // refinePoints (viba/problem/PointRefinement.cpp:171-196): stats6 = {totalStartCost, totalEndCost, nPoints, nFailures,
 // nTotalIterations, nAtLeastOneIt}; per_point (may be null) = {startCost, endCost, nIts} per refined landmark
 int orc_refine_points(OrcHandle* h, double* stats6, double* per_point) {

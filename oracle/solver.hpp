@@ -9,6 +9,7 @@
 // (no reference source or golden file fixes them); the solution vector is ordering independent
 // up to rounding, which is what tests compare (rel 1e-9).
 #pragma once
+#include "pcg.hpp"
 #include <queue>
 #include <numeric>
 #include "engine.hpp"
@@ -53,7 +54,7 @@ struct SchurSkylineSolver {
     }
     for (auto& a : adj) { std::sort(a.begin(), a.end()); a.erase(std::unique(a.begin(), a.end()), a.end()); }
     // reverse Cuthill-McKee over all components, seeds = min degree unvisited
-    std::vector<int64_t> orderC; orderC.reserve(nC);
+    orderC.clear(); orderC.reserve(nC);
     std::vector<char> vis(nC, 0);
     std::vector<int64_t> byDeg(nC);
     std::iota(byDeg.begin(), byDeg.end(), 0);
@@ -90,6 +91,7 @@ struct SchurSkylineSolver {
     for (int64_t i = 0; i < nr; i++) { const double w = double(i - first[i]); flopsChol += w * w; }
   }
   std::vector<int64_t> rowOfEntry;
+  std::vector<int64_t> orderC;   // camera blocks in the order of the reduced system (reverse Cuthill-McKee)
 
   inline double& at(int64_t i, int64_t j) { return S[rowStart[i] + (j - first[i])]; } // i >= j >= first[i]
 
@@ -233,20 +235,27 @@ struct SchurSkylineSolver {
   }
 
   // ---- iterative path: Optimizer.cpp:232-331 (PCG on the reduced camera system), PCG.cpp:15-97, and the two
-  // preconditioners whose definition is in the reference tree: IdentityPrecond and BlockJacobiPrecond
-  // (Preconditioner.h:52-116: the param-sized diagonal blocks, Cholesky-factored).  BlockGaussSeidelPrecond is
-  // Solver::pseudoFactorFrom and LowerPrecSolvePrecond a float factorFrom of BaSpaCho, whose source is absent.
+  // Preconditioners (Preconditioner.h:29-245).  IdentityPrecond and BlockJacobiPrecond (the param-sized diagonal blocks,
+  // Cholesky-factored) are defined in the reference tree.  BlockGaussSeidelPrecond is Solver::pseudoFactorFrom +
+  // solveLFrom + solveLtFrom of BaSpaCho (source absent): restated here from its call site, its name and its comment
+  // ("param-sized blocks are inverted") as the symmetric block Gauss-Seidel operator M = (D + E) D^-1 (D + E)^T over the
+  // param blocks (D block diagonal, E strict block lower part) — the operator a Cholesky sweep without Schur updates
+  // yields — and checked against the bound the reference's own test puts on it (TestPCG.cpp:139-141; parity unpinned
+  // beyond that).  LowerPrecSolvePrecond (:160-245) is fully defined by its call site: the Cholesky factor of the float
+  // copy of the system, diagonal raised by d -> d (1 + eps) + eps, eps = 1e-8, 3e-8, ... while the factor is not finite,
+  // applied in float.
   bool schurOnly = false, factoredDirect = false;
-  int pcgPrecond = 0;            // 0 identity, 1 block Jacobi
+  int pcgPrecond = 0;            // 0 identity, 1 block Jacobi, 2 block Gauss-Seidel, 3 lower-precision solve
   int pcgMaxIterations = 40; double pcgDesiredResidual = 1e-10;
   int pcgLastIterations = 0; double pcgLastResidual = 0;
-  // Optimizer::Settings::solverType (Optimizer.h:30-36,43): 0 direct, 1 PCG identity, 2 PCG block Jacobi
+  // Optimizer::Settings::solverType (Optimizer.h:30-36,43): 0 direct, 1 PCG identity, 2 Jacobi, 3 Gauss-Seidel, 4 lower-prec
   void setLinearSolver(int solverType, int maxIterations, double desiredResidual) {
-    if (solverType < 0 || solverType > 2)
-      throw std::runtime_error("oracle: Solver_PCG_GaussSeidel / LowerPrecSolve need BaSpaCho's pseudoFactorFrom / float factorFrom (source absent)");
-    schurOnly = solverType != 0; pcgPrecond = solverType == 2 ? 1 : 0;
+    if (solverType < 0 || solverType > 4) throw std::runtime_error("Unknown preconditioner " + std::to_string(solverType));   // Optimizer.cpp:243-245
+    schurOnly = solverType != 0; pcgPrecond = solverType > 0 ? solverType - 1 : 0;
     pcgMaxIterations = maxIterations; pcgDesiredResidual = desiredResidual;
   }
+  std::vector<float> Sf;         // lower-precision solve: float envelope Cholesky factor of the reduced system
+  float lowPrecEpsilon = 0;      // the diagonal raise its last init ended with (0: none was needed)
   std::vector<double> jac;       // per camera block: Cholesky factor of its diagonal block (d x d, lower), at jacOff
   std::vector<int64_t> jacOff;
 
@@ -265,57 +274,119 @@ struct SchurSkylineSolver {
     jacOff.assign(nC + 1, 0);
     for (int64_t c = 0; c < nC; c++) jacOff[c + 1] = jacOff[c] + (int64_t)e.P.blockSize[nP + c] * e.P.blockSize[nP + c];
     jac.assign(jacOff[nC], 0.0);
-    if (pcgPrecond != 1) return;
+    if (pcgPrecond == 3) { initLowPrec(); return; }
+    if (pcgPrecond != 1 && pcgPrecond != 2) return;
     for (int64_t c = 0; c < nC; c++) {
       const int d = e.P.blockSize[nP + c];
       double* L = &jac[jacOff[c]];
       for (int a = 0; a < d; a++) for (int b = 0; b <= a; b++) L[a * d + b] = S[rowStart[cstart[c] + a] + (cstart[c] + b - first[cstart[c] + a])];
-      for (int a = 0; a < d; a++) {   // in-place LLT
-        for (int b = 0; b < a; b++) { double t = L[a * d + b]; for (int k = 0; k < b; k++) t -= L[a * d + k] * L[b * d + k]; L[a * d + b] = t / L[b * d + b]; }
-        double t = L[a * d + a];
-        for (int k = 0; k < a; k++) t -= L[a * d + k] * L[a * d + k];
-        if (!(t > 0)) throw std::runtime_error("oracle: Jacobi block not positive definite");
-        L[a * d + a] = std::sqrt(t);
+      jacobiFactorBlock(L, d);
+    }
+  }
+  // LowerPrecSolvePrecond::init (Preconditioner.h:178-218)
+  void initLowPrec() {
+    float epsilon = 0.0f;
+    lowPrecEpsilon = 0.0f;
+    while (true) {
+      Sf.assign(S.begin(), S.end());
+      if (epsilon > 0) {
+        for (int64_t i = 0; i < nr; i++) { float& d = Sf[rowStart[i] + (i - first[i])]; d *= 1.0f + epsilon; d += epsilon; }
+        lowPrecEpsilon = epsilon;
+        epsilon *= 3.0f;
+      } else {
+        epsilon = 1e-8f;
       }
+      bool finite = true;
+      for (int64_t i = 0; i < nr && finite; i++) {   // the envelope Cholesky of factor(), in float
+        float* Li = &Sf[rowStart[i]];
+        const int64_t fi = first[i];
+        for (int64_t j = fi; j < i; j++) {
+          const float* Lj = &Sf[rowStart[j]];
+          const int64_t fj = first[j], k0 = std::max(fi, fj);
+          float t = Li[j - fi];
+          for (int64_t k = k0; k < j; k++) t -= Li[k - fi] * Lj[k - fj];
+          Li[j - fi] = t / Lj[j - fj];
+        }
+        float d = Li[i - fi];
+        for (int64_t k = 0; k < i - fi; k++) d -= Li[k] * Li[k];
+        Li[i - fi] = std::sqrt(d);
+        finite = std::isfinite(Li[i - fi]) && Li[i - fi] > 0.0f;
+      }
+      if (finite) return;
+      if (epsilon > 1e3f) throw std::runtime_error("oracle: lower-precision factor did not become finite");
     }
   }
   void applyPrecond(const std::vector<double>& r, std::vector<double>& z) const {
     z = r;
-    if (pcgPrecond != 1) return;
     const Engine& e = *E;
-    for (int64_t c = 0; c < nC; c++) {
-      const int d = e.P.blockSize[nP + c];
-      const double* L = &jac[jacOff[c]];
-      double* x = &z[cstart[c]];
-      for (int a = 0; a < d; a++) { double t = x[a]; for (int k = 0; k < a; k++) t -= L[a * d + k] * x[k]; x[a] = t / L[a * d + a]; }
-      for (int a = d - 1; a >= 0; a--) { double t = x[a]; for (int k = a + 1; k < d; k++) t -= L[k * d + a] * x[k]; x[a] = t / L[a * d + a]; }
+    if (pcgPrecond == 2) {   // (D + E) w = r ; u = D w ; (D + E)^T z = u
+      // blocks in the order of the reduced system (orderC), not in registration order
+      for (int64_t oc = 0; oc < nC; oc++) {
+        const int64_t c = orderC[oc];
+        const int d = e.P.blockSize[nP + c];
+        for (int a = 0; a < d; a++) {
+          const int64_t i = cstart[c] + a;
+          const double* Si = &S[rowStart[i]];
+          double t = z[i];
+          for (int64_t j = first[i]; j < cstart[c]; j++) t -= Si[j - first[i]] * z[j];
+          z[i] = t;
+        }
+        jacobiSolveBlock(&jac[jacOff[c]], d, &z[cstart[c]]);
+      }
+      for (int64_t c = 0; c < nC; c++) {   // u = D w
+        const int d = e.P.blockSize[nP + c];
+        double w[32], u[32];
+        for (int a = 0; a < d; a++) w[a] = z[cstart[c] + a];
+        for (int a = 0; a < d; a++) {
+          const int64_t i = cstart[c] + a;
+          double t = 0;
+          for (int b = 0; b < d; b++) {
+            const int64_t j = cstart[c] + b;
+            t += (b <= a ? S[rowStart[i] + (j - first[i])] : S[rowStart[j] + (i - first[j])]) * w[b];
+          }
+          u[a] = t;
+        }
+        for (int a = 0; a < d; a++) z[cstart[c] + a] = u[a];
+      }
+      for (int64_t oc = nC - 1; oc >= 0; oc--) {
+        const int64_t c = orderC[oc];
+        const int d = e.P.blockSize[nP + c];
+        jacobiSolveBlock(&jac[jacOff[c]], d, &z[cstart[c]]);
+        for (int a = 0; a < d; a++) {
+          const int64_t i = cstart[c] + a;
+          const double* Si = &S[rowStart[i]];
+          const double zi = z[i];
+          for (int64_t j = first[i]; j < cstart[c]; j++) z[j] -= Si[j - first[i]] * zi;
+        }
+      }
+      return;
     }
+    if (pcgPrecond == 3) {   // LowerPrecSolvePrecond::operator() (:220-239): cast, two float triangular solves, cast back
+      std::vector<float> y(r.begin(), r.end());
+      for (int64_t i = 0; i < nr; i++) {
+        const float* Li = &Sf[rowStart[i]];
+        float t = y[i];
+        for (int64_t k = first[i]; k < i; k++) t -= Li[k - first[i]] * y[k];
+        y[i] = t / Li[i - first[i]];
+      }
+      for (int64_t i = nr - 1; i >= 0; i--) {
+        const float* Li = &Sf[rowStart[i]];
+        y[i] /= Li[i - first[i]];
+        const float yi = y[i];
+        for (int64_t k = first[i]; k < i; k++) y[k] -= Li[k - first[i]] * yi;
+      }
+      for (int64_t i = 0; i < nr; i++) z[i] = (double)y[i];
+      return;
+    }
+    if (pcgPrecond != 1) return;
+    for (int64_t c = 0; c < nC; c++) jacobiSolveBlock(&jac[jacOff[c]], e.P.blockSize[nP + c], &z[cstart[c]]);
   }
   // PCG::solve (PCG.cpp:15-97): x0 = 0, stops on |r_k| / |r_0| < desired or at maxIterations
   void pcgSolve(const std::vector<double>& b, std::vector<double>& x) {
-    std::vector<double> xk(nr, 0.0), rk(b), zk, pk, Apk, zk1;
-    applyPrecond(rk, zk);
-    pk = zk;
-    auto dot = [&](const std::vector<double>& a, const std::vector<double>& c) { double s = 0; for (int64_t i = 0; i < nr; i++) s += a[i] * c[i]; return s; };
-    const double rk0norm = std::sqrt(dot(rk, rk));
-    double zk_rk = dot(zk, rk), rel = 0.0;
-    int k = 0;
-    while (true) {
-      reducedMatVec(pk, Apk);
-      const double alpha = zk_rk / dot(pk, Apk);
-      for (int64_t i = 0; i < nr; i++) { xk[i] += pk[i] * alpha; rk[i] -= Apk[i] * alpha; }
-      rel = std::sqrt(dot(rk, rk)) / rk0norm;
-      if (rel < pcgDesiredResidual) break;
-      if (k + 1 >= pcgMaxIterations) break;
-      applyPrecond(rk, zk1);
-      const double zk1_rk1 = dot(zk1, rk);
-      const double beta = zk1_rk1 / zk_rk;
-      for (int64_t i = 0; i < nr; i++) pk[i] = zk1[i] + pk[i] * beta;
-      zk_rk = zk1_rk1;
-      k++;
-    }
-    x = xk;
-    pcgLastIterations = k + 1; pcgLastResidual = rel;
+    const PcgResult r = pcgRun([&](const std::vector<double>& v, std::vector<double>& u) { reducedMatVec(v, u); },
+                               [&](const std::vector<double>& rr, std::vector<double>& z) { applyPrecond(rr, z); },
+                               b, pcgDesiredResidual, pcgMaxIterations, x);
+    pcgLastIterations = r.numIterations; pcgLastResidual = r.relativeResidual;
   }
 
   // Solver::solve (Optimizer.cpp:228) with the factor computed by factor(H)

@@ -4,7 +4,8 @@ named workload, beside the direct factor + solve on the same damped system.
 
     python profiles/pcg_bench.py [workload] > profiles/r02_pcg_<workload>.json
 
-One PCG iteration = one symmetric matrix-vector product over the unfactored supernode panels (every camera-panel double
+Preconditioners: identity, block Jacobi, block Gauss-Seidel (pseudo-factor + two supernodal solves per application) and
+lower-precision solve (complete factor of the float-rounded copy).  One PCG iteration = one symmetric matrix-vector product over the unfactored supernode panels (every camera-panel double
 read once: HBM-bound, algorithmic bytes = 8 x camera-panel doubles) + preconditioner + 2 fused dot kernels + 2 axpy
 kernels + one 48-byte read-back.  Wall-clock around calls that end in a stream synchronize; not under a profiler."""
 import json
@@ -42,8 +43,11 @@ def main():
         tf = timed(p.factor); ts = timed(lambda: p.solve(0))
     direct = p.step.copy()
     out["direct"] = {"factor_ms": tf, "solve_ms": ts}
-    for solver, label in ((G.SOLVER_PCG_JACOBI, "jacobi"), (G.SOLVER_PCG_TRIVIAL, "trivial")):
-        for max_it, res in ((40, 1e-10), (2000, 1e-8)):
+    plans = [(G.SOLVER_PCG_JACOBI, "jacobi", ((40, 1e-10), (2000, 1e-8))), (G.SOLVER_PCG_TRIVIAL, "trivial", ((40, 1e-10), (2000, 1e-8))),
+             (G.SOLVER_PCG_GAUSS_SEIDEL, "gauss-seidel", ((40, 1e-10), (400, 1e-8))),
+             (G.SOLVER_PCG_LOWER_PREC_SOLVE, "lower-prec-solve", ((40, 1e-10),))]
+    for solver, label, settings in plans:
+        for max_it, res in settings:
             for _ in range(2):
                 p.set_linear_solver(solver, max_it, res); system()
                 tf = timed(p.factor); ts = timed(lambda: p.solve(0))

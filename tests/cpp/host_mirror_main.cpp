@@ -159,6 +159,7 @@ int run(int argc, char** argv) {
   if (argc >= 5 && std::string(argv[3]) == "--optimize") optimizeIters = std::atoi(argv[4]);
   const bool withCallback = argc >= 6 && std::string(argv[5]) == "--callback";
   const bool withPcg = argc >= 6 && std::string(argv[5]) == "--pcg-jacobi";   // Settings::solverType = Solver_PCG_Jacobi
+  const bool withGs = argc >= 6 && std::string(argv[5]) == "--pcg-gauss-seidel";
   const bool withFacade = argc >= 4 && std::string(argv[3]) == "--facade";
 
   Reader in(argv[1]);
@@ -398,12 +399,13 @@ int run(int argc, char** argv) {
         if (calib) { calib->getData(rec.evalPoint.data()); calibSeen = rec.evalPoint[6]; }
       };
       Optimizer::Settings bad = st;
-      bad.solverType = Optimizer::Solver_PCG_GaussSeidel;   // BaSpaCho's pseudoFactorFrom: not built, must be refused up front
+      bad.solverType = (Optimizer::SolverType)9;   // "Unknown preconditioner" (Optimizer.cpp:243-245): refused up front
       bool threw = false;
       try { opt.optimize(bad); } catch (const std::runtime_error&) { threw = true; }
-      if (!threw || callbacks != 0) throw std::runtime_error("Solver_PCG_GaussSeidel was accepted");
+      if (!threw || callbacks != 0) throw std::runtime_error("an unknown solver type was accepted");
     }
     if (withPcg) { st.solverType = Optimizer::Solver_PCG_Jacobi; st.pcgMaxIterations = 8000; st.pcgDesiredResidual = 1e-12; }
+    if (withGs) { st.solverType = Optimizer::Solver_PCG_GaussSeidel; st.pcgMaxIterations = 8000; st.pcgDesiredResidual = 1e-12; }
     Optimizer::Summary sm = opt.optimize(st);
     const double cost1 = opt.computeCost();
     out.one<double>(sm.initialCost);

@@ -149,6 +149,20 @@ class Oracle:
         self.lib.orc_pcg_last(self.h, C.byref(it), C.byref(res))
         return it.value, res.value
 
+    @staticmethod
+    def pcg_dense(lib, A, b, block_size, precond, desired_residual, max_iterations):
+        """PCG::solve on a dense symmetric system with IdentityPrecond (0) / BlockJacobiPrecond (1): (x, iterations, residual)"""
+        A = np.ascontiguousarray(A, np.float64); b = np.ascontiguousarray(b, np.float64)
+        bs = np.ascontiguousarray(block_size, np.int32)
+        x = np.zeros(b.size); it = C.c_int(0); res = C.c_double(0)
+        lib.orc_pcg_dense.argtypes = [C.c_int64, _dp, _dp, C.POINTER(C.c_int32), C.c_int64, C.c_int, C.c_double, C.c_int, _dp,
+                                      C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        rc = lib.orc_pcg_dense(b.size, dptr(A), dptr(b), bs.ctypes.data_as(C.POINTER(C.c_int32)), bs.size, int(precond),
+                               float(desired_residual), int(max_iterations), dptr(x), C.byref(it), C.byref(res))
+        if rc != 0:
+            raise RuntimeError("orc_pcg_dense failed")
+        return x, it.value, res.value
+
     def refine_points(self):
         """refinePoints on the oracle: (stats dict, per-point [n, 3]); the landmark variables are updated"""
         n = len(set(int(v) for st in self.g.stores if st.type in (G.F_VISUAL, G.F_VISUAL_RS) for v in st.vars[:, 0]))

@@ -209,14 +209,15 @@ def test_mirror_optimize_matches_python_path(name, iters, mirror_bin, tmp_path):
 
 
 @pytest.mark.gpu
-def test_mirror_optimize_with_pcg_jacobi(mirror_bin, tmp_path):
-    """Settings::solverType = Solver_PCG_Jacobi through the C++ mirror (Optimizer.cpp:232-331): the same run as the Python
-    path with the same settings, and the direct solver's optimum"""
+@pytest.mark.parametrize("flag,solver_type", [("--pcg-jacobi", G.SOLVER_PCG_JACOBI), ("--pcg-gauss-seidel", G.SOLVER_PCG_GAUSS_SEIDEL)])
+def test_mirror_optimize_with_pcg(flag, solver_type, mirror_bin, tmp_path):
+    """Settings::solverType = Solver_PCG_Jacobi / Solver_PCG_GaussSeidel through the C++ mirror (Optimizer.cpp:232-331): the
+    same run as the Python path with the same settings, and the direct solver's optimum"""
     iters = 6
     s = synth.make_session(**synth.CONFIGS["small_rs"])
     g = merged(s.graph, s.ids["point"])
     dump(g, s.ids["point"], tmp_path / "in.bin")
-    r = subprocess.run([mirror_bin, str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "--optimize", str(iters), "--pcg-jacobi"],
+    r = subprocess.run([mirror_bin, str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "--optimize", str(iters), flag],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     out = np.fromfile(tmp_path / "out.bin", np.float64)
@@ -225,7 +226,7 @@ def test_mirror_optimize_with_pcg_jacobi(mirror_bin, tmp_path):
     ctx = capi.Context(0)
     st = G.default_settings(iters)
     p = capi.Problem(ctx, g); direct = p.optimize(st); p.close()
-    st.solver_type, st.pcg_max_iterations, st.pcg_desired_residual = G.SOLVER_PCG_JACOBI, 8000, 1e-12
+    st.solver_type, st.pcg_max_iterations, st.pcg_desired_residual = solver_type, 8000, 1e-12
     p = capi.Problem(ctx, g); summ = p.optimize(st); ref = p.vars; last = p.pcg_last(); p.close()
     ctx.close()
     assert last[0] > 1 and last[1] < 1e-12

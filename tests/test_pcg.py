@@ -1,8 +1,12 @@
 """The iterative path of the linear solve: lib/small_thing/Optimizer.cpp:232-331 — eliminate the
 landmarks, run preconditioned conjugate gradients (PCG.cpp:15-97) on the reduced camera system, back-substitute —
-with IdentityPrecond (Solver_PCG_Trivial) and BlockJacobiPrecond (Solver_PCG_Jacobi), Preconditioner.h:29-116.
-Solver_PCG_GaussSeidel / Solver_PCG_LowerPrecSolve call BaSpaCho's pseudoFactorFrom / float factorFrom, whose source
-is not in the reference tree: they are refused, here and in the library.
+with the four preconditioners of Preconditioner.h: identity (Solver_PCG_Trivial), block Jacobi, block Gauss-Seidel and
+lower-precision solve.  The first two are defined in the reference tree.  Gauss-Seidel is BaSpaCho's pseudoFactorFrom
+(source absent): restated as the Cholesky sweep without Schur updates, i.e. symmetric block Gauss-Seidel — over the
+param blocks in the oracle, over the supernode diagonal blocks in the library's own elimination order on the device, so
+the two agree on the converged solution, not on the iterates.  Lower-precision solve is the complete factor of the
+float copy: float arithmetic in the oracle, fp64 arithmetic on float-rounded data on the device.  All four are held to
+the iteration bounds of the reference's own test on its own recipe (test_reference_pcg_recipe).
 
 CPU part: the oracle's PCG converges to the oracle's direct solve; its iteration count obeys PCG.cpp's two exits.
 GPU part: the device PCG against the oracle's PCG (same algorithm, same stopping rule: iteration counts equal, steps
@@ -34,6 +38,11 @@ def oracle_step(o, solver_type, max_it=40, res=1e-10):
 # path is tested on "tiny", the "small" sessions compare cut-short iterates.
 CONVERGING = [("tiny", G.SOLVER_PCG_JACOBI, 4000), ("tiny", G.SOLVER_PCG_TRIVIAL, 40000),
               ("small_rs", G.SOLVER_PCG_JACOBI, 6000), ("small_lc_rs", G.SOLVER_PCG_JACOBI, 6000)]
+# preconditioners whose block partition / arithmetic differ between the oracle and the device: same solution, the
+# iteration counts only of the same order
+FACTORED = [("tiny", G.SOLVER_PCG_GAUSS_SEIDEL, 4000), ("small_rs", G.SOLVER_PCG_GAUSS_SEIDEL, 6000),
+            ("small_lc_rs", G.SOLVER_PCG_GAUSS_SEIDEL, 6000), ("tiny", G.SOLVER_PCG_LOWER_PREC_SOLVE, 40),
+            ("small_rs", G.SOLVER_PCG_LOWER_PREC_SOLVE, 40), ("small_lc_rs", G.SOLVER_PCG_LOWER_PREC_SOLVE, 40)]
 
 
 @pytest.mark.parametrize("name,solver_type,max_it", CONVERGING[:3])
@@ -63,11 +72,24 @@ def test_oracle_pcg_exits(oracle):
     assert it < 5000 and res < 1e-3
 
 
-def test_oracle_refuses_the_pseudo_factor_preconditioners(oracle):
+def test_oracle_refuses_unknown_solver_types(oracle):
     s, o = prepared_oracle(oracle, "tiny")
-    for t in (G.SOLVER_PCG_GAUSS_SEIDEL, G.SOLVER_PCG_LOWER_PREC_SOLVE, 7):
+    for t in (5, 7, -1):
         with pytest.raises(RuntimeError):
             o.set_linear_solver(t)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small_rs"])
+def test_oracle_gauss_seidel_and_lower_precision_converge(oracle, name):
+    """both reach the direct solution; Gauss-Seidel in fewer iterations than Jacobi, the lower-precision factor in a
+    handful (it is the inverse up to float rounding)"""
+    s, o = prepared_oracle(oracle, name)
+    direct = oracle_step(o, G.SOLVER_DIRECT)
+    oracle_step(o, G.SOLVER_PCG_JACOBI, 6000, 1e-12); it_j = o.pcg_last()[0]
+    x = oracle_step(o, G.SOLVER_PCG_GAUSS_SEIDEL, 6000, 1e-12); it_g, res_g = o.pcg_last()
+    assert res_g < 1e-12 and it_g < it_j and np.abs(x - direct).max() <= 1e-7 * np.abs(direct).max()
+    x = oracle_step(o, G.SOLVER_PCG_LOWER_PREC_SOLVE, 40, 1e-12); it_l, res_l = o.pcg_last()
+    assert res_l < 1e-12 and it_l <= 8 and np.abs(x - direct).max() <= 1e-7 * np.abs(direct).max()
 
 
 def test_oracle_optimize_through_pcg_matches_direct(oracle):
@@ -78,6 +100,53 @@ def test_oracle_optimize_through_pcg_matches_direct(oracle):
     b = Oracle(oracle, s.graph); sb = b.optimize(st)[0]
     assert sa.num_iterations == sb.num_iterations
     assert abs(sa.final_cost - sb.final_cost) <= 1e-6 * abs(sa.final_cost)
+
+
+def reference_recipe_system(seed):
+    """The random problem of the reference's own PCG test (lib/small_thing/tests/TestPCG.cpp:33-69) with numpy's generator
+    in place of BaSpaCho's testing utilities (absent): 215 params of 2-3 scalars, 3 % of the block pairs coupled, the
+    first 150 params mutually independent, data uniform in [-1, 1] on every stored block (the fill of eliminating the
+    first 100 params included), every diagonal entry raised by U(0.1, 0.5) x order."""
+    rng = np.random.default_rng(seed)
+    n_params, n_indep, n_elim = 215, 150, 100
+    size = rng.integers(2, 4, n_params)
+    start = np.concatenate([[0], np.cumsum(size)])
+    order = int(start[-1])
+    coupled = np.tril(rng.random((n_params, n_params)) < 0.03, -1)
+    coupled[:n_indep, :n_indep] = False
+    coupled = coupled | coupled.T
+    for p in range(n_elim):                      # fill: the neighbours of an eliminated param become coupled
+        nb = np.flatnonzero(coupled[p])
+        coupled[np.ix_(nb, nb)] = True
+    np.fill_diagonal(coupled, True)
+    M = np.zeros((order, order))
+    for i in range(n_params):
+        for j in range(i + 1):
+            if coupled[i, j]:
+                M[start[i]:start[i + 1], start[j]:start[j + 1]] = rng.uniform(-1, 1, (size[i], size[j]))
+    M = np.tril(M) + np.tril(M, -1).T
+    for i in range(n_params):
+        M[np.arange(start[i], start[i + 1]), np.arange(start[i], start[i + 1])] += rng.uniform(order * 0.1, order * 0.5)
+    b = rng.uniform(-1, 1, order)
+    return M, b, size, int(start[n_elim])
+
+
+@pytest.mark.parametrize("seed", [37, 38, 39])
+@pytest.mark.parametrize("precond,solve_before_it", [(0, 30), (1, 12), (2, 6), (3, 5)])
+def test_reference_pcg_recipe(oracle, seed, precond, solve_before_it):
+    """TestPCG.cpp:29-144 (TestPrecond.Identity / .Jacobi / .GaussSeidel / .LowerPrecSolve): eliminate the independent set, PCG (3e-10, 40 iterations) on
+    the reduced system, trace back, verify the residual of the FULL system; the reference's iteration bounds (30 / 12)
+    and tolerances (1e-9)"""
+    M, b, size, ne = reference_recipe_system(seed)
+    Mee, Mre = M[:ne, :ne], M[ne:, :ne]
+    y = np.linalg.solve(Mee, b[:ne])                             # factorUpTo + solveLUpTo
+    S = M[ne:, ne:] - Mre @ np.linalg.solve(Mee, Mre.T)
+    rhs = b[ne:] - Mre @ y
+    x_r, its, res = Oracle.pcg_dense(oracle, S, rhs, size[100:], precond, 3e-10, 40)
+    assert its < solve_before_it and abs(res) <= 1e-9
+    x_e = np.linalg.solve(Mee, b[:ne] - Mre.T @ x_r)              # solveLtUpTo
+    x = np.concatenate([x_e, x_r])
+    assert np.linalg.norm(b - M @ x) / np.linalg.norm(b) <= 1e-9
 
 
 # ---- device ----------------------------------------------------------------------------------------------------------
@@ -127,6 +196,32 @@ def test_device_pcg_converges_where_the_oracle_pcg_does(ctx, oracle, name, solve
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name,solver_type,max_it", FACTORED)
+def test_device_gauss_seidel_and_lower_precision(ctx, oracle, name, solver_type, max_it):
+    from visual_inertial_bundle_adjustment_b200 import capi
+    s, o = prepared_oracle(oracle, name)
+    p = capi.Problem(ctx, s.graph)
+    try:
+        p.compute_grad_hess(); p.add_damping(DAMP)
+        so = oracle_step(o, solver_type, max_it, 1e-12)
+        sg = to_reg(p, o, device_step(p, solver_type, max_it, 1e-12))
+        it_o, res_o = o.pcg_last(); it_g, res_g = p.pcg_last()
+        assert res_o < 1e-12 and res_g < 1e-12, (p.pcg_last(), o.pcg_last())
+        assert np.abs(sg - so).max() <= 1e-6 * np.abs(so).max()
+        if solver_type == G.SOLVER_PCG_LOWER_PREC_SOLVE:
+            assert it_g <= 8 and it_o <= 8
+        else:   # different blocks and sweep order than the oracle's: only "better than block Jacobi" is common ground
+            oracle_step(o, G.SOLVER_PCG_JACOBI, 6000, 1e-12)
+            assert it_g < o.pcg_last()[0], (it_g, it_o, o.pcg_last())
+        # against the device's own direct factorisation of the same system
+        p.compute_grad_hess(); p.add_damping(DAMP)
+        sd = to_reg(p, o, device_step(p, G.SOLVER_DIRECT))
+        assert np.abs(sg - sd).max() <= 1e-6 * np.abs(sd).max()
+    finally:
+        p.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("name", ["tiny", "small_rs", "small_lc_rs"])
 @pytest.mark.parametrize("solver_type", [G.SOLVER_PCG_TRIVIAL, G.SOLVER_PCG_JACOBI])
 def test_device_pcg_iterates_match_the_oracle_pcg(ctx, oracle, name, solver_type):
@@ -154,7 +249,9 @@ def test_device_pcg_iterates_match_the_oracle_pcg(ctx, oracle, name, solver_type
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,solver_type,max_it,damping_min", [("tiny", G.SOLVER_PCG_TRIVIAL, 40000, 1e-2), ("small_rs", G.SOLVER_PCG_JACOBI, 8000, 1e-4)])
+@pytest.mark.parametrize("name,solver_type,max_it,damping_min", [("tiny", G.SOLVER_PCG_TRIVIAL, 40000, 1e-2), ("small_rs", G.SOLVER_PCG_JACOBI, 8000, 1e-4),
+                                                                 ("small_rs", G.SOLVER_PCG_GAUSS_SEIDEL, 8000, 1e-4),
+                                                                 ("small_lc_rs", G.SOLVER_PCG_LOWER_PREC_SOLVE, 40, 1e-6)])
 def test_device_optimize_through_pcg_matches_the_oracle(ctx, oracle, name, solver_type, max_it, damping_min):
     """damping floored so that every PCG run converges within max_it (two unconverged CG runs are not comparable)"""
     from visual_inertial_bundle_adjustment_b200 import capi
@@ -173,7 +270,8 @@ def test_device_optimize_through_pcg_matches_the_oracle(ctx, oracle, name, solve
             assert abs(a["new_cost"] - b["new_cost"]) <= 1e-8 * abs(b["new_cost"])
             assert a["branch"] == b["branch"]
         assert np.abs(p.vars - o.vars).max() <= 1e-6
-        label = "jacobi" if solver_type == G.SOLVER_PCG_JACOBI else "trivial"
+        label = {G.SOLVER_PCG_TRIVIAL: "trivial", G.SOLVER_PCG_JACOBI: "jacobi", G.SOLVER_PCG_GAUSS_SEIDEL: "gauss-seidel",
+                 G.SOLVER_PCG_LOWER_PREC_SOLVE: "lower-prec-solve"}[solver_type]
         assert any(f"semi-precond({label})" in l and "iters: " in l and "residual: " in l for l in lines)
         # and lands where the direct solver lands
         st.solver_type = G.SOLVER_DIRECT
@@ -191,12 +289,12 @@ def test_device_refuses_what_it_does_not_build(ctx):
     s = synth.make_session(**synth.CONFIGS["tiny"])
     p = capi.Problem(ctx, s.graph)
     try:
-        for t in (G.SOLVER_PCG_GAUSS_SEIDEL, G.SOLVER_PCG_LOWER_PREC_SOLVE, 9, -1):
+        for t in (5, 9, -1):
             with pytest.raises(capi.VbError) as e:
                 p.set_linear_solver(t)
             assert e.value.code == 1
         st = G.default_settings(2)
-        st.solver_type = G.SOLVER_PCG_GAUSS_SEIDEL
+        st.solver_type = 5
         with pytest.raises(capi.VbError):
             p.optimize(st)
         with pytest.raises(capi.VbError):

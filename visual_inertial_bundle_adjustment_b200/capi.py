@@ -414,7 +414,7 @@ class Problem:
 
     def set_linear_solver(self, solver_type, max_iterations=40, desired_residual=1e-10):
         """Settings::solverType for vb_factor / vb_solve (optimize() takes it from its settings): graph.SOLVER_DIRECT,
-        SOLVER_PCG_TRIVIAL, SOLVER_PCG_JACOBI; the two BaSpaCho-pseudo-factor preconditioners raise"""
+        SOLVER_PCG_TRIVIAL, SOLVER_PCG_JACOBI, SOLVER_PCG_GAUSS_SEIDEL, SOLVER_PCG_LOWER_PREC_SOLVE"""
         _ck(self.lib, self.lib.vb_set_linear_solver(self.h, int(solver_type), int(max_iterations), float(desired_residual)))
 
     def pcg_last(self):

@@ -87,6 +87,8 @@ struct vb_problem {
   double *pcgX = nullptr, *pcgR = nullptr, *pcgZ = nullptr, *pcgP = nullptr, *pcgAp = nullptr, *pcgJac = nullptr, *pcgDots = nullptr;
   int64_t* pcgJacOff = nullptr;
   int2* pcgMvTasks = nullptr; int pcgNumMvTasks = 0;   // (supernode, row slice) of the matrix-vector product
+  double* pcgPanels = nullptr;   // Gauss-Seidel / lower-precision solve: factored copy of the camera panels
+  double pcgLowPrecEpsilon = 0.0;   // the diagonal raise the last lower-precision factor needed (0: none)
   double* fwdFused = nullptr;     // the vector whose forward solve the last factorAsync carried (consumed by solveAsync)
   RefineArgs refine{};            // refinePoints (vb_refine_points): landmark-major view of the visual stores
   bool refineReady = false;
@@ -1391,6 +1393,50 @@ static void factorPcgAsync(vb_problem* p, cudaEvent_t afterSchur) {
   launchSchur(p->sol, p->hess, p->schurTasks, p->nSchurTasks, p->errFlag, s);
   if (afterSchur) VB_CUDA(cudaEventRecord(afterSchur, s));
   if (p->solverType == VB_SOLVER_PCG_JACOBI) launchJacobiInit(p->sol, p->hess, p->pcgJacOff, p->pcgJac, p->errFlag, s);
+  if (p->solverType != VB_SOLVER_PCG_GAUSS_SEIDEL && p->solverType != VB_SOLVER_PCG_LOWER_PREC_SOLVE) return;
+  // Both preconditioners work on a copy of the unfactored camera panels, addressed through a "virtual" base pointer
+  // exactly as the reference does it (Preconditioner.h:131-137,183-186): the supernode kernels only touch panel
+  // offsets >= lmDataSize.
+  const Symbolic& S = p->S;
+  const int64_t camDoubles = S.dataSize - S.lmDataSize;
+  if (!p->pcgPanels) p->pcgPanels = p->alloc<double>(camDoubles);
+  double* virt = p->pcgPanels - S.lmDataSize;
+  const vb_problem::Sched& sc = p->sched[1];
+  VB_CUDA(cudaMemcpyAsync(p->pcgPanels, p->hess + S.lmDataSize, camDoubles * sizeof(double), cudaMemcpyDeviceToDevice, s));
+  if (p->solverType == VB_SOLVER_PCG_GAUSS_SEIDEL) {
+    // BlockGaussSeidelPrecond::init = Solver::pseudoFactorFrom: the Cholesky sweep without its Schur updates — every
+    // supernode's diagonal block factored, its panel multiplied by the inverse transpose — so that the two supernodal
+    // solves apply ((D + E) D^-1 (D + E)^T)^-1, D = the supernode diagonal blocks.  No dependencies: one launch pair.
+    const int nl = (int)(sc.lumpOff.back() - sc.lumpOff.front());
+    int maxBelow = 0, maxWidth = 1;
+    for (size_t lv = 0; lv + 1 < sc.lumpOff.size(); lv++) { maxBelow = std::max(maxBelow, (int)sc.maxBelow[lv]); maxWidth = std::max(maxWidth, (int)sc.maxWidth[lv]); }
+    if (nl > 0) launchLumpFactor(p->sol, virt, sc.lumps + sc.lumpOff.front(), nl, maxBelow, maxWidth, p->errFlag, s, nullptr);
+    return;
+  }
+  // LowerPrecSolvePrecond::init (Preconditioner.h:178-218): complete factor of the float copy; while it fails the
+  // diagonal is raised, d -> d (1 + eps) + eps with eps = 1e-8, 3e-8, ...  Here the DATA is rounded to float and the
+  // factorisation runs on the fp64 tensor path; "fails" = a non-positive pivot instead of the reference's NaN test.
+  double epsilon = 0.0;
+  p->pcgLowPrecEpsilon = 0.0;
+  int landmarkFlag = 0;
+  VB_CUDA(cudaMemcpyAsync(&landmarkFlag, p->errFlag, sizeof(int), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  if (landmarkFlag != 0) return;   // the landmark elimination failed: checkNumeric reports it
+  for (int attempt = 0; attempt < 64; attempt++) {
+    if (attempt > 0) VB_CUDA(cudaMemcpyAsync(p->pcgPanels, p->hess + S.lmDataSize, camDoubles * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    launchRoundToFloat(p->pcgPanels, camDoubles, s);
+    if (epsilon > 0) { launchCamDiagRaise(p->sol, virt, epsilon, s); p->pcgLowPrecEpsilon = epsilon; epsilon *= 3.0; }
+    else epsilon = 1e-8;
+    VB_CUDA(cudaMemsetAsync(p->errFlag, 0, sizeof(int), s));
+    std::swap(p->hess, virt);
+    try { factorLevels(p, 1); } catch (...) { std::swap(p->hess, virt); throw; }
+    std::swap(p->hess, virt);
+    int flag = 0;
+    VB_CUDA(cudaMemcpyAsync(&flag, p->errFlag, sizeof(int), cudaMemcpyDeviceToHost, s));
+    syncCheck(p);
+    if (flag == 0) return;
+  }
+  // still failing: errFlag stays set and checkNumeric turns it into VB_ERR_NUMERIC / a rejected step
 }
 // solveLUpTo + PCG::solve on the reduced system + solveLtUpTo (Optimizer.cpp:301-327, PCG.cpp:15-97)
 static void solvePcg(vb_problem* p, double* vec) {
@@ -1400,9 +1446,23 @@ static void solvePcg(vb_problem* p, double* vec) {
   double* cam = vec + p->sol.camVec0;
   double *x = p->pcgX, *r = p->pcgR, *z = p->pcgZ, *pk = p->pcgP, *Ap = p->pcgAp, *dots = p->pcgDots;
   const bool jacobi = p->solverType == VB_SOLVER_PCG_JACOBI;
+  const bool factored = p->solverType == VB_SOLVER_PCG_GAUSS_SEIDEL || p->solverType == VB_SOLVER_PCG_LOWER_PREC_SOLVE;
+  const bool lowPrec = p->solverType == VB_SOLVER_PCG_LOWER_PREC_SOLVE;
   auto precond = [&](const double* in, double* out) {
-    if (jacobi) launchJacobiApply(p->sol, p->pcgJacOff, p->pcgJac, in, out, s);
-    else VB_CUDA(cudaMemcpyAsync(out, in, nCam * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    if (jacobi) { launchJacobiApply(p->sol, p->pcgJacOff, p->pcgJac, in, out, s); return; }
+    VB_CUDA(cudaMemcpyAsync(out, in, nCam * sizeof(double), cudaMemcpyDeviceToDevice, s));
+    if (!factored) return;
+    // solveLFrom + solveLtFrom on the (pseudo-)factored copy (Preconditioner.h:139-153, 220-239); the supernode solve
+    // kernels address vec + camVec0 + ..., so the nCam-long vector goes in behind a virtual base as well
+    double* virt = p->pcgPanels - S.lmDataSize;
+    if (lowPrec) launchRoundToFloat(out, nCam, s);
+    std::swap(p->hess, virt);
+    try {
+      solveLevels(p, out - p->sol.camVec0, 1, true);
+      solveLevels(p, out - p->sol.camVec0, 1, false);
+    } catch (...) { std::swap(p->hess, virt); throw; }
+    std::swap(p->hess, virt);
+    if (lowPrec) launchRoundToFloat(out, nCam, s);
   };
   auto readDots = [&](double* host, int n) {
     VB_CUDA(cudaMemcpyAsync(host, dots, n * sizeof(double), cudaMemcpyDeviceToHost, s));
@@ -1452,10 +1512,17 @@ static void solvePcg(vb_problem* p, double* vec) {
   catch (const std::exception& ex) { g_err = ex.what(); return VB_ERR_CUDA; }        \
   return VB_OK;
 
+static const char* solverName(int solverType) {   // Optimizer::solverToString (Optimizer.cpp:148-164)
+  switch (solverType) {
+    case VB_SOLVER_DIRECT: return "direct";
+    case VB_SOLVER_PCG_TRIVIAL: return "trivial";
+    case VB_SOLVER_PCG_JACOBI: return "jacobi";
+    case VB_SOLVER_PCG_GAUSS_SEIDEL: return "gauss-seidel";
+    case VB_SOLVER_PCG_LOWER_PREC_SOLVE: return "lower-prec-solve";
+    default: return "<unknown>";
+  }
+}
 static void setLinearSolver(vb_problem* p, int solverType, int maxIterations, double desiredResidual) {
-  if (solverType == VB_SOLVER_PCG_GAUSS_SEIDEL || solverType == VB_SOLVER_PCG_LOWER_PREC_SOLVE)
-    throw std::invalid_argument("Solver_PCG_GaussSeidel / Solver_PCG_LowerPrecSolve need BaSpaCho's pseudoFactorFrom / float factorFrom, whose source "
-                                "is not part of the reference tree: not built (DESIGN.md section 9)");
   if (solverType < VB_SOLVER_DIRECT || solverType > VB_SOLVER_PCG_LOWER_PREC_SOLVE)
     throw std::invalid_argument("Unknown preconditioner " + std::to_string(solverType));   // Optimizer.cpp:243-245
   if (solverType != VB_SOLVER_DIRECT) {
@@ -1819,7 +1886,7 @@ int vb_optimize_ex(vb_problem* p, const vb_settings* st, vb_optimize_hooks* hook
       t += "     n." + std::to_string(iterationNum) + "; g/H: " + fmtDuration(secGradHess) + ", solver:\n";
       if (p->solverType == VB_SOLVER_DIRECT) t += "    direct, factor: " + fmtDuration(secFactor) + ", solve: " + fmtDuration(secSolve) + "\n";
       else   // Optimizer.cpp:298-327 (the per-stage split of the reference's report is folded into the two totals)
-        t += std::string("    semi-precond(") + (p->solverType == VB_SOLVER_PCG_JACOBI ? "jacobi" : "trivial") + "), factor[elims] + init precond: " +
+        t += std::string("    semi-precond(") + solverName(p->solverType) + "), factor[elims] + init precond: " +
              fmtDuration(secFactor) + "\n    solve[elims] + reduced-PCG + backsubst: " + fmtDuration(secSolve) + " (iters: " +
              std::to_string(p->pcgLastIterations) + ", residual: " + fmtG(p->pcgLastResidual) + ")\n";
       t += "     lmbd: " + fmtG(damping) + ", relRed: " + fmtPercent(ratioReductionToExpected) + ", improv: " + fmtG(costReduction) +

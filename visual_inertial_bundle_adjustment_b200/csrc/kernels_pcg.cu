@@ -7,8 +7,9 @@
 //   jacobiInitKernel   BlockJacobiPrecond::init (Preconditioner.h:71-82): Cholesky of every param-sized diagonal block
 //   jacobiApplyKernel  BlockJacobiPrecond::operator() (:84-107): two triangular solves per block
 //   pcg*Kernel         the vector updates and dot products of PCG::solve
-// IdentityPrecond (Preconditioner.h:29-47) is a copy.  BlockGaussSeidelPrecond / LowerPrecSolvePrecond are BaSpaCho's
-// pseudoFactorFrom / float factorFrom: source absent from the reference tree, not built.
+// IdentityPrecond (Preconditioner.h:29-47) is a copy.  BlockGaussSeidelPrecond (pseudo-factor: potrf + trsm of every
+// supernode without the Schur updates, then the supernodal solves) and LowerPrecSolvePrecond (the full supernodal factor
+// of a float-rounded copy) reuse the kernels of kernels_chol.cu on a copy of the camera panels (csrc/api.cu).
 #include "vb_internal.hpp"
 #include "dev_math.cuh"
 
@@ -159,6 +160,21 @@ __global__ void pcgDirKernel(double* p, const double* z, const double* num, cons
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = fma(beta, p[i], z[i]);
 }
 
+// LowerPrecSolvePrecond (Preconditioner.h:160-245): the copy of the camera panels is rounded to float, and so is every
+// vector that goes through the preconditioner; the arithmetic on the rounded data stays fp64
+__global__ void roundToFloatKernel(double* a, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) a[i] = (double)(float)a[i];
+}
+// d -> d (1 + eps) + eps on the diagonal of every camera block of the panel copy (Preconditioner.h:200-208)
+__global__ void camDiagRaiseKernel(DevSolver d, double* hess, double eps) {
+  const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= d.nC) return;
+  const int L = d.camLump[c];
+  const int w = d.lumpWidth[L], o = d.camStart[c] - d.camStart[d.lumpFirst[L]], n = d.camStart[c + 1] - d.camStart[c];
+  double* D = hess + d.lumpOff[L] + (int64_t)o * w + o;
+  for (int a = 0; a < n; a++) D[(int64_t)a * w + a] = D[(int64_t)a * w + a] * (1.0 + eps) + eps;
+}
+
 static int gridN(int64_t n) { return (int)std::min<int64_t>((n + 255) / 256, 148 * 8); }
 
 int camSymMvRows() { return kMvRows; }
@@ -177,6 +193,15 @@ void launchJacobiInit(const DevSolver& d, const double* hess, const int64_t* jac
 }
 void launchJacobiApply(const DevSolver& d, const int64_t* jacOff, const double* jac, const double* in, double* out, cudaStream_t s) {
   jacobiApplyKernel<<<(unsigned)((d.nC + 127) / 128), 128, 0, s>>>(d, jacOff, jac, in, out);
+  VB_CUDA(cudaGetLastError());
+}
+void launchRoundToFloat(double* a, int64_t n, cudaStream_t s) {
+  if (n <= 0) return;
+  roundToFloatKernel<<<gridN(n), 256, 0, s>>>(a, n);
+  VB_CUDA(cudaGetLastError());
+}
+void launchCamDiagRaise(const DevSolver& d, double* hess, double eps, cudaStream_t s) {
+  camDiagRaiseKernel<<<(unsigned)((d.nC + 127) / 128), 128, 0, s>>>(d, hess, eps);
   VB_CUDA(cudaGetLastError());
 }
 void launchPcgDot2(const double* a, const double* b, const double* c, const double* dd, int64_t n, double* out, cudaStream_t s) {

@@ -160,6 +160,8 @@ int camSymMvRows();
 void launchCamSymMv(const DevSolver& d, const double* hess, const int2* tasks, int nTasks, const double* v, double* u, int maxWidth, cudaStream_t s);
 void launchJacobiInit(const DevSolver& d, const double* hess, const int64_t* jacOff, double* jac, int* errFlag, cudaStream_t s);
 void launchJacobiApply(const DevSolver& d, const int64_t* jacOff, const double* jac, const double* in, double* out, cudaStream_t s);
+void launchRoundToFloat(double* a, int64_t n, cudaStream_t s);
+void launchCamDiagRaise(const DevSolver& d, double* hess, double eps, cudaStream_t s);
 void launchPcgDot2(const double* a, const double* b, const double* c, const double* dd, int64_t n, double* out, cudaStream_t s);
 void launchPcgStep(double* x, double* r, const double* p, const double* Ap, const double* num, const double* den, int64_t n, cudaStream_t s);
 void launchPcgDir(double* p, const double* z, const double* num, const double* den, int64_t n, cudaStream_t s);

@@ -297,6 +297,19 @@ int vb_eval_grad_new(vb_problem* p, int dont_retry_failed);
  * the iteration count and relative residual of the last PCG run.  Not available on a sharded problem. */
 int vb_set_linear_solver(vb_problem* p, int32_t solver_type, int32_t pcg_max_iterations, double pcg_desired_residual);
 int vb_pcg_last(const vb_problem* p, int32_t* iterations, double* relative_residual);
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  *out_dev = a . b over two
+ * caller-owned DEVICE vectors of n doubles, launched on `cuda_stream` (a cudaStream_t; NULL = the legacy default stream)
+ * of GPU `device`; returns without synchronising.  The allocation-free variant of the dot-product kernel behind vb_dot:
+ * its scratch (one partial sum per 16 384 elements + a ticket) is a fixed 128.25 KiB __device__ array that every GPU
+ * loading the library holds until exit, so the call performs no cudaMalloc / cudaFree and no allocating library call.
+ * n > VB_DOT_NO_ALLOC_MAX_N (or n < 0, or a null pointer) is VB_ERR_ARG with a text saying so; n = 0 gives 0.
+ * The result is deterministic (fixed summation order).  All calls on one GPU share the scratch: calls whose kernels
+ * OVERLAP on the GPU (different streams without an ordering between them) race; calls ordered on one stream or by events
+ * are safe.  The first call on a device looks the array's address up (cudaGetSymbolAddress): make one call before
+ * starting a graph capture. */
+#define VB_DOT_NO_ALLOC_MAX_N ((int64_t)268435456) /* 16 384 partial sums x 16 384 elements each = 2^28 */
+int vb_dot_no_alloc(int device, const double* a_dev, const double* b_dev, int64_t n, double* out_dev, void* cuda_stream);
 /* Optimizer::optimize (Optimizer.cpp:768-1106): the whole LM loop, host-controlled, device-resident */
 int vb_optimize(vb_problem* p, const vb_settings* s, vb_summary* out);
 /* same loop with the Settings hooks: preStepCallback (Optimizer.h:90, called at Optimizer.cpp:803-805),

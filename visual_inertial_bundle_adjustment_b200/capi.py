@@ -24,7 +24,7 @@ EXPORTS = [
     "vb_download_step", "vb_download_hess", "vb_upload_hess", "vb_upload_grad", "vb_download_factor_cache",
     "vb_upload_store_aux", "vb_upload_store_consts", "vb_measure_dmma_peak",
     "vb_download_store_aux", "vb_rs_set_imu", "vb_rs_refresh",
-    "vb_schur_plan_stats", "vb_measure_dmma_shapes", "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info", "vb_shard_factor_owners",
+    "vb_dot_no_alloc", "vb_schur_plan_stats", "vb_measure_dmma_shapes", "vb_ctx_create_on_stream", "vb_problem_create_sharded", "vb_shard_plan", "vb_shard_info", "vb_shard_factor_owners",
 ]
 # int fn(void* user, int op, double* dev_ptr, int64_t count, void* cuda_stream)  (include/viba_b200.h)
 COLLECTIVE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int64, C.c_void_p)
@@ -66,6 +66,7 @@ def load():
     lib.vb_damp.argtypes = [C.c_void_p, C.c_double]
     lib.vb_step_from_grad.argtypes = [C.c_void_p]
     lib.vb_factor.argtypes = [C.c_void_p]
+    lib.vb_dot_no_alloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
     lib.vb_set_linear_solver.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_double]
     lib.vb_pcg_last.argtypes = [C.c_void_p, C.POINTER(C.c_int32), _dp]
     lib.vb_solve.argtypes = [C.c_void_p, C.c_int]
@@ -118,6 +119,16 @@ def symbolic_only(graph):
     perm = np.zeros(graph.num_blocks, np.int64)
     _ck(lib, lib.vb_symbolic_only(C.byref(desc), C.byref(o), C.byref(ds), C.byref(nl), perm.ctypes.data_as(_ip), perm.size))
     return o.value, ds.value, nl.value, perm
+
+
+DOT_NO_ALLOC_MAX_N = 1 << 28
+
+
+def dot_no_alloc(device, a_ptr, b_ptr, n, out_ptr, stream=None):
+    """vb_dot_no_alloc: *out_ptr = a . b over raw DEVICE pointers (ints), on `stream` (raw cudaStream_t or None), without
+    any allocation and without synchronising; n <= DOT_NO_ALLOC_MAX_N"""
+    lib = load()
+    _ck(lib, lib.vb_dot_no_alloc(int(device), C.c_void_p(a_ptr), C.c_void_p(b_ptr), int(n), C.c_void_p(out_ptr), C.c_void_p(stream or 0)))
 
 
 def symbolic_stats(graph, max_lump_width=0, nd_leaf_blocks=600):

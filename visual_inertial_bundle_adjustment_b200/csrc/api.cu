@@ -13,6 +13,7 @@
 using namespace vb;
 
 static thread_local std::string g_err;
+namespace vb { void setLastError(const std::string& text) { g_err = text; } }   // for the other translation units (kernels_noalloc.cu)
 
 struct vb_ctx {
   int device = 0;

@@ -375,6 +375,21 @@ typedef struct vb_refine_stats {
 } vb_refine_stats;
 int vb_refine_points(vb_problem* p, vb_refine_stats* out, double* per_point, int64_t n_points);
 int64_t vb_refine_num_points(const vb_problem* p);
+/* Triangulation refinement (second half): SingleSessionAdapter::refineTriangulationResult,
+ * viba/single_session/Triangulation.cpp:99-161, as triangulatePoint runs it twice (:219-238; settings of pass 1 / 2 in
+ * Triangulation.h:29-39: 3.0, false, 3, 1.5 / 2.5, true, 3, 1.0) — for every landmark with visual factors at once:
+ * max_num_iterations undamped Gauss-Newton steps on the point with HuberLoss(huber_radius) on the weighted reprojection
+ * error, re-classifying the observations every iteration (inlier = unweighted image error below outlier_threshold pixels)
+ * and, with skip_outliers, leaving the outliers out of the normal equations.  Updates the landmark variables on the
+ * device.  per_point (may be null): {numInlierObservations, cost of the last iteration, status} per landmark, same order
+ * and count as vb_refine_points; status -1 = the 3x3 system was not positive definite (Eigen's llt() returns garbage
+ * there; here the point is kept), counted in *num_failures (may be null).  vb_refine_triangulation_inliers gives the
+ * inlierObservationIndices of the last call as one byte per factor of a visual store, in factor order.  The RANSAC
+ * candidate search of triangulatePoint (:33-97) and the track bookkeeping stay on the host (session builder, not
+ * restated).  Not available on a sharded problem. */
+int vb_refine_triangulation(vb_problem* p, double outlier_threshold, int32_t skip_outliers, int32_t max_num_iterations, double huber_radius,
+                            double* per_point, int64_t n_points, int64_t* num_failures);
+int vb_refine_triangulation_inliers(vb_problem* p, int32_t store, uint8_t* flags, int64_t n_factors);
 
 /* Per-iteration refresher of the preintegration records on the device (second half):
  * computePreIntegration (lib/motion/preintegration/PreIntegration.cpp:136-275, with CompensateJac.cpp:146-249 and

@@ -290,6 +290,18 @@ int orc_refine_points(OrcHandle* h, double* stats6, double* per_point) {
   stats6[4] = (double)r.nTotalIterations; stats6[5] = (double)r.nAtLeastOneIt;
   ORC_CATCH
 }
+// refineTriangulationResult (viba/single_session/Triangulation.cpp:99-161) over every landmark: per_point = {numInliers,
+// last cost, status} per refined landmark; inlier_flags (may be null) = one byte per factor, the visual stores
+// concatenated in graph order; *failures = landmarks whose 3x3 system was not positive definite
+int orc_refine_triangulation(OrcHandle* h, double outlier_threshold, int skip_outliers, int max_num_iterations, double huber_radius,
+                             double* per_point, uint8_t* inlier_flags, int64_t* failures) {
+  ORC_TRY
+  std::vector<std::vector<uint8_t>> fl;
+  const int64_t f = refineTriangulation(h->eng, outlier_threshold, skip_outliers != 0, max_num_iterations, huber_radius, per_point, &fl);
+  if (failures) *failures = f;
+  if (inlier_flags) { int64_t o = 0; for (const auto& v : fl) { std::copy(v.begin(), v.end(), inlier_flags + o); o += (int64_t)v.size(); } }
+  ORC_CATCH
+}
 // SingleSessionAdapter::regenerateAllPreintegrationsFromImuMeasurements (InertialFactors.cpp:45-70): same arguments as vb_preint_set_imu
 int orc_preint_set_imu(OrcHandle* h, int store, int64_t n_factors, const int64_t* start_us, const int64_t* end_us, const int32_t* calib_var,
                        int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel, const double* gyro_var3,

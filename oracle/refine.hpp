@@ -134,4 +134,69 @@ inline RefineStats refinePoints(Engine& e, double* perPoint /* 3 x npoints or nu
   return out;
 }
 
+// refineTriangulationResult (viba/single_session/Triangulation.cpp:99-161), the refinement half of triangulatePoint
+// (:165-240), applied to every landmark over its visual observations: maxNumIterations undamped Gauss-Newton steps on the
+// point with small_thing::HuberLoss(radius) (SoftLoss.h:64-113) on the weighted reprojection error; every iteration
+// re-classifies the observations — inlier = squared UNWEIGHTED image error below outlierThreshold^2 (:139-144) — and with
+// skipOutliers the outliers do not enter the normal equations.  The residual and d(residual)/d(point) are the visual
+// factors' own (VisualFactor / RollingShutterVisualFactor use the observed image row for the rolling-shutter pose,
+// VisualFactor.cpp:142-150, exactly as T_bodyImu_world_atImageRow does, :303-327); the unweighted error is recovered from
+// the weighted one through sqrtH^-1.  numInlierObservations / the inlier list are those of the LAST iteration, i.e. at
+// the point before the last update, as in the reference.  Eigen's llt() of a non-SPD 3x3 returns garbage there; here such
+// a landmark is left where it is and reported with status -1.
+// perPoint: {numInliers, cost of the last iteration, status}; inlier[s][k] = 1 for the inlier factors of store s.
+inline int64_t refineTriangulation(Engine& e, double outlierThreshold, bool skipOutliers, int maxNumIterations, double huberRadius,
+                                   double* perPoint /* 3 x npoints or null */, std::vector<std::vector<uint8_t>>* inlier) {
+  Problem& P = e.P;
+  const double thr2 = outlierThreshold * outlierThreshold, b = huberRadius * huberRadius;
+  std::vector<std::vector<std::pair<int, int64_t>>> lists(P.nv);
+  if (inlier) inlier->assign(P.stores.size(), {});
+  for (size_t s = 0; s < P.stores.size(); s++) {
+    const Store& st = P.stores[s];
+    if (st.type != VB_F_VISUAL && st.type != VB_F_VISUAL_RS) continue;
+    if (inlier) (*inlier)[s].assign((size_t)st.count, 0);
+    for (int64_t k = 0; k < st.count; k++) lists[st.vars[k * st.nvars]].push_back({(int)s, k});
+  }
+  int64_t pi = 0, failures = 0;
+  for (int64_t v = 0; v < P.nv; v++) {
+    const auto& fl = lists[v];
+    if (fl.empty()) continue;
+    double* X = P.data.data() + P.off[v];
+    double nIn = 0, cost = 0;
+    int status = 0;
+    for (int it = 0; it < maxNumIterations; it++) {
+      double grad[3] = {0, 0, 0}, hess[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      cost = 0; nIn = 0;
+      for (size_t q = 0; q < fl.size(); q++) {
+        const Store& st = P.stores[fl[q].first];
+        const int64_t k = fl[q].second;
+        if (inlier) (*inlier)[fl[q].first][(size_t)k] = 0;
+        double r[2], JX[6];
+        double* J[kMaxVars] = {JX, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        if (!e.evalFactor(st, k, r, J)) continue;
+        const double* c = st.consts.data() + k * (int64_t)st.cpf;   // uv(2), sqrtH(4) row-major, ...
+        const double det = c[2] * c[5] - c[3] * c[4];
+        const double e0 = (c[5] * r[0] - c[3] * r[1]) / det, e1 = (-c[4] * r[0] + c[2] * r[1]) / det;
+        if (e0 * e0 + e1 * e1 < thr2) { nIn += 1; if (inlier) (*inlier)[fl[q].first][(size_t)k] = 1; }
+        else if (skipOutliers) continue;
+        const double s2 = r[0] * r[0] + r[1] * r[1];
+        double soft = s2, d = 1.0;
+        if (s2 > b) { const double rr = std::sqrt(s2); soft = 2.0 * huberRadius * rr - b; d = huberRadius / rr; }
+        cost += 0.5 * soft;
+        for (int a = 0; a < 3; a++) {
+          grad[a] += d * (r[0] * JX[a] + r[1] * JX[3 + a]);
+          for (int bb = 0; bb < 3; bb++) hess[a * 3 + bb] += d * (JX[a] * JX[bb] + JX[3 + a] * JX[3 + bb]);
+        }
+      }
+      double step[3];
+      if (!solve3(hess, grad, step)) { status = -1; break; }
+      for (int a = 0; a < 3; a++) X[a] -= step[a];
+    }
+    failures += status < 0;
+    if (perPoint) { perPoint[3 * pi] = nIn; perPoint[3 * pi + 1] = cost; perPoint[3 * pi + 2] = status; }
+    pi++;
+  }
+  return failures;
+}
+
 }  // namespace orc

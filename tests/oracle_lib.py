@@ -172,6 +172,18 @@ class Oracle:
         keys = ["total_start_cost", "total_end_cost", "num_points", "num_failures", "num_total_iterations", "num_at_least_one_iteration"]
         return {k: (float(v) if i < 2 else int(v)) for i, (k, v) in enumerate(zip(keys, st))}, pp
 
+    def refine_triangulation(self, outlier_threshold, skip_outliers, max_num_iterations, huber_radius):
+        """refineTriangulationResult over every landmark: (per-point [n, 3] = numInliers, last cost, status; inlier flags of
+        the visual stores concatenated in graph order; failures); the landmark variables are updated"""
+        vis = [st for st in self.g.stores if st.type in (G.F_VISUAL, G.F_VISUAL_RS)]
+        n = len(set(int(v) for st in vis for v in st.vars[:, 0]))
+        pp = np.zeros((n, 3)); fl = np.zeros(sum(st.vars.shape[0] for st in vis), np.uint8); fails = C.c_int64(0)
+        self.lib.orc_refine_triangulation.argtypes = [C.c_void_p, C.c_double, C.c_int, C.c_int, C.c_double, _dp, C.POINTER(C.c_uint8),
+                                                      C.POINTER(C.c_int64)]
+        self._ck(self.lib.orc_refine_triangulation(self.h, float(outlier_threshold), int(bool(skip_outliers)), int(max_num_iterations),
+                                                   float(huber_radius), dptr(pp), fl.ctypes.data_as(C.POINTER(C.c_uint8)), C.byref(fails)))
+        return pp, fl, fails.value
+
     def rs_set_gravity_var(self, store, gravity_var):
         self.lib.orc_rs_set_gravity_var.argtypes = [C.c_void_p, C.c_int, C.c_int]
         self._ck(self.lib.orc_rs_set_gravity_var(self.h, int(store), int(gravity_var)))

@@ -489,6 +489,26 @@ class Problem:
         _ck(self.lib, self.lib.vb_refine_points(self.h, C.byref(st), _d(pp) if per_point else None, n))
         return {k: getattr(st, k) for k, _ in _S._fields_}, pp
 
+    def refine_triangulation(self, outlier_threshold, skip_outliers, max_num_iterations, huber_radius):
+        """refineTriangulationResult over every landmark (vb_refine_triangulation): (per-point [n, 3] = numInliers, last
+        cost, status; inlier flags of the visual stores concatenated in graph order; failures)"""
+        self.lib.vb_refine_num_points.restype = C.c_int64
+        self.lib.vb_refine_num_points.argtypes = [C.c_void_p]
+        n = self.lib.vb_refine_num_points(self.h)
+        pp = np.zeros((n, 3)); fails = C.c_int64(0)
+        self.lib.vb_refine_triangulation.argtypes = [C.c_void_p, C.c_double, C.c_int32, C.c_int32, C.c_double, _dp, C.c_int64, C.POINTER(C.c_int64)]
+        _ck(self.lib, self.lib.vb_refine_triangulation(self.h, float(outlier_threshold), int(bool(skip_outliers)), int(max_num_iterations),
+                                                       float(huber_radius), _d(pp), n, C.byref(fails)))
+        self.lib.vb_refine_triangulation_inliers.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_uint8), C.c_int64]
+        flags = []
+        for si, st in enumerate(self.g.stores):
+            if st.type not in (G.F_VISUAL, G.F_VISUAL_RS):
+                continue
+            f = np.zeros(st.vars.shape[0], np.uint8)
+            _ck(self.lib, self.lib.vb_refine_triangulation_inliers(self.h, si, f.ctypes.data_as(C.POINTER(C.c_uint8)), f.size))
+            flags.append(f)
+        return pp, (np.concatenate(flags) if flags else np.zeros(0, np.uint8)), fails.value
+
     def upload_store_aux(self, store, aux):
         aux = np.ascontiguousarray(aux, np.float64)
         _ck(self.lib, self.lib.vb_upload_store_aux(self.h, store, _d(aux), aux.size))

@@ -94,6 +94,10 @@ struct vb_problem {
   RefineArgs refine{};            // refinePoints (vb_refine_points): landmark-major view of the visual stores
   bool refineReady = false;
   double* refinePerPoint = nullptr;
+  // per refine store: its graph store, and the factor index of every slot of its landmark-major tables (host side, for
+  // vb_refine_triangulation_inliers)
+  std::vector<int32_t> refineStoreId;
+  std::vector<std::vector<int32_t>> refineSlotFactor;
   cudaEvent_t ev[10];
 
   template <typename T>
@@ -461,6 +465,7 @@ static void buildDeviceProblem(vb_problem& P) {
   // factor stores + scatter maps
   P.ds.resize(g.stores.size());
   std::vector<std::vector<int32_t>> refLmVar(g.stores.size());   // visual stores: landmark variable of every landmark-major slot
+  std::vector<std::vector<int32_t>> refSlotFactor(g.stores.size()); // ... and the factor index of the slot
   for (size_t s = 0; s < g.stores.size(); s++) {
     const HostGraph::Store& hs = g.stores[s];
     DevStore& d = P.ds[s];
@@ -595,6 +600,7 @@ static void buildDeviceProblem(vb_problem& P) {
         d.pk.lVar = P.upload(lVar); d.pk.lConst = P.upload(lConst); d.pk.lOut = P.upload(lOut);
         refLmVar[s].resize(nOwn);
         for (int64_t i = 0; i < nOwn; i++) refLmVar[s][i] = hs.vars[(int64_t)olmKeep[i] * nv];
+        refSlotFactor[s].assign(olmKeep.begin(), olmKeep.begin() + nOwn);
       }
     }
     if (hs.type == VB_F_VISUAL) P.visualBytes += 224.0 * hs.count; // SURVEY.md §8d algorithmic bytes/obs
@@ -625,6 +631,7 @@ static void buildDeviceProblem(vb_problem& P) {
       rs.backup = P.alloc<double>(lv.size());
       rs.aux = P.ds[s].aux; rs.loss_a = P.ds[s].loss_a; rs.loss_k = P.ds[s].loss_k; rs.cpf = P.ds[s].cpf;
       rs.rs = g.stores[s].type == VB_F_VISUAL_RS;
+      P.refineStoreId.push_back((int32_t)s); P.refineSlotFactor.push_back(refSlotFactor[s]);
     }
     if (ok && ns > 0) {
       std::vector<int64_t> lmOff(lms.size());
@@ -2135,6 +2142,44 @@ int vb_refine_points(vb_problem* p, vb_refine_stats* out, double* per_point, int
   VB_CATCH
 }
 int64_t vb_refine_num_points(const vb_problem* p) { return p && p->refineReady ? p->refine.nLm : 0; }
+int vb_refine_triangulation(vb_problem* p, double outlier_threshold, int32_t skip_outliers, int32_t max_num_iterations, double huber_radius,
+                            double* per_point, int64_t n_points, int64_t* num_failures) {
+  VB_TRY
+  requireProblem(p);
+  if (p->nranks > 1) throw std::logic_error("vb_refine_triangulation: not available on a sharded problem");
+  if (!p->refineReady) throw std::logic_error("vb_refine_triangulation: the problem has no visual factors in the packed layout");
+  if (per_point && n_points != p->refine.nLm) throw std::invalid_argument("per_point must hold 3 doubles per refined landmark");
+  if (!(outlier_threshold > 0.0) || !(huber_radius > 0.0) || max_num_iterations < 0)   // HuberLoss: BASPACHO_CHECK_GT(a, 0) (SoftLoss.h:66-68)
+    throw std::invalid_argument("vb_refine_triangulation: outlier_threshold > 0, huber_radius > 0, max_num_iterations >= 0 required");
+  cudaStream_t s = p->ctx->stream;
+  VB_CUDA(cudaMemsetAsync(p->acc, 0, 8 * sizeof(double), s));
+  VB_CUDA(cudaMemsetAsync(p->acc + kAccErrSlot, 0, sizeof(double), s));
+  launchRefineTriangulation(p->refine, p->dv, outlier_threshold, skip_outliers != 0, max_num_iterations, huber_radius, p->refinePerPoint, p->acc, s);
+  VB_CUDA(cudaMemcpyAsync(p->accHost, p->acc, 8 * sizeof(double), cudaMemcpyDeviceToHost, s));
+  VB_CUDA(cudaMemcpyAsync(p->accHost + kAccErrSlot, p->acc + kAccErrSlot, sizeof(double), cudaMemcpyDeviceToHost, s));
+  if (per_point) VB_CUDA(cudaMemcpyAsync(per_point, p->refinePerPoint, 3 * p->refine.nLm * sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  if (p->accHost[kAccErrSlot] != 0.0) throw std::domain_error("RollingShutterData::getEstimate: time shift outside the sampled window");
+  if (num_failures) *num_failures = (int64_t)p->accHost[0];
+  VB_CATCH_NUMERIC
+}
+int vb_refine_triangulation_inliers(vb_problem* p, int32_t store, uint8_t* flags, int64_t n_factors) {
+  VB_TRY
+  requireProblem(p);
+  if (!p->refineReady) throw std::logic_error("vb_refine_triangulation_inliers: the problem has no visual factors in the packed layout");
+  int rsIdx = -1;
+  for (size_t k = 0; k < p->refineStoreId.size(); k++) if (p->refineStoreId[k] == store) rsIdx = (int)k;
+  if (rsIdx < 0) throw std::invalid_argument("vb_refine_triangulation_inliers: not a visual store");
+  if (!flags || n_factors != (int64_t)p->g.stores[(size_t)store].count) throw std::invalid_argument("flags must hold one byte per factor of the store");
+  const std::vector<int32_t>& slot = p->refineSlotFactor[(size_t)rsIdx];
+  std::vector<double> host(slot.size());
+  cudaStream_t s = p->ctx->stream;
+  if (!slot.empty()) VB_CUDA(cudaMemcpyAsync(host.data(), p->refine.st[rsIdx].backup, slot.size() * sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  std::memset(flags, 0, (size_t)n_factors);
+  for (size_t i = 0; i < slot.size(); i++) flags[slot[i]] = host[i] == 1.0 ? 1 : 0;
+  VB_CATCH
+}
 int vb_preint_set_imu(vb_problem* p, int32_t store, int64_t n_factors, const int64_t* start_us, const int64_t* end_us, const int32_t* calib_var,
                       int64_t n_samples, const int64_t* sample_time_ns, const float* gyro, const float* accel, const double* gyro_var3,
                       const double* accel_var3) {

@@ -565,6 +565,79 @@ void launchRefinePoints(const RefineArgs& A, const DevVars& v, double* perPoint,
   VB_CUDA(cudaGetLastError());
 }
 
+// ---- refineTriangulationResult (second half) -------------------------------------------------------
+// viba/single_session/Triangulation.cpp:99-161, the refinement passes of triangulatePoint (:219-238), for every landmark at
+// once: maxIts undamped Gauss-Newton steps on the point with HuberLoss(radius) (SoftLoss.h:64-113) on the weighted
+// reprojection error; each iteration re-classifies the observations (inlier = squared unweighted image error < thr2,
+// :139-144; the unweighted error is sqrtH^-1 times the factor's residual) and with skipOutliers the outliers stay out of
+// the normal equations.  Same warp-per-landmark layout and the same refineEval as refinePointsKernel above.  The inlier
+// flags of the last iteration are left in the stores' per-observation scratch (RefineStore::backup: 1 inlier, 0 not);
+// perPoint = {numInliers, cost of the last iteration, status (0, or -1: 3x3 system not positive definite, point kept)}.
+__global__ void __launch_bounds__(128) refineTriangulationKernel(RefineArgs A, DevVars V, double thr2, int skipOutliers, int maxIts, double radius,
+                                                                 double* perPoint, double* statsAcc) {
+  const int lane = threadIdx.x & 31;
+  const int64_t j = blockIdx.x * 4ll + (threadIdx.x >> 5);
+  if (j >= A.nLm) return;
+  double* Xg = V.data + A.lmOff[j];
+  double X[3] = {Xg[0], Xg[1], Xg[2]};
+  const double b = radius * radius;
+  double nIn = 0.0, cost = 0.0;
+  int status = 0;
+  for (int it = 0; it < maxIts; it++) {
+    double acc[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // cost, g(3), lower H (6), inliers
+    for (int s = 0; s < A.nStores; s++) {
+      const RefineStore& S = A.st[s];
+      for (int64_t i = S.lmPtr[j] + lane; i < S.lmPtr[j + 1]; i += 32) {
+        double r[2], JX[6];
+        const int st = refineEval<true>(S, V, i, X, r, JX);
+        if (st == 2) V.errAcc[0] = 1.0;
+        if (st != 0) { S.backup[i] = 0.0; continue; }
+        const double* c = S.lConst + i * S.cpf;
+        const double det = c[2] * c[5] - c[3] * c[4];
+        const double e0 = (c[5] * r[0] - c[3] * r[1]) / det, e1 = (-c[4] * r[0] + c[2] * r[1]) / det;
+        const bool inl = e0 * e0 + e1 * e1 < thr2;
+        S.backup[i] = inl ? 1.0 : 0.0;
+        if (inl) acc[10] += 1.0;
+        else if (skipOutliers) continue;
+        const double s2 = r[0] * r[0] + r[1] * r[1];
+        double soft = s2, d = 1.0;
+        if (s2 > b) { const double rr = sqrt(s2); soft = 2.0 * radius * rr - b; d = radius / rr; }
+        acc[0] += 0.5 * soft;
+        int q = 4;
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+          acc[1 + a] += d * (r[0] * JX[a] + r[1] * JX[3 + a]);
+#pragma unroll
+          for (int bb = 0; bb <= a; bb++) acc[q++] += d * (JX[a] * JX[bb] + JX[3 + a] * JX[3 + bb]);
+        }
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 11; q++) acc[q] = warpSum(acc[q]);
+    cost = acc[0]; nIn = acc[10];
+    const double grad[3] = {acc[1], acc[2], acc[3]};
+    double hess[9];
+    hess[0] = acc[4]; hess[3] = hess[1] = acc[5]; hess[4] = acc[6]; hess[6] = hess[2] = acc[7]; hess[7] = hess[5] = acc[8]; hess[8] = acc[9];
+    double step[3];
+    if (!solve3v(hess, grad, step)) { status = -1; break; }
+#pragma unroll
+    for (int a = 0; a < 3; a++) X[a] -= step[a];
+  }
+  if (lane == 0) {
+    Xg[0] = X[0]; Xg[1] = X[1]; Xg[2] = X[2];
+    perPoint[3 * j] = nIn; perPoint[3 * j + 1] = cost; perPoint[3 * j + 2] = (double)status;
+    if (status < 0) red_add(statsAcc, 1.0);
+  }
+}
+
+void launchRefineTriangulation(const RefineArgs& A, const DevVars& v, double outlierThreshold, bool skipOutliers, int maxIts, double radius,
+                               double* perPoint, double* statsAcc, cudaStream_t s) {
+  if (A.nLm <= 0) return;
+  refineTriangulationKernel<<<(unsigned)((A.nLm + 3) / 4), 128, 0, s>>>(A, v, outlierThreshold * outlierThreshold, skipOutliers ? 1 : 0, maxIts, radius,
+                                                                         perPoint, statsAcc);
+  VB_CUDA(cudaGetLastError());
+}
+
 // ---- cost only: computeSingleCost (Factor.h:390-417) + CostStats for the visual stores, over the packed landmark-major
 // tables (coalesced constants, one index level).  acc = {cost, numTotal, numInvalid, numPrevInvalid}
 template <bool RS>

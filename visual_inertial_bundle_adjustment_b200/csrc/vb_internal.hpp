@@ -133,6 +133,8 @@ void launchVisualGradHess(const DevStore& st, const DevVars& v, double* grad, do
                           double* costAcc, cudaStream_t s);
 void launchVisualCost(const DevStore& st, const DevVars& v, int comparable, double* acc, cudaStream_t s);
 void launchRefinePoints(const RefineArgs& A, const DevVars& v, double* perPoint, double* statsAcc, cudaStream_t s);
+void launchRefineTriangulation(const RefineArgs& A, const DevVars& v, double outlierThreshold, bool skipOutliers, int maxIts, double radius,
+                               double* perPoint, double* statsAcc, cudaStream_t s);
 // kernels_solver.cu
 void launchSchurPrep(const DevSolver& d, double* hess, int* errFlag, cudaStream_t s);
 void launchZeroOwnedPanels(const DevSolver& d, double* hess, cudaStream_t s);

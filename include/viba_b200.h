@@ -363,6 +363,16 @@ int vb_rs_set_gravity_var(vb_problem* p, int32_t store, int32_t gravity_var);
 int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* cov, int64_t cov_len,
                                 int64_t* offsets, double* damping_used);
 
+/* Optimizer::computeMarginalProblem (Optimizer.cpp:422-494, the quantity TestOptimizer.cpp:74-82 multiplies with the joint
+ * covariance): the marginal problem of ONE list of registered variables — H = Schur complement of every other variable
+ * onto the listed ones (row-major D x D, blocks in list order, offsets[n + 1] may be null), b = the matching gradient,
+ * *cost = the cost minus what the eliminated variables can still remove (0.5 g_r^T H_rr^-1 g_r).  Damping and its retry as
+ * in vb_compute_joint_covariance; same side effects.  The reference reorders the listed variables last and reads a
+ * partial factorisation; here the ordering is fixed at problem creation and the same quantities come from complete
+ * solves (H = inverse of the joint covariance block, inverted on the host: D is small). */
+int vb_compute_marginal_problem(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* H, int64_t h_len, double* b,
+                                int64_t b_len, double* cost, int64_t* offsets, double* damping_used);
+
 /* refinePoints pre-pass: viba/problem/PointRefinement.cpp:96-196 — a 3x3 Levenberg-Marquardt per
  * landmark (lambda 1e-5, <= 5 iterations, reduced step on a poor one) over its visual factors with every other variable
  * held fixed (FactorStore::varGradHess / singleCost, lib/small_thing/Factor.h:230-232,419-468).  Updates the landmark

@@ -475,6 +475,19 @@ class Problem:
                                                            off.ctypes.data_as(_ip), C.byref(used)))
         return cov, off, used.value
 
+    def marginal_problem(self, indices, damping=1e-5):
+        """Optimizer::computeMarginalProblem for one list of registration indices: (H [D, D], b [D], cost, offsets, damping used)"""
+        idx = np.ascontiguousarray(indices, np.int64)
+        dims = [int(self.g.var_tdim[np.flatnonzero(self.g.var_index == i)[0]]) for i in idx]
+        D = int(sum(dims))
+        H, b, off = np.zeros((D, D)), np.zeros(D), np.zeros(idx.size + 1, np.int64)
+        cost, used = C.c_double(0), C.c_double(0)
+        self.lib.vb_compute_marginal_problem.argtypes = [C.c_void_p, C.c_double, C.c_int64, _ip, _dp, C.c_int64, _dp, C.c_int64,
+                                                         C.POINTER(C.c_double), _ip, C.POINTER(C.c_double)]
+        _ck(self.lib, self.lib.vb_compute_marginal_problem(self.h, damping, idx.size, idx.ctypes.data_as(_ip), _d(H), D * D, _d(b), D,
+                                                           C.byref(cost), off.ctypes.data_as(_ip), C.byref(used)))
+        return H, b, cost.value, off, used.value
+
     def refine_points(self, per_point=True):
         """refinePoints pre-pass (vb_refine_points): returns (stats dict, per-point array [n, 3] = startCost, endCost, nIts)"""
         class _S(C.Structure):

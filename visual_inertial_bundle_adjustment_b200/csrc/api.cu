@@ -2118,6 +2118,105 @@ int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const 
     }
   VB_CATCH_NUMERIC
 }
+// Optimizer::computeMarginalProblem (Optimizer.cpp:422-494): H = Schur complement of every other variable onto the listed ones
+// (with the damping of initDirectSolverData), b = the matching gradient, cost = cost - 0.5 |L^-1 g|^2 over the eliminated
+// part.  The reference orders the listed variables last and reads the bottom-right block of a partial factorisation; the
+// ordering here is fixed at problem creation, so the same quantities come from complete solves on the factored system:
+// C = [(H + D)^-1]_ii column by column (as vb_compute_joint_covariance), x = (H + D)^-1 g, then H_m = C^-1, b_m = H_m x_i,
+// g^T x = g_r^T H_rr^-1 g_r + b_m^T x_i.
+int vb_compute_marginal_problem(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* H, int64_t h_len, double* b,
+                                int64_t b_len, double* cost, int64_t* offsets, double* damping_used) {
+  VB_TRY
+  requireProblem(p);
+  if (p->nranks > 1) throw std::logic_error("vb_compute_marginal_problem: not available on a sharded problem");
+  if (p->solverType != VB_SOLVER_DIRECT) throw std::logic_error("vb_compute_marginal_problem: needs the direct solver (vb_set_linear_solver)");
+  if (n <= 0 || !indices || !H || !b) throw std::invalid_argument("null or empty index list");
+  const Symbolic& S = p->S;
+  std::vector<int64_t> start((size_t)n), size((size_t)n), off((size_t)n + 1, 0);
+  for (int64_t i = 0; i < n; i++) {
+    if (indices[i] < 0 || indices[i] >= S.nB) throw std::invalid_argument("taking index from an unregistered variable?");
+    for (int64_t j = 0; j < i; j++) if (indices[j] == indices[i]) throw std::invalid_argument("duplicated indices");
+    start[(size_t)i] = S.vecStart[S.pos[indices[i]]];
+    size[(size_t)i] = S.bsize[indices[i]];
+    off[(size_t)i + 1] = off[(size_t)i] + size[(size_t)i];
+  }
+  const int64_t D = off[(size_t)n];
+  if (h_len != D * D || b_len != D) throw std::invalid_argument("H must hold D^2 and b D doubles, D = sum of the tangent dims");
+  if (offsets) for (int64_t i = 0; i <= n; i++) offsets[i] = off[(size_t)i];
+  cudaStream_t s = p->ctx->stream;
+  double fullCost = 0.0;
+  while (true) {
+    fullCost = evalGradHess(p, p->grad, 1, 0, 0, true);
+    if (damping > 0) launchDamping(p->hess, p->diagOff, p->diagStride, p->diagSize, S.nB, damping, p->dampMask, s);
+    factorAsync(p, nullptr);
+    bool ok = true;
+    try { checkNumeric(p); } catch (const std::domain_error&) { ok = false; }
+    if (ok) break;
+    if (damping < 1e-9) damping += 1e-9; else damping *= 2.0;
+    if (damping > 1e12) throw std::domain_error("unable to compute the marginal problem: the system stays singular");
+  }
+  if (damping_used) *damping_used = damping;
+  std::vector<double> C((size_t)(D * D)), col((size_t)D), x((size_t)D);
+  const double one = 1.0;
+  for (int64_t i = 0; i < n; i++)
+    for (int64_t k = 0; k < size[(size_t)i]; k++) {
+      VB_CUDA(cudaMemsetAsync(p->step, 0, S.order * sizeof(double), s));
+      VB_CUDA(cudaMemcpyAsync(p->step + start[(size_t)i] + k, &one, sizeof(double), cudaMemcpyHostToDevice, s));
+      p->partial[0] = false;
+      solveAsync(p, p->step);
+      for (int64_t j = 0; j < n; j++)
+        VB_CUDA(cudaMemcpyAsync(col.data() + off[(size_t)j], p->step + start[(size_t)j], size[(size_t)j] * sizeof(double), cudaMemcpyDeviceToHost, s));
+      syncCheck(p);
+      for (int64_t r = 0; r < D; r++) C[(size_t)(r * D + off[(size_t)i] + k)] = col[(size_t)r];
+    }
+  // x = (H + D)^-1 g and g^T x
+  launchVecOp(0, p->step, p->grad, 0, S.order, nullptr, s);
+  p->partial[0] = false;
+  solveAsync(p, p->step);
+  const double gTx = dotVec(p, p->step, p->grad);
+  for (int64_t j = 0; j < n; j++)
+    VB_CUDA(cudaMemcpyAsync(x.data() + off[(size_t)j], p->step + start[(size_t)j], size[(size_t)j] * sizeof(double), cudaMemcpyDeviceToHost, s));
+  syncCheck(p);
+  // H_m = C^-1 on the host: C is symmetric positive definite (symmetrised first: its columns come from separate solves)
+  std::vector<double> L((size_t)(D * D), 0.0);
+  for (int64_t r = 0; r < D; r++)
+    for (int64_t c = 0; c <= r; c++) L[(size_t)(r * D + c)] = 0.5 * (C[(size_t)(r * D + c)] + C[(size_t)(c * D + r)]);
+  for (int64_t j = 0; j < D; j++) {
+    double d = L[(size_t)(j * D + j)];
+    for (int64_t k = 0; k < j; k++) d -= L[(size_t)(j * D + k)] * L[(size_t)(j * D + k)];
+    if (!(d > 0.0)) throw std::domain_error("vb_compute_marginal_problem: the covariance block is not positive definite");
+    const double ljj = std::sqrt(d);
+    L[(size_t)(j * D + j)] = ljj;
+    for (int64_t i = j + 1; i < D; i++) {
+      double t = L[(size_t)(i * D + j)];
+      for (int64_t k = 0; k < j; k++) t -= L[(size_t)(i * D + k)] * L[(size_t)(j * D + k)];
+      L[(size_t)(i * D + j)] = t / ljj;
+    }
+  }
+  std::vector<double> e((size_t)D);
+  for (int64_t c = 0; c < D; c++) {   // column c of C^-1: L L^T h = e_c
+    for (int64_t i = 0; i < D; i++) {
+      double t = i == c ? 1.0 : 0.0;
+      for (int64_t k = 0; k < i; k++) t -= L[(size_t)(i * D + k)] * e[(size_t)k];
+      e[(size_t)i] = t / L[(size_t)(i * D + i)];
+    }
+    for (int64_t i = D - 1; i >= 0; i--) {
+      double t = e[(size_t)i];
+      for (int64_t k = i + 1; k < D; k++) t -= L[(size_t)(k * D + i)] * e[(size_t)k];
+      e[(size_t)i] = t / L[(size_t)(i * D + i)];
+    }
+    for (int64_t r = 0; r < D; r++) H[r * D + c] = e[(size_t)r];
+  }
+  double bTx = 0.0;
+  for (int64_t r = 0; r < D; r++) {
+    double t = 0.0;
+    for (int64_t c = 0; c < D; c++) t += H[r * D + c] * x[(size_t)c];
+    b[r] = t;
+    bTx += t * x[(size_t)r];
+  }
+  if (cost) *cost = fullCost - 0.5 * (gTx - bTx);
+  VB_CATCH_NUMERIC
+}
 int vb_refine_points(vb_problem* p, vb_refine_stats* out, double* per_point, int64_t n_points) {
   VB_TRY
   requireProblem(p);

@@ -363,6 +363,13 @@ int vb_rs_set_gravity_var(vb_problem* p, int32_t store, int32_t gravity_var);
 int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* cov, int64_t cov_len,
                                 int64_t* offsets, double* damping_used);
 
+/* The same for MANY lists in one call, as SingleSessionProblem::computeCovariances uses it (SingleSessionProblem.cpp:100-126:
+ * one list per rig {pose, velocity[, omega]} + one per calibration variable): list l = indices[list_ptr[l] .. list_ptr[l + 1]);
+ * the system is linearised, damped and factored ONCE; cov receives the D_l x D_l blocks back to back (cov_ptr[n_lists + 1],
+ * may be null, gives where each starts). */
+int vb_compute_joint_covariances(vb_problem* p, double damping, int64_t n_lists, const int64_t* list_ptr, const int64_t* indices, double* cov,
+                                 int64_t cov_len, int64_t* cov_ptr, double* damping_used);
+
 /* Optimizer::computeMarginalProblem (Optimizer.cpp:422-494, the quantity TestOptimizer.cpp:74-82 multiplies with the joint
  * covariance): the marginal problem of ONE list of registered variables — H = Schur complement of every other variable
  * onto the listed ones (row-major D x D, blocks in list order, offsets[n + 1] may be null), b = the matching gradient,

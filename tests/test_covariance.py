@@ -48,6 +48,14 @@ def test_joint_covariance_is_a_block_of_the_inverse(oracle, cfg):
         assert np.abs(c1 - cov3[off3[k]:off3[k + 1], off3[k]:off3[k + 1]]).max() <= 1e-9 * np.abs(c1).max()
     with pytest.raises(Exception, match="duplicated"):
         p.joint_covariance([int(cams[0]), int(cams[0])], lam)
+    # all lists in one call (one factorisation), as SingleSessionProblem::computeCovariances does: the same blocks
+    covs, used = p.joint_covariances(lists, lam)
+    assert used == lam and len(covs) == len(lists)
+    for idx, cv in zip(lists, covs):
+        one, _, _ = p.joint_covariance(idx, lam)
+        assert cv.shape == one.shape and np.abs(cv - one).max() <= 1e-9 * np.abs(one).max()
+    with pytest.raises(Exception, match="duplicated"):
+        p.joint_covariances([lists[0], [int(cams[0]), int(cams[0])]], lam)
     p.close(); ctx.close()
 
 

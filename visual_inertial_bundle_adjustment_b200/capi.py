@@ -475,6 +475,19 @@ class Problem:
                                                            off.ctypes.data_as(_ip), C.byref(used)))
         return cov, off, used.value
 
+    def joint_covariances(self, lists, damping=1e-5):
+        """Optimizer::computeJointCovariances for several lists of registration indices, one factorisation: ([cov_l], damping used)"""
+        ptr = np.concatenate([[0], np.cumsum([len(l) for l in lists])]).astype(np.int64)
+        idx = np.ascontiguousarray(np.concatenate([np.asarray(l, np.int64) for l in lists]), np.int64)
+        tdim = {int(i): int(t) for i, t in zip(self.g.var_index, self.g.var_tdim) if i >= 0}
+        D = [sum(tdim[int(i)] for i in l) for l in lists]
+        total = int(sum(d * d for d in D))
+        cov, cptr, used = np.zeros(total), np.zeros(len(lists) + 1, np.int64), C.c_double(0)
+        self.lib.vb_compute_joint_covariances.argtypes = [C.c_void_p, C.c_double, C.c_int64, _ip, _ip, _dp, C.c_int64, _ip, C.POINTER(C.c_double)]
+        _ck(self.lib, self.lib.vb_compute_joint_covariances(self.h, damping, len(lists), ptr.ctypes.data_as(_ip), idx.ctypes.data_as(_ip), _d(cov),
+                                                            total, cptr.ctypes.data_as(_ip), C.byref(used)))
+        return [cov[cptr[l]:cptr[l + 1]].reshape(D[l], D[l]).copy() for l in range(len(lists))], used.value
+
     def marginal_problem(self, indices, damping=1e-5):
         """Optimizer::computeMarginalProblem for one list of registration indices: (H [D, D], b [D], cost, offsets, damping used)"""
         idx = np.ascontiguousarray(indices, np.int64)

@@ -2073,24 +2073,33 @@ int vb_rs_refresh(vb_problem* p, int32_t store) {
 // factorisation (:516-533: damping += 1e-9, then doubled) — and read the block of H^-1 column by column: one solve per
 // tangent scalar of the listed variables (the reference restricts each solve to the trailing part of the factor;
 // here the full forward / backward passes run, one right-hand side at a time).
-int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* cov, int64_t cov_len,
-                                int64_t* offsets, double* damping_used) {
+// Optimizer::computeJointCovariances (Optimizer.cpp:503-612) for MANY lists at once, as SingleSessionProblem::computeCovariances calls
+// it (one list per rig + one per calibration variable, SingleSessionProblem.cpp:100-126): linearise, damp and factor ONCE, then
+// one solve per tangent scalar of every list.
+int vb_compute_joint_covariances(vb_problem* p, double damping, int64_t n_lists, const int64_t* list_ptr, const int64_t* indices, double* cov,
+                                 int64_t cov_len, int64_t* cov_ptr, double* damping_used) {
   VB_TRY
   requireProblem(p);
   if (p->nranks > 1) throw std::logic_error("vb_compute_joint_covariance: not available on a sharded problem");
-  if (n <= 0 || !indices || !cov) throw std::invalid_argument("null or empty index list");
+  if (p->solverType != VB_SOLVER_DIRECT) throw std::logic_error("vb_compute_joint_covariance: needs the direct solver (vb_set_linear_solver)");
+  if (n_lists <= 0 || !list_ptr || !indices || !cov) throw std::invalid_argument("null or empty index list");
   const Symbolic& S = p->S;
-  std::vector<int64_t> start((size_t)n), size((size_t)n), off((size_t)n + 1, 0);
-  for (int64_t i = 0; i < n; i++) {
-    if (indices[i] < 0 || indices[i] >= S.nB) throw std::invalid_argument("taking index from an unregistered variable?");
-    for (int64_t j = 0; j < i; j++) if (indices[j] == indices[i]) throw std::invalid_argument("duplicated indices");
-    start[(size_t)i] = S.vecStart[S.pos[indices[i]]];
-    size[(size_t)i] = S.bsize[indices[i]];
-    off[(size_t)i + 1] = off[(size_t)i] + size[(size_t)i];
+  // validate every list and lay the output out before any device work
+  std::vector<int64_t> covOff((size_t)n_lists + 1, 0);
+  for (int64_t l = 0; l < n_lists; l++) {
+    const int64_t n = list_ptr[l + 1] - list_ptr[l];
+    if (n <= 0) throw std::invalid_argument("null or empty index list");
+    const int64_t* idx = indices + list_ptr[l];
+    int64_t D = 0;
+    for (int64_t i = 0; i < n; i++) {
+      if (idx[i] < 0 || idx[i] >= S.nB) throw std::invalid_argument("taking index from an unregistered variable?");
+      for (int64_t j = 0; j < i; j++) if (idx[j] == idx[i]) throw std::invalid_argument("duplicated indices");
+      D += S.bsize[idx[i]];
+    }
+    covOff[(size_t)l + 1] = covOff[(size_t)l] + D * D;
   }
-  const int64_t D = off[(size_t)n];
-  if (cov_len != D * D) throw std::invalid_argument("cov must hold (sum of tangent dims)^2 doubles");
-  if (offsets) for (int64_t i = 0; i <= n; i++) offsets[i] = off[(size_t)i];
+  if (cov_len != covOff[(size_t)n_lists]) throw std::invalid_argument("cov must hold (sum of tangent dims)^2 doubles per list");
+  if (cov_ptr) for (int64_t l = 0; l <= n_lists; l++) cov_ptr[l] = covOff[(size_t)l];
   cudaStream_t s = p->ctx->stream;
   while (true) {
     evalGradHess(p, p->grad, 1, 0, 0, true);
@@ -2103,20 +2112,47 @@ int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const 
     if (damping > 1e12) throw std::domain_error("unable to compute covariances: the system stays singular");
   }
   if (damping_used) *damping_used = damping;
-  std::vector<double> col((size_t)S.order);
   const double one = 1.0;
-  for (int64_t i = 0; i < n; i++)
-    for (int64_t k = 0; k < size[(size_t)i]; k++) {
-      VB_CUDA(cudaMemsetAsync(p->step, 0, S.order * sizeof(double), s));
-      VB_CUDA(cudaMemcpyAsync(p->step + start[(size_t)i] + k, &one, sizeof(double), cudaMemcpyHostToDevice, s));
-      p->partial[0] = false;
-      solveAsync(p, p->step);
-      for (int64_t j = 0; j < n; j++)
-        VB_CUDA(cudaMemcpyAsync(col.data() + off[(size_t)j], p->step + start[(size_t)j], size[(size_t)j] * sizeof(double), cudaMemcpyDeviceToHost, s));
-      syncCheck(p);
-      for (int64_t r = 0; r < D; r++) cov[r * D + off[(size_t)i] + k] = col[(size_t)r];
+  std::vector<int64_t> start, size, off;
+  std::vector<double> col;
+  for (int64_t l = 0; l < n_lists; l++) {
+    const int64_t n = list_ptr[l + 1] - list_ptr[l];
+    const int64_t* idx = indices + list_ptr[l];
+    start.assign((size_t)n, 0); size.assign((size_t)n, 0); off.assign((size_t)n + 1, 0);
+    for (int64_t i = 0; i < n; i++) {
+      start[(size_t)i] = S.vecStart[S.pos[idx[i]]];
+      size[(size_t)i] = S.bsize[idx[i]];
+      off[(size_t)i + 1] = off[(size_t)i] + size[(size_t)i];
     }
+    const int64_t D = off[(size_t)n];
+    double* out = cov + covOff[(size_t)l];
+    col.assign((size_t)D, 0.0);
+    for (int64_t i = 0; i < n; i++)
+      for (int64_t k = 0; k < size[(size_t)i]; k++) {
+        VB_CUDA(cudaMemsetAsync(p->step, 0, S.order * sizeof(double), s));
+        VB_CUDA(cudaMemcpyAsync(p->step + start[(size_t)i] + k, &one, sizeof(double), cudaMemcpyHostToDevice, s));
+        p->partial[0] = false;
+        solveAsync(p, p->step);
+        for (int64_t j = 0; j < n; j++)
+          VB_CUDA(cudaMemcpyAsync(col.data() + off[(size_t)j], p->step + start[(size_t)j], size[(size_t)j] * sizeof(double), cudaMemcpyDeviceToHost, s));
+        syncCheck(p);
+        for (int64_t r = 0; r < D; r++) out[r * D + off[(size_t)i] + k] = col[(size_t)r];
+      }
+  }
   VB_CATCH_NUMERIC
+}
+int vb_compute_joint_covariance(vb_problem* p, double damping, int64_t n, const int64_t* indices, double* cov, int64_t cov_len,
+                                int64_t* offsets, double* damping_used) {
+  if (offsets && p && indices && n > 0) {   // block offsets inside the one list (the batched call reports offsets between lists)
+    int64_t o = 0;
+    offsets[0] = 0;
+    for (int64_t i = 0; i < n; i++) {
+      if (indices[i] >= 0 && indices[i] < p->S.nB) o += p->S.bsize[indices[i]];
+      offsets[i + 1] = o;
+    }
+  }
+  const int64_t ptr[2] = {0, n};
+  return vb_compute_joint_covariances(p, damping, 1, ptr, indices, cov, cov_len, nullptr, damping_used);
 }
 // Optimizer::computeMarginalProblem (Optimizer.cpp:422-494): H = Schur complement of every other variable onto the listed ones
 // (with the damping of initDirectSolverData), b = the matching gradient, cost = cost - 0.5 |L^-1 g|^2 over the eliminated

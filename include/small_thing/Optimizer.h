@@ -235,6 +235,81 @@ class Optimizer {
     return problem_;
   }
 
+  // ---- covariances and marginal problems (Optimizer.h:101-106,294-326; Optimizer.cpp:422-696) -----------------------
+  // Eigen::MatrixXd of the reference -> a plain row-major matrix
+  struct DenseMatrix {
+    int64_t rows = 0, cols = 0;
+    std::vector<double> data;
+    double& operator()(int64_t r, int64_t c) { return data[(size_t)(r * cols + c)]; }
+    double operator()(int64_t r, int64_t c) const { return data[(size_t)(r * cols + c)]; }
+  };
+  struct MarginalProblem {   // Optimizer.h:101-106
+    DenseMatrix H;
+    std::vector<double> b;
+    double cost = 0.0;
+    std::vector<int64_t> offsets;
+  };
+
+  // returns a list of pairs {matrix, offsets}: joint covariance and offsets for each list of registration indices
+  // (Optimizer.cpp:503-612 -> vb_compute_joint_covariances: one linearisation + factorisation for all lists)
+  std::vector<std::pair<DenseMatrix, std::vector<int64_t>>> computeJointCovariances(const Settings& s,
+                                                                                     const std::vector<std::vector<int64_t>>& indicesLists) {
+    std::vector<std::pair<DenseMatrix, std::vector<int64_t>>> out;
+    if (indicesLists.empty()) return out;
+    ensureBackend(s.device);
+    std::vector<int64_t> ptr{0}, flat;
+    int64_t total = 0;
+    for (const auto& list : indicesLists) {
+      std::vector<int64_t> off{0};
+      for (int64_t i : list) {
+        if (i < 0 || i >= (int64_t)registered_.size()) throw std::runtime_error("small_thing: taking index from UNREGISTERED variable?");
+        off.push_back(off.back() + registered_[(size_t)i]->getTangentDim());
+        flat.push_back(i);
+      }
+      ptr.push_back((int64_t)flat.size());
+      DenseMatrix m;
+      m.rows = m.cols = off.back();
+      total += m.rows * m.cols;
+      out.emplace_back(std::move(m), std::move(off));
+    }
+    std::vector<double> cov((size_t)total);
+    std::vector<int64_t> covPtr(indicesLists.size() + 1);
+    check(vb_compute_joint_covariances(problem_, s.damping, (int64_t)indicesLists.size(), ptr.data(), flat.data(), cov.data(), total,
+                                       covPtr.data(), nullptr));
+    for (size_t l = 0; l < out.size(); l++) out[l].first.data.assign(cov.begin() + covPtr[l], cov.begin() + covPtr[l + 1]);
+    return out;
+  }
+  std::vector<std::pair<DenseMatrix, std::vector<int64_t>>> computeJointCovariances(const std::vector<std::vector<int64_t>>& indicesLists) {
+    return computeJointCovariances(Settings{}, indicesLists);
+  }
+  // compute covariance block for variables in list `indices`, one per variable (Optimizer.cpp:613-696)
+  std::vector<DenseMatrix> computeCovariances(const Settings& s, const std::vector<int64_t>& indices) {
+    std::vector<std::vector<int64_t>> lists;
+    for (int64_t i : indices) lists.push_back({i});
+    std::vector<DenseMatrix> out;
+    for (auto& pr : computeJointCovariances(s, lists)) out.push_back(std::move(pr.first));
+    return out;
+  }
+  std::vector<DenseMatrix> computeCovariances(const std::vector<int64_t>& indices) { return computeCovariances(Settings{}, indices); }
+  // compute big marginal block H and error b (Optimizer.cpp:422-494 -> vb_compute_marginal_problem)
+  MarginalProblem computeMarginalProblem(const Settings& s, const std::vector<int64_t>& indices) {
+    ensureBackend(s.device);
+    MarginalProblem m;
+    m.offsets.assign(indices.size() + 1, 0);
+    for (size_t k = 0; k < indices.size(); k++) {
+      if (indices[k] < 0 || indices[k] >= (int64_t)registered_.size()) throw std::runtime_error("small_thing: taking index from UNREGISTERED variable?");
+      m.offsets[k + 1] = m.offsets[k] + registered_[(size_t)indices[k]]->getTangentDim();
+    }
+    const int64_t D = m.offsets.back();
+    m.H.rows = m.H.cols = D;
+    m.H.data.assign((size_t)(D * D), 0.0);
+    m.b.assign((size_t)D, 0.0);
+    check(vb_compute_marginal_problem(problem_, s.damping, (int64_t)indices.size(), indices.data(), m.H.data.data(), D * D, m.b.data(), D, &m.cost,
+                                      nullptr, nullptr));
+    return m;
+  }
+  MarginalProblem computeMarginalProblem(const std::vector<int64_t>& indices) { return computeMarginalProblem(Settings{}, indices); }
+
   Summary optimize() { return optimize(Settings{}); }
 
   // Optimizer.cpp:768-1106 -> vb_optimize (same control flow, device resident), then the values

@@ -161,6 +161,7 @@ int run(int argc, char** argv) {
   const bool withPcg = argc >= 6 && std::string(argv[5]) == "--pcg-jacobi";   // Settings::solverType = Solver_PCG_Jacobi
   const bool withGs = argc >= 6 && std::string(argv[5]) == "--pcg-gauss-seidel";
   const bool withFacade = argc >= 4 && std::string(argv[3]) == "--facade";
+  const bool withCovariance = argc >= 4 && std::string(argv[3]) == "--covariance";
 
   Reader in(argv[1]);
   const int64_t nv = in.one<int64_t>();
@@ -374,6 +375,52 @@ int run(int argc, char** argv) {
     try { solver.factorUpTo(factored.data(), 1); } catch (const std::runtime_error&) { threw = true; }
     out.one<double>((double)n); out.one<double>((double)ds); out.one<double>((double)checked); out.one<double>(worst); out.one<double>(scale);
     out.one<double>(threw ? 1.0 : 0.0); out.one<double>(cost);
+    return 0;
+  }
+  if (withCovariance) {
+    // the recipe of the reference's own test (lib/small_thing/tests/TestOptimizer.cpp:52-83) through the mirror:
+    // computeCovariances, computeJointCovariances and computeMarginalProblem of the same variables; offsets agree,
+    // marginal information x joint covariance = I, the per-variable covariances are the diagonal blocks
+    int64_t nReg = 0;
+    for (auto& v : vars) nReg = std::max<int64_t>(nReg, v->index + 1);
+    const std::vector<int64_t> idx = {nReg - 1, nReg - 3, nReg - 4};
+    Optimizer::Settings st;
+    st.damping = 1e-5;
+    auto covs = opt.computeCovariances(st, idx);
+    auto joint = opt.computeJointCovariances(st, {idx, {idx[1]}});
+    auto mProb = opt.computeMarginalProblem(st, idx);
+    if (covs.size() != idx.size() || joint.size() != 2) throw std::runtime_error("wrong number of covariance blocks");
+    const auto& cov = joint[0].first;
+    const auto& covOffs = joint[0].second;
+    if (covOffs.size() != mProb.offsets.size()) throw std::runtime_error("offset lists differ in size");
+    for (size_t i = 0; i < covOffs.size(); i++)
+      if (covOffs[i] != mProb.offsets[i]) throw std::runtime_error("offsets differ");
+    const int64_t D = cov.rows;
+    if (mProb.H.rows != D || (int64_t)mProb.b.size() != D) throw std::runtime_error("marginal problem of the wrong size");
+    double delta2 = 0, diagDiff = 0, diagScale = 0;
+    for (int64_t r = 0; r < D; r++)
+      for (int64_t c = 0; c < D; c++) {
+        double t = r == c ? -1.0 : 0.0;
+        for (int64_t k = 0; k < D; k++) t += mProb.H(r, k) * cov(k, c);
+        delta2 += t * t;
+      }
+    for (size_t v = 0; v < idx.size(); v++) {
+      const int64_t o = covOffs[v], d = covOffs[v + 1] - o;
+      if (covs[v].rows != d) throw std::runtime_error("per-variable covariance of the wrong size");
+      for (int64_t r = 0; r < d; r++)
+        for (int64_t c = 0; c < d; c++) {
+          diagDiff = std::max(diagDiff, std::fabs(covs[v](r, c) - cov(o + r, o + c)));
+          diagScale = std::max(diagScale, std::fabs(cov(o + r, o + c)));
+        }
+    }
+    // the second list of the joint call is variable idx[1] alone
+    const int64_t o1 = covOffs[1], d1 = covOffs[2] - o1;
+    for (int64_t r = 0; r < d1; r++)
+      for (int64_t c = 0; c < d1; c++) diagDiff = std::max(diagDiff, std::fabs(joint[1].first(r, c) - cov(o1 + r, o1 + c)));
+    bool threw = false;
+    try { opt.computeMarginalProblem(st, {idx[0], idx[0]}); } catch (const std::runtime_error&) { threw = true; }
+    out.one<double>((double)D); out.one<double>(std::sqrt(delta2)); out.one<double>(diagDiff); out.one<double>(diagScale);
+    out.one<double>(mProb.cost); out.one<double>(opt.computeCost()); out.one<double>(threw ? 1.0 : 0.0);
     return 0;
   }
   if (optimizeIters >= 0) {

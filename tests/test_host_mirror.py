@@ -237,6 +237,23 @@ def test_mirror_optimize_with_pcg(flag, solver_type, mirror_bin, tmp_path):
 
 
 @pytest.mark.gpu
+def test_mirror_covariances_and_marginal_problem(mirror_bin, tmp_path):
+    """the recipe of the reference's TestOptimizer.cpp:52-83 through the C++ mirror: computeCovariances,
+    computeJointCovariances and computeMarginalProblem agree on offsets, marginal information x covariance = I, the
+    per-variable covariances are the diagonal blocks of the joint one, duplicated indices throw"""
+    s = synth.make_session(**synth.CONFIGS["tiny_rs"])
+    g = merged(s.graph, s.ids["point"])
+    dump(g, s.ids["point"], tmp_path / "in.bin")
+    r = subprocess.run([mirror_bin, str(tmp_path / "in.bin"), str(tmp_path / "out.bin"), "--covariance"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    D, delta, diag_diff, diag_scale, m_cost, cost, threw = np.fromfile(tmp_path / "out.bin", np.float64)[:7]
+    assert D >= 3 and threw == 1.0
+    assert delta <= 1e-6                      # 1e-9 in the reference, on a 6-variable spring chain
+    assert diag_diff <= 1e-9 * diag_scale
+    assert 0 <= m_cost <= cost * (1 + 1e-12)  # the eliminated variables can only remove cost
+
+
+@pytest.mark.gpu
 def test_mirror_pre_step_callback_matches_oracle(oracle, mirror_bin, tmp_path):
     """Settings::preStepCallback through the C++ mirror: user code rewrites a preintegration record at iteration 2 from
     the calibration it reads in its own Variable at that moment; the oracle driven the same way gives the same run"""
